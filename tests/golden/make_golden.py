@@ -10,6 +10,11 @@ blend_reference_goldens.npz
     and expected outputs for expected.png, expected_alpha.png,
     expected_seams.png, expected.tif and expected_16bit.tif.
 
+warp_cv2_goldens.npz
+    Vectors recorded from Python cv2 for the OpenCV half of the path
+    (RotationWarper maps/ROIs/points, remap, resize(INTER_LINEAR_EXACT),
+    dilate, float resize).
+
 blend_ref_outputs.npz
     Outputs of the UNMODIFIED reference library (oracle/_ref/libmb_ref.so) on
     the seeded synthetic cases of tests/synth.py (inputs are regenerated from
@@ -47,7 +52,93 @@ REF_CASES = [
 ]
 
 
+def rot(yaw, pitch, roll):
+    cy, sy = np.cos(yaw), np.sin(yaw)
+    cp, sp = np.cos(pitch), np.sin(pitch)
+    cr, sr = np.cos(roll), np.sin(roll)
+    ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    rx = np.array([[1, 0, 0], [0, cp, -sp], [0, sp, cp]])
+    rz = np.array([[cr, -sr, 0], [sr, cr, 0], [0, 0, 1]])
+    return (ry @ rx @ rz).astype(np.float32)
+
+
+WARP_NAMES = ["plane", "cylindrical", "spherical", "fisheye", "stereographic",
+              "compressedPlaneA2B1", "compressedPlaneA1.5B1",
+              "compressedPlanePortraitA2B1", "paniniA2B1", "paniniA1.5B1",
+              "paniniPortraitA2B1", "mercator", "transverseMercator"]
+WARP_SIZE = (200, 150)
+WARP_SCALE = 160.0
+WARP_ROT = (0.4, -0.1, 0.05)
+WARP_STEP = 5          # maps are stored subsampled
+RESIZE_CASES = [(57, 43, 311, 271), (33, 21, 330, 210), (40, 30, 41, 31),
+                (1, 5, 7, 9), (64, 48, 32, 24)]
+
+
+def warp_goldens():
+    """Vectors recorded from Python cv2 (the OpenCV half of the path is a
+    third-party dependency)."""
+    w, h = WARP_SIZE
+    K = np.array([[150, 0, w / 2], [0, 150, h / 2], [0, 0, 1]], np.float32)
+    R = rot(*WARP_ROT)
+    g = {"K": K, "R": R, "cv2_version": np.array(cv2.__version__)}
+    rng = np.random.default_rng(5)
+    src8 = synth.texture(h, w, 77, 3, 8)
+    src16 = synth.texture(h, w, 78, 3, 16)
+    g["src8"], g["src16"] = src8, src16
+    for name in WARP_NAMES:
+        cw = cv2.PyRotationWarper(name, WARP_SCALE)
+        g[f"roi_{name}"] = np.array(cw.warpRoi((w, h), K, R))
+        _, xm, ym = cw.buildMaps((w, h), K, R)
+        g[f"xmap_{name}"] = xm[::WARP_STEP, ::WARP_STEP].copy()
+        g[f"ymap_{name}"] = ym[::WARP_STEP, ::WARP_STEP].copy()
+        g[f"pt_{name}"] = np.array(cw.warpPoint((123.5, 77.25), K, R),
+                                   np.float32)
+        try:  # not implemented for every warper in the Python binding
+            g[f"ptb_{name}"] = np.array(
+                cw.warpPointBackward((10.0, 20.0), K, R), np.float32)
+        except cv2.error:
+            pass
+    for name in ("spherical", "cylindrical", "mercator"):
+        cw = cv2.PyRotationWarper(name, WARP_SCALE)
+        c, d8 = cw.warp(src8, K, R, cv2.INTER_LINEAR, cv2.BORDER_REFLECT)
+        if name == "spherical":
+            _, d16 = cw.warp(src16, K, R, cv2.INTER_LINEAR,
+                             cv2.BORDER_REFLECT)
+            g[f"warp16_{name}"] = d16
+        _, m = cw.warp(np.full((h, w), 255, np.uint8), K, R,
+                       cv2.INTER_NEAREST, cv2.BORDER_CONSTANT)
+        g[f"warp8_{name}"] = d8
+        g[f"warpmask_{name}"] = m
+        g[f"corner_{name}"] = np.array(c)
+    # remap on wild maps (far outside, integers, -1)
+    xm = rng.uniform(-3 * w, 4 * w, (60, 90)).astype(np.float32)
+    ym = rng.uniform(-3 * h, 4 * h, (60, 90)).astype(np.float32)
+    xm[:15] = np.round(xm[:15])
+    ym[:15] = np.round(ym[:15])
+    xm[15:20] = ym[15:20] = -1
+    g["wild_x"], g["wild_y"] = xm, ym
+    g["wild8"] = cv2.remap(src8, xm, ym, cv2.INTER_LINEAR,
+                           borderMode=cv2.BORDER_REFLECT)
+    g["wild16"] = cv2.remap(src16, xm, ym, cv2.INTER_LINEAR,
+                            borderMode=cv2.BORDER_REFLECT)
+    g["wildmask"] = cv2.remap(np.full((h, w), 255, np.uint8), xm, ym,
+                              cv2.INTER_NEAREST,
+                              borderMode=cv2.BORDER_CONSTANT)
+    for k, (sw, sh, dw, dh) in enumerate(RESIZE_CASES):
+        m = (rng.random((sh, sw)) < 0.5).astype(np.uint8) * 255
+        g[f"rs_src_{k}"] = m
+        g[f"rs_dst_{k}"] = cv2.resize(m, (dw, dh),
+                                      interpolation=cv2.INTER_LINEAR_EXACT)
+        g[f"dil_{k}"] = cv2.dilate(m, None)
+        gm = rng.uniform(0.7, 1.4, (sh, sw)).astype(np.float32)
+        g[f"gain_src_{k}"] = gm
+        g[f"gain_dst_{k}"] = cv2.resize(gm, (dw, dh),
+                                        interpolation=cv2.INTER_LINEAR)
+    np.savez_compressed(os.path.join(HERE, "warp_cv2_goldens.npz"), **g)
+
+
 def main():
+    warp_goldens()
     g = {}
     pos_png = [(-91, 204), (-167, 202), (-41, 193)]
     pos_tif = [(76, 11), (0, 9), (126, 0)]
@@ -79,7 +170,8 @@ def main():
         r[f"mask_{seed}"] = res.mask
         r[f"meta_{seed}"] = np.array([res.min_x, res.min_y, int(res.no_mask)])
     np.savez_compressed(os.path.join(HERE, "blend_ref_outputs.npz"), **r)
-    for f in ("blend_reference_goldens.npz", "blend_ref_outputs.npz"):
+    for f in ("blend_reference_goldens.npz", "blend_ref_outputs.npz",
+              "warp_cv2_goldens.npz"):
         print(f, os.path.getsize(os.path.join(HERE, f)) // 1024, "KiB")
 
 
