@@ -1,0 +1,261 @@
+/* xpano_b200 -- C ABI of the B200-native full-resolution export hot path.
+ *
+ * Drop-in boundary: the two OpenCV interfaces xpano's
+ * stitcher drives polymorphically,
+ *   cv::detail::RotationWarper   (xpano/algorithm/stitcher.cc:160,377,384;
+ *                                 creators xpano/algorithm/algorithm.cc:43-105,
+ *                                 xpano/algorithm/warpers.h:9-31)
+ *   cv::detail::Blender          (xpano/algorithm/blenders.h:25-39,
+ *                                 xpano/algorithm/blenders.cc:116-158)
+ * plus the compose loop that sits between them
+ *   Stitcher::ComposePanorama    (xpano/algorithm/stitcher.cc:299-432).
+ *
+ * Plain pointers and sizes only; every call returns an xp_status, never
+ * throws; xp_last_error() gives the message of the last failure on the
+ * calling thread. All calls are synchronous at return (the reference API is).
+ * Pointers are host pointers unless the `mem` argument says XP_MEM_DEVICE.
+ * There is no CPU fallback: without a CUDA device every compute entry point
+ * fails with XP_ERR_CUDA.
+ */
+#ifndef XPANO_B200_H_
+#define XPANO_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int xp_status;
+enum {
+  XP_OK = 0,
+  XP_ERR_INVALID = 1,     /* bad argument (CV_Assert in the reference)      */
+  XP_ERR_CUDA = 2,        /* CUDA runtime failure / no device               */
+  XP_ERR_UNSUPPORTED = 3, /* combination the reference path never uses      */
+  XP_ERR_EMPTY = 4,       /* image without an opaque pixel / nothing fed    */
+  XP_ERR_NOMEM = 5
+};
+
+enum { XP_MEM_HOST = 0, XP_MEM_DEVICE = 1 };
+
+/* xpano::algorithm::ProjectionType order (xpano/algorithm/options.h:16-26) */
+enum {
+  XP_PROJ_PERSPECTIVE = 0,
+  XP_PROJ_CYLINDRICAL = 1,
+  XP_PROJ_SPHERICAL = 2,
+  XP_PROJ_FISHEYE = 3,
+  XP_PROJ_STEREOGRAPHIC = 4,
+  XP_PROJ_COMPRESSED_RECTILINEAR = 5,
+  XP_PROJ_PANINI = 6,
+  XP_PROJ_MERCATOR = 7,
+  XP_PROJ_TRANSVERSE_MERCATOR = 8
+};
+
+/* cv::InterpolationFlags / cv::BorderTypes values used on the path */
+enum { XP_INTER_NEAREST = 0, XP_INTER_LINEAR = 1 };
+enum { XP_BORDER_CONSTANT = 0, XP_BORDER_REFLECT = 2 };
+
+const char* xp_last_error(void);
+const char* xp_version(void);
+/* number of CUDA devices visible; 0 when there is none */
+int xp_device_count(void);
+
+/* ------------------------------------------------------------------------
+ * Warper: replaces cv::WarperCreator::create(scale) ->
+ * cv::Ptr<cv::detail::RotationWarper> (algorithm.cc:43-105). `portrait`
+ * selects the *PortraitWarper of warpers.h:9-31 / PickWarperPortrait;
+ * a, b are ProjectionOptions::a_param / b_param (options.h:82-86).
+ * ---------------------------------------------------------------------- */
+typedef struct xp_warper xp_warper;
+
+xp_status xp_warper_create(int projection, int portrait, float scale, float a,
+                           float b, int device, xp_warper** out);
+void xp_warper_destroy(xp_warper* w);
+/* RotationWarper::getScale / setScale */
+float xp_warper_get_scale(const xp_warper* w);
+xp_status xp_warper_set_scale(xp_warper* w, float scale);
+/* Use the caller's CUDA stream (a cudaStream_t) instead of the warper's own */
+xp_status xp_warper_set_stream(xp_warper* w, void* cuda_stream);
+
+/* Rect warpRoi(Size src, K, R) (stitcher.cc:160): out = {x, y, w, h};
+ * K, R are 3x3 row-major float32 (CV_32F, stitcher.cc:158,372,540). */
+xp_status xp_warper_warp_roi(xp_warper* w, int src_w, int src_h,
+                             const float K[9], const float R[9],
+                             int out_xywh[4]);
+/* Point2f warpPoint / warpPointBackward (gui/widgets/rotate.cc:94,130,196,372);
+ * scalar host arithmetic, no device needed. */
+xp_status xp_warper_warp_point(xp_warper* w, const float xy[2],
+                               const float K[9], const float R[9],
+                               float uv_out[2]);
+xp_status xp_warper_warp_point_backward(xp_warper* w, const float uv[2],
+                                        const float K[9], const float R[9],
+                                        float xy_out[2]);
+/* Rect buildMaps(Size, K, R, xmap, ymap): maps are roi_h x roi_w float32 with
+ * the given strides in floats (0 = tightly packed). */
+xp_status xp_warper_build_maps(xp_warper* w, int src_w, int src_h,
+                               const float K[9], const float R[9], float* xmap,
+                               float* ymap, size_t stride, int mem,
+                               int out_xywh[4]);
+/* Point warp(src, K, R, interp, border, dst) (stitcher.cc:377-385).
+ * depth 8|16, channels 1|3, strides in bytes (0 = packed). dst must hold the
+ * warp_roi rectangle. Supported (= what the path calls): INTER_LINEAR with
+ * BORDER_REFLECT, INTER_NEAREST with BORDER_CONSTANT. */
+xp_status xp_warper_warp(xp_warper* w, const void* src, int src_w, int src_h,
+                         size_t src_stride, int depth, int channels,
+                         const float K[9], const float R[9], int interp,
+                         int border, void* dst, size_t dst_stride, int mem,
+                         int out_corner[2]);
+
+/* Fused form of stitcher.cc:377-405 + blenders.cc:99-112 for one image: warp
+ * image (LINEAR/REFLECT) and all-255 mask (NEAREST/CONSTANT) from one map
+ * evaluation, apply the exposure gain map (BlocksCompensator::apply: bilinear
+ * upsample of gain, multiply, saturate), upsample the dilated seam mask
+ * (dilate 3x3 + resize INTER_LINEAR_EXACT), AND, binarise, and pack
+ * B,G,R,alpha. gain / seam_mask may be NULL (no compensation / all-255).
+ * dst is roi_h x roi_w x 4 samples of `depth` bits. */
+typedef struct {
+  const float* gain;        /* gain_h x gain_w float32, or NULL             */
+  int gain_w, gain_h;
+  const uint8_t* seam_mask; /* seam_h x seam_w u8 (undilated), or NULL      */
+  int seam_w, seam_h;
+} xp_compose_aux;
+
+xp_status xp_warper_warp_bgra(xp_warper* w, const void* src, int src_w,
+                              int src_h, size_t src_stride, int depth,
+                              const float K[9], const float R[9],
+                              const xp_compose_aux* aux, int aux_mem, void* dst,
+                              size_t dst_stride, int mem, int out_xywh[4]);
+
+/* ------------------------------------------------------------------------
+ * Blender: replaces xpano::algorithm::blenders::Multiblend
+ * (blenders.h:25-39) and, underneath, multiblend::Multiblend()
+ * (external/multiblend/src/multiblend.cpp:66-1307) with its Options
+ * (external/multiblend/include/mb/multiblend.h:29-45).
+ * ---------------------------------------------------------------------- */
+typedef struct xp_blender xp_blender;
+
+typedef struct {
+  int output_bpp;   /* 0 = auto (8 unless inputs are 16), 8, 16             */
+  int fixed_levels; /* 0 = auto                                             */
+  int add_levels;
+  int dither;       /* reference default: 1                                 */
+  int reverse;
+  int device;       /* CUDA device ordinal                                  */
+  int keep_debug;   /* keep intermediates for xp_blender_debug_fetch        */
+} xp_blend_opts;
+
+/* multiblend::TimingResult (mb/multiblend.h:16-27), milliseconds on device */
+typedef struct {
+  double images, seam, shrink_mask, copy, shrink, laplace, blend, collapse,
+      out, total;
+} xp_timing;
+
+void xp_blend_opts_default(xp_blend_opts* o);
+xp_status xp_blender_create(const xp_blend_opts* opts, xp_blender** out);
+void xp_blender_destroy(xp_blender* b);
+xp_status xp_blender_set_stream(xp_blender* b, void* cuda_stream);
+/* Blender::prepare(Rect dst_roi) (blenders.cc:116) */
+xp_status xp_blender_prepare(xp_blender* b, int x, int y, int w, int h);
+/* Blender::feed(img CV_8UC3|CV_16UC3, mask CV_8U, tl) (blenders.cc:120-139):
+ * copies (uploads) the data; the caller keeps ownership. */
+xp_status xp_blender_feed(xp_blender* b, const void* bgr, size_t stride,
+                          const uint8_t* mask, size_t mask_stride, int w,
+                          int h, int depth, int tl_x, int tl_y, int mem);
+/* multiblend::io::InMemoryImage with spp 3 or 4 (mb/image.h:28-37): already
+ * interleaved samples, alpha last when spp == 4. */
+xp_status xp_blender_feed_interleaved(xp_blender* b, const void* data,
+                                      size_t stride, int w, int h, int depth,
+                                      int spp, int tl_x, int tl_y, int mem);
+/* Blender::blend(dst, dst_mask) (blenders.cc:142-158). Two-step form: the
+ * first call runs the blend on the device and reports the size (dst NULL is
+ * allowed: size query); xp_blender_fetch copies the result out.
+ * out_wh = {width, height}; out_min_xy = Result.min_xpos/min_ypos. */
+xp_status xp_blender_blend(xp_blender* b, int out_wh[2], int out_min_xy[2],
+                           int* out_bpp, int* out_no_mask, xp_timing* timing);
+/* interleaved B,G,R (samples of output bpp) with pixels outside the mask set
+ * to 0 (blenders.cc:151-154) and the 0/255 mask; either pointer may be NULL.
+ * Strides in bytes (0 = packed). */
+xp_status xp_blender_fetch(xp_blender* b, void* dst_bgr, size_t dst_stride,
+                           uint8_t* dst_mask, size_t mask_stride, int mem);
+/* Result.output_channels as the library returns them: 3 planes, not zeroed
+ * outside the mask. */
+xp_status xp_blender_fetch_planes(xp_blender* b, void* planes, int mem);
+
+/* Intermediates for stage-level parity tests (needs keep_debug). `what`:
+ *  "labels" (i32 HxW), "seam_bwd"/"seam_fwd" (u64 HxW), "xor_mask" (u8),
+ *  "trim" (i32[6]: left, top, w, h, xpos, ypos; image), "opaque" (u8; image),
+ *  "chan" (u8/u16; image, channel), "collapsed" (f32, pitch in dims[2];
+ *  channel), "totals" (u64[4]: 3 channel totals + total_pixels),
+ *  "mask" (f32; image, level), "lap" (f32; image, channel, level),
+ *  "out" (f32; channel, level). dims = {rows, cols, pitch_elems}.
+ * dst NULL = size query (dims and *bytes filled). */
+xp_status xp_blender_debug_fetch(xp_blender* b, const char* what, int image,
+                                 int channel, int level, void* dst,
+                                 size_t cap, int dims[3], size_t* bytes);
+
+/* Stage entry points (device-run) mirroring the oracle's, used by the
+ * parity tests: pyramid geometry (pyramid.cpp:21-98) and level count
+ * (multiblend.cpp:161-206) are host arithmetic. */
+int xp_pyramid_geometry(int width, int height, int levels, int x, int y,
+                        int* lw, int* lh, int* lx, int* ly, int* xshift,
+                        int* yshift, int* pitch);
+int xp_blend_levels(int n, const int* widths, const int* heights,
+                    int fixed_levels, int add_levels);
+
+/* ------------------------------------------------------------------------
+ * Compose driver: Stitcher::ComposePanorama (stitcher.cc:299-432) with
+ * ComputeRoi (:144-169) and the size cap (:318-335), cameras given
+ * (registration is out of scope). Everything between the uploaded sources
+ * and the downloaded panorama stays on the device.
+ * ---------------------------------------------------------------------- */
+typedef struct {
+  const void* data; /* 8UC3 / 16UC3 interleaved                            */
+  int w, h;
+  size_t stride;    /* bytes, 0 = packed                                    */
+  float K[9];       /* already scaled by 1/work_scale (utils/opencv.cc:14-26)*/
+  float R[9];
+  xp_compose_aux aux; /* host pointers                                      */
+} xp_compose_image;
+
+typedef struct {
+  int projection, portrait;
+  float a, b;
+  float warp_scale;     /* warped_image_scale * compose_work_aspect         */
+  double max_pano_mpx;  /* StitchUserOptions::max_pano_mpx (constants.h:106)*/
+  int depth;            /* 8 or 16                                          */
+  xp_blend_opts blend;
+} xp_compose_opts;
+
+typedef struct xp_composer xp_composer;
+typedef struct {
+  int width, height, min_x, min_y, bpp, levels, resolution_capped;
+  int roi[4];           /* ComputeRoi rect                                  */
+  float warp_scale;     /* after the cap                                    */
+  double warp_ms, blend_ms, h2d_ms, d2h_ms;
+  xp_timing timing;
+  /* workload sizes for the roofline */
+  double s_src, s_w, s_t, c;
+} xp_compose_info;
+
+void xp_compose_opts_default(xp_compose_opts* o);
+xp_status xp_composer_create(const xp_compose_opts* opts, xp_composer** out);
+void xp_composer_destroy(xp_composer* c);
+xp_status xp_composer_set_stream(xp_composer* c, void* cuda_stream);
+/* Upload (or adopt, mem == XP_MEM_DEVICE) the source images. */
+xp_status xp_composer_set_images(xp_composer* c, int n,
+                                 const xp_compose_image* images, int mem);
+/* Run warp -> feed -> blend on the device; result stays resident. */
+xp_status xp_composer_run(xp_composer* c, xp_compose_info* info);
+/* Copy the panorama (interleaved BGR, zero outside mask) and mask out. */
+xp_status xp_composer_fetch(xp_composer* c, void* dst_bgr, size_t dst_stride,
+                            uint8_t* dst_mask, size_t mask_stride, int mem);
+/* the blender a composer drives (for debug_fetch) */
+xp_blender* xp_composer_blender(xp_composer* c);
+/* number of kernels this library launched since process start */
+unsigned long long xp_kernel_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* XPANO_B200_H_ */

@@ -1,0 +1,184 @@
+// TEST INFRASTRUCTURE ONLY: host SIMT emulator for the wavefront kernels.
+//
+// Compiles the product's device-agnostic sources (xpano_b200/csrc/wavefront.h,
+// scan_problems.h) with g++ and runs them with one OS thread per lane, 32
+// lanes per emulated warp, warp shuffles and __syncwarp implemented with
+// barriers, progress counters with atomics. This lets the CPU test suite
+// (-m "not gpu") check the exact code the GPU runs -- skew arithmetic, tile
+// staging, band hand-over -- against the oracle without a device.
+//
+// Build: g++ -O2 -std=c++20 -pthread -shared -fPIC (tests/test_emu_wavefront.py)
+#include <atomic>
+#include <barrier>
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <thread>
+#include <vector>
+
+#include "../../xpano_b200/csrc/scan_problems.h"
+#include "../../xpano_b200/csrc/wavefront.h"
+
+using namespace xp;
+
+namespace {
+
+struct EmuWarp {
+  std::barrier<> bar{32};
+  uint64_t x[32];
+};
+
+struct EmuCtx {
+  EmuWarp* w;
+  int lane_;
+  int lane() const { return lane_; }
+  int atomic_add(int* p, int v) {
+    return __atomic_fetch_add(p, v, __ATOMIC_ACQ_REL);
+  }
+  uint64_t exchange(uint64_t v, int src) {
+    w->x[lane_] = v;
+    w->bar.arrive_and_wait();
+    uint64_t r = (src >= 0 && src < 32) ? w->x[src] : v;
+    w->bar.arrive_and_wait();
+    return r;
+  }
+  int bcast(int v) { return (int)exchange((uint64_t)(uint32_t)v, 0); }
+  uint64_t shfl_up1(uint64_t v) { return exchange(v, lane_ - 1); }
+  uint64_t shfl_idx(uint64_t v, int src) { return exchange(v, src & 31); }
+  void sync() { w->bar.arrive_and_wait(); }
+  void wait_ge(const int* p, int need) {
+    while (__atomic_load_n(p, __ATOMIC_ACQUIRE) < need)
+      std::this_thread::yield();
+  }
+  void publish(int* p, int v) { __atomic_store_n(p, v, __ATOMIC_RELEASE); }
+};
+
+template <class P>
+void run_emulated(const P& prob, int n_warps) {
+  if (prob.n_bands <= 0) return;
+  if (n_warps > prob.n_bands) n_warps = prob.n_bands;
+  int counter = 0;
+  std::vector<int> progress(prob.n_bands, 0);
+  std::vector<std::unique_ptr<EmuWarp>> warps;
+  std::vector<std::vector<unsigned char>> smem(n_warps);
+  for (int i = 0; i < n_warps; ++i) {
+    warps.emplace_back(new EmuWarp());
+    smem[i].resize(wf::tile_bytes<P>());
+  }
+  std::vector<std::thread> threads;
+  for (int wi = 0; wi < n_warps; ++wi)
+    for (int l = 0; l < 32; ++l)
+      threads.emplace_back([&, wi, l] {
+        EmuCtx ctx{warps[wi].get(), l};
+        wf::run(ctx, prob, &counter, progress.data(), smem[wi].data());
+      });
+  for (auto& t : threads) t.join();
+}
+
+// mirrors cover_kernel in seams.cu
+template <class C>
+void build_cover(std::vector<C>& cover, int CW, int CH, int n, const int* xpos,
+                 const int* ypos, const int* w, const int* h,
+                 const uint8_t* const* opaque) {
+  cover.assign((size_t)CW * CH, 0);
+  for (int i = 0; i < n; ++i)
+    for (int ly = 0; ly < h[i]; ++ly)
+      for (int lx = 0; lx <= w[i]; ++lx) {
+        int cx = xpos[i] + lx, cy = ypos[i] + ly;
+        if (cx >= CW) continue;
+        C add = 0;
+        if (lx < w[i]) {
+          const uint8_t* op = opaque[i] + (size_t)ly * w[i];
+          if (op[lx]) add |= (C)1 << i;
+          if (lx == 0 || (op[lx] != 0) != (op[lx - 1] != 0))
+            add |= CoverTraits<C>::rs_bit;
+        } else {
+          add |= CoverTraits<C>::rs_bit;
+        }
+        cover[(size_t)cy * CW + cx] |= add;
+      }
+}
+
+template <class C>
+void seams_t(int n, const int* xpos, const int* ypos, const int* w,
+             const int* h, const uint8_t* const* opaque, int W, int H,
+             int reverse, int32_t* labels, uint64_t* bwd, uint64_t* fwd,
+             int n_warps) {
+  std::vector<C> cover;
+  build_cover(cover, W, H, n, xpos, ypos, w, h, opaque);
+  std::vector<uint8_t> lab8((size_t)W * H);
+  const int n_bands = (H + 31) / 32;
+  SeamBwd<C> pb{n_bands, W, H, cover.data(), bwd};
+  run_emulated(pb, n_warps);
+  SeamFwd<C> pf{n_bands, W, H, reverse, cover.data(), bwd, fwd, lab8.data()};
+  run_emulated(pf, n_warps);
+  for (size_t i = 0; i < lab8.size(); ++i) labels[i] = lab8[i];
+}
+
+}  // namespace
+
+extern "C" {
+
+void emu_seams(int n, const int* xpos, const int* ypos, const int* w,
+               const int* h, const uint8_t* const* opaque, int W, int H,
+               int reverse, int wide, int32_t* labels, uint64_t* bwd,
+               uint64_t* fwd, int n_warps) {
+  if (wide)
+    seams_t<u64>(n, xpos, ypos, w, h, opaque, W, H, reverse, labels, bwd, fwd,
+                 n_warps);
+  else
+    seams_t<u32>(n, xpos, ypos, w, h, opaque, W, H, reverse, labels, bwd, fwd,
+                 n_warps);
+}
+
+// Inpaints n images at once (the band table interleaves them like the
+// product does). data[i]: 4-sample interleaved pixels, modified in place by
+// gathering the final source indices; bbox[i*4..] = left, top, w, h.
+void emu_inpaint(int n, void* const* data, const int* tiff_w, int bpp,
+                 const int* bbox, int n_warps) {
+  std::vector<InpaintJob> jobs(n);
+  std::vector<std::vector<u64>> fwd(n), bwd(n);
+  int max_bands = 0;
+  for (int i = 0; i < n; ++i) {
+    const int* b = bbox + 4 * i;
+    fwd[i].assign((size_t)b[2] * b[3], 0);
+    bwd[i].assign((size_t)b[2] * b[3], 0);
+    jobs[i] = InpaintJob{data[i],       tiff_w[i],     b[0], b[1], b[2],
+                         b[3],          fwd[i].data(), bwd[i].data(), 0};
+    max_bands = std::max(max_bands, (b[3] + 31) / 32);
+  }
+  // band-major table; dep = global index of the previous band of the same job
+  std::vector<InpaintBandRef> bands;
+  std::vector<int> prev(n, -1);
+  for (int lb = 0; lb < max_bands; ++lb)
+    for (int i = 0; i < n; ++i)
+      if (lb < (jobs[i].h + 31) / 32) {
+        bands.push_back(InpaintBandRef{i, lb, prev[i]});
+        prev[i] = (int)bands.size() - 1;
+      }
+  const int nb = (int)bands.size();
+  if (bpp == 8) {
+    InpaintFwd<8> pf{nb, jobs.data(), bands.data()};
+    run_emulated(pf, n_warps);
+  } else {
+    InpaintFwd<16> pf{nb, jobs.data(), bands.data()};
+    run_emulated(pf, n_warps);
+  }
+  InpaintBwd pb{nb, jobs.data(), bands.data()};
+  run_emulated(pb, n_warps);
+  for (int i = 0; i < n; ++i) {
+    const InpaintJob& j = jobs[i];
+    const size_t px = bpp == 8 ? 4 : 8;
+    std::vector<unsigned char> copy((size_t)j.tiff_w * (j.top + j.h) * px);
+    memcpy(copy.data(), j.data, copy.size());
+    for (int y = 0; y < j.h; ++y)
+      for (int x = 0; x < j.w; ++x) {
+        u32 src = (u32)bwd[i][(size_t)y * j.w + x];
+        size_t dst = (size_t)(j.top + y) * j.tiff_w + j.left + x;
+        memcpy((unsigned char*)data[i] + dst * px, copy.data() + src * px, px);
+      }
+  }
+}
+
+}  // extern "C"

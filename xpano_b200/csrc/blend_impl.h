@@ -1,0 +1,114 @@
+// Internal declarations shared by the blend translation units.
+#pragma once
+
+#include <cstdint>
+
+#include "common.h"
+#include "scan_problems.h"
+
+namespace xp {
+
+constexpr int kMaxLevels = 24;
+constexpr int kMaxImages = 63;
+
+// One fed image after trim, as the kernels see it.
+struct ImgDev {
+  const void* data;  // interleaved 4-sample pixels, untrimmed
+  int tiff_w, tiff_h;
+  int left, top, w, h;  // trim bbox
+  int xpos, ypos;       // canvas position of the bbox after tighten
+};
+
+struct CanvasStats {
+  unsigned long long totals[4];  // 3 channel sums + pixel count over xor px
+  int uncovered;                 // some canvas pixel has no image
+  int pad;
+  int box[64][4];                // owner-region bbox per image (x0,y0,x1,y1)
+};
+
+// Pyramid level geometry (pyramid.cpp:21-98)
+struct LevelGeom {
+  int w, h, pitch, rows;
+  int x, y, xs, ys;
+  size_t offset;  // float offset of this level inside one channel
+};
+
+struct PyrGeom {
+  int n = 0;
+  LevelGeom lv[kMaxLevels];
+  size_t channel_floats = 0;  // floats per channel (all levels)
+};
+
+PyrGeom make_pyramid(int width, int height, int levels, int x, int y);
+
+// Dense mask pyramid level of one image, stored over a sub-rectangle of the
+// canvas level grid (zero outside).
+struct MaskLevel {
+  int x0, y0, w, h;  // rect on the canvas level grid; w == 0: empty
+  int cw, ch;        // canvas level size (functions.cpp:188-191)
+  size_t offset;     // float offset in the image's mask buffer
+};
+
+// seams.cu
+void launch_trim(const void* data, int w, int h, int bpp, int* d_bbox,
+                 cudaStream_t s);
+void launch_cover(void* cover, int cover_bytes, int CW, const ImgDev& im,
+                  int bpp, int bit, unsigned long long* d_transparent,
+                  cudaStream_t s);
+void launch_seams(const void* cover, int cover_bytes, int W, int H,
+                  int reverse, u64* bwd, u64* fwd, uint8_t* labels,
+                  int* counter, int* progress, cudaStream_t s);
+void launch_inpaint(const InpaintJob* d_jobs, const InpaintBandRef* d_bands,
+                    int n_bands, int bpp, int* counter, int* progress,
+                    cudaStream_t s);
+void launch_canvas_stats(const void* cover, int cover_bytes,
+                         const uint8_t* labels, int W, int H,
+                         const ImgDev* d_imgs, int n, int bpp,
+                         uint8_t* full_mask, uint8_t* xor_mask,
+                         CanvasStats* d_stats, cudaStream_t s);
+
+// pyramid.cu
+// level 0 of an image pyramid from the (inpainted) source pixels.
+// src_index: h x w u64 whose low 32 bits index `im.data`, or null (identity).
+void launch_copy_level0(const ImgDev& im, int bpp, const u64* src_index,
+                        float mul, const PyrGeom& g, float* pyr,
+                        cudaStream_t s);
+void launch_shrink(const PyrGeom& g, float* pyr, int level, int channels,
+                   cudaStream_t s);
+// hi <- expand(lo) - hi for `level` (Laplace and Collapse are the same op)
+void launch_laplace(const PyrGeom& g, float* pyr, int level, int channels,
+                    cudaStream_t s);
+void launch_mask_level1(const uint8_t* labels, int CW, int CH, int image,
+                        const MaskLevel& out, float* mask, cudaStream_t s);
+void launch_mask_shrink(const MaskLevel& in, const MaskLevel& out, float* mask,
+                        cudaStream_t s);
+// out level (+)= in level * mask (functions.cpp:319-411)
+void launch_composite(const PyrGeom& in_g, const float* in_pyr,
+                      const PyrGeom& out_g, float* out_pyr, int level,
+                      const uint8_t* labels, int image, const MaskLevel& m,
+                      const float* mask, cudaStream_t s);
+void launch_pad_level(const PyrGeom& g, float* pyr, int level, int channels,
+                      cudaStream_t s);
+// Σ level0 over xor pixels (double), per channel -> d_sums[3]
+void launch_xor_sum(const PyrGeom& g, const float* pyr,
+                    const uint8_t* xor_mask, int W, int H, double* d_partials,
+                    double* d_sums, cudaStream_t s);
+// offset add (from device scalars) + dither + clamp + round + planar/BGR pack
+void launch_out(const PyrGeom& g, const float* pyr, int W, int H, int out_bpp,
+                int dither, int apply_add, const CanvasStats* d_stats,
+                const double* d_sums, int in_bpp,
+                const uint8_t* full_mask, void* planes, void* bgr,
+                cudaStream_t s);
+// debug helpers
+void launch_extract_chan(const ImgDev& im, int bpp, const u64* src_index,
+                         int channel, void* out, cudaStream_t s);
+void launch_extract_opaque(const ImgDev& im, int bpp, uint8_t* out,
+                           cudaStream_t s);
+void launch_labels_to_i32(const uint8_t* labels, size_t n, int32_t* out,
+                          cudaStream_t s);
+// BGR (+mask) -> 4-sample interleaved (blenders.cc:99-112)
+void launch_pack_bgra(const void* bgr, size_t bgr_pitch, const uint8_t* mask,
+                      size_t mask_pitch, int w, int h, int depth, int spp_in,
+                      void* out, cudaStream_t s);
+
+}  // namespace xp

@@ -1,0 +1,127 @@
+// Shared host-side helpers of libxpano_b200: error convention, CUDA checks,
+// device buffers, launch counting. Not part of the public ABI.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/xpano_b200.h"
+
+namespace xp {
+
+void set_error(const char* fmt, ...);
+extern std::atomic<unsigned long long> g_launches;
+
+struct Error : std::runtime_error {
+  xp_status code;
+  Error(xp_status c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+
+[[noreturn]] void fail(xp_status code, const char* fmt, ...);
+
+#define XP_CUDA(expr)                                                        \
+  do {                                                                       \
+    cudaError_t e__ = (expr);                                                \
+    if (e__ != cudaSuccess)                                                  \
+      ::xp::fail(XP_ERR_CUDA, "%s failed: %s (%s:%d)", #expr,                \
+                 cudaGetErrorString(e__), __FILE__, __LINE__);               \
+  } while (0)
+
+#define XP_REQUIRE(cond, ...)                                 \
+  do {                                                        \
+    if (!(cond)) ::xp::fail(XP_ERR_INVALID, __VA_ARGS__);     \
+  } while (0)
+
+// counts a kernel launch and checks the launch error
+#define XP_LAUNCHED()                                                       \
+  do {                                                                      \
+    ::xp::g_launches.fetch_add(1, std::memory_order_relaxed);               \
+    XP_CUDA(cudaGetLastError());                                            \
+  } while (0)
+
+// Wraps a C-ABI body: exceptions never cross the ABI.
+template <class F>
+xp_status guard(F&& f) {
+  try {
+    f();
+    return XP_OK;
+  } catch (const Error& e) {
+    set_error("%s", e.what());
+    return e.code;
+  } catch (const std::bad_alloc&) {
+    set_error("out of host memory");
+    return XP_ERR_NOMEM;
+  } catch (const std::exception& e) {
+    set_error("%s", e.what());
+    return XP_ERR_INVALID;
+  }
+}
+
+// Owning device allocation.
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  DevBuf() = default;
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) {
+    o.p = nullptr;
+    o.bytes = 0;
+  }
+  DevBuf& operator=(DevBuf&& o) noexcept {
+    if (this != &o) {
+      release();
+      p = o.p;
+      bytes = o.bytes;
+      o.p = nullptr;
+      o.bytes = 0;
+    }
+    return *this;
+  }
+  ~DevBuf() { release(); }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+  }
+  // grow-only (re)allocation; contents are not preserved
+  void reserve(size_t n) {
+    if (n <= bytes) return;
+    release();
+    if (n == 0) return;
+    cudaError_t e = cudaMalloc(&p, n);
+    if (e != cudaSuccess) {
+      p = nullptr;
+      fail(e == cudaErrorMemoryAllocation ? XP_ERR_NOMEM : XP_ERR_CUDA,
+           "cudaMalloc(%zu) failed: %s", n, cudaGetErrorString(e));
+    }
+    bytes = n;
+  }
+  template <class T>
+  T* as() const {
+    return static_cast<T*>(p);
+  }
+};
+
+inline int div_up(int a, int b) { return (a + b - 1) / b; }
+inline size_t div_up(size_t a, size_t b) { return (a + b - 1) / b; }
+
+void select_device(int device);
+
+// 2-D copy helper between host/device according to `mem` of the *user* side.
+void copy_in_2d(void* dev, size_t dev_pitch, const void* user,
+                size_t user_pitch, size_t row_bytes, size_t rows, int mem,
+                cudaStream_t s);
+void copy_out_2d(void* user, size_t user_pitch, const void* dev,
+                 size_t dev_pitch, size_t row_bytes, size_t rows, int mem,
+                 cudaStream_t s);
+
+}  // namespace xp

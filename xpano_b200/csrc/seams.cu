@@ -1,0 +1,320 @@
+// Mask / seam stage on the device: trim bbox, cover map, the two inpaint
+// passes and the two seam passes (wavefront kernels), canvas statistics.
+//
+// Replaces external/multiblend/src/image.cpp:396-812 (trim, inpaint) and
+// src/multiblend.cpp:229-823 (seams, full/xor masks, channel sums).
+#include <climits>
+
+#include "blend_impl.h"
+#include "common.h"
+#include "scan_problems.h"
+#include "wavefront.h"
+
+namespace xp {
+
+// ---------------------------------------------------------------------------
+// device warp context for the wavefront driver
+// ---------------------------------------------------------------------------
+struct DevCtx {
+  __device__ __forceinline__ int lane() const { return threadIdx.x & 31; }
+  __device__ __forceinline__ int atomic_add(int* p, int v) {
+    return atomicAdd(p, v);
+  }
+  __device__ __forceinline__ int bcast(int v) {
+    return __shfl_sync(0xffffffffu, v, 0);
+  }
+  __device__ __forceinline__ u64 shfl_up1(u64 v) {
+    return __shfl_up_sync(0xffffffffu, v, 1);
+  }
+  __device__ __forceinline__ u64 shfl_idx(u64 v, int src) {
+    return __shfl_sync(0xffffffffu, v, src);
+  }
+  __device__ __forceinline__ void sync() { __syncwarp(); }
+  __device__ __forceinline__ void wait_ge(const int* p, int need) {
+    int v;
+    for (;;) {
+      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];"
+                   : "=r"(v)
+                   : "l"(p)
+                   : "memory");
+      if (v >= need) break;
+      __nanosleep(32);
+    }
+  }
+  __device__ __forceinline__ void publish(int* p, int v) {
+    __threadfence();
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v)
+                 : "memory");
+  }
+};
+
+template <class P>
+__global__ void __launch_bounds__(32)
+    wavefront_kernel(P prob, int* counter, int* progress) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  DevCtx ctx;
+  wf::run(ctx, prob, counter, progress, smem);
+}
+
+template <class P>
+static void launch_wavefront(const P& prob, int* counter, int* progress,
+                             cudaStream_t s) {
+  if (prob.n_bands <= 0) return;
+  XP_CUDA(cudaMemsetAsync(counter, 0, sizeof(int), s));
+  XP_CUDA(cudaMemsetAsync(progress, 0, sizeof(int) * (size_t)prob.n_bands, s));
+  const size_t smem = wf::tile_bytes<P>();
+  const int blocks = std::min(prob.n_bands, 148 * 8);
+  wavefront_kernel<P><<<blocks, 32, smem, s>>>(prob, counter, progress);
+  XP_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// trim: bbox of alpha == max (image.cpp:396-447; the widening loops make the
+// result the exact bounding box of the opaque pixels)
+// ---------------------------------------------------------------------------
+template <int BPP>
+__global__ void trim_kernel(const void* data, int w, int h, int* bbox) {
+  int minx = INT_MAX, miny = INT_MAX, maxx = -1, maxy = -1;
+  const size_t n = (size_t)w * h;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x) {
+    if (px_opaque<BPP>(data, i)) {
+      const int x = (int)(i % w), y = (int)(i / w);
+      minx = min(minx, x);
+      maxx = max(maxx, x);
+      miny = min(miny, y);
+      maxy = max(maxy, y);
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    minx = min(minx, __shfl_xor_sync(~0u, minx, o));
+    miny = min(miny, __shfl_xor_sync(~0u, miny, o));
+    maxx = max(maxx, __shfl_xor_sync(~0u, maxx, o));
+    maxy = max(maxy, __shfl_xor_sync(~0u, maxy, o));
+  }
+  if ((threadIdx.x & 31) == 0 && maxx >= 0) {
+    atomicMin(bbox + 0, minx);
+    atomicMin(bbox + 1, miny);
+    atomicMax(bbox + 2, maxx);
+    atomicMax(bbox + 3, maxy);
+  }
+}
+
+void launch_trim(const void* data, int w, int h, int bpp, int* d_bbox,
+                 cudaStream_t s) {
+  const int blocks =
+      (int)std::min<size_t>(div_up((size_t)w * h, (size_t)256), 148 * 8);
+  if (bpp == 8)
+    trim_kernel<8><<<blocks, 256, 0, s>>>(data, w, h, d_bbox);
+  else
+    trim_kernel<16><<<blocks, 256, 0, s>>>(data, w, h, d_bbox);
+  XP_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// cover map: bit i = image i opaque here; top bit = a run of the reference's
+// RLE walk starts here (bbox edges and opacity changes of any image,
+// multiblend.cpp:509-534). Also counts the image's non-opaque bbox pixels.
+// ---------------------------------------------------------------------------
+template <class C, int BPP>
+__global__ void cover_kernel(C* cover, int CW, ImgDev im, int bit,
+                             unsigned long long* transparent) {
+  const int lx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int ly = blockIdx.y * blockDim.y + threadIdx.y;
+  int holes = 0;
+  if (lx <= im.w && ly < im.h) {
+    const int cx = im.xpos + lx, cy = im.ypos + ly;
+    if (cx < CW) {
+      C add = 0;
+      if (lx < im.w) {
+        const size_t p = (size_t)(im.top + ly) * im.tiff_w + im.left + lx;
+        const bool op = px_opaque<BPP>(im.data, p);
+        if (op) add |= (C)1 << bit;
+        if (lx == 0 || op != px_opaque<BPP>(im.data, p - 1))
+          add |= CoverTraits<C>::rs_bit;
+        holes = op ? 0 : 1;
+      } else {
+        add |= CoverTraits<C>::rs_bit;
+      }
+      if (add) cover[(size_t)cy * CW + cx] |= add;
+    }
+  }
+  holes = __syncthreads_count(holes);
+  if (threadIdx.x == 0 && threadIdx.y == 0 && holes)
+    atomicAdd(transparent, (unsigned long long)holes);
+}
+
+void launch_cover(void* cover, int cover_bytes, int CW, const ImgDev& im,
+                  int bpp, int bit, unsigned long long* d_transparent,
+                  cudaStream_t s) {
+  dim3 b(32, 8);
+  dim3 g(div_up(im.w + 1, 32), div_up(im.h, 8));
+#define XP_COVER(C, BPP)                                                  \
+  cover_kernel<C, BPP><<<g, b, 0, s>>>((C*)cover, CW, im, bit, d_transparent)
+  if (cover_bytes == 4) {
+    if (bpp == 8)
+      XP_COVER(u32, 8);
+    else
+      XP_COVER(u32, 16);
+  } else {
+    if (bpp == 8)
+      XP_COVER(u64, 8);
+    else
+      XP_COVER(u64, 16);
+  }
+#undef XP_COVER
+  XP_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// seams
+// ---------------------------------------------------------------------------
+void launch_seams(const void* cover, int cover_bytes, int W, int H,
+                  int reverse, u64* bwd, u64* fwd, uint8_t* labels,
+                  int* counter, int* progress, cudaStream_t s) {
+  const int n_bands = div_up(H, wf::kLanes);
+  if (cover_bytes == 4) {
+    SeamBwd<u32> pb{n_bands, W, H, (const u32*)cover, bwd};
+    launch_wavefront(pb, counter, progress, s);
+    SeamFwd<u32> pf{n_bands, W, H, reverse, (const u32*)cover, bwd, fwd,
+                    labels};
+    launch_wavefront(pf, counter, progress, s);
+  } else {
+    SeamBwd<u64> pb{n_bands, W, H, (const u64*)cover, bwd};
+    launch_wavefront(pb, counter, progress, s);
+    SeamFwd<u64> pf{n_bands, W, H, reverse, (const u64*)cover, bwd, fwd,
+                    labels};
+    launch_wavefront(pf, counter, progress, s);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// inpaint
+// ---------------------------------------------------------------------------
+void launch_inpaint(const InpaintJob* d_jobs, const InpaintBandRef* d_bands,
+                    int n_bands, int bpp, int* counter, int* progress,
+                    cudaStream_t s) {
+  if (bpp == 8) {
+    InpaintFwd<8> pf{n_bands, d_jobs, d_bands};
+    launch_wavefront(pf, counter, progress, s);
+  } else {
+    InpaintFwd<16> pf{n_bands, d_jobs, d_bands};
+    launch_wavefront(pf, counter, progress, s);
+  }
+  InpaintBwd pb{n_bands, d_jobs, d_bands};
+  launch_wavefront(pb, counter, progress, s);
+}
+
+// ---------------------------------------------------------------------------
+// canvas statistics (multiblend.cpp:536-616, 821-823): full / xor masks,
+// per-channel sums of the inputs over exclusively covered pixels, whether any
+// pixel is uncovered, and the bounding box of every image's owner region.
+// ---------------------------------------------------------------------------
+template <class C, int BPP>
+__global__ void canvas_stats_kernel(const C* __restrict__ cover,
+                                    const uint8_t* __restrict__ labels, int W,
+                                    int H, const ImgDev* __restrict__ imgs,
+                                    int n, uint8_t* __restrict__ full_mask,
+                                    uint8_t* __restrict__ xor_mask,
+                                    CanvasStats* stats) {
+  __shared__ int s_box[64][4];
+  __shared__ unsigned long long s_sum[4];
+  __shared__ int s_uncovered;
+  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+  for (int i = tid; i < 64; i += blockDim.x * blockDim.y) {
+    s_box[i][0] = INT_MAX;
+    s_box[i][1] = INT_MAX;
+    s_box[i][2] = -1;
+    s_box[i][3] = -1;
+  }
+  if (tid < 4) s_sum[tid] = 0;
+  if (tid == 0) s_uncovered = 0;
+  __syncthreads();
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  unsigned long long sum[4] = {0, 0, 0, 0};
+  if (x < W && y < H) {
+    const size_t p = (size_t)y * W + x;
+    const C bits = cover[p] & ~CoverTraits<C>::rs_bit;
+    const int cnt = popc_c(bits);
+    full_mask[p] = cnt ? 255 : 0;
+    xor_mask[p] = cnt == 1 ? 1 : 0;
+    if (cnt == 0) s_uncovered = 1;
+    if (cnt == 1) {
+      const ImgDev im = imgs[ctz_c(bits)];
+      const size_t q =
+          (size_t)(im.top + y - im.ypos) * im.tiff_w + im.left + x - im.xpos;
+      if (BPP == 8) {
+        const u32 v = static_cast<const u32*>(im.data)[q];
+        sum[0] = v & 0xff;
+        sum[1] = (v >> 8) & 0xff;
+        sum[2] = (v >> 16) & 0xff;
+      } else {
+        const u64 v = static_cast<const u64*>(im.data)[q];
+        sum[0] = v & 0xffff;
+        sum[1] = (v >> 16) & 0xffff;
+        sum[2] = (v >> 32) & 0xffff;
+      }
+      sum[3] = 1;
+    }
+    if (n > 1) {
+      const int l = labels[p];
+      atomicMin(&s_box[l][0], x);
+      atomicMin(&s_box[l][1], y);
+      atomicMax(&s_box[l][2], x);
+      atomicMax(&s_box[l][3], y);
+    }
+  }
+  for (int k = 0; k < 4; ++k) {
+    unsigned long long v = sum[k];
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(~0u, v, o);
+    if ((tid & 31) == 0 && v) atomicAdd(&s_sum[k], v);
+  }
+  __syncthreads();
+  if (tid < 4 && s_sum[tid]) atomicAdd(&stats->totals[tid], s_sum[tid]);
+  if (tid == 0 && s_uncovered) stats->uncovered = 1;
+  for (int i = tid; i < n; i += blockDim.x * blockDim.y) {
+    if (s_box[i][2] >= 0) {
+      atomicMin(&stats->box[i][0], s_box[i][0]);
+      atomicMin(&stats->box[i][1], s_box[i][1]);
+      atomicMax(&stats->box[i][2], s_box[i][2]);
+      atomicMax(&stats->box[i][3], s_box[i][3]);
+    }
+  }
+}
+
+void launch_canvas_stats(const void* cover, int cover_bytes,
+                         const uint8_t* labels, int W, int H,
+                         const ImgDev* d_imgs, int n, int bpp,
+                         uint8_t* full_mask, uint8_t* xor_mask,
+                         CanvasStats* d_stats, cudaStream_t s) {
+  CanvasStats init;
+  memset(&init, 0, sizeof(init));
+  for (int i = 0; i < 64; ++i) {
+    init.box[i][0] = init.box[i][1] = INT_MAX;
+    init.box[i][2] = init.box[i][3] = -1;
+  }
+  XP_CUDA(cudaMemcpyAsync(d_stats, &init, sizeof(init), cudaMemcpyHostToDevice,
+                          s));
+  dim3 b(32, 8);
+  dim3 g(div_up(W, 32), div_up(H, 8));
+#define XP_STATS(C, BPP)                                                    \
+  canvas_stats_kernel<C, BPP><<<g, b, 0, s>>>((const C*)cover, labels, W, H, \
+                                              d_imgs, n, full_mask,          \
+                                              xor_mask, d_stats)
+  if (cover_bytes == 4) {
+    if (bpp == 8)
+      XP_STATS(u32, 8);
+    else
+      XP_STATS(u32, 16);
+  } else {
+    if (bpp == 8)
+      XP_STATS(u64, 8);
+    else
+      XP_STATS(u64, 16);
+  }
+#undef XP_STATS
+  XP_LAUNCHED();
+}
+
+}  // namespace xp
