@@ -1,0 +1,187 @@
+// Blender: device-resident restatement of multiblend::Multiblend() as xpano
+// calls it (in-memory images, no gamma, no wrap), behind the
+// cv::detail::Blender-shaped prepare / feed / blend surface of
+// xpano/algorithm/blenders.cc:116-158.
+//
+// Stage order follows external/multiblend/src/multiblend.cpp:66-1307:
+// read/trim/inpaint (image.cpp:336-919) -> tighten (:139-154) -> level count
+// (:161-206) -> seams (:254-823) -> mask pyramids (:919-930) -> per image
+// copy/shrink/laplace/composite (:1057-1126) -> collapse (:1129) -> offset
+// correction (:1232-1267) -> out (:1274-1286) -> blenders.cc:151-154.
+#include <algorithm>
+#include <climits>
+#include <cmath>
+
+#include "blender.h"
+#include "common.h"
+
+namespace xp {
+
+// ---------------------------------------------------------------------------
+// level count: multiblend.cpp:161-206
+// ---------------------------------------------------------------------------
+int blend_levels(int n, const int* widths, const int* heights,
+                 int fixed_levels, int add_levels) {
+  int levels;
+  if (fixed_levels == 0) {
+    std::vector<int> ws(widths, widths + n), hs(heights, heights + n);
+    std::sort(ws.begin(), ws.end());
+    std::sort(hs.begin(), hs.end());
+    const int half = (n - 1) >> 1;
+    const int mw = (n & 1) ? ws[half] : (ws[half] + ws[half + 1] + 1) >> 1;
+    const int mh = (n & 1) ? hs[half] : (hs[half] + hs[half + 1] + 1) >> 1;
+    const int blend_wh = std::max(mw, mh);
+    // std::log2(blend_wh + 4.0f) is evaluated in float
+    levels = (int)floorf(log2f((float)blend_wh + 4.0f) - 1);
+  } else {
+    levels = fixed_levels;
+  }
+  levels += add_levels;
+  if (n == 1) levels = 0;
+  return levels;
+}
+
+// ---------------------------------------------------------------------------
+// stage timing with CUDA events on the blender's stream
+// ---------------------------------------------------------------------------
+StageTimer::~StageTimer() {
+  for (cudaEvent_t e : pool) cudaEventDestroy(e);
+}
+cudaEvent_t StageTimer::get() {
+  if (used == pool.size()) {
+    cudaEvent_t e;
+    XP_CUDA(cudaEventCreate(&e));
+    pool.push_back(e);
+  }
+  return pool[used++];
+}
+void StageTimer::reset(cudaStream_t stream) {
+  spans.clear();
+  used = 0;
+  s = stream;
+}
+int StageTimer::begin(int stage) {
+  Span sp{stage, get(), get()};
+  XP_CUDA(cudaEventRecord(sp.a, s));
+  spans.push_back(sp);
+  return (int)spans.size() - 1;
+}
+void StageTimer::end(int idx) { XP_CUDA(cudaEventRecord(spans[idx].b, s)); }
+void StageTimer::collect(double out[16]) {
+  for (int i = 0; i < 16; ++i) out[i] = 0;
+  for (const Span& sp : spans) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess)
+      out[sp.stage] += ms;
+  }
+}
+
+enum {
+  ST_IMAGES = 0, ST_SEAM, ST_SHRINK_MASK, ST_COPY, ST_SHRINK, ST_LAPLACE,
+  ST_BLEND, ST_COLLAPSE, ST_OUT, ST_TOTAL
+};
+
+struct Scope {
+  StageTimer& t;
+  int idx;
+  Scope(StageTimer& tt, int stage) : t(tt), idx(tt.begin(stage)) {}
+  ~Scope() {
+    if (cudaEventRecord(t.spans[idx].b, t.s) != cudaSuccess) cudaGetLastError();
+  }
+};
+
+// ---------------------------------------------------------------------------
+// Blender basics
+// ---------------------------------------------------------------------------
+Blender::~Blender() {
+  if (own_stream) cudaStreamDestroy(own_stream);
+}
+
+void Blender::ensure_device() {
+  select_device(opts.device);
+  if (!stream && !external_stream) {
+    XP_CUDA(cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
+    stream = own_stream;
+  }
+}
+
+Fed* Blender::new_fed(int w, int h, int depth, int tl_x, int tl_y) {
+  XP_REQUIRE(w > 0 && h > 0, "feed: empty image");
+  XP_REQUIRE(depth == 8 || depth == 16, "feed: depth must be 8 or 16");
+  XP_REQUIRE((size_t)w * h < (1ull << 32), "feed: image too large");
+  XP_REQUIRE(!blended, "blender instances are single-use (blenders.cc)");
+  if (!fed.empty())
+    XP_REQUIRE(fed[0]->depth == depth,
+               "mixture of 8bpp and 16bpp images (multiblend.cpp:100-117)");
+  XP_REQUIRE((int)fed.size() < kMaxImages, "more than %d images", kMaxImages);
+  ensure_device();
+  std::unique_ptr<Fed> f(new Fed());
+  f->w = w;
+  f->h = h;
+  f->depth = depth;
+  f->xpos = tl_x;
+  f->ypos = tl_y;
+  f->data.reserve((size_t)w * h * 4 * (depth / 8));
+  fed.push_back(std::move(f));
+  return fed.back().get();
+}
+
+void Blender::feed(const void* data, size_t stride, const uint8_t* mask,
+                   size_t mask_stride, int w, int h, int depth, int spp,
+                   int tl_x, int tl_y, int mem) {
+  XP_REQUIRE(data, "feed: null image");
+  XP_REQUIRE(spp == 3 || spp == 4, "feed: spp must be 3 or 4");
+  const size_t bs = depth / 8;
+  const size_t row = (size_t)w * spp * bs;
+  if (stride == 0) stride = row;
+  if (mask_stride == 0) mask_stride = w;
+  Fed* f = new_fed(w, h, depth, tl_x, tl_y);
+  const void* dsrc = data;
+  size_t dpitch = stride;
+  const uint8_t* dmask = mask;
+  size_t mpitch = mask_stride;
+  if (mem == XP_MEM_HOST) {
+    staging.reserve(row * (size_t)h);
+    copy_in_2d(staging.p, row, data, stride, row, h, mem, stream);
+    dsrc = staging.p;
+    dpitch = row;
+    if (mask) {
+      staging_mask.reserve((size_t)w * h);
+      copy_in_2d(staging_mask.p, w, mask, mask_stride, w, h, mem, stream);
+      dmask = staging_mask.as<uint8_t>();
+      mpitch = w;
+    }
+  }
+  launch_pack_bgra(dsrc, dpitch, dmask, mpitch, w, h, depth, spp, f->data.p,
+                   stream);
+  XP_CUDA(cudaStreamSynchronize(stream));
+}
+
+// mask pyramid rectangle of the next level (functions.cpp:188-191 geometry:
+// output j reads inputs 2j-4 .. 2j, clamped into the level)
+static void next_mask_rect(const MaskLevel& in, MaskLevel& out) {
+  out.cw = (in.cw + 6) >> 1;
+  out.ch = (in.ch + 6) >> 1;
+  if (in.w <= 0 || in.h <= 0) {
+    out.x0 = out.y0 = out.w = out.h = 0;
+    return;
+  }
+  auto range = [](int s0, int s1, int in_size, int out_size, int& j0, int& j1) {
+    j0 = s0 == 0 ? 0 : (s0 + 1) >> 1;
+    j1 = s1 == in_size - 1 ? out_size - 1 : (s1 + 4) >> 1;
+    if (j0 < 0) j0 = 0;
+    if (j1 > out_size - 1) j1 = out_size - 1;
+  };
+  int j0, j1, k0, k1;
+  range(in.x0, in.x0 + in.w - 1, in.cw, out.cw, j0, j1);
+  range(in.y0, in.y0 + in.h - 1, in.ch, out.ch, k0, k1);
+  out.x0 = j0;
+  out.y0 = k0;
+  out.w = j1 - j0 + 1;
+  out.h = k1 - k0 + 1;
+}
+
+}  // namespace xp
+
+#include "blend_run.inc"
+#include "blend_api.inc"

@@ -100,6 +100,10 @@ void launch_out(const PyrGeom& g, const float* pyr, int W, int H, int out_bpp,
                 const uint8_t* full_mask, void* planes, void* bgr,
                 cudaStream_t s);
 // debug helpers
+void launch_debug_collapsed(const PyrGeom& g, const float* pyr, int apply_add,
+                            const CanvasStats* d_stats, const double* d_sums,
+                            int in_bpp, int out_bpp, float* out,
+                            cudaStream_t s);
 void launch_extract_chan(const ImgDev& im, int bpp, const u64* src_index,
                          int channel, void* out, cudaStream_t s);
 void launch_extract_opaque(const ImgDev& im, int bpp, uint8_t* out,

@@ -1,0 +1,89 @@
+// Blender object behind the xp_blender_* C ABI (see blend.cu).
+#pragma once
+
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "blend_impl.h"
+
+namespace xp {
+
+struct Fed {
+  int w = 0, h = 0, depth = 8, xpos = 0, ypos = 0;
+  DevBuf data;  // w*h pixels of 4 samples (B, G, R, alpha)
+};
+
+struct StageTimer {
+  struct Span {
+    int stage;
+    cudaEvent_t a, b;
+  };
+  std::vector<Span> spans;
+  std::vector<cudaEvent_t> pool;
+  size_t used = 0;
+  cudaStream_t s = nullptr;
+  ~StageTimer();
+  cudaEvent_t get();
+  void reset(cudaStream_t stream);
+  int begin(int stage);
+  void end(int idx);
+  void collect(double out[16]);
+};
+
+struct Blender {
+  xp_blend_opts opts;
+  cudaStream_t stream = nullptr, own_stream = nullptr;
+  bool external_stream = false;
+  int roi[4] = {0, 0, 0, 0};
+  std::vector<std::unique_ptr<Fed>> fed;
+  DevBuf staging, staging_mask;
+
+  // ---- results of blend() ----
+  bool blended = false;
+  int n = 0, in_bpp = 8, out_bpp = 8;
+  int W = 0, H = 0, min_x = 0, min_y = 0, no_mask = 0, levels = 0;
+  std::vector<ImgDev> im;
+  CanvasStats stats;
+  std::vector<unsigned long long> transparent;
+  PyrGeom out_g;
+  DevBuf d_bbox, d_transparent, d_imgs, d_stats, d_jobs, d_bands, d_counter,
+      d_progress, d_partials, d_sums;
+  DevBuf cover, seam_bwd, seam_fwd, labels, full_mask, xor_mask;
+  std::vector<DevBuf> inp_fwd, inp_bwd;  // per image (empty if no holes)
+  DevBuf img_pyr, mask_buf, out_pyr, planes, bgr;
+  int cover_bytes = 4;
+  int apply_add = 0;
+  StageTimer timer;
+  // workload sizes (pixels)
+  double s_t = 0, c_px = 0;
+
+  // ---- debug copies (keep_debug) ----
+  std::vector<DevBuf> dbg_lap, dbg_mask;
+  std::vector<PyrGeom> dbg_lap_g;
+  std::vector<std::vector<MaskLevel>> dbg_mask_lv;
+  DevBuf dbg_out, dbg_collapsed;
+
+  explicit Blender(const xp_blend_opts& o) : opts(o) {}
+  ~Blender();
+  void ensure_device();
+  Fed* new_fed(int w, int h, int depth, int tl_x, int tl_y);
+  void feed(const void* data, size_t stride, const uint8_t* mask,
+            size_t mask_stride, int w, int h, int depth, int spp, int tl_x,
+            int tl_y, int mem);
+  void blend(xp_timing* timing);
+  void fetch(void* dst_bgr, size_t dst_stride, uint8_t* dst_mask,
+             size_t mask_stride, int mem);
+  void fetch_planes(void* planes_out, int mem);
+  void debug_fetch(const char* what, int image, int channel, int level,
+                   void* dst, size_t cap, int dims[3], size_t* bytes);
+  const u64* src_index(int i) const {
+    return inp_bwd.size() > (size_t)i && inp_bwd[i].p ? inp_bwd[i].as<u64>()
+                                                      : nullptr;
+  }
+};
+
+int blend_levels(int n, const int* widths, const int* heights,
+                 int fixed_levels, int add_levels);
+
+}  // namespace xp

@@ -1,0 +1,273 @@
+// Compose driver: the full-resolution loop of Stitcher::ComposePanorama
+// (xpano/algorithm/stitcher.cc:299-432) with ComputeRoi (:144-169) and the
+// panorama size cap (:318-335). Cameras, gain maps and low-resolution seam
+// masks are inputs (registration and seam estimation are outside the path).
+// Sources are uploaded once; warp -> feed -> blend stays on the device.
+#include <climits>
+#include <cmath>
+#include <memory>
+
+#include "blender.h"
+#include "common.h"
+#include "warp.h"
+
+namespace xp {
+
+struct SrcImage {
+  int w = 0, h = 0;
+  size_t pitch = 0;
+  const void* dev = nullptr;  // device pointer (owned in `buf` unless adopted)
+  DevBuf buf, gain, seam;
+  int gw = 0, gh = 0, mw = 0, mh = 0;
+  bool skip = false;  // countNonZero(seam mask) == 0 (stitcher.cc:360-364)
+  float K[9], R[9];
+};
+
+struct Composer {
+  xp_compose_opts opts;
+  Warper warper;
+  std::unique_ptr<Blender> blender;
+  std::vector<std::unique_ptr<SrcImage>> src;
+  cudaStream_t stream = nullptr, own_stream = nullptr;
+  bool external_stream = false;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  double h2d_ms = 0;
+
+  ~Composer() {
+    for (cudaEvent_t e : ev)
+      if (e) cudaEventDestroy(e);
+    if (own_stream) cudaStreamDestroy(own_stream);
+  }
+
+  void ensure_device() {
+    select_device(opts.blend.device);
+    if (!stream && !external_stream) {
+      XP_CUDA(cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
+      stream = own_stream;
+    }
+    for (cudaEvent_t& e : ev)
+      if (!e) XP_CUDA(cudaEventCreate(&e));
+    warper.type = opts.projection;
+    warper.portrait = opts.portrait ? 1 : 0;
+    warper.a = opts.a;
+    warper.b = opts.b;
+    warper.device = opts.blend.device;
+    warper.stream = stream;
+    warper.external_stream = true;
+  }
+
+  void set_images(int n, const xp_compose_image* images, int mem) {
+    XP_REQUIRE(n >= 1 && images, "set_images: no images");
+    XP_REQUIRE(opts.depth == 8 || opts.depth == 16, "depth must be 8 or 16");
+    ensure_device();
+    src.clear();
+    const size_t bs = opts.depth / 8;
+    XP_CUDA(cudaEventRecord(ev[0], stream));
+    for (int i = 0; i < n; ++i) {
+      const xp_compose_image& in = images[i];
+      XP_REQUIRE(in.data && in.w > 0 && in.h > 0, "image %d is empty", i);
+      std::unique_ptr<SrcImage> s(new SrcImage());
+      s->w = in.w;
+      s->h = in.h;
+      memcpy(s->K, in.K, sizeof(s->K));
+      memcpy(s->R, in.R, sizeof(s->R));
+      const size_t row = (size_t)in.w * 3 * bs;
+      const size_t stride = in.stride ? in.stride : row;
+      if (mem == XP_MEM_DEVICE) {
+        s->dev = in.data;
+        s->pitch = stride;
+      } else {
+        s->buf.reserve(row * (size_t)in.h);
+        copy_in_2d(s->buf.p, row, in.data, stride, row, in.h, mem, stream);
+        s->dev = s->buf.p;
+        s->pitch = row;
+      }
+      if (in.aux.gain) {
+        s->gw = in.aux.gain_w;
+        s->gh = in.aux.gain_h;
+        XP_REQUIRE(s->gw > 0 && s->gh > 0, "image %d: empty gain map", i);
+        const size_t b = sizeof(float) * (size_t)s->gw * s->gh;
+        s->gain.reserve(b);
+        XP_CUDA(cudaMemcpyAsync(s->gain.p, in.aux.gain, b,
+                                cudaMemcpyHostToDevice, stream));
+      }
+      if (in.aux.seam_mask) {
+        s->mw = in.aux.seam_w;
+        s->mh = in.aux.seam_h;
+        XP_REQUIRE(s->mw > 0 && s->mh > 0, "image %d: empty seam mask", i);
+        const size_t b = (size_t)s->mw * s->mh;
+        bool any = false;
+        for (size_t k = 0; k < b && !any; ++k) any = in.aux.seam_mask[k] != 0;
+        s->skip = !any;
+        s->seam.reserve(b);
+        XP_CUDA(cudaMemcpyAsync(s->seam.p, in.aux.seam_mask, b,
+                                cudaMemcpyHostToDevice, stream));
+      }
+      src.push_back(std::move(s));
+    }
+    XP_CUDA(cudaEventRecord(ev[1], stream));
+    XP_CUDA(cudaStreamSynchronize(stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ev[0], ev[1]);
+    h2d_ms = ms;
+  }
+
+  // ComputeRoi (stitcher.cc:144-169)
+  void compute_roi(float scale, std::vector<int>& rois, int rect[4]) {
+    warper.scale = scale;
+    const int n = (int)src.size();
+    rois.resize(4 * n);
+    long x0 = LONG_MAX, y0 = LONG_MAX, x1 = LONG_MIN, y1 = LONG_MIN;
+    for (int i = 0; i < n; ++i) {
+      int* r = &rois[4 * i];
+      warper.warp_roi(src[i]->w, src[i]->h, src[i]->K, src[i]->R, r);
+      x0 = std::min<long>(x0, r[0]);
+      y0 = std::min<long>(y0, r[1]);
+      x1 = std::max<long>(x1, (long)r[0] + r[2]);
+      y1 = std::max<long>(y1, (long)r[1] + r[3]);
+    }
+    rect[0] = (int)x0;
+    rect[1] = (int)y0;
+    rect[2] = (int)(x1 - x0);
+    rect[3] = (int)(y1 - y0);
+  }
+
+  void run(xp_compose_info* info) {
+    XP_REQUIRE(!src.empty(), "run: set_images first");
+    ensure_device();
+    float scale = opts.warp_scale;
+    std::vector<int> rois;
+    int rect[4];
+    compute_roi(scale, rois, rect);
+    bool capped = false;
+    const double mpx = (double)rect[2] * rect[3] / 1e6;
+    if (opts.max_pano_mpx > 0 && mpx > opts.max_pano_mpx) {  // :318-335
+      const float ratio = (float)std::sqrt(opts.max_pano_mpx / mpx);
+      scale = (float)((double)scale * ratio);
+      compute_roi(scale, rois, rect);
+      capped = true;
+    }
+    xp_blend_opts bo = opts.blend;
+    blender.reset(new Blender(bo));
+    blender->stream = stream;
+    blender->external_stream = true;
+    blender->roi[0] = rect[0];
+    blender->roi[1] = rect[1];
+    blender->roi[2] = rect[2];
+    blender->roi[3] = rect[3];
+    double s_src = 0, s_w = 0;
+    XP_CUDA(cudaEventRecord(ev[0], stream));
+    const size_t bs = opts.depth / 8;
+    for (size_t i = 0; i < src.size(); ++i) {
+      SrcImage& s = *src[i];
+      if (s.skip) continue;
+      const int* r = &rois[4 * i];
+      const int roi_incl[4] = {r[0], r[1], r[0] + r[2] - 1, r[1] + r[3] - 1};
+      Fed* f = blender->new_fed(r[2], r[3], opts.depth, r[0], r[1]);
+      const Projector p = warper.projector(s.K, s.R);
+      warper.warp_bgra_device(s.dev, s.w, s.h, s.pitch, opts.depth, p,
+                              roi_incl, s.gain.as<float>(), s.gw, s.gh,
+                              s.seam.as<uint8_t>(), s.mw, s.mh, f->data.p,
+                              (size_t)r[2] * 4 * bs);
+      s_src += (double)s.w * s.h;
+      s_w += (double)r[2] * r[3];
+    }
+    XP_CUDA(cudaEventRecord(ev[1], stream));
+    xp_timing tm;
+    memset(&tm, 0, sizeof(tm));
+    blender->blend(&tm);
+    XP_CUDA(cudaEventRecord(ev[2], stream));
+    XP_CUDA(cudaStreamSynchronize(stream));
+    if (info) {
+      memset(info, 0, sizeof(*info));
+      float a = 0, b = 0;
+      cudaEventElapsedTime(&a, ev[0], ev[1]);
+      cudaEventElapsedTime(&b, ev[1], ev[2]);
+      info->width = blender->W;
+      info->height = blender->H;
+      info->min_x = blender->min_x;
+      info->min_y = blender->min_y;
+      info->bpp = blender->out_bpp;
+      info->levels = blender->levels;
+      info->resolution_capped = capped ? 1 : 0;
+      memcpy(info->roi, rect, sizeof(rect));
+      info->warp_scale = scale;
+      info->warp_ms = a;
+      info->blend_ms = b;
+      info->h2d_ms = h2d_ms;
+      info->timing = tm;
+      info->s_src = s_src;
+      info->s_w = s_w;
+      info->s_t = blender->s_t;
+      info->c = blender->c_px;
+    }
+  }
+};
+
+}  // namespace xp
+
+struct xp_composer : xp::Composer {};
+
+extern "C" {
+
+void xp_compose_opts_default(xp_compose_opts* o) {
+  if (!o) return;
+  memset(o, 0, sizeof(*o));
+  o->projection = XP_PROJ_SPHERICAL;  // options.h:83
+  o->a = 2.0f;
+  o->b = 1.0f;
+  o->warp_scale = 1.0f;
+  o->max_pano_mpx = 100.0;  // constants.h:106
+  o->depth = 8;
+  xp_blend_opts_default(&o->blend);
+}
+
+xp_status xp_composer_create(const xp_compose_opts* opts, xp_composer** out) {
+  return xp::guard([&] {
+    XP_REQUIRE(opts && out, "xp_composer_create: null argument");
+    XP_REQUIRE(opts->projection >= 0 && opts->projection <= 8,
+               "unknown projection %d", opts->projection);
+    auto* c = new xp_composer();
+    c->opts = *opts;
+    *out = c;
+  });
+}
+
+void xp_composer_destroy(xp_composer* c) { delete c; }
+
+xp_status xp_composer_set_stream(xp_composer* c, void* cuda_stream) {
+  return xp::guard([&] {
+    XP_REQUIRE(c, "null composer");
+    c->stream = (cudaStream_t)cuda_stream;
+    c->external_stream = true;
+  });
+}
+
+xp_status xp_composer_set_images(xp_composer* c, int n,
+                                 const xp_compose_image* images, int mem) {
+  return xp::guard([&] {
+    XP_REQUIRE(c, "null composer");
+    c->set_images(n, images, mem);
+  });
+}
+
+xp_status xp_composer_run(xp_composer* c, xp_compose_info* info) {
+  return xp::guard([&] {
+    XP_REQUIRE(c, "null composer");
+    c->run(info);
+  });
+}
+
+xp_status xp_composer_fetch(xp_composer* c, void* dst_bgr, size_t dst_stride,
+                            uint8_t* dst_mask, size_t mask_stride, int mem) {
+  return xp::guard([&] {
+    XP_REQUIRE(c && c->blender, "fetch before run");
+    c->blender->fetch(dst_bgr, dst_stride, dst_mask, mask_stride, mem);
+  });
+}
+
+xp_blender* xp_composer_blender(xp_composer* c) {
+  return c ? reinterpret_cast<xp_blender*>(c->blender.get()) : nullptr;
+}
+
+}  // extern "C"

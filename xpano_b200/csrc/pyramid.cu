@@ -1,0 +1,557 @@
+// Pyramid / blend kernels: level-0 copy, 5-tap reduce, expand-subtract
+// (Laplace and Collapse), mask pyramid, masked composite, offset correction,
+// dither/clamp/pack.
+//
+// Replaces external/multiblend/src/pyramid.cpp (Copy :233-408, Shrink :584-823,
+// LaplaceCollapse :828-1038, Add :1084-1110, Out :1563-1794),
+// src/functions.cpp (ShrinkMasks :172-314, CompositeLine :319-411) and the
+// blend loop / offset correction of src/multiblend.cpp:1057-1131, 1232-1267,
+// plus xpano/algorithm/blenders.cc:64-77,99-112,151-154 (pack / unpack).
+// All arithmetic lives in pyramid_math.h; the whole library is built with
+// -fmad=false so results are bit-comparable with the SSE reference.
+#include "blend_impl.h"
+#include "common.h"
+#include "pyramid_math.h"
+
+namespace xp {
+
+PyrGeom make_pyramid(int width, int height, int levels, int x, int y) {
+  PyrGeom g;
+  XP_REQUIRE(levels <= kMaxLevels, "too many pyramid levels (%d)", levels);
+  int b = 0, req = 2;
+  size_t off = 0;
+  for (int n = 0; n < levels; ++n) {
+    LevelGeom& L = g.lv[n];
+    L.xs = ((x - b) & (req - 1)) != 0;
+    L.ys = ((y - b) & (req - 1)) != 0;
+    L.w = width;
+    L.h = height;
+    L.x = x;
+    L.y = y;
+    L.pitch = (width + L.xs + 7) & ~7;
+    L.rows = (height + L.ys + 3) & ~3;
+    L.offset = off;
+    off += (size_t)L.pitch * L.rows;
+    x -= L.xs << n;
+    y -= L.ys << n;
+    x -= req;
+    y -= req;
+    b -= req;
+    req <<= 1;
+    width = (width + L.xs + 6) >> 1;
+    height = (height + L.ys + 6) >> 1;
+  }
+  g.n = levels;
+  g.channel_floats = off;
+  return g;
+}
+
+static dim3 grid3(int w, int h, int z, dim3 b) {
+  return dim3(div_up(w, (int)b.x), div_up(h, (int)b.y), z);
+}
+
+// ---------------------------------------------------------------------------
+// level 0 copy (+ inpaint gather + de-interleave)
+// ---------------------------------------------------------------------------
+template <int BPP>
+__global__ void copy_level0_kernel(ImgDev im, const u64* __restrict__ src_index,
+                                   float mul, int pitch, size_t chan_stride,
+                                   float* __restrict__ out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= pitch || y >= im.h) return;
+  const int xx = x < im.w ? x : im.w - 1;  // pad: replicate the last pixel
+  size_t idx;
+  if (src_index)
+    idx = (u32)src_index[(size_t)y * im.w + xx];
+  else
+    idx = (size_t)(im.top + y) * im.tiff_w + im.left + xx;
+  float c0, c1, c2;
+  if (BPP == 8) {
+    const u32 v = static_cast<const u32*>(im.data)[idx];
+    c0 = (float)(v & 0xff);
+    c1 = (float)((v >> 8) & 0xff);
+    c2 = (float)((v >> 16) & 0xff);
+  } else {
+    const u64 v = static_cast<const u64*>(im.data)[idx];
+    c0 = (float)(u32)(v & 0xffff);
+    c1 = (float)(u32)((v >> 16) & 0xffff);
+    c2 = (float)(u32)((v >> 32) & 0xffff);
+  }
+  if (mul != 1.0f) {
+    c0 *= mul;
+    c1 *= mul;
+    c2 *= mul;
+  }
+  const size_t o = (size_t)y * pitch + x;
+  out[o] = c0;
+  out[o + chan_stride] = c1;
+  out[o + 2 * chan_stride] = c2;
+}
+
+void launch_copy_level0(const ImgDev& im, int bpp, const u64* src_index,
+                        float mul, const PyrGeom& g, float* pyr,
+                        cudaStream_t s) {
+  const LevelGeom& L = g.lv[0];
+  dim3 b(32, 8);
+  dim3 gr = grid3(L.pitch, L.h, 1, b);
+  if (bpp == 8)
+    copy_level0_kernel<8><<<gr, b, 0, s>>>(im, src_index, mul, L.pitch,
+                                           g.channel_floats, pyr + L.offset);
+  else
+    copy_level0_kernel<16><<<gr, b, 0, s>>>(im, src_index, mul, L.pitch,
+                                            g.channel_floats, pyr + L.offset);
+  XP_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// shrink
+// ---------------------------------------------------------------------------
+__global__ void shrink_kernel(const float* __restrict__ hi, int hh, int hp,
+                              int xs, int ys, float* __restrict__ lo, int lo_h,
+                              int lo_pitch, size_t chan_stride) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (j >= lo_pitch || y >= lo_h) return;
+  const size_t co = (size_t)blockIdx.z * chan_stride;
+  lo[co + (size_t)y * lo_pitch + j] =
+      pm::shrink_sample(hi + co, hh, hp, xs, ys, lo_h, j, y);
+}
+
+void launch_shrink(const PyrGeom& g, float* pyr, int level, int channels,
+                   cudaStream_t s) {
+  const LevelGeom& H = g.lv[level];
+  const LevelGeom& L = g.lv[level + 1];
+  dim3 b(32, 8);
+  shrink_kernel<<<grid3(L.pitch, L.h, channels, b), b, 0, s>>>(
+      pyr + H.offset, H.h, H.pitch, H.xs, H.ys, pyr + L.offset, L.h, L.pitch,
+      g.channel_floats);
+  XP_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// laplace / collapse: hi <- expand(lo) - hi
+// ---------------------------------------------------------------------------
+__global__ void laplace_kernel(float* __restrict__ hi, int hh, int hp, int xs,
+                               int ys, const float* __restrict__ lo,
+                               int lo_pitch, size_t chan_stride) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= hp || y >= hh) return;
+  const size_t co = (size_t)blockIdx.z * chan_stride;
+  const size_t o = co + (size_t)y * hp + x;
+  hi[o] = pm::expand_sample(lo + co, lo_pitch, xs, ys, x, y) - hi[o];
+}
+
+void launch_laplace(const PyrGeom& g, float* pyr, int level, int channels,
+                    cudaStream_t s) {
+  const LevelGeom& H = g.lv[level];
+  const LevelGeom& L = g.lv[level + 1];
+  dim3 b(32, 8);
+  laplace_kernel<<<grid3(H.pitch, H.h, channels, b), b, 0, s>>>(
+      pyr + H.offset, H.h, H.pitch, H.xs, H.ys, pyr + L.offset, L.pitch,
+      g.channel_floats);
+  XP_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// mask pyramid
+// ---------------------------------------------------------------------------
+struct LabelSrc {
+  const uint8_t* labels;
+  int W, H, image;
+  __device__ __forceinline__ float at(int r, int c) const {
+    return labels[(size_t)r * W + c] == image ? 1.0f : 0.0f;
+  }
+  __device__ __forceinline__ int width() const { return W; }
+  __device__ __forceinline__ int height() const { return H; }
+};
+
+struct RectSrc {
+  const float* data;
+  int x0, y0, w, h, cw, ch;
+  __device__ __forceinline__ float at(int r, int c) const {
+    const int rx = c - x0, ry = r - y0;
+    if ((unsigned)rx >= (unsigned)w || (unsigned)ry >= (unsigned)h) return 0.f;
+    return data[(size_t)ry * w + rx];
+  }
+  __device__ __forceinline__ int width() const { return cw; }
+  __device__ __forceinline__ int height() const { return ch; }
+};
+
+template <class Src>
+__device__ __forceinline__ float mask_squish(const Src& s, int r, int X) {
+  const int wmax = s.width() - 1;
+  float t[5];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) t[k] = s.at(r, pm::clampi(2 * X - 4 + k, 0, wmax));
+  return pm::mask_h_combine(t[0], t[1], t[2], t[3], t[4]);
+}
+
+template <class Src>
+__global__ void mask_shrink_kernel(Src src, MaskLevel out, float* dst) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= out.w || y >= out.h) return;
+  const int X = out.x0 + x, Y = out.y0 + y;
+  float v;
+  if (Y == 0) {  // functions.cpp:195-214: squished first line verbatim
+    v = mask_squish(src, 0, X);
+  } else {
+    const int hmax = src.height() - 1;
+    float t[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k)
+      t[k] = mask_squish(src, pm::clampi(2 * Y - 4 + k, 0, hmax), X);
+    v = pm::mask_v_combine(t[0], t[1], t[2], t[3], t[4]);
+  }
+  dst[(size_t)y * out.w + x] = v;
+}
+
+void launch_mask_level1(const uint8_t* labels, int CW, int CH, int image,
+                        const MaskLevel& out, float* mask, cudaStream_t s) {
+  if (out.w <= 0 || out.h <= 0) return;
+  dim3 b(32, 8);
+  LabelSrc src{labels, CW, CH, image};
+  mask_shrink_kernel<<<grid3(out.w, out.h, 1, b), b, 0, s>>>(
+      src, out, mask + out.offset);
+  XP_LAUNCHED();
+}
+
+void launch_mask_shrink(const MaskLevel& in, const MaskLevel& out, float* mask,
+                        cudaStream_t s) {
+  if (out.w <= 0 || out.h <= 0) return;
+  dim3 b(32, 8);
+  RectSrc src{mask + in.offset, in.x0, in.y0, in.w, in.h, in.cw, in.ch};
+  mask_shrink_kernel<<<grid3(out.w, out.h, 1, b), b, 0, s>>>(
+      src, out, mask + out.offset);
+  XP_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// composite: out (+)= in * mask over the mask's rectangle
+// ---------------------------------------------------------------------------
+__global__ void composite_kernel(const float* __restrict__ in, int in_w,
+                                 int in_h, int in_pitch, size_t in_cs,
+                                 float* __restrict__ out, int out_pitch,
+                                 size_t out_cs, int x_off, int y_off,
+                                 MaskLevel m, const float* __restrict__ mask,
+                                 const uint8_t* __restrict__ labels,
+                                 int image) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= m.w || y >= m.h) return;
+  const int X = m.x0 + x, Y = m.y0 + y;
+  float mv;
+  if (labels)
+    mv = labels[(size_t)Y * m.cw + X] == image ? 1.0f : 0.0f;
+  else
+    mv = mask[(size_t)y * m.w + x];
+  if (mv == 0.0f) return;  // functions.cpp:347-351 (skip)
+  const int ix = pm::clampi(X - x_off, 0, in_w - 1);
+  const int iy = pm::clampi(Y - y_off, 0, in_h - 1);
+  const size_t io = (size_t)iy * in_pitch + ix;
+  const size_t oo = (size_t)Y * out_pitch + X;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+    out[oo + c * out_cs] = out[oo + c * out_cs] + in[io + c * in_cs] * mv;
+}
+
+void launch_composite(const PyrGeom& in_g, const float* in_pyr,
+                      const PyrGeom& out_g, float* out_pyr, int level,
+                      const uint8_t* labels, int image, const MaskLevel& m,
+                      const float* mask, cudaStream_t s) {
+  if (m.w <= 0 || m.h <= 0) return;
+  const LevelGeom& I = in_g.lv[level];
+  const LevelGeom& O = out_g.lv[level];
+  const int x_off = (I.x - O.x) >> level;
+  const int y_off = (I.y - O.y) >> level;
+  dim3 b(32, 8);
+  composite_kernel<<<grid3(m.w, m.h, 1, b), b, 0, s>>>(
+      in_pyr + I.offset, I.w, I.h, I.pitch, in_g.channel_floats,
+      out_pyr + O.offset, O.pitch, out_g.channel_floats, x_off, y_off, m,
+      level == 0 ? nullptr : mask + m.offset, level == 0 ? labels : nullptr,
+      image);
+  XP_LAUNCHED();
+}
+
+// pad columns [w, pitch) with the last pixel (functions.cpp:403-410)
+__global__ void pad_kernel(float* lvl, int w, int h, int pitch,
+                           size_t chan_stride) {
+  const int pad = pitch - w;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= pad * h) return;
+  const int y = i / pad, x = w + i % pad;
+  float* row = lvl + (size_t)blockIdx.z * chan_stride + (size_t)y * pitch;
+  row[x] = row[w - 1];
+}
+
+void launch_pad_level(const PyrGeom& g, float* pyr, int level, int channels,
+                      cudaStream_t s) {
+  const LevelGeom& L = g.lv[level];
+  const int pad = L.pitch - L.w;
+  if (pad <= 0) return;
+  pad_kernel<<<dim3(div_up(pad * L.h, 256), 1, channels), 256, 0, s>>>(
+      pyr + L.offset, L.w, L.h, L.pitch, g.channel_floats);
+  XP_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// offset correction: double sum of level 0 over the xor mask
+// (multiblend.cpp:1232-1258). Fixed-shape two-stage tree: deterministic.
+// ---------------------------------------------------------------------------
+constexpr int kSumBlocks = 1024;
+
+__global__ void xor_sum_kernel(const float* __restrict__ lvl0, int pitch,
+                               size_t chan_stride,
+                               const uint8_t* __restrict__ xor_mask, int W,
+                               int H, double* __restrict__ partials) {
+  __shared__ double sh[3][8];
+  const size_t n = (size_t)W * H;
+  const size_t per = (n + gridDim.x - 1) / gridDim.x;
+  const size_t beg = per * blockIdx.x;
+  const size_t end = beg + per < n ? beg + per : n;
+  double acc[3] = {0, 0, 0};
+  for (size_t i = beg + threadIdx.x; i < end; i += blockDim.x) {
+    if (xor_mask[i]) {
+      const size_t o = (i / W) * (size_t)pitch + (i % W);
+      acc[0] += lvl0[o];
+      acc[1] += lvl0[o + chan_stride];
+      acc[2] += lvl0[o + 2 * chan_stride];
+    }
+  }
+  for (int c = 0; c < 3; ++c) {
+    double v = acc[c];
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(~0u, v, o);
+    if ((threadIdx.x & 31) == 0) sh[c][threadIdx.x >> 5] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    double v = 0;
+    for (int k = 0; k < 8; ++k) v += sh[threadIdx.x][k];
+    partials[threadIdx.x * gridDim.x + blockIdx.x] = v;
+  }
+}
+
+__global__ void xor_sum_final_kernel(const double* __restrict__ partials,
+                                     int n, double* sums) {
+  // one warp per channel, fixed order
+  const int c = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double v = 0;
+  for (int i = lane; i < n; i += 32) v += partials[c * n + i];
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(~0u, v, o);
+  if (lane == 0) sums[c] = v;
+}
+
+void launch_xor_sum(const PyrGeom& g, const float* pyr,
+                    const uint8_t* xor_mask, int W, int H, double* d_partials,
+                    double* d_sums, cudaStream_t s) {
+  const LevelGeom& L = g.lv[0];
+  xor_sum_kernel<<<kSumBlocks, 256, 0, s>>>(pyr + L.offset, L.pitch,
+                                            g.channel_floats, xor_mask, W, H,
+                                            d_partials);
+  XP_LAUNCHED();
+  xor_sum_final_kernel<<<1, 96, 0, s>>>(d_partials, kSumBlocks, d_sums);
+  XP_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// Out: offset add + dither + clamp + round-half-even, planar and packed BGR
+// with pixels outside the mask zeroed (pyramid.cpp:1563-1794,
+// blenders.cc:64-77,151-154)
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void out_kernel(const float* __restrict__ lvl0, int pitch,
+                           size_t chan_stride, int W, int H, int dither,
+                           int apply_add, const CanvasStats* __restrict__ stats,
+                           const double* __restrict__ sums, int in_bpp,
+                           const uint8_t* __restrict__ full_mask,
+                           T* __restrict__ planes, T* __restrict__ bgr) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= W || y >= H) return;
+  const float maxv = sizeof(T) == 1 ? 255.0f : 65535.0f;
+  const int out_bpp = sizeof(T) * 8;
+  const size_t p = (size_t)y * W + x;
+  const unsigned long long total_px = stats->totals[3];
+  const bool masked = full_mask[p] != 0;
+  const float dv = dither ? pm::dither_value(y, x) : 0.0f;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    float v = lvl0[(size_t)y * pitch + x + c * chan_stride];
+    if (apply_add && total_px != 0) {
+      float avg = __ull2float_rn(stats->totals[c]) / __ull2float_rn(total_px);
+      if (out_bpp != in_bpp) avg = out_bpp == 8 ? avg / 256 : avg * 256;
+      const float output_avg =
+          __double2float_rn(sums[c]) / __ull2float_rn(total_px);
+      const float add = avg - output_avg;
+      v = add + v;
+    }
+    if (dither) v = v + dv;
+    v = v > 0.0f ? v : 0.0f;
+    v = v < maxv ? v : maxv;
+    const T q = (T)__float2int_rn(v);
+    planes[(size_t)c * W * H + p] = q;
+    bgr[p * 3 + c] = masked ? q : (T)0;
+  }
+}
+
+void launch_out(const PyrGeom& g, const float* pyr, int W, int H, int out_bpp,
+                int dither, int apply_add, const CanvasStats* d_stats,
+                const double* d_sums, int in_bpp, const uint8_t* full_mask,
+                void* planes, void* bgr, cudaStream_t s) {
+  const LevelGeom& L = g.lv[0];
+  dim3 b(32, 8);
+  dim3 gr = grid3(W, H, 1, b);
+  if (out_bpp == 8)
+    out_kernel<uint8_t><<<gr, b, 0, s>>>(pyr + L.offset, L.pitch,
+                                         g.channel_floats, W, H, dither,
+                                         apply_add, d_stats, d_sums, in_bpp,
+                                         full_mask, (uint8_t*)planes,
+                                         (uint8_t*)bgr);
+  else
+    out_kernel<uint16_t><<<gr, b, 0, s>>>(pyr + L.offset, L.pitch,
+                                          g.channel_floats, W, H, dither,
+                                          apply_add, d_stats, d_sums, in_bpp,
+                                          full_mask, (uint16_t*)planes,
+                                          (uint16_t*)bgr);
+  XP_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// debug / packing helpers
+// ---------------------------------------------------------------------------
+template <int BPP>
+__global__ void extract_chan_kernel(ImgDev im, const u64* src_index,
+                                    int channel, void* out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= im.w || y >= im.h) return;
+  size_t idx = src_index ? (size_t)(u32)src_index[(size_t)y * im.w + x]
+                         : (size_t)(im.top + y) * im.tiff_w + im.left + x;
+  if (BPP == 8)
+    static_cast<uint8_t*>(out)[(size_t)y * im.w + x] =
+        (uint8_t)(static_cast<const u32*>(im.data)[idx] >> (8 * channel));
+  else
+    static_cast<uint16_t*>(out)[(size_t)y * im.w + x] =
+        (uint16_t)(static_cast<const u64*>(im.data)[idx] >> (16 * channel));
+}
+
+void launch_extract_chan(const ImgDev& im, int bpp, const u64* src_index,
+                         int channel, void* out, cudaStream_t s) {
+  dim3 b(32, 8);
+  dim3 g = grid3(im.w, im.h, 1, b);
+  if (bpp == 8)
+    extract_chan_kernel<8><<<g, b, 0, s>>>(im, src_index, channel, out);
+  else
+    extract_chan_kernel<16><<<g, b, 0, s>>>(im, src_index, channel, out);
+  XP_LAUNCHED();
+}
+
+template <int BPP>
+__global__ void extract_opaque_kernel(ImgDev im, uint8_t* out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= im.w || y >= im.h) return;
+  out[(size_t)y * im.w + x] =
+      px_opaque<BPP>(im.data, (size_t)(im.top + y) * im.tiff_w + im.left + x);
+}
+
+void launch_extract_opaque(const ImgDev& im, int bpp, uint8_t* out,
+                           cudaStream_t s) {
+  dim3 b(32, 8);
+  dim3 g = grid3(im.w, im.h, 1, b);
+  if (bpp == 8)
+    extract_opaque_kernel<8><<<g, b, 0, s>>>(im, out);
+  else
+    extract_opaque_kernel<16><<<g, b, 0, s>>>(im, out);
+  XP_LAUNCHED();
+}
+
+__global__ void labels_to_i32_kernel(const uint8_t* labels, size_t n,
+                                     int32_t* out) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i < n) out[i] = labels[i];
+}
+
+void launch_labels_to_i32(const uint8_t* labels, size_t n, int32_t* out,
+                          cudaStream_t s) {
+  labels_to_i32_kernel<<<(unsigned)div_up(n, (size_t)256), 256, 0, s>>>(
+      labels, n, out);
+  XP_LAUNCHED();
+}
+
+// BGR(+mask) or already-interleaved samples -> 4-sample pixels
+// (blenders.cc:99-112: alpha = mask != 0 ? max : 0)
+template <typename T>
+__global__ void pack_bgra_kernel(const T* __restrict__ src, size_t src_pitch,
+                                 const uint8_t* __restrict__ mask,
+                                 size_t mask_pitch, int w, int h, int spp_in,
+                                 T* __restrict__ out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= w || y >= h) return;
+  const T amax = (T)(sizeof(T) == 1 ? 255 : 65535);
+  const T* s = src + (size_t)y * src_pitch + (size_t)x * spp_in;
+  T a = amax;
+  if (spp_in == 4) a = s[3];
+  if (mask) a = mask[(size_t)y * mask_pitch + x] != 0 ? amax : (T)0;
+  T* d = out + ((size_t)y * w + x) * 4;
+  d[0] = s[0];
+  d[1] = s[1];
+  d[2] = s[2];
+  d[3] = a;
+}
+
+void launch_pack_bgra(const void* bgr, size_t bgr_pitch, const uint8_t* mask,
+                      size_t mask_pitch, int w, int h, int depth, int spp_in,
+                      void* out, cudaStream_t s) {
+  dim3 b(32, 8);
+  dim3 g = grid3(w, h, 1, b);
+  if (depth == 8)
+    pack_bgra_kernel<uint8_t><<<g, b, 0, s>>>((const uint8_t*)bgr, bgr_pitch,
+                                              mask, mask_pitch, w, h, spp_in,
+                                              (uint8_t*)out);
+  else
+    pack_bgra_kernel<uint16_t><<<g, b, 0, s>>>(
+        (const uint16_t*)bgr, bgr_pitch / 2, mask, mask_pitch, w, h, spp_in,
+        (uint16_t*)out);
+  XP_LAUNCHED();
+}
+
+// debug: level 0 after the offset add (what the oracle keeps as "collapsed")
+__global__ void debug_collapsed_kernel(const float* __restrict__ lvl0,
+                                       size_t n, size_t chan_stride,
+                                       int apply_add,
+                                       const CanvasStats* __restrict__ stats,
+                                       const double* __restrict__ sums,
+                                       int in_bpp, int out_bpp,
+                                       float* __restrict__ out) {
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int c = blockIdx.y;
+  float v = lvl0[i + c * chan_stride];
+  const unsigned long long total_px = stats->totals[3];
+  if (apply_add && total_px != 0) {
+    float avg = __ull2float_rn(stats->totals[c]) / __ull2float_rn(total_px);
+    if (out_bpp != in_bpp) avg = out_bpp == 8 ? avg / 256 : avg * 256;
+    const float output_avg =
+        __double2float_rn(sums[c]) / __ull2float_rn(total_px);
+    v = (avg - output_avg) + v;
+  }
+  out[i + c * n] = v;
+}
+
+void launch_debug_collapsed(const PyrGeom& g, const float* pyr, int apply_add,
+                            const CanvasStats* d_stats, const double* d_sums,
+                            int in_bpp, int out_bpp, float* out,
+                            cudaStream_t s) {
+  const LevelGeom& L = g.lv[0];
+  const size_t n = (size_t)L.pitch * L.h;
+  debug_collapsed_kernel<<<dim3((unsigned)div_up(n, (size_t)256), 3), 256, 0,
+                           s>>>(pyr + L.offset, n, g.channel_floats, apply_add,
+                                d_stats, d_sums, in_bpp, out_bpp, out);
+  XP_LAUNCHED();
+}
+
+}  // namespace xp
