@@ -1,0 +1,98 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU restatement of the compose loop
+(Stitcher::ComposePanorama, xpano/algorithm/stitcher.cc:299-432, with
+ComputeRoi :144-169 and the size cap :318-335) on top of the oracle's warp
+and blend halves. Used as the checker for the device compose driver and as
+the timed CPU port in bench.py's cpu_baseline leg."""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+
+from oracle import mb_oracle
+from oracle import warp_oracle as wo
+
+
+def make_cameras(n_cols, n_rows, w, h, focal, yaw_step, pitches, seed,
+                 extra=None):
+    """Synthetic registered cameras: pin-hole K,
+    R = Ry(yaw) Rx(pitch) Rz(roll) with small seeded jitter."""
+    rng = np.random.default_rng(seed)
+    Ks, Rs = [], []
+    for r in range(n_rows):
+        for c in range(n_cols):
+            yaw = (c - (n_cols - 1) / 2) * yaw_step
+            pitch = pitches[r] + math.radians(rng.uniform(-1, 1))
+            roll = math.radians(rng.uniform(-0.5, 0.5))
+            R = rot(yaw, pitch, roll)
+            if extra is not None:  # algorithm::Rotate: R <- M * R
+                R = (np.asarray(extra, np.float32) @ R).astype(np.float32)
+            Ks.append(np.array([[focal, 0, w / 2], [0, focal, h / 2],
+                                [0, 0, 1]], np.float32))
+            Rs.append(R)
+    return Ks, Rs
+
+
+def rot(yaw, pitch, roll):
+    cy, sy = math.cos(yaw), math.sin(yaw)
+    cp, sp = math.cos(pitch), math.sin(pitch)
+    cr, sr = math.cos(roll), math.sin(roll)
+    ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    rx = np.array([[1, 0, 0], [0, cp, -sp], [0, sp, cp]])
+    rz = np.array([[cr, -sr, 0], [sr, cr, 0], [0, 0, 1]])
+    return (ry @ rx @ rz).astype(np.float32)
+
+
+def compute_roi(warper, sizes, Ks, Rs):
+    rois = [warper.warp_roi(s, K, R) for s, K, R in zip(sizes, Ks, Rs)]
+    x0 = min(r[0] for r in rois)
+    y0 = min(r[1] for r in rois)
+    x1 = max(r[0] + r[2] for r in rois)
+    y1 = max(r[1] + r[3] for r in rois)
+    return rois, (x0, y0, x1 - x0, y1 - y0)
+
+
+def compose(images, Ks, Rs, projection=wo.SPHERICAL, warp_scale=1.0,
+            portrait=False, a=2.0, b=1.0, max_pano_mpx=100.0, gains=None,
+            seam_masks=None, keep_fed=False, **blend_kw):
+    """-> dict(pano (H, W, 3) zeroed outside mask, mask, planes, min_x, min_y,
+    warp_scale, capped, fed=[(bgra, corner)])."""
+    sizes = [(im.shape[1], im.shape[0]) for im in images]
+    scale = np.float32(warp_scale)
+    warper = wo.Warper(projection, float(scale), portrait, a, b)
+    rois, rect = compute_roi(warper, sizes, Ks, Rs)
+    mpx = rect[2] * rect[3] / 1e6
+    capped = False
+    if max_pano_mpx > 0 and mpx > max_pano_mpx:
+        ratio = np.float32(math.sqrt(max_pano_mpx / mpx))
+        scale = np.float32(float(scale) * float(ratio))
+        warper = wo.Warper(projection, float(scale), portrait, a, b)
+        rois, rect = compute_roi(warper, sizes, Ks, Rs)
+        capped = True
+    fed, posn = [], []
+    for i, im in enumerate(images):
+        if seam_masks is not None and seam_masks[i] is not None \
+                and not seam_masks[i].any():
+            continue
+        corner, warped = warper.warp(im, Ks[i], Rs[i])
+        _, mask = warper.warp_mask(sizes[i], Ks[i], Rs[i])
+        H, W = mask.shape
+        if gains is not None and gains[i] is not None:
+            assert warped.dtype == np.uint8
+            gm = wo.resize_linear_f32(gains[i], (W, H))
+            warped = wo.apply_gain_u8(warped, gm)
+        if seam_masks is not None and seam_masks[i] is not None:
+            sm = wo.resize_linear_exact_u8(wo.dilate3x3_u8(seam_masks[i]),
+                                           (W, H))
+            mask = np.bitwise_and(sm, mask)
+        maxv = 255 if warped.dtype == np.uint8 else 65535
+        alpha = np.where(mask != 0, maxv, 0).astype(warped.dtype)
+        fed.append(np.dstack([warped, alpha]))
+        posn.append(corner)
+    o = mb_oracle.blend(fed, posn, **blend_kw)
+    out = dict(pano=o.interleaved(True), mask=o.mask, planes=o.planes,
+               min_x=o.min_x, min_y=o.min_y, warp_scale=float(scale),
+               capped=capped, rect=rect, levels=o.levels)
+    if keep_fed:
+        out["fed"] = list(zip(fed, posn))
+    return out

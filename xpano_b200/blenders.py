@@ -1,0 +1,135 @@
+"""Host-side mirror of xpano::algorithm::blenders::Multiblend
+(xpano/algorithm/blenders.h:25-39, blenders.cc:116-158): prepare / feed /
+blend, executed by libxpano_b200.so on the GPU.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+from . import _lib
+from ._lib import c_void_p, check
+
+
+class Multiblend:
+    """cv::detail::Blender look-alike behind xpano's multiblend wrapper.
+
+    Options follow multiblend::Options (mb/multiblend.h:29-45); xpano itself
+    only sets output_bpp = 8 (blenders.cc:145-149)."""
+
+    def __init__(self, output_bpp=0, fixed_levels=0, add_levels=0,
+                 dither=True, reverse=False, device=0, keep_debug=False):
+        self._lib = _lib.load()
+        self._h = c_void_p()
+        o = _lib.BlendOpts(int(output_bpp), int(fixed_levels),
+                           int(add_levels), int(bool(dither)),
+                           int(bool(reverse)), int(device),
+                           int(bool(keep_debug)))
+        check(self._lib.xp_blender_create(ctypes.byref(o),
+                                          ctypes.byref(self._h)))
+        self.timing = None
+        self.size = None
+        self.min_pos = None
+        self.no_mask = None
+        self.bpp = None
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.xp_blender_destroy(self._h)
+            self._h = c_void_p()
+
+    def set_stream(self, cuda_stream):
+        check(self._lib.xp_blender_set_stream(self._h, c_void_p(cuda_stream)))
+
+    def prepare(self, dst_roi):
+        x, y, w, h = dst_roi
+        check(self._lib.xp_blender_prepare(self._h, int(x), int(y), int(w),
+                                           int(h)))
+
+    def feed(self, img, mask, tl):
+        """img: (h, w, 3) u8/u16, mask: (h, w) u8, tl: (x, y)."""
+        img = np.ascontiguousarray(img)
+        mask = np.ascontiguousarray(mask, np.uint8)
+        if img.ndim != 3 or img.shape[2] != 3:
+            raise ValueError("feed: CV_Assert(img.type() == CV_8UC3)")
+        if mask.shape != img.shape[:2]:
+            raise ValueError("feed: mask size differs from the image")
+        h, w = mask.shape
+        check(self._lib.xp_blender_feed(
+            self._h, img.ctypes.data, 0, mask.ctypes.data, 0, w, h,
+            8 * img.dtype.itemsize, int(tl[0]), int(tl[1]), _lib.MEM_HOST))
+
+    def feed_interleaved(self, data, tl):
+        """multiblend::io::InMemoryImage with spp 3 or 4."""
+        data = np.ascontiguousarray(data)
+        h, w, spp = data.shape
+        check(self._lib.xp_blender_feed_interleaved(
+            self._h, data.ctypes.data, 0, w, h, 8 * data.dtype.itemsize, spp,
+            int(tl[0]), int(tl[1]), _lib.MEM_HOST))
+
+    def run(self):
+        """Run the blend on the device; results stay resident."""
+        wh = (ctypes.c_int * 2)()
+        mn = (ctypes.c_int * 2)()
+        bpp, nm = ctypes.c_int(), ctypes.c_int()
+        t = _lib.Timing()
+        check(self._lib.xp_blender_blend(self._h, wh, mn, ctypes.byref(bpp),
+                                         ctypes.byref(nm), ctypes.byref(t)))
+        self.size = (wh[0], wh[1])
+        self.min_pos = (mn[0], mn[1])
+        self.bpp, self.no_mask = bpp.value, bool(nm.value)
+        if self.timing is None:
+            self.timing = t.as_dict()
+        return self.size
+
+    def blend(self):
+        """-> (dst (H, W, 3) zeroed outside the mask, dst_mask (H, W) 0/255)
+        as Blender::blend returns them (blenders.cc:151-154)."""
+        W, H = self.run()
+        dt = np.uint16 if self.bpp == 16 else np.uint8
+        dst = np.empty((H, W, 3), dt)
+        mask = np.empty((H, W), np.uint8)
+        check(self._lib.xp_blender_fetch(self._h, dst.ctypes.data, 0,
+                                         mask.ctypes.data, 0, _lib.MEM_HOST))
+        return dst, mask
+
+    def planes(self):
+        """Result.output_channels: (3, H, W), not zeroed outside the mask."""
+        W, H = self.run()
+        dt = np.uint16 if self.bpp == 16 else np.uint8
+        out = np.empty((3, H, W), dt)
+        check(self._lib.xp_blender_fetch_planes(self._h, out.ctypes.data,
+                                                _lib.MEM_HOST))
+        return out
+
+    def debug(self, what, image=0, channel=0, level=0, dtype=None):
+        """Intermediate arrays for stage-level parity tests."""
+        return debug_fetch(self._lib, self._h, what, image, channel, level,
+                           dtype)
+
+
+_DEBUG_DTYPES = {"labels": np.int32, "seam_bwd": np.uint64,
+                 "seam_fwd": np.uint64, "xor_mask": np.uint8,
+                 "full_mask": np.uint8, "trim": np.int32,
+                 "totals": np.uint64, "opaque": np.uint8,
+                 "collapsed": np.float32, "mask": np.float32,
+                 "mask_rect": np.int32, "lap": np.float32, "out": np.float32}
+
+
+def debug_fetch(lib, handle, what, image=0, channel=0, level=0, dtype=None):
+    dims = (ctypes.c_int * 3)()
+    nbytes = ctypes.c_size_t()
+    key = what.encode()
+    check(lib.xp_blender_debug_fetch(handle, key, image, channel, level, None,
+                                     0, dims, ctypes.byref(nbytes)))
+    dt = np.dtype(dtype or _DEBUG_DTYPES.get(what, np.uint8))
+    buf = np.empty(max(nbytes.value, 1), np.uint8)
+    check(lib.xp_blender_debug_fetch(handle, key, image, channel, level,
+                                     buf.ctypes.data, buf.size, dims,
+                                     ctypes.byref(nbytes)))
+    arr = buf[:nbytes.value].view(dt)
+    rows, cols, pitch = dims[0], dims[1], dims[2]
+    if rows * pitch == arr.size and rows > 0:
+        arr = arr.reshape(rows, pitch)[:, :cols]
+    return arr

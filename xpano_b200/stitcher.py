@@ -1,0 +1,122 @@
+"""Host-side mirror of the compose step: Stitcher::ComposePanorama
+(xpano/algorithm/stitcher.cc:299-432) with cameras given, executed by the
+device-resident compose driver of libxpano_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _lib
+from ._lib import c_void_p, check
+from .blenders import debug_fetch
+
+
+@dataclass
+class ComposeResult:
+    pano: np.ndarray | None
+    mask: np.ndarray | None
+    info: dict = field(default_factory=dict)
+
+
+class Composer:
+    """Upload sources once, run warp -> feed -> blend on the GPU, fetch."""
+
+    def __init__(self, projection=2, warp_scale=1.0, portrait=False, a=2.0,
+                 b=1.0, max_pano_mpx=100.0, depth=8, output_bpp=0,
+                 fixed_levels=0, add_levels=0, dither=True, reverse=False,
+                 device=0, keep_debug=False):
+        self._lib = _lib.load()
+        o = _lib.ComposeOpts()
+        self._lib.xp_compose_opts_default(ctypes.byref(o))
+        o.projection, o.portrait = int(projection), int(bool(portrait))
+        o.a, o.b, o.warp_scale = float(a), float(b), float(warp_scale)
+        o.max_pano_mpx, o.depth = float(max_pano_mpx), int(depth)
+        o.blend = _lib.BlendOpts(int(output_bpp), int(fixed_levels),
+                                 int(add_levels), int(bool(dither)),
+                                 int(bool(reverse)), int(device),
+                                 int(bool(keep_debug)))
+        self._h = c_void_p()
+        check(self._lib.xp_composer_create(ctypes.byref(o),
+                                           ctypes.byref(self._h)))
+        self._keep = []
+        self.info = None
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.xp_composer_destroy(self._h)
+            self._h = c_void_p()
+
+    def set_stream(self, cuda_stream):
+        check(self._lib.xp_composer_set_stream(self._h, c_void_p(cuda_stream)))
+
+    def set_images(self, images, Ks, Rs, gains=None, seam_masks=None):
+        """images: list of (h, w, 3) host arrays; Ks/Rs: 3x3 float32 each;
+        gains / seam_masks: optional per-image low-resolution arrays."""
+        n = len(images)
+        arr = (_lib.ComposeImage * n)()
+        keep = []
+        for i, im in enumerate(images):
+            im = np.ascontiguousarray(im)
+            keep.append(im)
+            arr[i].data = im.ctypes.data
+            arr[i].h, arr[i].w = im.shape[:2]
+            arr[i].stride = 0
+            arr[i].K = (ctypes.c_float * 9)(
+                *np.asarray(Ks[i], np.float32).reshape(9))
+            arr[i].R = (ctypes.c_float * 9)(
+                *np.asarray(Rs[i], np.float32).reshape(9))
+            if gains is not None and gains[i] is not None:
+                g = np.ascontiguousarray(gains[i], np.float32)
+                keep.append(g)
+                arr[i].aux.gain = g.ctypes.data
+                arr[i].aux.gain_h, arr[i].aux.gain_w = g.shape
+            if seam_masks is not None and seam_masks[i] is not None:
+                m = np.ascontiguousarray(seam_masks[i], np.uint8)
+                keep.append(m)
+                arr[i].aux.seam_mask = m.ctypes.data
+                arr[i].aux.seam_h, arr[i].aux.seam_w = m.shape
+        check(self._lib.xp_composer_set_images(self._h, n, arr,
+                                               _lib.MEM_HOST))
+        self._keep = keep
+
+    def run(self):
+        info = _lib.ComposeInfo()
+        check(self._lib.xp_composer_run(self._h, ctypes.byref(info)))
+        self.info = {
+            "width": info.width, "height": info.height, "min_x": info.min_x,
+            "min_y": info.min_y, "bpp": info.bpp, "levels": info.levels,
+            "resolution_capped": bool(info.resolution_capped),
+            "roi": tuple(info.roi), "warp_scale": info.warp_scale,
+            "warp_ms": info.warp_ms, "blend_ms": info.blend_ms,
+            "h2d_ms": info.h2d_ms, "timing": info.timing.as_dict(),
+            "s_src": info.s_src, "s_w": info.s_w, "s_t": info.s_t,
+            "c": info.c}
+        return self.info
+
+    def fetch(self, pano=None, mask=None):
+        W, H = self.info["width"], self.info["height"]
+        dt = np.uint16 if self.info["bpp"] == 16 else np.uint8
+        if pano is None:
+            pano = np.empty((H, W, 3), dt)
+        if mask is None:
+            mask = np.empty((H, W), np.uint8)
+        check(self._lib.xp_composer_fetch(self._h, pano.ctypes.data, 0,
+                                          mask.ctypes.data, 0, _lib.MEM_HOST))
+        return pano, mask
+
+    def debug(self, what, image=0, channel=0, level=0, dtype=None):
+        h = self._lib.xp_composer_blender(self._h)
+        return debug_fetch(self._lib, c_void_p(h), what, image, channel, level,
+                           dtype)
+
+
+def compose_panorama(images, Ks, Rs, gains=None, seam_masks=None, **opts):
+    """One-call form: -> ComposeResult(pano, mask, info)."""
+    c = Composer(**opts)
+    c.set_images(images, Ks, Rs, gains, seam_masks)
+    info = c.run()
+    pano, mask = c.fetch()
+    return ComposeResult(pano, mask, info)
