@@ -130,6 +130,6 @@ def debug_fetch(lib, handle, what, image=0, channel=0, level=0, dtype=None):
                                      ctypes.byref(nbytes)))
     arr = buf[:nbytes.value].view(dt)
     rows, cols, pitch = dims[0], dims[1], dims[2]
-    if rows * pitch == arr.size and rows > 0:
+    if rows * pitch == arr.size and rows > 1:
         arr = arr.reshape(rows, pitch)[:, :cols]
     return arr
