@@ -1,0 +1,429 @@
+#!/usr/bin/env python
+"""Benchmark of the full-resolution export hot path (warp + seams/masks +
+multiband blend), BASELINE.json metric "output megapixels/sec".
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+A step is one pass of the hot path over one synthetic image set: N=1 runs
+BASELINE.json configs[1] (8 x 12-MP inputs -> ~60-MP spherical panorama,
+5 pyramid levels). With N > 1 (torchrun, one rank per GPU) every rank
+composes its own panorama group -- the path shards by group with no data-path
+collective -- and `value` is the total output MP of all
+ranks over the slowest rank's time ("weak" scaling).
+
+`value`   : sources resident in HBM at t0, panorama resident at t1.
+`e2e`     : the same through the public call with HOST buffers: upload of the
+            sources from pinned memory and download of panorama + mask inside
+            the timed region.
+`roofline`: dominant HBM-bound stage, algorithmic bytes / CUDA-event time
+            against MEASURED_PEAKS.json.
+`--impl reference` times the reference's own CPU implementation (cv2 warp
+exactly as stitcher.cc:377-385 calls it + the unmodified multiblend library,
+oracle/_ref) on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "output megapixels/sec (warp+multiband blend)"
+UNIT = "MP/s"
+
+CONFIGS = {
+    # BASELINE.json configs[1]
+    "cfg2": dict(n_cols=8, n_rows=1, w=4000, h=3000, focal=3600.0,
+                 step=0.66, pitches=[0.0], projection=2, fixed_levels=5,
+                 bpp=8, max_pano_mpx=100.0,
+                 name="8x12MP u8 -> ~60MP spherical, 5 levels"),
+    # BASELINE.json configs[2] (one GPU holds it; canvas tiling is future work)
+    "cfg3": dict(n_cols=8, n_rows=3, w=6000, h=4000, focal=4500.0,
+                 step=0.55, pitches=[-math.radians(25), 0.0,
+                                     math.radians(25)],
+                 projection=2, fixed_levels=7, bpp=8, max_pano_mpx=100.0,
+                 name="24x24MP u8 -> 100MP spherical (capped), 7 levels"),
+    # reduced shapes for smoke runs
+    "small": dict(n_cols=4, n_rows=1, w=800, h=600, focal=700.0, step=0.62,
+                  pitches=[0.0], projection=2, fixed_levels=5, bpp=8,
+                  max_pano_mpx=100.0, name="4x0.5MP u8 smoke shape"),
+}
+
+
+def make_image(w, h, seed, bpp=8):
+    """Band-limited synthetic texture of SURVEY.md section 8d (sinusoids with
+    periods 97/131/211 px, +-4 hash noise, per-image gain), vectorised."""
+    rng = np.random.default_rng(seed)
+    x = np.arange(w, dtype=np.float32)
+    y = np.arange(h, dtype=np.float32)
+    cy = np.cos(2 * np.pi * y / 131.0)[:, None]
+    diag = 40 * np.sin(2 * np.pi * np.arange(w + h, dtype=np.float32) / 211.0)
+    dsum = diag[np.add.outer(np.arange(h), np.arange(w))]
+    gain = rng.uniform(0.9, 1.1)
+    out = np.empty((h, w, 3), np.uint8 if bpp == 8 else np.uint16)
+    for c in range(3):
+        sx = 60 * np.sin(2 * np.pi * (x / 97.0 + rng.uniform(0, 1)))[None, :]
+        img = (128 + sx * cy + dsum) * gain
+        img += rng.integers(-4, 5, (h, w)).astype(np.float32)
+        np.clip(img, 0, 255, out=img)
+        out[..., c] = img if bpp == 8 else img * 257
+    return out
+
+
+def make_workload(cfg, group):
+    import compose_oracle as co
+    hfov = 2 * math.atan(cfg["w"] / 2 / cfg["focal"])
+    Ks, Rs = co.make_cameras(cfg["n_cols"], cfg["n_rows"], cfg["w"], cfg["h"],
+                             cfg["focal"], cfg["step"] * hfov, cfg["pitches"],
+                             2000 + 10 * group)
+    ims = [make_image(cfg["w"], cfg["h"], 2000 + 10 * group + i, cfg["bpp"])
+           for i in range(len(Ks))]
+    return ims, Ks, Rs
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,"
+         "clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(
+                ["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            pass
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+            out, _ = self.p.communicate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                 "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [v.strip() for v in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------
+# reference arm: the reference's own CPU implementation of the path
+# ---------------------------------------------------------------------------
+def host_cores():
+    return len(os.sched_getaffinity(0))
+
+
+def reference_step(ims, Ks, Rs, cfg, cores):
+    """One pass of the CPU path on the given images. Returns (canvas MP,
+    seconds, kind). kind "reference": cv2 RotationWarper.warp twice per image
+    (stitcher.cc:377-385) + unmodified multiblend (oracle/_ref) with
+    max(2, cores-1) threads (stitcher_pipeline.h:148-149); kind "port": the
+    oracle's C restatement (single thread) when either is unavailable."""
+    from oracle import mb_ref
+    try:
+        import cv2
+    except Exception:  # pragma: no cover
+        cv2 = None
+    names = {2: "spherical", 1: "cylindrical", 7: "mercator", 0: "plane"}
+    use_ref = cv2 is not None and mb_ref.available() \
+        and cfg["projection"] in names
+    t0 = time.perf_counter()
+    if use_ref:
+        cv2.setNumThreads(cores)
+        warper = cv2.PyRotationWarper(names[cfg["projection"]],
+                                      float(cfg["focal"]))
+        fed, pos = [], []
+        for im, K, R in zip(ims, Ks, Rs):
+            corner, warped = warper.warp(im, K, R, cv2.INTER_LINEAR,
+                                         cv2.BORDER_REFLECT)
+            mask = np.full(im.shape[:2], 255, np.uint8)
+            _, mw = warper.warp(mask, K, R, cv2.INTER_NEAREST,
+                                cv2.BORDER_CONSTANT)
+            alpha = cv2.compare(mw, 0, cv2.CMP_NE)          # blenders.cc:106
+            if warped.dtype == np.uint16:
+                alpha = alpha.astype(np.uint16) * 257
+            fed.append(cv2.merge(list(cv2.split(warped)) + [alpha]))
+            pos.append(corner)
+        res = mb_ref.blend(fed, pos, fixed_levels=cfg["fixed_levels"],
+                           n_threads=max(2, cores - 1))
+        mp = res.width * res.height / 1e6
+        kind = "reference"
+    else:
+        import compose_oracle as co
+        res = co.compose(ims, Ks, Rs, projection=cfg["projection"],
+                         warp_scale=cfg["focal"],
+                         max_pano_mpx=cfg["max_pano_mpx"],
+                         fixed_levels=cfg["fixed_levels"])
+        mp = res["pano"].shape[0] * res["pano"].shape[1] / 1e6
+        kind = "port"
+    return mp, time.perf_counter() - t0, kind
+
+
+def sample_of(cfg, ims, Ks, Rs, n_sample):
+    n = min(n_sample, len(ims))
+    return ims[:n], Ks[:n], Rs[:n], (
+        f"first {n} of {len(ims)} images of the workload "
+        f"({n} x {cfg['w']}x{cfg['h']})")
+
+
+def run_reference(args, cfg):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = host_cores()
+    ims, Ks, Rs = make_workload(cfg, 0)
+    ims, Ks, Rs, sample = sample_of(cfg, ims, Ks, Rs, args.ref_images)
+    kind = "port"
+    for _ in range(args.warmup):
+        reference_step(ims, Ks, Rs, cfg, cores)
+    total_mp, total_s = 0.0, 0.0
+    for _ in range(args.steps):
+        mp, s, kind = reference_step(ims, Ks, Rs, cfg, cores)
+        total_mp += mp
+        total_s += s
+    value = total_mp / total_s
+    used = cores if kind == "reference" else 1
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data":
+        "synthetic", "config": {"workload": cfg["name"], "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": used,
+                         "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# ---------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------
+HBM_STAGES = ("warp", "shrink_mask", "copy", "shrink", "laplace", "blend",
+              "collapse", "out")
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def run_ours(args, cfg):
+    import torch
+    import torch.distributed as dist
+    import xpano_b200 as xb
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; xpano_b200 has no CPU "
+                         "fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = xb._lib.load()
+
+    ims, Ks, Rs = make_workload(cfg, rank)
+    # host sources in pinned memory (e2e leg copies from here every step)
+    pinned = []
+    for im in ims:
+        t = torch.empty(im.shape, dtype=torch.uint8 if im.dtype == np.uint8
+                        else torch.uint16, pin_memory=True)
+        t.numpy()[...] = im
+        pinned.append(t)
+    host = [t.numpy() for t in pinned]
+
+    stream = torch.cuda.current_stream().cuda_stream
+    comp = xb.Composer(projection=cfg["projection"], warp_scale=cfg["focal"],
+                       max_pano_mpx=cfg["max_pano_mpx"], depth=cfg["bpp"],
+                       fixed_levels=cfg["fixed_levels"], device=local)
+    comp.set_stream(stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # ---- resident leg ------------------------------------------------------
+    comp.set_images(host, Ks, Rs)
+    info = None
+    for _ in range(args.warmup):
+        info = comp.run()
+    barrier()
+    clocks = ClockSampler(local)
+    launches0 = lib.xp_kernel_launch_count()
+    ev0, ev1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    stage_ms = {}
+    ev0.record()
+    for _ in range(args.steps):
+        info = comp.run()
+        for k, v in info["timing"].items():
+            stage_ms[k] = stage_ms.get(k, 0.0) + v
+        stage_ms["warp"] = stage_ms.get("warp", 0.0) + info["warp_ms"]
+    ev1.record()
+    barrier()
+    launches = lib.xp_kernel_launch_count() - launches0
+    clk = clocks.stop()
+    ms = max_over_ranks(ev0.elapsed_time(ev1))
+    mp_rank = info["width"] * info["height"] / 1e6
+    total_mp = sum_over_ranks(mp_rank)
+    value = total_mp * args.steps / (ms / 1e3)
+
+    # ---- e2e leg: host buffers in, host panorama out, every step -----------
+    W, H = info["width"], info["height"]
+    dt = torch.uint8 if info["bpp"] == 8 else torch.uint16
+    pano = torch.empty((H, W, 3), dtype=dt, pin_memory=True)
+    mask = torch.empty((H, W), dtype=torch.uint8, pin_memory=True)
+    pano_np, mask_np = pano.numpy(), mask.numpy()
+    h2d = sum(im.nbytes for im in host)
+    d2h = pano_np.nbytes + mask_np.nbytes
+    e2e_steps = max(1, min(args.steps, 5))
+    for _ in range(min(args.warmup, 2)):
+        comp.set_images(host, Ks, Rs)
+        comp.run()
+        comp.fetch(pano_np, mask_np)
+    barrier()
+    t0 = time.perf_counter()
+    ev0.record()
+    for _ in range(e2e_steps):
+        comp.set_images(host, Ks, Rs)
+        comp.run()
+        comp.fetch(pano_np, mask_np)
+    ev1.record()
+    barrier()
+    wall = time.perf_counter() - t0
+    e2e_ms = max_over_ranks(max(ev0.elapsed_time(ev1), 0.0))
+    e2e_value = total_mp * e2e_steps / (e2e_ms / 1e3)
+
+    # ---- roofline of the dominant HBM-bound stage --------------------------
+    peak, peak_src = measured_peaks()
+    sbytes = dict(info["stage_bytes"])
+    sbytes["warp"] = info["warp_bytes"]
+    slaunch = dict(info["stage_launches"])
+    slaunch["warp"] = info["warp_launches"]
+    per_stage = {}
+    for k in HBM_STAGES:
+        t = stage_ms.get(k, 0.0) / args.steps
+        if t > 0 and sbytes.get(k, 0) > 0:
+            gbs = sbytes[k] / (t / 1e3) / 1e9
+            per_stage[k] = {"ms": round(t, 4), "launches": slaunch.get(k, 0),
+                            "alg_GB": round(sbytes[k] / 1e9, 4),
+                            "GBps": round(gbs, 1),
+                            "frac": round(gbs / peak, 4)}
+    dom = max(per_stage, key=lambda k: per_stage[k]["ms"])
+    hbm_ms = sum(v["ms"] for v in per_stage.values())
+    hbm_bytes = sum(sbytes[k] for k in per_stage)
+    roof = {"bound": "hbm", "kernel": dom,
+            "achieved": per_stage[dom]["GBps"], "peak": peak,
+            "peak_source": peak_src, "unit": "GB/s",
+            "frac": per_stage[dom]["frac"], "traffic": None,
+            "bytes_per_launch": sbytes[dom] / max(1, slaunch[dom]),
+            "ms_per_launch": per_stage[dom]["ms"] / max(1, slaunch[dom]),
+            "all_hbm_stages": {"ms": round(hbm_ms, 3),
+                               "GBps": round(hbm_bytes / hbm_ms / 1e6, 1),
+                               "frac": round(hbm_bytes / hbm_ms / 1e6 / peak,
+                                             4)}}
+    serial = {k: round(stage_ms.get(k, 0.0) / args.steps, 3)
+              for k in ("images", "seam")}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8" if cfg["bpp"] == 8
+        else "u16", "data": "synthetic",
+        "config": {"workload": cfg["name"], "canvas": [W, H],
+                   "levels": info["levels"], "sharding": "panorama group per "
+                   "GPU, no data-path collective" if world > 1 else "1 GPU",
+                   "l2": "inputs and intermediates (>2 GB per step) exceed "
+                   "the 126 MB L2"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / e2e_steps,
+                "steps": e2e_steps, "wall_ms_per_step": 1e3 * wall / e2e_steps},
+        "gpu_launches": int(launches), "clocks": clk, "roofline": roof,
+        "stages": per_stage, "latency_bound_stages_ms": serial,
+        "sizes_mp": {"s_src": info["s_src"] / 1e6, "s_w": info["s_w"] / 1e6,
+                     "s_t": info["s_t"] / 1e6, "c": info["c"] / 1e6},
+    }
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = host_cores()
+        si, sK, sR, sample = sample_of(cfg, ims, Ks, Rs, args.ref_images)
+        mp, s, kind = reference_step(si, sK, sR, cfg, cores)
+        line["cpu_baseline"] = {"value": mp / s, "unit": UNIT,
+                                "cores": cores if kind == "reference" else 1,
+                                "kind": kind, "sample": sample,
+                                "seconds": round(s, 2)}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="cfg2", choices=sorted(CONFIGS))
+    ap.add_argument("--ref-images", type=int, default=3,
+                    help="images in the bounded CPU sample")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    cfg = CONFIGS[args.config]
+    if args.impl == "reference":
+        run_reference(args, cfg)
+    else:
+        run_ours(args, cfg)
+
+
+if __name__ == "__main__":
+    main()

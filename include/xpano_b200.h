@@ -182,6 +182,11 @@ xp_status xp_blender_fetch(xp_blender* b, void* dst_bgr, size_t dst_stride,
  * outside the mask. */
 xp_status xp_blender_fetch_planes(xp_blender* b, void* planes, int mem);
 
+/* Algorithmic bytes (inputs once + outputs once) and kernel launches per
+ * stage of the last blend, in xp_timing field order (9 entries). */
+xp_status xp_blender_stage_bytes(xp_blender* b, double bytes[9],
+                                 int launches[9]);
+
 /* Intermediates for stage-level parity tests (needs keep_debug). `what`:
  *  "labels" (i32 HxW), "seam_bwd"/"seam_fwd" (u64 HxW), "xor_mask" (u8),
  *  "trim" (i32[6]: left, top, w, h, xpos, ypos; image), "opaque" (u8; image),
@@ -236,6 +241,13 @@ typedef struct {
   xp_timing timing;
   /* workload sizes for the roofline */
   double s_src, s_w, s_t, c;
+  /* algorithmic bytes and kernel launches per stage, in xp_timing order
+   * (images, seam, shrink_mask, copy, shrink, laplace, blend, collapse, out);
+   * warp stage separately */
+  double stage_bytes[9];
+  int stage_launches[9];
+  double warp_bytes;
+  int warp_launches;
 } xp_compose_info;
 
 void xp_compose_opts_default(xp_compose_opts* o);

@@ -65,7 +65,10 @@ class ComposeInfo(ctypes.Structure):
                 ("blend_ms", ctypes.c_double), ("h2d_ms", ctypes.c_double),
                 ("d2h_ms", ctypes.c_double), ("timing", Timing),
                 ("s_src", ctypes.c_double), ("s_w", ctypes.c_double),
-                ("s_t", ctypes.c_double), ("c", ctypes.c_double)]
+                ("s_t", ctypes.c_double), ("c", ctypes.c_double),
+                ("stage_bytes", ctypes.c_double * 9),
+                ("stage_launches", c_int * 9),
+                ("warp_bytes", ctypes.c_double), ("warp_launches", c_int)]
 
 
 # every symbol include/xpano_b200.h declares: (restype, argtypes)
@@ -109,6 +112,7 @@ SYMBOLS = {
     "xp_blender_fetch": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p,
                                  c_size_t, c_int]),
     "xp_blender_fetch_planes": (c_int, [c_void_p, c_void_p, c_int]),
+    "xp_blender_stage_bytes": (c_int, [c_void_p, c_void_p, c_void_p]),
     "xp_blender_debug_fetch": (c_int, [c_void_p, ctypes.c_char_p, c_int, c_int,
                                        c_int, c_void_p, c_size_t, c_void_p,
                                        P(c_size_t)]),

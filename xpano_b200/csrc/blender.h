@@ -54,6 +54,8 @@ struct Blender {
   DevBuf img_pyr, mask_buf, out_pyr, planes, bgr;
   int cover_bytes = 4;
   int apply_add = 0;
+  double stage_bytes[16] = {0};
+  int stage_launches[16] = {0};
   StageTimer timer;
   // workload sizes (pixels)
   double s_t = 0, c_px = 0;

@@ -156,6 +156,7 @@ struct Composer {
     blender->roi[2] = rect[2];
     blender->roi[3] = rect[3];
     double s_src = 0, s_w = 0;
+    int warp_launches = 0;
     XP_CUDA(cudaEventRecord(ev[0], stream));
     const size_t bs = opts.depth / 8;
     for (size_t i = 0; i < src.size(); ++i) {
@@ -169,6 +170,7 @@ struct Composer {
                               roi_incl, s.gain.as<float>(), s.gw, s.gh,
                               s.seam.as<uint8_t>(), s.mw, s.mh, f->data.p,
                               (size_t)r[2] * 4 * bs);
+      warp_launches += 1 + (s.seam.p ? 1 : 0) + (is_separable(p.type) ? 1 : 0);
       s_src += (double)s.w * s.h;
       s_w += (double)r[2] * r[3];
     }
@@ -200,6 +202,12 @@ struct Composer {
       info->s_w = s_w;
       info->s_t = blender->s_t;
       info->c = blender->c_px;
+      for (int k = 0; k < 9; ++k) {
+        info->stage_bytes[k] = blender->stage_bytes[k];
+        info->stage_launches[k] = blender->stage_launches[k];
+      }
+      info->warp_bytes = (3.0 * s_src + 4.0 * s_w) * bs;
+      info->warp_launches = warp_launches;
     }
   }
 };

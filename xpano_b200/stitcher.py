@@ -14,6 +14,10 @@ from ._lib import c_void_p, check
 from .blenders import debug_fetch
 
 
+_STAGES = ("images", "seam", "shrink_mask", "copy", "shrink", "laplace",
+           "blend", "collapse", "out")
+
+
 @dataclass
 class ComposeResult:
     pano: np.ndarray | None
@@ -93,7 +97,11 @@ class Composer:
             "warp_ms": info.warp_ms, "blend_ms": info.blend_ms,
             "h2d_ms": info.h2d_ms, "timing": info.timing.as_dict(),
             "s_src": info.s_src, "s_w": info.s_w, "s_t": info.s_t,
-            "c": info.c}
+            "c": info.c,
+            "stage_bytes": dict(zip(_STAGES, info.stage_bytes)),
+            "stage_launches": dict(zip(_STAGES, info.stage_launches)),
+            "warp_bytes": info.warp_bytes,
+            "warp_launches": info.warp_launches}
         return self.info
 
     def fetch(self, pano=None, mask=None):
