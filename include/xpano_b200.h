@@ -264,6 +264,9 @@ xp_status xp_composer_fetch(xp_composer* c, void* dst_bgr, size_t dst_stride,
                             uint8_t* dst_mask, size_t mask_stride, int mem);
 /* the blender a composer drives (for debug_fetch) */
 xp_blender* xp_composer_blender(xp_composer* c);
+/* Device buffers are cached across objects (a blender is single-use, like the
+ * reference's); this returns the cached blocks to the driver. */
+void xp_trim_memory(void);
 /* number of kernels this library launched since process start */
 unsigned long long xp_kernel_launch_count(void);
 

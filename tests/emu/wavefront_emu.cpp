@@ -17,6 +17,9 @@
 #include <thread>
 #include <vector>
 
+static std::atomic<long> g_fast_chunks{0}, g_slow_chunks{0};
+#define XP_WF_STATS(fast) ((fast) ? ++g_fast_chunks : ++g_slow_chunks)
+
 #include "../../xpano_b200/csrc/scan_problems.h"
 #include "../../xpano_b200/csrc/wavefront.h"
 
@@ -44,14 +47,38 @@ struct EmuCtx {
     return r;
   }
   int bcast(int v) { return (int)exchange((uint64_t)(uint32_t)v, 0); }
-  uint64_t shfl_up1(uint64_t v) { return exchange(v, lane_ - 1); }
-  uint64_t shfl_idx(uint64_t v, int src) { return exchange(v, src & 31); }
+  template <class T>
+  T shfl_up1(T v) {
+    return (T)exchange((uint64_t)v, lane_ - 1);
+  }
+  template <class T>
+  T shfl_idx(T v, int src) {
+    return (T)exchange((uint64_t)v, src & 31);
+  }
   void sync() { w->bar.arrive_and_wait(); }
+  bool all(bool v) {
+    w->x[lane_] = v ? 1 : 0;
+    w->bar.arrive_and_wait();
+    bool r = true;
+    for (int i = 0; i < 32; ++i) r = r && w->x[i] != 0;
+    w->bar.arrive_and_wait();
+    return r;
+  }
   void wait_ge(const int* p, int need) {
     while (__atomic_load_n(p, __ATOMIC_ACQUIRE) < need)
       std::this_thread::yield();
   }
+  int peek(const int* p) {
+    int v = lane_ == 0 ? __atomic_load_n(p, __ATOMIC_ACQUIRE) : 0;
+    return bcast(v);
+  }
   void publish(int* p, int v) { __atomic_store_n(p, v, __ATOMIC_RELEASE); }
+  void cp_async(void* dst, const void* src, int bytes) {
+    memcpy(dst, src, (size_t)bytes);
+  }
+  void cp_commit() {}
+  void cp_wait_all_but_one() {}
+  void cp_wait_all() {}
 };
 
 template <class P>
@@ -108,17 +135,29 @@ void seams_t(int n, const int* xpos, const int* ypos, const int* w,
   std::vector<C> cover;
   build_cover(cover, W, H, n, xpos, ypos, w, h, opaque);
   std::vector<uint8_t> lab8((size_t)W * H);
+  std::vector<u32> b32((size_t)W * H), f32((size_t)W * H);
   const int n_bands = (H + 31) / 32;
-  SeamBwd<C> pb{n_bands, W, H, cover.data(), bwd};
+  SeamBwd<C> pb{n_bands, W, H, cover.data(), b32.data()};
   run_emulated(pb, n_warps);
-  SeamFwd<C> pf{n_bands, W, H, reverse, cover.data(), bwd, fwd, lab8.data()};
+  SeamFwd<C> pf{n_bands, W,          H,          reverse,
+                cover.data(), b32.data(), f32.data(), lab8.data()};
   run_emulated(pf, n_warps);
-  for (size_t i = 0; i < lab8.size(); ++i) labels[i] = lab8[i];
+  for (size_t i = 0; i < lab8.size(); ++i) {
+    labels[i] = lab8[i];
+    bwd[i] = seam_unpack(b32[i]);
+    fwd[i] = seam_unpack(f32[i]);
+  }
 }
 
 }  // namespace
 
 extern "C" {
+
+// chunks that took the parallel fast path / the stepped path since last call
+void emu_chunk_stats(long* fast, long* slow) {
+  *fast = g_fast_chunks.exchange(0);
+  *slow = g_slow_chunks.exchange(0);
+}
 
 void emu_seams(int n, const int* xpos, const int* ypos, const int* w,
                const int* h, const uint8_t* const* opaque, int W, int H,

@@ -81,7 +81,32 @@ def _emu_seams(lib, ops, tpos, W, H, reverse, wide, n_warps):
 ])
 def test_emulated_seams_match_oracle(emu, seed, n, mode, reverse, wide,
                                      n_warps):
-    ops, tpos, W, H = _seam_inputs(seed, n, mode)
+    _check_seams(emu, seed, n, mode, reverse, wide, n_warps, 70, 50)
+
+
+@pytest.mark.parametrize("seed,n,mode,reverse,wide,n_warps", [
+    (21, 3, "full", 0, 0, 3),
+    (22, 3, "ellipse", 1, 0, 2),
+])
+def test_emulated_seams_seed_only_chunks(emu, seed, n, mode, reverse, wide,
+                                         n_warps):
+    """Images wide enough that whole 32-step chunks consist of seed pixels and
+    take the wavefront's parallel fast path (wavefront.h) between ordinary
+    chunks."""
+    _chunk_stats(emu)
+    _check_seams(emu, seed, n, mode, reverse, wide, n_warps, 260, 100)
+    fast, slow = _chunk_stats(emu)
+    assert fast > 0 and slow > 0, (fast, slow)
+
+
+def _chunk_stats(emu):
+    fast, slow = ctypes.c_long(), ctypes.c_long()
+    emu.emu_chunk_stats(ctypes.byref(fast), ctypes.byref(slow))
+    return fast.value, slow.value
+
+
+def _check_seams(emu, seed, n, mode, reverse, wide, n_warps, w, h):
+    ops, tpos, W, H = _seam_inputs(seed, n, mode, w=w, h=h)
     ref_l, ref_b, ref_f = mb_oracle.seams(ops, tpos, W, H, reverse=bool(reverse),
                                           debug=True)
     l, b, f = _emu_seams(emu, ops, tpos, W, H, reverse, wide, n_warps)
@@ -90,11 +115,12 @@ def test_emulated_seams_match_oracle(emu, seed, n, mode, reverse, wide,
     assert np.array_equal(l, ref_l)
 
 
-@pytest.mark.parametrize("seed,mode,bpp,n_warps", [
-    (11, "ellipse", 8, 2), (12, "blobs", 8, 3), (13, "ellipse", 16, 2),
+@pytest.mark.parametrize("seed,mode,bpp,n_warps,w,h", [
+    (11, "ellipse", 8, 2, 60, 45), (12, "blobs", 8, 3, 60, 45),
+    (13, "ellipse", 16, 2, 60, 45), (14, "ellipse", 8, 3, 280, 110),
 ])
-def test_emulated_inpaint_matches_oracle(emu, seed, mode, bpp, n_warps):
-    ims, _ = synth.blend_case(seed, n=3, w=60, h=45, mode=mode, bpp=bpp)
+def test_emulated_inpaint_matches_oracle(emu, seed, mode, bpp, n_warps, w, h):
+    ims, _ = synth.blend_case(seed, n=3, w=w, h=h, mode=mode, bpp=bpp)
     bbs = [mb_oracle.trim(im) for im in ims]
     want = [mb_oracle.inpaint(im, bb)[0] for im, bb in zip(ims, bbs)]
     got = [np.ascontiguousarray(im).copy() for im in ims]
@@ -102,7 +128,10 @@ def test_emulated_inpaint_matches_oracle(emu, seed, mode, bpp, n_warps):
     ptrs = (ctypes.c_void_p * n)(*[g.ctypes.data for g in got])
     tw = (ctypes.c_int * n)(*[g.shape[1] for g in got])
     bb = (ctypes.c_int * (4 * n))(*[v for b in bbs for v in b])
+    _chunk_stats(emu)
     emu.emu_inpaint(n, ptrs, tw, bpp, bb, n_warps)
+    fast, slow = _chunk_stats(emu)
+    assert slow > 0 and (w < 200 or fast > 0), (fast, slow)
     for g, w_, b in zip(got, want, bbs):
         l, t, ww, hh = b
         assert np.array_equal(g[t:t + hh, l:l + ww], w_[t:t + hh, l:l + ww])

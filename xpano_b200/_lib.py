@@ -77,6 +77,7 @@ SYMBOLS = {
     "xp_version": (ctypes.c_char_p, []),
     "xp_device_count": (c_int, []),
     "xp_kernel_launch_count": (ctypes.c_ulonglong, []),
+    "xp_trim_memory": (None, []),
     "xp_warper_create": (c_int, [c_int, c_int, c_float, c_float, c_float,
                                  c_int, P(c_void_p)]),
     "xp_warper_destroy": (None, [c_void_p]),

@@ -94,6 +94,8 @@ struct Scope {
 // Blender basics
 // ---------------------------------------------------------------------------
 Blender::~Blender() {
+  // buffers go back to the caching pool: nothing may still be using them
+  if (stream) cudaStreamSynchronize(stream);
   if (own_stream) cudaStreamDestroy(own_stream);
 }
 

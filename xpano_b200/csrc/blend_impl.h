@@ -56,8 +56,10 @@ void launch_cover(void* cover, int cover_bytes, int CW, const ImgDev& im,
                   int bpp, int bit, unsigned long long* d_transparent,
                   cudaStream_t s);
 void launch_seams(const void* cover, int cover_bytes, int W, int H,
-                  int reverse, u64* bwd, u64* fwd, uint8_t* labels,
+                  int reverse, uint32_t* bwd, uint32_t* fwd, uint8_t* labels,
                   int* counter, int* progress, cudaStream_t s);
+void launch_seam_unpack(const uint32_t* in, size_t n, uint64_t* out,
+                        cudaStream_t s);
 void launch_inpaint(const InpaintJob* d_jobs, const InpaintBandRef* d_bands,
                     int n_bands, int bpp, int* counter, int* progress,
                     cudaStream_t s);

@@ -1,5 +1,8 @@
 #include "common.h"
 
+#include <map>
+#include <mutex>
+
 namespace xp {
 
 static thread_local char g_err[512] = "";
@@ -19,6 +22,80 @@ void fail(xp_status code, const char* fmt, ...) {
   vsnprintf(buf, sizeof(buf), fmt, ap);
   va_end(ap);
   throw Error(code, buf);
+}
+
+// ---------------------------------------------------------------------------
+// caching device allocator
+// ---------------------------------------------------------------------------
+namespace {
+struct Pool {
+  std::mutex mu;
+  std::multimap<size_t, void*> free_blocks[16];  // per device, by size
+};
+Pool& pool() {
+  static Pool* p = new Pool();  // leaked on purpose: outlives static dtors
+  return *p;
+}
+}  // namespace
+
+void* pool_alloc(size_t n, size_t* got, int* device) {
+  int dev = 0;
+  XP_CUDA(cudaGetDevice(&dev));
+  *device = dev;
+  // round up so near-equal requests of successive panoramas hit the cache
+  const size_t gran = n < (1u << 20) ? 4096 : (size_t)1 << 20;
+  n = (n + gran - 1) / gran * gran;
+  Pool& P = pool();
+  if (dev < 16) {
+    std::lock_guard<std::mutex> lk(P.mu);
+    auto& fb = P.free_blocks[dev];
+    auto it = fb.lower_bound(n);
+    if (it != fb.end() && it->first <= n + n / 4 + (1 << 20)) {
+      void* p = it->second;
+      *got = it->first;
+      fb.erase(it);
+      return p;
+    }
+  }
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, n);
+  if (e == cudaErrorMemoryAllocation) {
+    cudaGetLastError();
+    pool_trim();
+    e = cudaMalloc(&p, n);
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    fail(e == cudaErrorMemoryAllocation ? XP_ERR_NOMEM : XP_ERR_CUDA,
+         "cudaMalloc(%zu) failed: %s", n, cudaGetErrorString(e));
+  }
+  *got = n;
+  return p;
+}
+
+void pool_free(void* p, size_t bytes, int device) {
+  if (!p) return;
+  Pool& P = pool();
+  if (device >= 0 && device < 16) {
+    std::lock_guard<std::mutex> lk(P.mu);
+    P.free_blocks[device].emplace(bytes, p);
+    return;
+  }
+  cudaFree(p);
+}
+
+void pool_trim() {
+  Pool& P = pool();
+  std::lock_guard<std::mutex> lk(P.mu);
+  int cur = 0;
+  cudaGetDevice(&cur);
+  for (int d = 0; d < 16; ++d) {
+    if (P.free_blocks[d].empty()) continue;
+    cudaSetDevice(d);
+    for (auto& kv : P.free_blocks[d]) cudaFree(kv.second);
+    P.free_blocks[d].clear();
+  }
+  cudaSetDevice(cur);
 }
 
 void select_device(int device) {
@@ -68,6 +145,8 @@ int xp_device_count(void) {
   }
   return n;
 }
+
+void xp_trim_memory(void) { xp::pool_trim(); }
 
 unsigned long long xp_kernel_launch_count(void) {
   return xp::g_launches.load(std::memory_order_relaxed);

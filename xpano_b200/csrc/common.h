@@ -66,13 +66,22 @@ xp_status guard(F&& f) {
 }
 
 // Owning device allocation.
+// caching device allocator (common.cu); blocks are reused only after the
+// owning stream work was synchronised by the caller's own stream order: every
+// user of a block in this library runs on one stream per object and buffers
+// are released at object destruction, after a stream synchronisation.
+void* pool_alloc(size_t n, size_t* got, int* device);
+void pool_free(void* p, size_t bytes, int device);
+void pool_trim();
+
 struct DevBuf {
   void* p = nullptr;
   size_t bytes = 0;
+  int device = 0;
   DevBuf() = default;
   DevBuf(const DevBuf&) = delete;
   DevBuf& operator=(const DevBuf&) = delete;
-  DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) {
+  DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes), device(o.device) {
     o.p = nullptr;
     o.bytes = 0;
   }
@@ -81,6 +90,7 @@ struct DevBuf {
       release();
       p = o.p;
       bytes = o.bytes;
+      device = o.device;
       o.p = nullptr;
       o.bytes = 0;
     }
@@ -88,22 +98,18 @@ struct DevBuf {
   }
   ~DevBuf() { release(); }
   void release() {
-    if (p) cudaFree(p);
+    if (p) pool_free(p, bytes, device);
     p = nullptr;
     bytes = 0;
   }
-  // grow-only (re)allocation; contents are not preserved
+  // grow-only (re)allocation; contents are not preserved. Blocks come from a
+  // per-device caching pool: a blender is single-use like the reference's, so
+  // without the pool every panorama would pay cudaMalloc/cudaFree again.
   void reserve(size_t n) {
     if (n <= bytes) return;
     release();
     if (n == 0) return;
-    cudaError_t e = cudaMalloc(&p, n);
-    if (e != cudaSuccess) {
-      p = nullptr;
-      fail(e == cudaErrorMemoryAllocation ? XP_ERR_NOMEM : XP_ERR_CUDA,
-           "cudaMalloc(%zu) failed: %s", n, cudaGetErrorString(e));
-    }
-    bytes = n;
+    p = pool_alloc(n, &bytes, &device);
   }
   template <class T>
   T* as() const {

@@ -34,6 +34,11 @@ struct Composer {
   double h2d_ms = 0;
 
   ~Composer() {
+    if (stream) cudaStreamSynchronize(stream);
+    // members that remember the stream must go before it is destroyed
+    blender.reset();
+    src.clear();
+    warper.stream = nullptr;
     for (cudaEvent_t e : ev)
       if (e) cudaEventDestroy(e);
     if (own_stream) cudaStreamDestroy(own_stream);

@@ -5,12 +5,21 @@
 //   InpaintFwd / InpaintBwd : external/multiblend/src/image.cpp:550-812
 //   SeamBwd / SeamFwd       : external/multiblend/src/multiblend.cpp:254-823
 //
-// Values are u64. Seams: dist << 32 | image id, top bit = "that image does
-// not cover this pixel" (maskval, multiblend.cpp:74-76). Inpaint: dist << 32 |
-// index of the source pixel whose colour the reference would have copied here
-// (the reference copies the whole pixel in place from the winning neighbour;
-// carrying the winner's source index and gathering once at the end is the
-// same function of the input).
+// Seam values: the reference's u64 is dist << 32 | image id with the top bit
+// meaning "that image does not cover this pixel" (maskval,
+// multiblend.cpp:74-76). They are carried here packed in 32 bits,
+// flag << 31 | dist23 << 8 | id, by an order-preserving map (seam_pack /
+// seam_unpack below): real distances stay below 2^22 for any canvas with
+// W + H < kSeamMaxExtent, and the DT_MAX family 0x10000000 + k maps to
+// 2^22 + k. Comparisons, +3/+4 and re-masking commute with the map, so the
+// unpacked result is bit-identical to the reference's.
+// Inpaint values are u64: dist << 32 | index of the source pixel whose colour
+// the reference would have copied here (the reference copies the whole pixel
+// in place from the winning neighbour; carrying the winner's source index and
+// gathering once at the end is the same function of the input).
+//
+// Every step() is branch-free (selects only): one warp per band runs it as a
+// serial dependent chain, so instruction count and divergence are the cost.
 #pragma once
 
 #include <cstdint>
@@ -83,13 +92,29 @@ XP_HD int clz_top(u64 v) {
 #endif
 }
 
+// ---------------------------------------------------------------------------
+// packed seam values
+// ---------------------------------------------------------------------------
+constexpr u32 kTop32 = 0x80000000u;
+constexpr u32 kInf32 = 0xffffffffu;
+constexpr u32 kDtMax32 = 0xC0000000u;  // flag | (1 << 22) << 8 | label 0
+constexpr u32 kD3 = 3u << 8, kD4 = 4u << 8;
+constexpr int kSeamMaxExtent = 1000000;  // W + H bound for the 23-bit field
+
+XP_HD u64 seam_unpack(u32 v) {
+  const u32 d23 = (v >> 8) & 0x7fffffu;
+  const u32 dist =
+      d23 >= 0x400000u ? d23 - 0x400000u + 0x10000000u : d23;
+  return ((u64)(v >> 31) << 63) | ((u64)dist << 32) | (u64)(v & 0xffu);
+}
+
 // maskval (multiblend.cpp:74-76): re-evaluate the cover flag of v's label
 template <class C>
-XP_HD u64 maskval(u64 v, C bits) {
-  const u32 lab = (u32)v;
-  const bool covered = (bits >> (lab & (sizeof(C) * 8 - 1))) & 1;
-  return (v & kLow63) | (covered ? 0 : kTopBit);
+XP_HD u32 mask32(u32 v, C bits) {
+  const u32 covered = (u32)(bits >> (v & (sizeof(C) * 8 - 1))) & 1u;
+  return (v & 0x7fffffffu) | ((covered ^ 1u) << 31);
 }
+XP_HD u32 min32(u32 a, u32 b) { return a < b ? a : b; }
 
 struct NoRow {};
 
@@ -99,13 +124,15 @@ struct NoRow {};
 // ---------------------------------------------------------------------------
 template <class C>
 struct SeamBwd {
-  typedef C In;
+  typedef u32 Val;
+  typedef C In0;
+  typedef wf::NoInput In1;
   struct Row {
     bool first_run;  // still inside the first run of the bottom row
   };
   int n_bands, W, H;
   const C* cover;  // H x W, bit i = image i opaque, top bit = run start
-  u64* out;        // H x W backward values
+  u32* out;        // H x W packed backward values
 
   XP_HD wf::Band band(int i) const {
     return wf::Band{0, i * wf::kLanes, W, H, i - 1};
@@ -114,38 +141,44 @@ struct SeamBwd {
   XP_HD size_t at(int rho, int q) const {
     return (size_t)(H - 1 - rho) * W + (W - 1 - q);
   }
-  XP_HD In load_in(const wf::Band&, int rho, int q) const {
-    return cover[at(rho, q)];
+  XP_HD const C* in0_ptr(const wf::Band&, int rho, int q) const {
+    return cover + at(rho, q);
   }
-  XP_HD u64 load_val(const wf::Band&, int rho, int q) const {
+  XP_HD const void* in1_ptr(const wf::Band&, int, int) const { return 0; }
+  XP_HD u32 load_val(const wf::Band&, int rho, int q) const {
     return out[at(rho, q)];
   }
-  XP_HD void store(const wf::Band&, int rho, int q, u64 v) const {
+  XP_HD void store(const wf::Band&, int rho, int q, u32 v) const {
     out[at(rho, q)] = v;
   }
+  // chunks made of seeds only skip the recurrence; not on the bottom band,
+  // whose first row carries the first_run state
+  XP_HD bool allow_trivial(const wf::Band& B) const { return B.rho0 != 0; }
+  XP_HD bool trivial(C cov, In1) const {
+    return popc_c((C)(cov & ~CoverTraits<C>::rs_bit)) == 1;
+  }
+  XP_HD u32 trivial_value(const wf::Band&, const Row&, int, int, C cov,
+                          In1) const {
+    return (u32)ctz_c((C)(cov | CoverTraits<C>::rs_bit));
+  }
   // last = (x+1, y); w0 = (x+1, y+1); w1 = (x, y+1); w2 = (x-1, y+1)
-  XP_HD u64 step(const wf::Band&, Row& row, int rho, int q, In cov, u64 last,
-                 u64 w0, u64 w1, u64 w2) const {
+  XP_HD u32 step(const wf::Band&, Row& row, bool active, int rho, int q, C cov,
+                 In1, u32 last, u32 w0, u32 w1, u32 w2) const {
     const C bits = cov & ~CoverTraits<C>::rs_bit;
     const bool was_first = row.first_run;
-    if (cov & CoverTraits<C>::rs_bit) row.first_run = false;
-    if (popc_c(bits) == 1) return (u64)ctz_c(bits);  // :327-331
-    if (rho == 0) {                                  // bottom row :333-346
-      if (was_first) return kDtMax;
-      return maskval(last, bits) + d32(3);
-    }
-    u64 d = ~0ull, t;
-    if (q > 0) {
-      d = maskval(last + d32(3), bits);
-      t = maskval(w0 + d32(4), bits);
-      if (t < d) d = t;
-    }
-    if (q < W - 1) {
-      t = maskval(w2 + d32(4), bits);
-      if (t < d) d = t;
-    }
-    t = maskval(w1 + d32(3), bits);
-    if (t < d) d = t;
+    if (active && (cov & CoverTraits<C>::rs_bit)) row.first_run = false;
+    // bottom row :333-346
+    const u32 bottom = was_first ? kDtMax32 : mask32(last, bits) + kD3;
+    u32 cl = mask32(last + kD3, bits);
+    u32 c0 = mask32(w0 + kD4, bits);
+    const u32 c1 = mask32(w1 + kD3, bits);
+    u32 c2 = mask32(w2 + kD4, bits);
+    if (q <= 0) cl = kInf32, c0 = kInf32;
+    if (q >= W - 1) c2 = kInf32;
+    u32 d = min32(min32(cl, c0), min32(c1, c2));
+    if (rho == 0) d = bottom;
+    if (popc_c(bits) == 1)  // :327-331
+      d = (u32)ctz_c((C)(cov | CoverTraits<C>::rs_bit));
     return d;
   }
 };
@@ -154,66 +187,68 @@ struct SeamBwd {
 // Seams, forward pass: rows top -> bottom, x left -> right. q = x, rho = y.
 // ---------------------------------------------------------------------------
 template <class C>
-struct SeamFwdIn {
-  u64 bw;
-  C cov;
-};
-
-template <class C>
 struct SeamFwd {
-  typedef SeamFwdIn<C> In;
+  typedef u32 Val;
+  typedef u32 In0;  // packed backward value of this pixel
+  typedef C In1;    // cover word
   typedef NoRow Row;
   int n_bands, W, H, reverse;
   const C* cover;
-  const u64* bwd;
-  u64* out;         // H x W forward values (also the band hand-over rows)
+  const u32* bwd;
+  u32* out;         // H x W packed forward values (also the hand-over rows)
   uint8_t* labels;  // H x W owner image
 
   XP_HD wf::Band band(int i) const {
     return wf::Band{0, i * wf::kLanes, W, H, i - 1};
   }
   XP_HD Row row_init(const wf::Band&, int) const { return Row{}; }
-  XP_HD In load_in(const wf::Band&, int rho, int q) const {
-    const size_t p = (size_t)rho * W + q;
-    return In{bwd[p], cover[p]};
+  XP_HD const u32* in0_ptr(const wf::Band&, int rho, int q) const {
+    return bwd + (size_t)rho * W + q;
   }
-  XP_HD u64 load_val(const wf::Band&, int rho, int q) const {
+  XP_HD const C* in1_ptr(const wf::Band&, int rho, int q) const {
+    return cover + (size_t)rho * W + q;
+  }
+  XP_HD u32 load_val(const wf::Band&, int rho, int q) const {
     return out[(size_t)rho * W + q];
   }
-  XP_HD void store(const wf::Band&, int rho, int q, u64 v) const {
+  XP_HD void store(const wf::Band&, int rho, int q, u32 v) const {
     const size_t p = (size_t)rho * W + q;
     out[p] = v;
     labels[p] = (uint8_t)(v & 0xffu);
   }
+  XP_HD bool allow_trivial(const wf::Band&) const { return true; }
+  XP_HD bool trivial(u32, C cov) const {
+    return popc_c((C)(cov & ~CoverTraits<C>::rs_bit)) == 1;
+  }
+  XP_HD u32 trivial_value(const wf::Band&, const Row&, int, int, u32,
+                          C cov) const {
+    return (u32)ctz_c((C)(cov | CoverTraits<C>::rs_bit));
+  }
   // last = (x-1, y); w0 = (x-1, y-1); w1 = (x, y-1); w2 = (x+1, y-1)
-  XP_HD u64 step(const wf::Band&, Row&, int y, int x, In in, u64 last, u64 w0,
-                 u64 w1, u64 w2) const {
-    const C bits = in.cov & ~CoverTraits<C>::rs_bit;
-    const bool rs = (in.cov & CoverTraits<C>::rs_bit) != 0;
+  XP_HD u32 step(const wf::Band&, Row&, bool, int y, int x, u32 bw, C cov,
+                 u32 last, u32 w0, u32 w1, u32 w2) const {
+    const C bits = cov & ~CoverTraits<C>::rs_bit;
+    const bool rs = (cov & CoverTraits<C>::rs_bit) != 0;
     const int cnt = popc_c(bits);
-    if (cnt == 1) return (u64)ctz_c(bits);  // :607-616
-    u64 best = in.bw, t;                    // ReadSeamDT, unmasked
-    if (y > 0) {
-      if (x > 0) {
-        t = maskval(w0 + d32(4), bits);
-        if (t < best) best = t;
-      }
-      t = maskval(w1 + d32(3), bits);
-      if (t < best) best = t;
-      if (x < W - 1) {
-        t = maskval(w2 + d32(4), bits);
-        if (t < best) best = t;
-      }
-    }
-    if (x > 0) {
-      // re-masked only on the top row, at x == 1 and at a run start
-      // (:629-630, :704-705); raw inside a run (:750)
-      t = last + d32(3);
-      if (y == 0 || x == 1 || rs) t = maskval(t, bits);
-      if (t < best) best = t;
-    }
-    if ((best & kTopBit) && cnt != 0)  // arbitrary seam :732-742
-      best = kTopBit | (u64)(reverse ? clz_top(bits) : ctz_c(bits));
+    u32 c0 = mask32(w0 + kD4, bits);
+    u32 c1 = mask32(w1 + kD3, bits);
+    u32 c2 = mask32(w2 + kD4, bits);
+    // the left neighbour is re-masked only on the top row, at x == 1 and at
+    // a run start (:629-630, :704-705); raw inside a run (:750)
+    u32 cl = last + kD3;
+    const u32 clm = mask32(cl, bits);
+    if (y == 0 || x == 1 || rs) cl = clm;
+    if (x <= 0) cl = kInf32;
+    if (y == 0 || x <= 0) c0 = kInf32;
+    if (y == 0) c1 = kInf32;
+    if (y == 0 || x >= W - 1) c2 = kInf32;
+    // ReadSeamDT value enters unmasked
+    u32 best = min32(min32(min32(bw, c0), min32(c1, c2)), cl);
+    const int low = ctz_c((C)(cov | CoverTraits<C>::rs_bit));
+    const int pick = reverse ? clz_top((C)(bits | 1)) : low;
+    if ((best & kTop32) && cnt != 0)  // arbitrary seam :732-742
+      best = kTop32 | (u32)pick;
+    if (cnt == 1) best = (u32)low;  // :607-616
     return best;
   }
 };
@@ -237,17 +272,35 @@ struct InpaintBandRef {
 };
 
 template <int BPP>
+struct PixelOf {
+  typedef u32 type;
+};
+template <>
+struct PixelOf<16> {
+  typedef u64 type;
+};
+XP_HD bool pixel_opaque(u32 px) { return (px >> 24) == 0xffu; }
+XP_HD bool pixel_opaque(u64 px) { return (px >> 48) == 0xffffull; }
+
+template <int BPP>
 XP_HD bool px_opaque(const void* data, size_t idx) {
   if (BPP == 8)
     return (static_cast<const u32*>(data)[idx] >> 24) == 0xffu;
   return (static_cast<const u64*>(data)[idx] >> 48) == 0xffffull;
 }
 
+XP_HD u32 hi32(u64 v) { return (u32)(v >> 32); }
+XP_HD u32 lo32(u64 v) { return (u32)v; }
+
 // forward pass: q = x, rho = y (image.cpp:550-694)
 template <int BPP>
 struct InpaintFwd {
-  typedef u32 In;  // 1 = opaque
-  typedef NoRow Row;
+  typedef u64 Val;
+  typedef typename PixelOf<BPP>::type In0;  // the pixel (alpha on top)
+  typedef wf::NoInput In1;
+  struct Row {
+    u32 base;  // index of (x = 0, this row) in the untrimmed image
+  };
   int n_bands;
   const InpaintJob* jobs;
   const InpaintBandRef* bands;
@@ -257,66 +310,55 @@ struct InpaintFwd {
     const InpaintJob& j = jobs[r.job];
     return wf::Band{r.job, r.local * wf::kLanes, j.w, j.h, r.dep};
   }
-  XP_HD Row row_init(const wf::Band&, int) const { return Row{}; }
-  XP_HD u32 self(const InpaintJob& j, int y, int x) const {
-    return (u32)((size_t)(j.top + y) * j.tiff_w + j.left + x);
-  }
-  XP_HD In load_in(const wf::Band& B, int y, int x) const {
+  XP_HD Row row_init(const wf::Band& B, int y) const {
     const InpaintJob& j = jobs[B.job];
-    return px_opaque<BPP>(j.data, self(j, y, x)) ? 1u : 0u;
+    return Row{(u32)((size_t)(j.top + y) * j.tiff_w + j.left)};
   }
+  XP_HD const In0* in0_ptr(const wf::Band& B, int y, int x) const {
+    const InpaintJob& j = jobs[B.job];
+    return static_cast<const In0*>(j.data) +
+           ((size_t)(j.top + y) * j.tiff_w + j.left + x);
+  }
+  XP_HD const void* in1_ptr(const wf::Band&, int, int) const { return 0; }
   XP_HD u64 load_val(const wf::Band& B, int y, int x) const {
     return jobs[B.job].fwd[(size_t)y * B.W + x];
   }
   XP_HD void store(const wf::Band& B, int y, int x, u64 v) const {
     jobs[B.job].fwd[(size_t)y * B.W + x] = v;
   }
+  XP_HD bool allow_trivial(const wf::Band&) const { return true; }
+  XP_HD bool trivial(In0 px, In1) const { return pixel_opaque(px); }
+  // `row` is the calling lane's; the wavefront asks for other rows of the
+  // band too, which sit at a fixed stride from it
+  XP_HD u64 trivial_value(const wf::Band& B, const Row& row, int dy, int x,
+                          In0, In1) const {
+    return (u64)(row.base + (u32)(dy * jobs[B.job].tiff_w) + (u32)x);
+  }
   // last = (x-1, y); w0 = (x-1, y-1); w1 = (x, y-1); w2 = (x+1, y-1)
-  XP_HD u64 step(const wf::Band& B, Row&, int y, int x, In opaque, u64 last,
-                 u64 w0, u64 w1, u64 w2) const {
-    const u32 me = self(jobs[B.job], y, x);
-    if (opaque) return (u64)me;  // dist 0 (:659-662)
-    u32 d, src;
-    if (y == 0) {  // :573-583
-      if (x == 0) return d32(0x80000000u) | me;
-      d = (u32)(last >> 32) + 3;
-      src = (u32)last;
-    } else if (x == 0) {  // :585-603, tie goes to up-right
-      const u32 b = (u32)(w1 >> 32) + 3;
-      const u32 c = B.W > 1 ? (u32)(w2 >> 32) + 4 : 0xffffffffu;
-      if (b < c) {
-        d = b;
-        src = (u32)w1;
-      } else {
-        d = c;
-        src = (u32)w2;
-      }
-    } else {  // :609-641
-      d = (u32)(last >> 32) + 3;
-      src = (u32)last;
-      const u32 a = (u32)(w0 >> 32) + 4;
-      const u32 b = (u32)(w1 >> 32) + 3;
-      const u32 c = x < B.W - 1 ? (u32)(w2 >> 32) + 4 : 0xffffffffu;
-      if (a < d) {
-        d = a;
-        src = (u32)w0;
-      }
-      if (b < d) {
-        d = b;
-        src = (u32)w1;
-      }
-      if (c < d) {
-        d = c;
-        src = (u32)w2;
-      }
-    }
-    return d32(d) | src;
+  XP_HD u64 step(const wf::Band& B, Row& row, bool, int y, int x, In0 px, In1,
+                 u64 last, u64 w0, u64 w1, u64 w2) const {
+    const u32 me = row.base + (u32)x;
+    // own row :573-583 / :609-641; the very first pixel seeds 0x80000000
+    u32 d = hi32(last) + 3, s = lo32(last);
+    if (x == 0) d = y == 0 ? 0x80000000u : kInf32, s = me;
+    u32 a = hi32(w0) + 4, b = hi32(w1) + 3, c = hi32(w2) + 4;
+    if (y == 0 || x == 0) a = kInf32;
+    if (y == 0) b = kInf32;
+    if (y == 0 || x >= B.W - 1) c = kInf32;
+    if (a < d) d = a, s = lo32(w0);
+    if (b < d) d = b, s = lo32(w1);
+    // in column 0 a tie between up and up-right goes to up-right (:585-603)
+    if (c < d || (x == 0 && c == d)) d = c, s = lo32(w2);
+    if (pixel_opaque(px)) d = 0, s = me;  // :659-662
+    return d32(d) | s;
   }
 };
 
 // backward pass: q = w-1-x, rho = h-1-y (image.cpp:711-812)
 struct InpaintBwd {
-  typedef u64 In;  // forward value of this pixel (dist 0 <=> opaque)
+  typedef u64 Val;
+  typedef u64 In0;  // forward value of this pixel (dist 0 <=> opaque)
+  typedef wf::NoInput In1;
   typedef NoRow Row;
   int n_bands;
   const InpaintJob* jobs;
@@ -331,52 +373,41 @@ struct InpaintBwd {
   XP_HD size_t at(const wf::Band& B, int rho, int q) const {
     return (size_t)(B.H - 1 - rho) * B.W + (B.W - 1 - q);
   }
-  XP_HD In load_in(const wf::Band& B, int rho, int q) const {
-    return jobs[B.job].fwd[at(B, rho, q)];
+  XP_HD const u64* in0_ptr(const wf::Band& B, int rho, int q) const {
+    return jobs[B.job].fwd + at(B, rho, q);
   }
+  XP_HD const void* in1_ptr(const wf::Band&, int, int) const { return 0; }
   XP_HD u64 load_val(const wf::Band& B, int rho, int q) const {
     return jobs[B.job].bwd[at(B, rho, q)];
   }
   XP_HD void store(const wf::Band& B, int rho, int q, u64 v) const {
     jobs[B.job].bwd[at(B, rho, q)] = v;
   }
+  XP_HD bool allow_trivial(const wf::Band&) const { return true; }
+  XP_HD bool trivial(u64 fwd, In1) const { return (fwd >> 32) == 0; }
+  XP_HD u64 trivial_value(const wf::Band&, const Row&, int, int, u64 fwd,
+                          In1) const {
+    return fwd;
+  }
   // last = (x+1, y); w0 = (x+1, y+1); w1 = (x, y+1); w2 = (x-1, y+1)
-  XP_HD u64 step(const wf::Band& B, Row&, int rho, int q, In fwd, u64 last,
-                 u64 w0, u64 w1, u64 w2) const {
-    u32 best = (u32)(fwd >> 32);
-    u32 src = (u32)fwd;
-    if (best == 0) return fwd;  // opaque: cur = 0, d = 3
-    // candidate from the right neighbour: its final distance + 3; at the row
-    // start the reference seeds d with 0x80000000 (or nothing on the last line)
-    const bool has_right = q > 0;
-    const u32 d = has_right ? (u32)(last >> 32) + 3 : 0x80000000u;
-    if (rho == 0) {  // last line :711-747
-      if (has_right && d < best) {
-        best = d;
-        src = (u32)last;
-      }
-      return d32(best) | src;
-    }
-    const u32 a = q < B.W - 1 ? (u32)(w2 >> 32) + 4 : 0x80000000u;  // x-1
-    const u32 b = (u32)(w1 >> 32) + 3;
-    const u32 c = q > 0 ? (u32)(w0 >> 32) + 4 : 0x80000000u;        // x+1
-    if (a < best) {
-      best = a;
-      src = (u32)w2;
-    }
-    if (b < best) {
-      best = b;
-      src = (u32)w1;
-    }
-    if (c < best) {
-      best = c;
-      src = (u32)w0;
-    }
-    if (d < best) {
-      best = d;
-      src = (u32)last;
-    }
-    return d32(best) | src;
+  XP_HD u64 step(const wf::Band& B, Row&, bool, int rho, int q, u64 fwd, In1,
+                 u64 last, u64 w0, u64 w1, u64 w2) const {
+    u32 best = hi32(fwd), src = lo32(fwd);
+    const bool opaque = best == 0;  // cur = 0, d = 3
+    const bool bottom = rho == 0;   // last line :711-747: right neighbour only
+    // at the row start the reference seeds the running distance with
+    // 0x80000000 (nothing on the last line)
+    u32 a = q < B.W - 1 ? hi32(w2) + 4 : 0x80000000u;  // x-1
+    u32 b = hi32(w1) + 3;
+    u32 c = q > 0 ? hi32(w0) + 4 : 0x80000000u;        // x+1
+    u32 d = q > 0 ? hi32(last) + 3 : (bottom ? kInf32 : 0x80000000u);
+    if (bottom) a = kInf32, b = kInf32, c = kInf32;
+    if (a < best) best = a, src = lo32(w2);
+    if (b < best) best = b, src = lo32(w1);
+    if (c < best) best = c, src = lo32(w0);
+    if (d < best) best = d, src = lo32(last);
+    const u64 v = d32(best) | src;
+    return opaque ? fwd : v;
   }
 };
 

@@ -23,13 +23,18 @@ struct DevCtx {
   __device__ __forceinline__ int bcast(int v) {
     return __shfl_sync(0xffffffffu, v, 0);
   }
-  __device__ __forceinline__ u64 shfl_up1(u64 v) {
+  template <class T>
+  __device__ __forceinline__ T shfl_up1(T v) {
     return __shfl_up_sync(0xffffffffu, v, 1);
   }
-  __device__ __forceinline__ u64 shfl_idx(u64 v, int src) {
+  template <class T>
+  __device__ __forceinline__ T shfl_idx(T v, int src) {
     return __shfl_sync(0xffffffffu, v, src);
   }
   __device__ __forceinline__ void sync() { __syncwarp(); }
+  __device__ __forceinline__ bool all(bool v) {
+    return __all_sync(0xffffffffu, v);
+  }
   __device__ __forceinline__ void wait_ge(const int* p, int need) {
     int v;
     for (;;) {
@@ -41,10 +46,41 @@ struct DevCtx {
       __nanosleep(32);
     }
   }
+  __device__ __forceinline__ int peek(const int* p) {
+    int v = 0;
+    if ((threadIdx.x & 31) == 0)
+      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];"
+                   : "=r"(v)
+                   : "l"(p)
+                   : "memory");
+    return __shfl_sync(0xffffffffu, v, 0);
+  }
+  // release is cumulative over the __syncwarp that precedes it: the other
+  // lanes' tile stores are ordered before the counter becomes visible
   __device__ __forceinline__ void publish(int* p, int v) {
-    __threadfence();
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v)
                  : "memory");
+  }
+  __device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc,
+                                           int bytes) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    if (bytes == 4)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d),
+                   "l"(gsrc)
+                   : "memory");
+    else
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d),
+                   "l"(gsrc)
+                   : "memory");
+  }
+  __device__ __forceinline__ void cp_commit() {
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  __device__ __forceinline__ void cp_wait_all_but_one() {
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+  }
+  __device__ __forceinline__ void cp_wait_all() {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
   }
 };
 
@@ -169,9 +205,25 @@ void launch_cover(void* cover, int cover_bytes, int CW, const ImgDev& im,
 // ---------------------------------------------------------------------------
 // seams
 // ---------------------------------------------------------------------------
+__global__ void seam_unpack_kernel(const u32* __restrict__ in, size_t n,
+                                   u64* __restrict__ out) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x)
+    out[i] = seam_unpack(in[i]);
+}
+
+// debug view: the reference's u64 encoding of the packed seam values
+void launch_seam_unpack(const u32* in, size_t n, u64* out, cudaStream_t s) {
+  const int blocks = (int)std::min<size_t>(div_up(n, (size_t)256), 148 * 16);
+  seam_unpack_kernel<<<blocks, 256, 0, s>>>(in, n, out);
+  XP_LAUNCHED();
+}
+
 void launch_seams(const void* cover, int cover_bytes, int W, int H,
-                  int reverse, u64* bwd, u64* fwd, uint8_t* labels,
+                  int reverse, u32* bwd, u32* fwd, uint8_t* labels,
                   int* counter, int* progress, cudaStream_t s) {
+  XP_REQUIRE((long)W + H < kSeamMaxExtent,
+             "canvas %d x %d exceeds the seam distance range", W, H);
   const int n_bands = div_up(H, wf::kLanes);
   if (cover_bytes == 4) {
     SeamBwd<u32> pb{n_bands, W, H, (const u32*)cover, bwd};

@@ -521,6 +521,7 @@ void Warper::ensure_device() {
 }
 
 Warper::~Warper() {
+  if (stream) cudaStreamSynchronize(stream);
   if (own_stream) cudaStreamDestroy(own_stream);
 }
 

@@ -16,8 +16,9 @@
 //     reads the last row of the previous band from global memory behind a
 //     monotone progress counter (one-directional: a band never waits for a
 //     later band, so any number of resident warps makes progress);
-//   * inputs and outputs move through per-warp shared-memory tiles so global
-//     traffic is coalesced along rows although lanes work on 32 different rows.
+//   * inputs move global -> shared with cp.async one 32-step chunk ahead
+//     (double-buffered tiles, coalesced along rows although the lanes work on
+//     32 different rows); outputs leave through a shared tile the same way.
 //
 // Total depth is (W + 2H) steps instead of W*H. The code is written against a
 // small warp-context interface so the identical source runs on the device and
@@ -35,6 +36,7 @@ namespace wf {
 constexpr int kLanes = 32;
 constexpr int kChunk = 32;          // steps per tile
 constexpr int kTilePitch = kChunk + 1;
+constexpr int kTileElems = kLanes * kTilePitch;
 constexpr int kSkew = 2;            // pixels a lane trails the lane above it
 
 struct Band {
@@ -44,10 +46,26 @@ struct Band {
   int dep;    // global index of the band that owns row rho0-1, or -1
 };
 
-// Shared-memory bytes one warp needs for problem P.
+struct NoInput {};  // second input stream of single-stream problems
+
+template <class T>
+struct StreamBytes {
+  static constexpr size_t value = sizeof(T);
+};
+template <>
+struct StreamBytes<NoInput> {
+  static constexpr size_t value = 0;
+};
+
+// Shared-memory bytes one warp needs for problem P: two buffers of each input
+// tile, one output tile and one row of hand-over values.
 template <class P>
 constexpr size_t tile_bytes() {
-  return (sizeof(typename P::In) + sizeof(uint64_t)) * kLanes * kTilePitch;
+  return (2 * (StreamBytes<typename P::In0>::value +
+               StreamBytes<typename P::In1>::value) +
+          sizeof(typename P::Val)) *
+             kTileElems +
+         sizeof(typename P::Val) * kChunk;
 }
 
 // Runs problem P over all its bands. `counter` is a zero-initialised claim
@@ -56,12 +74,20 @@ constexpr size_t tile_bytes() {
 template <class Ctx, class P>
 XP_HD void run(Ctx& ctx, const P& prob, int* counter, int* progress,
                unsigned char* smem_warp) {
-  using In = typename P::In;
-  using Val = uint64_t;
+  using In0 = typename P::In0;
+  using In1 = typename P::In1;
+  using Val = typename P::Val;
+  constexpr size_t kB0 = StreamBytes<In0>::value;
+  constexpr size_t kB1 = StreamBytes<In1>::value;
   const int lane = ctx.lane();
-  In* in_tile = reinterpret_cast<In*>(smem_warp);
-  Val* out_tile =
-      reinterpret_cast<Val*>(smem_warp + sizeof(In) * kLanes * kTilePitch);
+  // layout: out tile | hand-over row | in0[2] | in1[2], widest type first
+  Val* out_tile = reinterpret_cast<Val*>(smem_warp);
+  Val* pv_row = out_tile + kTileElems;
+  unsigned char* base_a = reinterpret_cast<unsigned char*>(pv_row + kChunk);
+  unsigned char* in0_base =
+      kB0 >= kB1 ? base_a : base_a + 2 * kB1 * kTileElems;
+  unsigned char* in1_base =
+      kB0 >= kB1 ? base_a + 2 * kB0 * kTileElems : base_a;
 
   for (;;) {
     int band_idx = 0;
@@ -75,7 +101,28 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, int* progress,
     typename P::Row row_state = prob.row_init(B, rho);
     const int n_chunks = (W + kSkew * (kLanes - 1) + kChunk - 1) / kChunk;
 
-    Val last = 0, w0 = 0, w1 = 0, w2 = 0, pv = 0;
+    // stage the inputs of chunk c into buffer c & 1: row r, positions
+    // c*32 - 2r + lane
+    auto prefetch = [&](int c) {
+      const int s0 = c * kChunk;
+      In0* t0 = reinterpret_cast<In0*>(in0_base + (c & 1) * kB0 * kTileElems);
+      In1* t1 = reinterpret_cast<In1*>(in1_base + (c & 1) * kB1 * kTileElems);
+      for (int r = 0; r < kLanes; ++r) {
+        const int q = s0 - kSkew * r + lane;
+        if (B.rho0 + r < B.H && q >= 0 && q < W) {
+          ctx.cp_async(t0 + r * kTilePitch + lane,
+                       prob.in0_ptr(B, B.rho0 + r, q), (int)kB0);
+          if (kB1)
+            ctx.cp_async(t1 + r * kTilePitch + lane,
+                         prob.in1_ptr(B, B.rho0 + r, q), (int)kB1);
+        }
+      }
+      ctx.cp_commit();
+    };
+
+    Val last = 0, w0 = 0, w1 = 0, w2 = 0, pv = 0, pv_next = 0;
+    bool have_next = false;
+    prefetch(0);
     if (B.dep >= 0) {
       // lane 0 starts with (q=0, rho0-1) in the slot that shifts into w1
       ctx.wait_ge(progress + B.dep, W < 1 ? W : 1);
@@ -84,33 +131,113 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, int* progress,
 
     for (int c = 0; c < n_chunks; ++c) {
       const int s0 = c * kChunk;
-      // ---- stage inputs: row r, positions s0 - 2r + lane ----
-      for (int r = 0; r < kLanes; ++r) {
-        const int q = s0 - kSkew * r + lane;
-        if (B.rho0 + r < B.H && q >= 0 && q < W)
-          in_tile[r * kTilePitch + lane] = prob.load_in(B, B.rho0 + r, q);
-      }
+      if (c + 1 < n_chunks) prefetch(c + 1);
+      // previous band's last row, positions s0+1 .. s0+32 (one per lane)
       if (B.dep >= 0) {
-        int need = s0 + kChunk + 1;
-        if (need > W) need = W;
-        ctx.wait_ge(progress + B.dep, need);
-        const int pos = s0 + 1 + lane;
-        pv = pos < W ? prob.load_val(B, B.rho0 - 1, pos) : 0;
+        if (have_next) {
+          pv = pv_next;
+        } else {
+          int need = s0 + kChunk + 1;
+          if (need > W) need = W;
+          ctx.wait_ge(progress + B.dep, need);
+          const int pos = s0 + 1 + lane;
+          pv = pos < W ? prob.load_val(B, B.rho0 - 1, pos) : 0;
+        }
+        // opportunistically fetch the next chunk's row now if it is ready
+        have_next = false;
+        if (c + 1 < n_chunks) {
+          int need = s0 + 2 * kChunk + 1;
+          if (need > W) need = W;
+          if (ctx.peek(progress + B.dep) >= need) {
+            const int pos = s0 + kChunk + 1 + lane;
+            pv_next = pos < W ? prob.load_val(B, B.rho0 - 1, pos) : 0;
+            have_next = true;
+          }
+        }
       }
+      pv_row[lane] = pv;
+      if (c + 1 < n_chunks)
+        ctx.cp_wait_all_but_one();
+      else
+        ctx.cp_wait_all();
       ctx.sync();
-      // ---- 32 skewed steps ----
-      for (int t = 0; t < kChunk; ++t) {
-        const int q = s0 + t - kSkew * lane;
-        Val up = ctx.shfl_up1(last);
-        const Val hv = ctx.shfl_idx(pv, t);
-        if (lane == 0) up = hv;
-        w0 = w1;
-        w1 = w2;
-        w2 = up;
-        if (row_ok && q >= 0 && q < W) {
-          const In in = in_tile[lane * kTilePitch + t];
-          last = prob.step(B, row_state, rho, q, in, last, w0, w1, w2);
-          out_tile[lane * kTilePitch + t] = last;
+      const In0* t0 =
+          reinterpret_cast<const In0*>(in0_base + (c & 1) * kB0 * kTileElems);
+      const In1* t1 =
+          reinterpret_cast<const In1*>(in1_base + (c & 1) * kB1 * kTileElems);
+      // ---- fast path: every pixel of the chunk is determined by its own
+      // input alone (a seed / an opaque pixel), so the tile is filled in
+      // parallel and the lane state is rebuilt from it ----
+      bool trivial = prob.allow_trivial(B);
+      if (trivial) {
+        for (int r = 0; r < kLanes; ++r) {
+          const int q = s0 - kSkew * r + lane;
+          if (B.rho0 + r < B.H && q >= 0 && q < W) {
+            In1 b = In1();
+            if (kB1) b = t1[r * kTilePitch + lane];
+            trivial = trivial && prob.trivial(t0[r * kTilePitch + lane], b);
+          }
+        }
+      }
+      trivial = ctx.all(trivial);
+#ifdef XP_WF_STATS
+      if (lane == 0) XP_WF_STATS(trivial);
+#endif
+      if (trivial) {
+        for (int r = 0; r < kLanes; ++r) {
+          const int q = s0 - kSkew * r + lane;
+          if (B.rho0 + r < B.H && q >= 0 && q < W) {
+            In1 b = In1();
+            if (kB1) b = t1[r * kTilePitch + lane];
+            out_tile[r * kTilePitch + lane] = prob.trivial_value(
+                B, row_state, r - lane, q, t0[r * kTilePitch + lane], b);
+          }
+        }
+        ctx.sync();
+        // own row: the last position this lane has produced so far
+        int t_last = W - 1 - s0 + kSkew * lane;
+        if (t_last > kChunk - 1) t_last = kChunk - 1;
+        if (row_ok && t_last >= 0 && s0 + t_last - kSkew * lane >= 0)
+          last = out_tile[lane * kTilePitch + t_last];
+        // row above at positions q_e and q_e + 1 (columns 29, 30 of lane-1)
+        if (lane > 0) {
+          w1 = out_tile[(lane - 1) * kTilePitch + kChunk - 3];
+          w2 = out_tile[(lane - 1) * kTilePitch + kChunk - 2];
+        }
+        const Val p30 = ctx.shfl_idx(pv, kChunk - 2);
+        const Val p31 = ctx.shfl_idx(pv, kChunk - 1);
+        if (lane == 0) {
+          w1 = p30;
+          w2 = p31;
+        }
+      } else {
+        // ---- 32 skewed steps; everything but the chain through `last` and
+        // the shuffle is independent of the previous step ----
+        const In0* r0 = t0 + lane * kTilePitch;
+        const In1* r1 = t1 + lane * kTilePitch;
+        Val* ro = out_tile + lane * kTilePitch;
+        const int q0 = s0 - kSkew * lane;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int t = 0; t < kChunk; ++t) {
+          const int q = q0 + t;
+          const bool active = row_ok && q >= 0 && q < W;
+          const In0 a = r0[t];
+          In1 b = In1();
+          if (kB1) b = r1[t];
+          const Val hv = pv_row[t];
+          Val up = ctx.shfl_up1(last);
+          if (lane == 0) up = hv;
+          w0 = w1;
+          w1 = w2;
+          w2 = up;
+          const Val nv =
+              prob.step(B, row_state, active, rho, q, a, b, last, w0, w1, w2);
+          if (active) {
+            last = nv;
+            ro[t] = nv;
+          }
         }
       }
       ctx.sync();
@@ -125,7 +252,7 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, int* progress,
         int done = s0 + kChunk - kSkew * (kLanes - 1);
         if (done < 0) done = 0;
         if (done > W || c == n_chunks - 1) done = W;
-        ctx.publish(progress + band_idx, done);
+        if (done > 0) ctx.publish(progress + band_idx, done);
       }
     }
   }
