@@ -64,15 +64,11 @@ struct EmuCtx {
     w->bar.arrive_and_wait();
     return r;
   }
-  void wait_ge(const int* p, int need) {
-    while (__atomic_load_n(p, __ATOMIC_ACQUIRE) < need)
-      std::this_thread::yield();
+  template <class T>
+  T ld_poll(const T* p) {
+    return __atomic_load_n(p, __ATOMIC_RELAXED);
   }
-  int peek(const int* p) {
-    int v = lane_ == 0 ? __atomic_load_n(p, __ATOMIC_ACQUIRE) : 0;
-    return bcast(v);
-  }
-  void publish(int* p, int v) { __atomic_store_n(p, v, __ATOMIC_RELEASE); }
+  void backoff() { std::this_thread::yield(); }
   void cp_async(void* dst, const void* src, int bytes) {
     memcpy(dst, src, (size_t)bytes);
   }
@@ -82,23 +78,39 @@ struct EmuCtx {
 };
 
 template <class P>
-void run_emulated(const P& prob, int n_warps) {
+void run_emulated(const P& prob, int n_warps, int max_w) {
   if (prob.n_bands <= 0) return;
   if (n_warps > prob.n_bands) n_warps = prob.n_bands;
   int counter = 0;
-  std::vector<int> progress(prob.n_bands, 0);
+  const int flag_pitch = wf::chunks_of(max_w);
+  std::vector<uint8_t> flags((size_t)prob.n_bands * flag_pitch, 0);
   std::vector<std::unique_ptr<EmuWarp>> warps;
   std::vector<std::vector<unsigned char>> smem(n_warps);
   for (int i = 0; i < n_warps; ++i) {
     warps.emplace_back(new EmuWarp());
     smem[i].resize(wf::tile_bytes<P>());
   }
+  // classification pass: warp wi takes tiles wi, wi + n_warps, ...
+  {
+    std::vector<std::thread> threads;
+    for (int wi = 0; wi < n_warps; ++wi)
+      for (int l = 0; l < 32; ++l)
+        threads.emplace_back([&, wi, l] {
+          EmuCtx ctx{warps[wi].get(), l};
+          const size_t tiles = (size_t)prob.n_bands * flag_pitch;
+          for (size_t t = wi; t < tiles; t += n_warps)
+            wf::classify_tile(ctx, prob, (int)(t / flag_pitch),
+                              (int)(t % flag_pitch), flags.data(), flag_pitch);
+        });
+    for (auto& t : threads) t.join();
+  }
   std::vector<std::thread> threads;
   for (int wi = 0; wi < n_warps; ++wi)
     for (int l = 0; l < 32; ++l)
       threads.emplace_back([&, wi, l] {
         EmuCtx ctx{warps[wi].get(), l};
-        wf::run(ctx, prob, &counter, progress.data(), smem[wi].data());
+        wf::run(ctx, prob, &counter, flags.data(), flag_pitch,
+                smem[wi].data());
       });
   for (auto& t : threads) t.join();
 }
@@ -138,10 +150,10 @@ void seams_t(int n, const int* xpos, const int* ypos, const int* w,
   std::vector<u32> b32((size_t)W * H), f32((size_t)W * H);
   const int n_bands = (H + 31) / 32;
   SeamBwd<C> pb{n_bands, W, H, cover.data(), b32.data()};
-  run_emulated(pb, n_warps);
+  run_emulated(pb, n_warps, W);
   SeamFwd<C> pf{n_bands, W,          H,          reverse,
                 cover.data(), b32.data(), f32.data(), lab8.data()};
-  run_emulated(pf, n_warps);
+  run_emulated(pf, n_warps, W);
   for (size_t i = 0; i < lab8.size(); ++i) {
     labels[i] = lab8[i];
     bwd[i] = seam_unpack(b32[i]);
@@ -178,9 +190,10 @@ void emu_inpaint(int n, void* const* data, const int* tiff_w, int bpp,
                  const int* bbox, int n_warps) {
   std::vector<InpaintJob> jobs(n);
   std::vector<std::vector<u64>> fwd(n), bwd(n);
-  int max_bands = 0;
+  int max_bands = 0, max_w = 0;
   for (int i = 0; i < n; ++i) {
     const int* b = bbox + 4 * i;
+    max_w = std::max(max_w, b[2]);
     fwd[i].assign((size_t)b[2] * b[3], 0);
     bwd[i].assign((size_t)b[2] * b[3], 0);
     jobs[i] = InpaintJob{data[i],       tiff_w[i],     b[0], b[1], b[2],
@@ -199,13 +212,13 @@ void emu_inpaint(int n, void* const* data, const int* tiff_w, int bpp,
   const int nb = (int)bands.size();
   if (bpp == 8) {
     InpaintFwd<8> pf{nb, jobs.data(), bands.data()};
-    run_emulated(pf, n_warps);
+    run_emulated(pf, n_warps, max_w);
   } else {
     InpaintFwd<16> pf{nb, jobs.data(), bands.data()};
-    run_emulated(pf, n_warps);
+    run_emulated(pf, n_warps, max_w);
   }
   InpaintBwd pb{nb, jobs.data(), bands.data()};
-  run_emulated(pb, n_warps);
+  run_emulated(pb, n_warps, max_w);
   for (int i = 0; i < n; ++i) {
     const InpaintJob& j = jobs[i];
     const size_t px = bpp == 8 ? 4 : 8;

@@ -57,12 +57,14 @@ void launch_cover(void* cover, int cover_bytes, int CW, const ImgDev& im,
                   cudaStream_t s);
 void launch_seams(const void* cover, int cover_bytes, int W, int H,
                   int reverse, uint32_t* bwd, uint32_t* fwd, uint8_t* labels,
-                  int* counter, int* progress, cudaStream_t s);
+                  int* counter, uint8_t* flags, cudaStream_t s);
+// bytes of tile flags launch_seams / launch_inpaint need
+size_t wavefront_flag_bytes(int n_bands, int max_w);
 void launch_seam_unpack(const uint32_t* in, size_t n, uint64_t* out,
                         cudaStream_t s);
 void launch_inpaint(const InpaintJob* d_jobs, const InpaintBandRef* d_bands,
-                    int n_bands, int bpp, int* counter, int* progress,
-                    cudaStream_t s);
+                    int n_bands, int max_w, int bpp, int* counter,
+                    uint8_t* flags, cudaStream_t s);
 void launch_canvas_stats(const void* cover, int cover_bytes,
                          const uint8_t* labels, int W, int H,
                          const ImgDev* d_imgs, int n, int bpp,

@@ -148,6 +148,10 @@ struct SeamBwd {
   XP_HD u32 load_val(const wf::Band&, int rho, int q) const {
     return out[at(rho, q)];
   }
+  XP_HD const u32* val_ptr(const wf::Band&, int rho, int q) const {
+    return out + at(rho, q);
+  }
+  XP_HD u32 sentinel() const { return kInf32; }
   XP_HD void store(const wf::Band&, int rho, int q, u32 v) const {
     out[at(rho, q)] = v;
   }
@@ -211,6 +215,10 @@ struct SeamFwd {
   XP_HD u32 load_val(const wf::Band&, int rho, int q) const {
     return out[(size_t)rho * W + q];
   }
+  XP_HD const u32* val_ptr(const wf::Band&, int rho, int q) const {
+    return out + ((size_t)rho * W + q);
+  }
+  XP_HD u32 sentinel() const { return kInf32; }
   XP_HD void store(const wf::Band&, int rho, int q, u32 v) const {
     const size_t p = (size_t)rho * W + q;
     out[p] = v;
@@ -323,6 +331,10 @@ struct InpaintFwd {
   XP_HD u64 load_val(const wf::Band& B, int y, int x) const {
     return jobs[B.job].fwd[(size_t)y * B.W + x];
   }
+  XP_HD const u64* val_ptr(const wf::Band& B, int y, int x) const {
+    return jobs[B.job].fwd + ((size_t)y * B.W + x);
+  }
+  XP_HD u64 sentinel() const { return ~0ull; }
   XP_HD void store(const wf::Band& B, int y, int x, u64 v) const {
     jobs[B.job].fwd[(size_t)y * B.W + x] = v;
   }
@@ -380,6 +392,10 @@ struct InpaintBwd {
   XP_HD u64 load_val(const wf::Band& B, int rho, int q) const {
     return jobs[B.job].bwd[at(B, rho, q)];
   }
+  XP_HD const u64* val_ptr(const wf::Band& B, int rho, int q) const {
+    return jobs[B.job].bwd + at(B, rho, q);
+  }
+  XP_HD u64 sentinel() const { return ~0ull; }
   XP_HD void store(const wf::Band& B, int rho, int q, u64 v) const {
     jobs[B.job].bwd[at(B, rho, q)] = v;
   }

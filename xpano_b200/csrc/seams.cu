@@ -5,6 +5,31 @@
 // src/multiblend.cpp:229-823 (seams, full/xor masks, channel sums).
 #include <climits>
 
+#ifdef XP_WF_PROFILE
+#include <cstdio>
+static __host__ __device__ inline long long wf_now() {
+#ifdef __CUDA_ARCH__
+  return clock64();
+#else
+  return 0;
+#endif
+}
+#define XP_WF_CLOCK_BEGIN() \
+  long long wf_prof[8] = {0, 0, 0, 0, 0, 0, 0, 0}, wf_prev = wf_now()
+#define XP_WF_CLOCK(i)                \
+  {                                   \
+    const long long now = wf_now();   \
+    wf_prof[i] += now - wf_prev;      \
+    wf_prev = now;                    \
+  }
+#define XP_WF_CLOCK_END(band, nb, fast, slow)                                 \
+  if (lane == 0 && (band == (nb) / 2 || band == (nb)-1))                      \
+  printf("band %d/%d fast %d slow %d | prefetch %lld dep %lld cpwait %lld "   \
+         "check %lld steps %lld flush %lld publish %lld loop %lld\n",         \
+         band, nb, fast, slow, wf_prof[0], wf_prof[1], wf_prof[2],            \
+         wf_prof[3], wf_prof[4], wf_prof[5], wf_prof[6], wf_prof[7])
+#endif
+
 #include "blend_impl.h"
 #include "common.h"
 #include "scan_problems.h"
@@ -35,32 +60,25 @@ struct DevCtx {
   __device__ __forceinline__ bool all(bool v) {
     return __all_sync(0xffffffffu, v);
   }
-  __device__ __forceinline__ void wait_ge(const int* p, int need) {
-    int v;
-    for (;;) {
-      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];"
-                   : "=r"(v)
-                   : "l"(p)
-                   : "memory");
-      if (v >= need) break;
-      __nanosleep(32);
-    }
-  }
-  __device__ __forceinline__ int peek(const int* p) {
-    int v = 0;
-    if ((threadIdx.x & 31) == 0)
-      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];"
-                   : "=r"(v)
-                   : "l"(p)
-                   : "memory");
-    return __shfl_sync(0xffffffffu, v, 0);
-  }
-  // release is cumulative over the __syncwarp that precedes it: the other
-  // lanes' tile stores are ordered before the counter becomes visible
-  __device__ __forceinline__ void publish(int* p, int v) {
-    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v)
+  // polling loads go to L2 every time (values are published by plain stores
+  // of whole words; a word that is not the sentinel is final)
+  __device__ __forceinline__ u32 ld_poll(const u32* p) {
+    u32 v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];"
+                 : "=r"(v)
+                 : "l"(p)
                  : "memory");
+    return v;
   }
+  __device__ __forceinline__ u64 ld_poll(const u64* p) {
+    u64 v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];"
+                 : "=l"(v)
+                 : "l"(p)
+                 : "memory");
+    return v;
+  }
+  __device__ __forceinline__ void backoff() { __nanosleep(20); }
   __device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc,
                                            int bytes) {
     const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -86,21 +104,39 @@ struct DevCtx {
 
 template <class P>
 __global__ void __launch_bounds__(32)
-    wavefront_kernel(P prob, int* counter, int* progress) {
+    wavefront_kernel(P prob, int* counter, const uint8_t* flags,
+                     int flag_pitch) {
   extern __shared__ __align__(16) unsigned char smem[];
   DevCtx ctx;
-  wf::run(ctx, prob, counter, progress, smem);
+  wf::run(ctx, prob, counter, flags, flag_pitch, smem);
 }
 
 template <class P>
-static void launch_wavefront(const P& prob, int* counter, int* progress,
-                             cudaStream_t s) {
+__global__ void __launch_bounds__(128)
+    classify_kernel(P prob, uint8_t* flags, int flag_pitch) {
+  DevCtx ctx;
+  const size_t tile = blockIdx.x * (size_t)(blockDim.x / 32) + threadIdx.x / 32;
+  const int band = (int)(tile / flag_pitch);
+  if (band >= prob.n_bands) return;
+  wf::classify_tile(ctx, prob, band, (int)(tile % flag_pitch), flags,
+                    flag_pitch);
+}
+
+// `flags` needs n_bands * flag_pitch bytes, flag_pitch >= chunks of the
+// widest band
+template <class P>
+static void launch_wavefront(const P& prob, int* counter, uint8_t* flags,
+                             int flag_pitch, cudaStream_t s) {
   if (prob.n_bands <= 0) return;
   XP_CUDA(cudaMemsetAsync(counter, 0, sizeof(int), s));
-  XP_CUDA(cudaMemsetAsync(progress, 0, sizeof(int) * (size_t)prob.n_bands, s));
+  const size_t tiles = (size_t)prob.n_bands * flag_pitch;
+  classify_kernel<P><<<(unsigned)div_up(tiles, (size_t)4), 128, 0, s>>>(
+      prob, flags, flag_pitch);
+  XP_LAUNCHED();
   const size_t smem = wf::tile_bytes<P>();
   const int blocks = std::min(prob.n_bands, 148 * 8);
-  wavefront_kernel<P><<<blocks, 32, smem, s>>>(prob, counter, progress);
+  wavefront_kernel<P><<<blocks, 32, smem, s>>>(prob, counter, flags,
+                                               flag_pitch);
   XP_LAUNCHED();
 }
 
@@ -205,6 +241,10 @@ void launch_cover(void* cover, int cover_bytes, int CW, const ImgDev& im,
 // ---------------------------------------------------------------------------
 // seams
 // ---------------------------------------------------------------------------
+size_t wavefront_flag_bytes(int n_bands, int max_w) {
+  return (size_t)n_bands * wf::chunks_of(max_w);
+}
+
 __global__ void seam_unpack_kernel(const u32* __restrict__ in, size_t n,
                                    u64* __restrict__ out) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n;
@@ -221,22 +261,23 @@ void launch_seam_unpack(const u32* in, size_t n, u64* out, cudaStream_t s) {
 
 void launch_seams(const void* cover, int cover_bytes, int W, int H,
                   int reverse, u32* bwd, u32* fwd, uint8_t* labels,
-                  int* counter, int* progress, cudaStream_t s) {
+                  int* counter, uint8_t* flags, cudaStream_t s) {
   XP_REQUIRE((long)W + H < kSeamMaxExtent,
              "canvas %d x %d exceeds the seam distance range", W, H);
   const int n_bands = div_up(H, wf::kLanes);
+  const int fp = wf::chunks_of(W);
   if (cover_bytes == 4) {
     SeamBwd<u32> pb{n_bands, W, H, (const u32*)cover, bwd};
-    launch_wavefront(pb, counter, progress, s);
+    launch_wavefront(pb, counter, flags, fp, s);
     SeamFwd<u32> pf{n_bands, W, H, reverse, (const u32*)cover, bwd, fwd,
                     labels};
-    launch_wavefront(pf, counter, progress, s);
+    launch_wavefront(pf, counter, flags, fp, s);
   } else {
     SeamBwd<u64> pb{n_bands, W, H, (const u64*)cover, bwd};
-    launch_wavefront(pb, counter, progress, s);
+    launch_wavefront(pb, counter, flags, fp, s);
     SeamFwd<u64> pf{n_bands, W, H, reverse, (const u64*)cover, bwd, fwd,
                     labels};
-    launch_wavefront(pf, counter, progress, s);
+    launch_wavefront(pf, counter, flags, fp, s);
   }
 }
 
@@ -244,17 +285,18 @@ void launch_seams(const void* cover, int cover_bytes, int W, int H,
 // inpaint
 // ---------------------------------------------------------------------------
 void launch_inpaint(const InpaintJob* d_jobs, const InpaintBandRef* d_bands,
-                    int n_bands, int bpp, int* counter, int* progress,
-                    cudaStream_t s) {
+                    int n_bands, int max_w, int bpp, int* counter,
+                    uint8_t* flags, cudaStream_t s) {
+  const int fp = wf::chunks_of(max_w);
   if (bpp == 8) {
     InpaintFwd<8> pf{n_bands, d_jobs, d_bands};
-    launch_wavefront(pf, counter, progress, s);
+    launch_wavefront(pf, counter, flags, fp, s);
   } else {
     InpaintFwd<16> pf{n_bands, d_jobs, d_bands};
-    launch_wavefront(pf, counter, progress, s);
+    launch_wavefront(pf, counter, flags, fp, s);
   }
   InpaintBwd pb{n_bands, d_jobs, d_bands};
-  launch_wavefront(pb, counter, progress, s);
+  launch_wavefront(pb, counter, flags, fp, s);
 }
 
 // ---------------------------------------------------------------------------

@@ -13,14 +13,21 @@
 //     from the row above was produced by its neighbour lane one step earlier
 //     and arrives by a single shuffle; its own-row predecessor is a register;
 //   * bands are claimed in order from an atomic counter; lane 0 of a band
-//     reads the last row of the previous band from global memory behind a
-//     monotone progress counter (one-directional: a band never waits for a
-//     later band, so any number of resident warps makes progress);
+//     reads the last row of the previous band from global memory, polling
+//     the values themselves: outputs start as a sentinel no recurrence can
+//     produce, so a non-sentinel word is final (one-directional: a band never
+//     waits for a later band, so any number of resident warps makes progress);
 //   * inputs move global -> shared with cp.async one 32-step chunk ahead
 //     (double-buffered tiles, coalesced along rows although the lanes work on
-//     32 different rows); outputs leave through a shared tile the same way.
+//     32 different rows); outputs leave through a shared tile the same way;
+//   * a fully parallel classification pass (classify_tile) runs first: pixels
+//     whose value follows from their own input alone (a seam seed, an opaque
+//     pixel) are written there, every other output becomes the sentinel, and
+//     each 32x32 skewed tile that consists of such pixels only is flagged. The
+//     wavefront skips flagged tiles and rebuilds its lane state from global
+//     memory when the next unflagged tile starts.
 //
-// Total depth is (W + 2H) steps instead of W*H. The code is written against a
+// Total depth is at most (W + 3H) steps instead of W*H. The code is written against a
 // small warp-context interface so the identical source runs on the device and
 // under a host SIMT emulator (tests/emu) used for CPU-side verification.
 #pragma once
@@ -29,6 +36,13 @@
 #include <cstdint>
 
 #include "hd.h"
+
+// phase timing hooks (development builds only)
+#ifndef XP_WF_CLOCK
+#define XP_WF_CLOCK(i)
+#define XP_WF_CLOCK_BEGIN()
+#define XP_WF_CLOCK_END(band, nb, fast, slow)
+#endif
 
 namespace xp {
 namespace wf {
@@ -57,6 +71,10 @@ struct StreamBytes<NoInput> {
   static constexpr size_t value = 0;
 };
 
+XP_HD int chunks_of(int W) {
+  return (W + kSkew * (kLanes - 1) + kChunk - 1) / kChunk;
+}
+
 // Shared-memory bytes one warp needs for problem P: two buffers of each input
 // tile, one output tile and one row of hand-over values.
 template <class P>
@@ -68,18 +86,52 @@ constexpr size_t tile_bytes() {
          sizeof(typename P::Val) * kChunk;
 }
 
-// Runs problem P over all its bands. `counter` is a zero-initialised claim
-// counter, `progress[b]` (zero-initialised) counts the positions of the last
-// row of band b that are final in global memory.
+// Classification pass, one warp per (band, chunk) tile: writes the value of
+// every self-determined pixel, the sentinel everywhere else, and the tile's
+// "nothing to propagate here" flag.
 template <class Ctx, class P>
-XP_HD void run(Ctx& ctx, const P& prob, int* counter, int* progress,
-               unsigned char* smem_warp) {
+XP_HD void classify_tile(Ctx& ctx, const P& prob, int band_idx, int c,
+                         uint8_t* flags, int flag_pitch) {
+  using In0 = typename P::In0;
+  using In1 = typename P::In1;
+  constexpr size_t kB1 = StreamBytes<In1>::value;
+  const int lane = ctx.lane();
+  const Band B = prob.band(band_idx);
+  if (c >= chunks_of(B.W)) return;
+  const typename P::Row row = prob.row_init(B, B.rho0 + lane);
+  const int s0 = c * kChunk;
+  bool all_trivial = true;
+  for (int r = 0; r < kLanes; ++r) {
+    const int q = s0 - kSkew * r + lane;
+    if (B.rho0 + r < B.H && q >= 0 && q < B.W) {
+      const In0 a = *prob.in0_ptr(B, B.rho0 + r, q);
+      In1 b = In1();
+      if (kB1) b = *static_cast<const In1*>(prob.in1_ptr(B, B.rho0 + r, q));
+      const bool t = prob.trivial(a, b);
+      prob.store(B, B.rho0 + r, q,
+                 t ? prob.trivial_value(B, row, r - lane, q, a, b)
+                   : prob.sentinel());
+      all_trivial = all_trivial && t;
+    }
+  }
+  all_trivial = ctx.all(all_trivial);
+  if (lane == 0)
+    flags[(size_t)band_idx * flag_pitch + c] =
+        all_trivial && prob.allow_trivial(B) ? 1 : 0;
+}
+
+// Runs problem P over all its bands. `counter` is a zero-initialised claim
+// counter; `flags` comes from classify_tile over every tile of the problem.
+template <class Ctx, class P>
+XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
+               int flag_pitch, unsigned char* smem_warp) {
   using In0 = typename P::In0;
   using In1 = typename P::In1;
   using Val = typename P::Val;
   constexpr size_t kB0 = StreamBytes<In0>::value;
   constexpr size_t kB1 = StreamBytes<In1>::value;
   const int lane = ctx.lane();
+  const Val kSentinel = prob.sentinel();
   // layout: out tile | hand-over row | in0[2] | in1[2], widest type first
   Val* out_tile = reinterpret_cast<Val*>(smem_warp);
   Val* pv_row = out_tile + kTileElems;
@@ -99,7 +151,8 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, int* progress,
     const int rho = B.rho0 + lane;
     const bool row_ok = rho < B.H;
     typename P::Row row_state = prob.row_init(B, rho);
-    const int n_chunks = (W + kSkew * (kLanes - 1) + kChunk - 1) / kChunk;
+    const int n_chunks = chunks_of(W);
+    const uint8_t* band_flags = flags + (size_t)band_idx * flag_pitch;
 
     // stage the inputs of chunk c into buffer c & 1: row r, positions
     // c*32 - 2r + lane
@@ -119,98 +172,87 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, int* progress,
       }
       ctx.cp_commit();
     };
+    // previous band's last row at position pos (lane-private), once final
+    auto poll = [&](bool want, int pos) -> Val {
+      const bool valid = want && pos >= 0 && pos < W;
+      const Val* p = prob.val_ptr(B, B.rho0 - 1, valid ? pos : 0);
+      Val v = 0;
+      for (;;) {
+        if (valid) v = ctx.ld_poll(p);
+        if (ctx.all(!valid || v != kSentinel)) break;
+        ctx.backoff();
+      }
+      return v;
+    };
 
-    Val last = 0, w0 = 0, w1 = 0, w2 = 0, pv = 0, pv_next = 0;
-    bool have_next = false;
-    prefetch(0);
-    if (B.dep >= 0) {
-      // lane 0 starts with (q=0, rho0-1) in the slot that shifts into w1
-      ctx.wait_ge(progress + B.dep, W < 1 ? W : 1);
-      if (lane == 0) w2 = prob.load_val(B, B.rho0 - 1, 0);
-    }
-
+    Val last = 0, w0 = 0, w1 = 0, w2 = 0;
+    unsigned flag_word = 0;  // lane l: flag of chunk (c & ~31) + l
+    int staged = -1;         // chunk whose inputs were requested last
+    bool restore = true;     // lane state must be rebuilt from global memory
+    XP_WF_CLOCK_BEGIN();
+    int n_fast = 0, n_slow = 0;
     for (int c = 0; c < n_chunks; ++c) {
       const int s0 = c * kChunk;
-      if (c + 1 < n_chunks) prefetch(c + 1);
-      // previous band's last row, positions s0+1 .. s0+32 (one per lane)
-      if (B.dep >= 0) {
-        if (have_next) {
-          pv = pv_next;
-        } else {
-          int need = s0 + kChunk + 1;
-          if (need > W) need = W;
-          ctx.wait_ge(progress + B.dep, need);
-          const int pos = s0 + 1 + lane;
-          pv = pos < W ? prob.load_val(B, B.rho0 - 1, pos) : 0;
-        }
-        // opportunistically fetch the next chunk's row now if it is ready
-        have_next = false;
-        if (c + 1 < n_chunks) {
-          int need = s0 + 2 * kChunk + 1;
-          if (need > W) need = W;
-          if (ctx.peek(progress + B.dep) >= need) {
-            const int pos = s0 + kChunk + 1 + lane;
-            pv_next = pos < W ? prob.load_val(B, B.rho0 - 1, pos) : 0;
-            have_next = true;
-          }
-        }
+      XP_WF_CLOCK(7);
+      if ((c & 31) == 0)
+        flag_word = c + lane < n_chunks ? band_flags[c + lane] : 0u;
+      // flags of this chunk and the next (the next may sit in the next word)
+      const bool skip = ctx.shfl_idx(flag_word, c & 31) != 0;
+#ifdef XP_WF_STATS
+      if (lane == 0) XP_WF_STATS(skip);
+#endif
+      n_fast += skip ? 1 : 0;
+      n_slow += skip ? 0 : 1;
+      if (skip) {
+        restore = true;
+        continue;
       }
+      bool next_slow = false;
+      if (c + 1 < n_chunks) {
+        unsigned nf = ctx.shfl_idx(flag_word, (c + 1) & 31);
+        if (((c + 1) & 31) == 0) nf = band_flags[c + 1];
+        next_slow = nf == 0;
+      }
+      if (staged != c) prefetch(c);
+      if (next_slow) {
+        prefetch(c + 1);
+        staged = c + 1;
+      }
+      XP_WF_CLOCK(0);
+      if (restore) {
+        // state at the end of chunk c-1, all of whose pixels (rows of this
+        // band) were written by the classification pass
+        const int qe = s0 - 1 - kSkew * lane;
+        if (row_ok && qe >= 0 && qe < W) last = prob.load_val(B, rho, qe);
+        if (row_ok && lane > 0) {
+          if (qe >= 0 && qe < W) w1 = prob.load_val(B, rho - 1, qe);
+          if (qe + 1 >= 0 && qe + 1 < W) w2 = prob.load_val(B, rho - 1, qe + 1);
+        }
+        if (B.dep >= 0) {
+          // lane 0's row above belongs to the previous band: lanes 0/1 fetch
+          // positions s0-1 and s0
+          const Val pr = poll(lane < 2, s0 - 1 + lane);
+          const Val p0 = ctx.shfl_idx(pr, 0), p1 = ctx.shfl_idx(pr, 1);
+          if (lane == 0) w1 = p0, w2 = p1;
+        }
+        restore = false;
+      }
+      // previous band's last row, positions s0+1 .. s0+32 (one per lane)
+      Val pv = 0;
+      if (B.dep >= 0) pv = poll(true, s0 + 1 + lane);
+      XP_WF_CLOCK(1);
       pv_row[lane] = pv;
-      if (c + 1 < n_chunks)
+      if (next_slow)
         ctx.cp_wait_all_but_one();
       else
         ctx.cp_wait_all();
       ctx.sync();
+      XP_WF_CLOCK(2);
       const In0* t0 =
           reinterpret_cast<const In0*>(in0_base + (c & 1) * kB0 * kTileElems);
       const In1* t1 =
           reinterpret_cast<const In1*>(in1_base + (c & 1) * kB1 * kTileElems);
-      // ---- fast path: every pixel of the chunk is determined by its own
-      // input alone (a seed / an opaque pixel), so the tile is filled in
-      // parallel and the lane state is rebuilt from it ----
-      bool trivial = prob.allow_trivial(B);
-      if (trivial) {
-        for (int r = 0; r < kLanes; ++r) {
-          const int q = s0 - kSkew * r + lane;
-          if (B.rho0 + r < B.H && q >= 0 && q < W) {
-            In1 b = In1();
-            if (kB1) b = t1[r * kTilePitch + lane];
-            trivial = trivial && prob.trivial(t0[r * kTilePitch + lane], b);
-          }
-        }
-      }
-      trivial = ctx.all(trivial);
-#ifdef XP_WF_STATS
-      if (lane == 0) XP_WF_STATS(trivial);
-#endif
-      if (trivial) {
-        for (int r = 0; r < kLanes; ++r) {
-          const int q = s0 - kSkew * r + lane;
-          if (B.rho0 + r < B.H && q >= 0 && q < W) {
-            In1 b = In1();
-            if (kB1) b = t1[r * kTilePitch + lane];
-            out_tile[r * kTilePitch + lane] = prob.trivial_value(
-                B, row_state, r - lane, q, t0[r * kTilePitch + lane], b);
-          }
-        }
-        ctx.sync();
-        // own row: the last position this lane has produced so far
-        int t_last = W - 1 - s0 + kSkew * lane;
-        if (t_last > kChunk - 1) t_last = kChunk - 1;
-        if (row_ok && t_last >= 0 && s0 + t_last - kSkew * lane >= 0)
-          last = out_tile[lane * kTilePitch + t_last];
-        // row above at positions q_e and q_e + 1 (columns 29, 30 of lane-1)
-        if (lane > 0) {
-          w1 = out_tile[(lane - 1) * kTilePitch + kChunk - 3];
-          w2 = out_tile[(lane - 1) * kTilePitch + kChunk - 2];
-        }
-        const Val p30 = ctx.shfl_idx(pv, kChunk - 2);
-        const Val p31 = ctx.shfl_idx(pv, kChunk - 1);
-        if (lane == 0) {
-          w1 = p30;
-          w2 = p31;
-        }
-      } else {
+      {
         // ---- 32 skewed steps; everything but the chain through `last` and
         // the shuffle is independent of the previous step ----
         const In0* r0 = t0 + lane * kTilePitch;
@@ -241,6 +283,7 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, int* progress,
         }
       }
       ctx.sync();
+      XP_WF_CLOCK(4);
       // ---- flush outputs, coalesced per row ----
       for (int r = 0; r < kLanes; ++r) {
         const int q = s0 - kSkew * r + lane;
@@ -248,13 +291,11 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, int* progress,
           prob.store(B, B.rho0 + r, q, out_tile[r * kTilePitch + lane]);
       }
       ctx.sync();
-      if (lane == 0) {
-        int done = s0 + kChunk - kSkew * (kLanes - 1);
-        if (done < 0) done = 0;
-        if (done > W || c == n_chunks - 1) done = W;
-        if (done > 0) ctx.publish(progress + band_idx, done);
-      }
+      XP_WF_CLOCK(5);
     }
+    (void)n_fast;
+    (void)n_slow;
+    XP_WF_CLOCK_END(band_idx, prob.n_bands, n_fast, n_slow);
   }
 }
 
