@@ -60,13 +60,15 @@ void StageTimer::reset(cudaStream_t stream) {
   used = 0;
   s = stream;
 }
-int StageTimer::begin(int stage) {
-  Span sp{stage, get(), get()};
-  XP_CUDA(cudaEventRecord(sp.a, s));
+int StageTimer::begin(int stage, cudaStream_t on) {
+  Span sp{stage, get(), get(), on ? on : s};
+  XP_CUDA(cudaEventRecord(sp.a, sp.s));
   spans.push_back(sp);
   return (int)spans.size() - 1;
 }
-void StageTimer::end(int idx) { XP_CUDA(cudaEventRecord(spans[idx].b, s)); }
+void StageTimer::end(int idx) {
+  XP_CUDA(cudaEventRecord(spans[idx].b, spans[idx].s));
+}
 void StageTimer::collect(double out[16]) {
   for (int i = 0; i < 16; ++i) out[i] = 0;
   for (const Span& sp : spans) {
@@ -84,9 +86,11 @@ enum {
 struct Scope {
   StageTimer& t;
   int idx;
-  Scope(StageTimer& tt, int stage) : t(tt), idx(tt.begin(stage)) {}
+  Scope(StageTimer& tt, int stage, cudaStream_t on = nullptr)
+      : t(tt), idx(tt.begin(stage, on)) {}
   ~Scope() {
-    if (cudaEventRecord(t.spans[idx].b, t.s) != cudaSuccess) cudaGetLastError();
+    if (cudaEventRecord(t.spans[idx].b, t.spans[idx].s) != cudaSuccess)
+      cudaGetLastError();
   }
 };
 
@@ -95,7 +99,11 @@ struct Scope {
 // ---------------------------------------------------------------------------
 Blender::~Blender() {
   // buffers go back to the caching pool: nothing may still be using them
+  if (side_stream) cudaStreamSynchronize(side_stream);
   if (stream) cudaStreamSynchronize(stream);
+  if (ev_fork) cudaEventDestroy(ev_fork);
+  if (ev_join) cudaEventDestroy(ev_join);
+  if (side_stream) cudaStreamDestroy(side_stream);
   if (own_stream) cudaStreamDestroy(own_stream);
 }
 
@@ -104,6 +112,11 @@ void Blender::ensure_device() {
   if (!stream && !external_stream) {
     XP_CUDA(cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
     stream = own_stream;
+  }
+  if (!side_stream) {
+    XP_CUDA(cudaStreamCreateWithFlags(&side_stream, cudaStreamNonBlocking));
+    XP_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+    XP_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
   }
 }
 

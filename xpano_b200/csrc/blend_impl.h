@@ -51,10 +51,9 @@ struct MaskLevel {
 
 // seams.cu
 void launch_trim(const void* data, int w, int h, int bpp, int* d_bbox,
-                 cudaStream_t s);
+                 unsigned long long* d_opaque_count, cudaStream_t s);
 void launch_cover(void* cover, int cover_bytes, int CW, const ImgDev& im,
-                  int bpp, int bit, unsigned long long* d_transparent,
-                  cudaStream_t s);
+                  int bpp, int bit, cudaStream_t s);
 void launch_seams(const void* cover, int cover_bytes, int W, int H,
                   int reverse, uint32_t* bwd, uint32_t* fwd, uint8_t* labels,
                   int* counter, uint8_t* flags, cudaStream_t s);

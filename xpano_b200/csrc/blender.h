@@ -18,6 +18,7 @@ struct StageTimer {
   struct Span {
     int stage;
     cudaEvent_t a, b;
+    cudaStream_t s;
   };
   std::vector<Span> spans;
   std::vector<cudaEvent_t> pool;
@@ -26,7 +27,7 @@ struct StageTimer {
   ~StageTimer();
   cudaEvent_t get();
   void reset(cudaStream_t stream);
-  int begin(int stage);
+  int begin(int stage, cudaStream_t on = nullptr);
   void end(int idx);
   void collect(double out[16]);
 };
@@ -34,6 +35,8 @@ struct StageTimer {
 struct Blender {
   xp_blend_opts opts;
   cudaStream_t stream = nullptr, own_stream = nullptr;
+  cudaStream_t side_stream = nullptr;  // inpaint runs beside the seam passes
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool external_stream = false;
   int roi[4] = {0, 0, 0, 0};
   std::vector<std::unique_ptr<Fed>> fed;
@@ -48,7 +51,7 @@ struct Blender {
   std::vector<unsigned long long> transparent;
   PyrGeom out_g;
   DevBuf d_bbox, d_transparent, d_imgs, d_stats, d_jobs, d_bands, d_counter,
-      d_progress, d_partials, d_sums;
+      d_progress, d_flags_inp, d_partials, d_sums;
   DevBuf cover, seam_bwd, seam_fwd, labels, full_mask, xor_mask;
   std::vector<DevBuf> inp_fwd, inp_bwd;  // per image (empty if no holes)
   DevBuf img_pyr, mask_buf, out_pyr, planes, bgr;

@@ -145,8 +145,9 @@ static void launch_wavefront(const P& prob, int* counter, uint8_t* flags,
 // result the exact bounding box of the opaque pixels)
 // ---------------------------------------------------------------------------
 template <int BPP>
-__global__ void trim_kernel(const void* data, int w, int h, int* bbox) {
-  int minx = INT_MAX, miny = INT_MAX, maxx = -1, maxy = -1;
+__global__ void trim_kernel(const void* data, int w, int h, int* bbox,
+                            unsigned long long* opaque_count) {
+  int minx = INT_MAX, miny = INT_MAX, maxx = -1, maxy = -1, cnt = 0;
   const size_t n = (size_t)w * h;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n;
        i += (size_t)gridDim.x * blockDim.x) {
@@ -156,9 +157,11 @@ __global__ void trim_kernel(const void* data, int w, int h, int* bbox) {
       maxx = max(maxx, x);
       miny = min(miny, y);
       maxy = max(maxy, y);
+      ++cnt;
     }
   }
   for (int o = 16; o > 0; o >>= 1) {
+    cnt += __shfl_xor_sync(~0u, cnt, o);
     minx = min(minx, __shfl_xor_sync(~0u, minx, o));
     miny = min(miny, __shfl_xor_sync(~0u, miny, o));
     maxx = max(maxx, __shfl_xor_sync(~0u, maxx, o));
@@ -169,31 +172,30 @@ __global__ void trim_kernel(const void* data, int w, int h, int* bbox) {
     atomicMin(bbox + 1, miny);
     atomicMax(bbox + 2, maxx);
     atomicMax(bbox + 3, maxy);
+    atomicAdd(opaque_count, (unsigned long long)cnt);
   }
 }
 
 void launch_trim(const void* data, int w, int h, int bpp, int* d_bbox,
-                 cudaStream_t s) {
+                 unsigned long long* d_opaque_count, cudaStream_t s) {
   const int blocks =
       (int)std::min<size_t>(div_up((size_t)w * h, (size_t)256), 148 * 8);
   if (bpp == 8)
-    trim_kernel<8><<<blocks, 256, 0, s>>>(data, w, h, d_bbox);
+    trim_kernel<8><<<blocks, 256, 0, s>>>(data, w, h, d_bbox, d_opaque_count);
   else
-    trim_kernel<16><<<blocks, 256, 0, s>>>(data, w, h, d_bbox);
+    trim_kernel<16><<<blocks, 256, 0, s>>>(data, w, h, d_bbox, d_opaque_count);
   XP_LAUNCHED();
 }
 
 // ---------------------------------------------------------------------------
 // cover map: bit i = image i opaque here; top bit = a run of the reference's
 // RLE walk starts here (bbox edges and opacity changes of any image,
-// multiblend.cpp:509-534). Also counts the image's non-opaque bbox pixels.
+// multiblend.cpp:509-534).
 // ---------------------------------------------------------------------------
 template <class C, int BPP>
-__global__ void cover_kernel(C* cover, int CW, ImgDev im, int bit,
-                             unsigned long long* transparent) {
+__global__ void cover_kernel(C* cover, int CW, ImgDev im, int bit) {
   const int lx = blockIdx.x * blockDim.x + threadIdx.x;
   const int ly = blockIdx.y * blockDim.y + threadIdx.y;
-  int holes = 0;
   if (lx <= im.w && ly < im.h) {
     const int cx = im.xpos + lx, cy = im.ypos + ly;
     if (cx < CW) {
@@ -204,25 +206,20 @@ __global__ void cover_kernel(C* cover, int CW, ImgDev im, int bit,
         if (op) add |= (C)1 << bit;
         if (lx == 0 || op != px_opaque<BPP>(im.data, p - 1))
           add |= CoverTraits<C>::rs_bit;
-        holes = op ? 0 : 1;
       } else {
         add |= CoverTraits<C>::rs_bit;
       }
       if (add) cover[(size_t)cy * CW + cx] |= add;
     }
   }
-  holes = __syncthreads_count(holes);
-  if (threadIdx.x == 0 && threadIdx.y == 0 && holes)
-    atomicAdd(transparent, (unsigned long long)holes);
 }
 
 void launch_cover(void* cover, int cover_bytes, int CW, const ImgDev& im,
-                  int bpp, int bit, unsigned long long* d_transparent,
-                  cudaStream_t s) {
+                  int bpp, int bit, cudaStream_t s) {
   dim3 b(32, 8);
   dim3 g(div_up(im.w + 1, 32), div_up(im.h, 8));
 #define XP_COVER(C, BPP)                                                  \
-  cover_kernel<C, BPP><<<g, b, 0, s>>>((C*)cover, CW, im, bit, d_transparent)
+  cover_kernel<C, BPP><<<g, b, 0, s>>>((C*)cover, CW, im, bit)
   if (cover_bytes == 4) {
     if (bpp == 8)
       XP_COVER(u32, 8);
