@@ -105,17 +105,63 @@ void launch_copy_level0(const ImgDev& im, int bpp, const u64* src_index,
 }
 
 // ---------------------------------------------------------------------------
-// shrink
+// shrink: four lo samples per thread. Away from the left/right borders the
+// eleven hi columns they need are read as aligned float4 (three, or four when
+// the level is x-shifted) from each of the form's rows; groups that touch a
+// border clamp per sample (pm::shrink_sample).
 // ---------------------------------------------------------------------------
-__global__ void shrink_kernel(const float* __restrict__ hi, int hh, int hp,
-                              int xs, int ys, float* __restrict__ lo, int lo_h,
-                              int lo_pitch, size_t chan_stride) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ float4 ldg4(const float* p) {
+  return __ldg(reinterpret_cast<const float4*>(p));
+}
+
+__global__ void __launch_bounds__(256)
+    shrink_kernel(const float* __restrict__ hi, int hh, int hp, int xs, int ys,
+                  float* __restrict__ lo, int lo_h, int lo_pitch,
+                  size_t chan_stride) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  if (j >= lo_pitch || y >= lo_h) return;
+  if (4 * i >= lo_pitch || y >= lo_h) return;
   const size_t co = (size_t)blockIdx.z * chan_stride;
-  lo[co + (size_t)y * lo_pitch + j] =
-      pm::shrink_sample(hi + co, hh, hp, xs, ys, lo_h, j, y);
+  const float* h = hi + co;
+  float out[4];
+  if (i >= 1 && 8 * i + 6 <= hp - 1) {
+    const pm::VForm f = pm::shrink_vform(hh, ys, lo_h, y);
+    // v[c] = vertical form at hi column 8i - 8 + c, c = 0..15
+    float v[16];
+    const int c0 = xs ? 0 : 1;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      if (c < c0) continue;
+      const float* col = h + 8 * i - 8 + 4 * c;
+      float4 r[5];
+      const int taps = f.kind == 3 ? 5 : (f.kind == 1 ? 3 : (f.kind == 0 ? 1 : 2));
+#pragma unroll
+      for (int k = 0; k < 5; ++k)
+        r[k] = k < taps ? ldg4(col + (size_t)f.r[k] * hp)
+                        : make_float4(0.f, 0.f, 0.f, 0.f);
+      v[4 * c + 0] = pm::shrink_vcombine(f.kind, r[0].x, r[1].x, r[2].x, r[3].x, r[4].x);
+      v[4 * c + 1] = pm::shrink_vcombine(f.kind, r[0].y, r[1].y, r[2].y, r[3].y, r[4].y);
+      v[4 * c + 2] = pm::shrink_vcombine(f.kind, r[0].z, r[1].z, r[2].z, r[3].z, r[4].z);
+      v[4 * c + 3] = pm::shrink_vcombine(f.kind, r[0].w, r[1].w, r[2].w, r[3].w, r[4].w);
+    }
+    // sample j = 4i + k reads hi columns 2j - 4 - xs + (0..4)
+    //   = 8i - 8 + (4 - xs + 2k) + (0..4)
+    const int base = 4 - xs;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float t[5];
+#pragma unroll
+      for (int m = 0; m < 5; ++m) t[m] = xs ? v[3 + 2 * k + m] : v[4 + 2 * k + m];
+      out[k] = pm::squeeze_combine(t, f.mul);
+    }
+    (void)base;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      out[k] = pm::shrink_sample(h, hh, hp, xs, ys, lo_h, 4 * i + k, y);
+  }
+  *reinterpret_cast<float4*>(lo + co + (size_t)y * lo_pitch + 4 * i) =
+      make_float4(out[0], out[1], out[2], out[3]);
 }
 
 void launch_shrink(const PyrGeom& g, float* pyr, int level, int channels,
@@ -123,24 +169,57 @@ void launch_shrink(const PyrGeom& g, float* pyr, int level, int channels,
   const LevelGeom& H = g.lv[level];
   const LevelGeom& L = g.lv[level + 1];
   dim3 b(32, 8);
-  shrink_kernel<<<grid3(L.pitch, L.h, channels, b), b, 0, s>>>(
+  shrink_kernel<<<grid3(L.pitch / 4, L.h, channels, b), b, 0, s>>>(
       pyr + H.offset, H.h, H.pitch, H.xs, H.ys, pyr + L.offset, L.h, L.pitch,
       g.channel_floats);
   XP_LAUNCHED();
 }
 
 // ---------------------------------------------------------------------------
-// laplace / collapse: hi <- expand(lo) - hi
+// laplace / collapse: hi <- expand(lo) - hi, four hi samples per thread
 // ---------------------------------------------------------------------------
-__global__ void laplace_kernel(float* __restrict__ hi, int hh, int hp, int xs,
-                               int ys, const float* __restrict__ lo,
-                               int lo_pitch, size_t chan_stride) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void expand_row4(const float* __restrict__ r, int i,
+                                            int xs, float e[4]) {
+  const float2 p = __ldg(reinterpret_cast<const float2*>(r + 2 * i));
+  const float2 q = __ldg(reinterpret_cast<const float2*>(r + 2 * i + 2));
+  const float a[5] = {p.x, p.y, q.x, q.y, __ldg(r + 2 * i + 4)};
+  pm::expand_h4(a, xs, e);
+}
+
+// expand(lo) at hi samples (4i .. 4i+3, y)
+__device__ __forceinline__ void expand4(const float* __restrict__ lo,
+                                        int lo_pitch, int xs, int ys, int i,
+                                        int y, float e[4]) {
+  if (2 * i + 4 < lo_pitch) {
+    const int t = y + ys;
+    const float* r1 = lo + (size_t)((t >> 1) + 1) * lo_pitch;
+    float e0[4] = {0.f, 0.f, 0.f, 0.f}, e1[4], e2[4];
+    expand_row4(r1, i, xs, e1);
+    expand_row4(r1 + lo_pitch, i, xs, e2);
+    const int even = (t & 1) == 0;
+    if (even) expand_row4(r1 - lo_pitch, i, xs, e0);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) e[k] = pm::expand_v(even, e0[k], e1[k], e2[k]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      e[k] = pm::expand_sample(lo, lo_pitch, xs, ys, 4 * i + k, y);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    laplace_kernel(float* __restrict__ hi, int hh, int hp, int xs, int ys,
+                   const float* __restrict__ lo, int lo_pitch,
+                   size_t chan_stride) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  if (x >= hp || y >= hh) return;
+  if (4 * i >= hp || y >= hh) return;
   const size_t co = (size_t)blockIdx.z * chan_stride;
-  const size_t o = co + (size_t)y * hp + x;
-  hi[o] = pm::expand_sample(lo + co, lo_pitch, xs, ys, x, y) - hi[o];
+  float e[4];
+  expand4(lo + co, lo_pitch, xs, ys, i, y, e);
+  float4* dst = reinterpret_cast<float4*>(hi + co + (size_t)y * hp + 4 * i);
+  const float4 h = *dst;
+  *dst = make_float4(e[0] - h.x, e[1] - h.y, e[2] - h.z, e[3] - h.w);
 }
 
 void launch_laplace(const PyrGeom& g, float* pyr, int level, int channels,
@@ -148,7 +227,7 @@ void launch_laplace(const PyrGeom& g, float* pyr, int level, int channels,
   const LevelGeom& H = g.lv[level];
   const LevelGeom& L = g.lv[level + 1];
   dim3 b(32, 8);
-  laplace_kernel<<<grid3(H.pitch, H.h, channels, b), b, 0, s>>>(
+  laplace_kernel<<<grid3(H.pitch / 4, H.h, channels, b), b, 0, s>>>(
       pyr + H.offset, H.h, H.pitch, H.xs, H.ys, pyr + L.offset, L.pitch,
       g.channel_floats);
   XP_LAUNCHED();

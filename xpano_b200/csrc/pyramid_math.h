@@ -145,6 +145,46 @@ XP_HD float expand_h(const float* lo, int lo_pitch, int x, int shifted) {
   return ((x & 3) == 1) ? a + (b + c) : (a + b) + c;
 }
 
+// expand_h for the four samples x = 4i .. 4i+3 at once, from a[k] = lo[2i+k],
+// k = 0..4 (no clamping: the caller guarantees 2i+4 < lo_pitch). Same
+// association as expand_h for each (x & 3).
+XP_HD void expand_h4(const float a[5], int shifted, float e[4]) {
+  if (!shifted) {
+    e[0] = (0.125f * a[0] + 0.75f * a[1]) + 0.125f * a[2];
+    e[1] = 0.5f * a[1] + 0.5f * a[2];
+    e[2] = 0.125f * a[1] + (0.75f * a[2] + 0.125f * a[3]);
+    e[3] = 0.5f * a[2] + 0.5f * a[3];
+  } else {
+    e[0] = 0.5f * a[1] + 0.5f * a[2];
+    e[1] = 0.125f * a[1] + (0.75f * a[2] + 0.125f * a[3]);
+    e[2] = 0.5f * a[2] + 0.5f * a[3];
+    e[3] = (0.125f * a[2] + 0.75f * a[3]) + 0.125f * a[4];
+  }
+}
+
+// vertical part of expand_sample: t = y + ys
+XP_HD float expand_v(int t_even, float e0, float e1, float e2) {
+  if (t_even) return (e0 + e2) * 0.125f + e1 * 0.75f;  // LaplaceLine3
+  return (e1 + e2) * 0.5f;                             // LaplaceLine2
+}
+
+// vertical form of Shrink on already loaded rows v[k] = hi[f.r[k]][col]
+XP_HD float shrink_vcombine(int kind, float v0, float v1, float v2, float v3,
+                            float v4) {
+  switch (kind) {
+    case 0:
+      return v0;
+    case 1:
+      return (v0 * 11.0f + v1 * 4.0f) + v2;
+    case 2:
+      return v0 * 15.0f + v1;
+    case 3:
+      return ((v0 + v4) + (v1 + v3) * 4.0f) + v2 * 6.0f;
+    default:
+      return v0 + v1 * 15.0f;
+  }
+}
+
 // expand(lo) at hi sample (x, y); hi level has shifts (xs, ys)
 XP_HD float expand_sample(const float* lo, int lo_pitch, int xs, int ys, int x,
                           int y) {
