@@ -235,6 +235,24 @@ def test_recorded_reference_outputs(case):
     assert d.max() <= 1 and (d > 0).mean() < 1e-4, (d.max(), (d > 0).mean())
 
 
+@pytest.mark.parametrize("case", CASES, ids=[str(c[0]) for c in CASES])
+def test_streaming_path_equals_staged_and_oracle(case):
+    """Without keep_debug the blender never materialises level 0 or the
+    Laplacian (pyramid_fused.cu); the result must be bit-identical to the
+    staged kernels and to the oracle's planes."""
+    seed, ckw, bkw = case
+    ims, pos = synth.blend_case(seed, **ckw)
+    staged = _gpu_blend(ims, pos, debug=True, **bkw)
+    stream = _gpu_blend(ims, pos, debug=False, **bkw)
+    ps, pf = staged.planes(), stream.planes()
+    assert np.array_equal(ps, pf), int(np.abs(ps.astype(int) - pf).max())
+    o = mb_oracle.blend(ims, pos, **bkw)
+    assert np.array_equal(pf, o.planes)
+    _, ms = staged.blend()
+    _, mf = stream.blend()
+    assert np.array_equal(ms, mf)
+
+
 def test_many_images_wide_cover():
     """More than 31 images switches the cover map to 64-bit words."""
     ims, pos = synth.blend_case(33, n=34, w=60, h=50, mode="ellipse")

@@ -102,6 +102,15 @@ void launch_out(const PyrGeom& g, const float* pyr, int W, int H, int out_bpp,
                 const double* d_sums, int in_bpp,
                 const uint8_t* full_mask, void* planes, void* bgr,
                 cudaStream_t s);
+// pyramid_fused.cu: streaming path (level 0 and the Laplacian stay virtual)
+void launch_inpaint_gather(const ImgDev& im, int bpp, const u64* src_index,
+                           cudaStream_t s);
+void launch_shrink0(const ImgDev& im, int bpp, float mul, const PyrGeom& g,
+                    float* pyr, cudaStream_t s);
+void launch_lapcomp(const ImgDev& im, int bpp, float mul, const PyrGeom& in_g,
+                    const float* in_pyr, const PyrGeom& out_g, float* out_pyr,
+                    int level, const uint8_t* labels, int image,
+                    const MaskLevel& m, const float* mask, cudaStream_t s);
 // debug helpers
 void launch_debug_collapsed(const PyrGeom& g, const float* pyr, int apply_add,
                             const CanvasStats* d_stats, const double* d_sums,

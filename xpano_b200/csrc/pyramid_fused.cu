@@ -1,0 +1,319 @@
+// Streaming form of the per-image pyramid work (SURVEY.md 8(d) byte model):
+//
+//   * level 0 of an image pyramid is never materialised as floats: the
+//     inpainted pixels stay in the interleaved source buffer (the inpaint
+//     result is gathered into it in place) and are converted on the fly;
+//   * the Laplacian is never materialised either: expand(lo) - hi is formed in
+//     registers and multiplied straight into the canvas pyramid, and only
+//     where the image's mask is non-zero.
+//
+// Same per-sample arithmetic, in the same order, as the staged kernels in
+// pyramid.cu (pyramid_math.h), which remain as the keep_debug path.
+// Replaces external/multiblend/src/pyramid.cpp Copy :233-408 + Shrink
+// :584-823 (first level), LaplaceCollapse :828-1038 + functions.cpp
+// CompositeLine :319-411 (all levels below the top).
+#include "blend_impl.h"
+#include "common.h"
+#include "pyramid_dev.h"
+#include "pyramid_math.h"
+
+namespace xp {
+
+// ---------------------------------------------------------------------------
+// virtual level 0: the trimmed, inpainted source pixels as floats
+// ---------------------------------------------------------------------------
+template <int BPP>
+struct Level0 {
+  typedef typename PixelOf<BPP>::type Px;
+  const Px* data;
+  int tiff_w, left, top, w, h;
+  float mul;
+  // raw pixel at level coordinates; columns past w replicate the last pixel
+  // (pyramid.cpp:268-330)
+  __device__ __forceinline__ Px px(int row, int col) const {
+    const int c = col < w ? col : w - 1;
+    return __ldg(data + ((size_t)(top + row) * tiff_w + left + c));
+  }
+  static __device__ __forceinline__ float chan(Px v, int c) {
+    if (BPP == 8) return (float)((u32)(v >> (8 * c)) & 0xffu);
+    return (float)((u32)((u64)v >> (16 * c)) & 0xffffu);
+  }
+  __device__ __forceinline__ float at(int c, int row, int col) const {
+    if (row >= h) return 0.0f;  // rows the staged path leaves zeroed
+    return chan(px(row, col), c) * mul;
+  }
+};
+
+template <int BPP>
+static Level0<BPP> make_level0(const ImgDev& im, float mul) {
+  return Level0<BPP>{static_cast<const typename PixelOf<BPP>::type*>(im.data),
+                     im.tiff_w, im.left, im.top, im.w, im.h, mul};
+}
+
+// ---------------------------------------------------------------------------
+// inpaint gather, in place: every non-opaque bbox pixel takes the colour of
+// its source (always an opaque pixel, never written here); alpha is kept so
+// the cover map, which may be read concurrently, is unaffected
+// ---------------------------------------------------------------------------
+template <int BPP>
+__global__ void inpaint_gather_kernel(ImgDev im, const u64* __restrict__ src) {
+  typedef typename PixelOf<BPP>::type Px;
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= im.w || y >= im.h) return;
+  Px* data = static_cast<Px*>(const_cast<void*>(im.data));
+  const size_t me = (size_t)(im.top + y) * im.tiff_w + im.left + x;
+  const Px mine = data[me];
+  if (pixel_opaque(mine)) return;
+  const u32 from = (u32)src[(size_t)y * im.w + x];
+  if (from == (u32)me) return;
+  const Px colour = data[from];
+  const int ab = BPP == 8 ? 24 : 48;
+  const Px amask = (Px)(BPP == 8 ? 0xffull : 0xffffull) << ab;
+  data[me] = (colour & ~amask) | (mine & amask);
+}
+
+void launch_inpaint_gather(const ImgDev& im, int bpp, const u64* src_index,
+                           cudaStream_t s) {
+  dim3 b(32, 8);
+  dim3 g(div_up(im.w, 32), div_up(im.h, 8));
+  if (bpp == 8)
+    inpaint_gather_kernel<8><<<g, b, 0, s>>>(im, src_index);
+  else
+    inpaint_gather_kernel<16><<<g, b, 0, s>>>(im, src_index);
+  XP_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// shrink level 0 -> 1 straight from the source pixels, 3 channels together,
+// four lo samples per thread
+// ---------------------------------------------------------------------------
+template <int BPP>
+__global__ void __launch_bounds__(256)
+    shrink0_kernel(Level0<BPP> L0, int hh, int hp, int xs, int ys,
+                   float* __restrict__ lo, int lo_h, int lo_pitch,
+                   size_t chan_stride) {
+  typedef typename PixelOf<BPP>::type Px;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (4 * i >= lo_pitch || y >= lo_h) return;
+  const pm::VForm f = pm::shrink_vform(hh, ys, lo_h, y);
+  float out[3][4];
+  // interior: no horizontal clamp, and every form row is a real image row
+  bool fast = i >= 1 && 8 * i + 6 <= hp - 1;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) fast = fast && f.r[k] < L0.h;
+  if (fast) {
+    const int taps =
+        f.kind == 3 ? 5 : (f.kind == 1 ? 3 : (f.kind == 0 ? 1 : 2));
+    // v[c][m] = vertical form of channel c at hi column 8i - 4 - xs + m
+    float v[3][11];
+    const int col0 = 8 * i - 4 - xs;
+#pragma unroll
+    for (int m = 0; m < 11; ++m) {
+      Px r[5];
+#pragma unroll
+      for (int k = 0; k < 5; ++k) r[k] = k < taps ? L0.px(f.r[k], col0 + m) : 0;
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        v[c][m] = pm::shrink_vcombine(
+            f.kind, L0.chan(r[0], c) * L0.mul, L0.chan(r[1], c) * L0.mul,
+            L0.chan(r[2], c) * L0.mul, L0.chan(r[3], c) * L0.mul,
+            L0.chan(r[4], c) * L0.mul);
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float t[5];
+#pragma unroll
+        for (int m = 0; m < 5; ++m) t[m] = v[c][2 * k + m];
+        out[c][k] = pm::squeeze_combine(t, f.mul);
+      }
+  } else {
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float t[5];
+#pragma unroll
+        for (int m = 0; m < 5; ++m) {
+          const int col = pm::squeeze_col(4 * i + k, m, hp, xs);
+          t[m] = pm::shrink_vcombine(f.kind, L0.at(c, f.r[0], col),
+                                     L0.at(c, f.r[1], col),
+                                     L0.at(c, f.r[2], col),
+                                     L0.at(c, f.r[3], col),
+                                     L0.at(c, f.r[4], col));
+        }
+        out[c][k] = pm::squeeze_combine(t, f.mul);
+      }
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+    *reinterpret_cast<float4*>(lo + c * chan_stride + (size_t)y * lo_pitch +
+                               4 * i) =
+        make_float4(out[c][0], out[c][1], out[c][2], out[c][3]);
+}
+
+void launch_shrink0(const ImgDev& im, int bpp, float mul, const PyrGeom& g,
+                    float* pyr, cudaStream_t s) {
+  const LevelGeom& H = g.lv[0];
+  const LevelGeom& L = g.lv[1];
+  dim3 b(32, 8);
+  dim3 gr(div_up(L.pitch / 4, 32), div_up(L.h, 8));
+  if (bpp == 8)
+    shrink0_kernel<8><<<gr, b, 0, s>>>(make_level0<8>(im, mul), H.h, H.pitch,
+                                       H.xs, H.ys, pyr + L.offset, L.h,
+                                       L.pitch, g.channel_floats);
+  else
+    shrink0_kernel<16><<<gr, b, 0, s>>>(make_level0<16>(im, mul), H.h, H.pitch,
+                                        H.xs, H.ys, pyr + L.offset, L.h,
+                                        L.pitch, g.channel_floats);
+  XP_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// fused Laplace + composite for one level below the top:
+//   out(X, Y) += (expand(lo) - hi)(clamp(X - x_off), clamp(Y - y_off)) * mask
+// over the mask rectangle, 3 channels together, four consecutive image
+// samples per thread. `Hi` is either a float level or the virtual level 0.
+// ---------------------------------------------------------------------------
+struct FloatLevel {
+  const float* p;  // channel 0 of the level
+  int pitch;
+  size_t cs;  // channel stride
+  __device__ __forceinline__ float at(int c, int row, int col) const {
+    return p[c * cs + (size_t)row * pitch + col];
+  }
+  // samples (row, 4g .. 4g+3) of all three channels
+  __device__ __forceinline__ void load4(int row, int g, float h[3][4]) const {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float4 v = *reinterpret_cast<const float4*>(
+          p + c * cs + (size_t)row * pitch + 4 * g);
+      h[c][0] = v.x, h[c][1] = v.y, h[c][2] = v.z, h[c][3] = v.w;
+    }
+  }
+};
+
+template <int BPP>
+struct PixelLevel : Level0<BPP> {
+  __device__ __forceinline__ void load4(int row, int g, float h[3][4]) const {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const typename Level0<BPP>::Px v = this->px(row, 4 * g + k);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) h[c][k] = this->chan(v, c) * this->mul;
+    }
+  }
+};
+
+__device__ __forceinline__ int floor_div4(int a) {
+  return a >= 0 ? a >> 2 : -((-a + 3) >> 2);
+}
+
+template <class Hi>
+__global__ void __launch_bounds__(256)
+    lapcomp_kernel(Hi hi, int in_w, int in_h, int xs, int ys,
+                   const float* __restrict__ lo, int lo_pitch, size_t in_cs,
+                   float* __restrict__ out, int out_pitch, size_t out_cs,
+                   int x_off, int y_off, MaskLevel m,
+                   const float* __restrict__ mask,
+                   const uint8_t* __restrict__ labels, int image) {
+  const int g = floor_div4(m.x0 - x_off) + blockIdx.x * blockDim.x + threadIdx.x;
+  const int Y = m.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  if (Y >= m.y0 + m.h) return;
+  const int X0 = 4 * g + x_off;
+  if (X0 >= m.x0 + m.w) return;
+  float mv[4];
+  bool any = false;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int X = X0 + k;
+    float v = 0.0f;
+    if (X >= m.x0 && X < m.x0 + m.w) {
+      if (labels)
+        v = labels[(size_t)Y * m.cw + X] == image ? 1.0f : 0.0f;
+      else
+        v = mask[(size_t)(Y - m.y0) * m.w + (X - m.x0)];
+    }
+    mv[k] = v;
+    any = any || v != 0.0f;
+  }
+  if (!any) return;  // functions.cpp:347-351 (skip)
+  const int iy = pm::clampi(Y - y_off, 0, in_h - 1);
+  float lap[3][4];
+  if (g >= 0 && 4 * g + 3 <= in_w - 1) {
+    float h[3][4];
+    hi.load4(iy, g, h);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      float e[4];
+      expand4(lo + c * in_cs, lo_pitch, xs, ys, g, iy, e);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) lap[c][k] = e[k] - h[c][k];
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int ix = pm::clampi(4 * g + k, 0, in_w - 1);
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        lap[c][k] = mv[k] != 0.0f
+                        ? pm::expand_sample(lo + c * in_cs, lo_pitch, xs, ys,
+                                            ix, iy) -
+                              hi.at(c, iy, ix)
+                        : 0.0f;
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    float* row = out + c * out_cs + (size_t)Y * out_pitch + X0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (mv[k] != 0.0f) row[k] = row[k] + lap[c][k] * mv[k];
+  }
+}
+
+void launch_lapcomp(const ImgDev& im, int bpp, float mul, const PyrGeom& in_g,
+                    const float* in_pyr, const PyrGeom& out_g, float* out_pyr,
+                    int level, const uint8_t* labels, int image,
+                    const MaskLevel& m, const float* mask, cudaStream_t s) {
+  if (m.w <= 0 || m.h <= 0) return;
+  const LevelGeom& I = in_g.lv[level];
+  const LevelGeom& Lo = in_g.lv[level + 1];
+  const LevelGeom& O = out_g.lv[level];
+  const int x_off = (I.x - O.x) >> level;
+  const int y_off = (I.y - O.y) >> level;
+  const int g0 = (m.x0 - x_off) >= 0 ? (m.x0 - x_off) >> 2
+                                     : -((-(m.x0 - x_off) + 3) >> 2);
+  const int last = m.x0 + m.w - 1 - x_off;
+  const int g1 = last >= 0 ? last >> 2 : -((-last + 3) >> 2);
+  dim3 b(32, 8);
+  dim3 gr(div_up(g1 - g0 + 1, 32), div_up(m.h, 8));
+  const float* lo = in_pyr + Lo.offset;
+  float* out = out_pyr + O.offset;
+  const float* mk = level == 0 ? nullptr : mask + m.offset;
+  const uint8_t* lb = level == 0 ? labels : nullptr;
+#define XP_LAPCOMP(HI)                                                       \
+  lapcomp_kernel<<<gr, b, 0, s>>>(HI, I.w, I.h, I.xs, I.ys, lo, Lo.pitch,    \
+                                  in_g.channel_floats, out, O.pitch,         \
+                                  out_g.channel_floats, x_off, y_off, m, mk, \
+                                  lb, image)
+  if (level > 0) {
+    FloatLevel hi{in_pyr + I.offset, I.pitch, in_g.channel_floats};
+    XP_LAPCOMP(hi);
+  } else if (bpp == 8) {
+    PixelLevel<8> hi;
+    static_cast<Level0<8>&>(hi) = make_level0<8>(im, mul);
+    XP_LAPCOMP(hi);
+  } else {
+    PixelLevel<16> hi;
+    static_cast<Level0<16>&>(hi) = make_level0<16>(im, mul);
+    XP_LAPCOMP(hi);
+  }
+#undef XP_LAPCOMP
+  XP_LAUNCHED();
+}
+
+}  // namespace xp
