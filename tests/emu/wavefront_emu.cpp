@@ -32,10 +32,23 @@ struct EmuWarp {
   uint64_t x[32];
 };
 
+struct EmuBlock {
+  std::barrier<> bar{32 * wf::kWarpsPerBand};
+  int slot = 0;
+  std::atomic<int> sig[wf::kSignals];
+  EmuWarp warps[wf::kWarpsPerBand];
+  EmuBlock() {
+    for (auto& s : sig) s.store(0);
+  }
+};
+
 struct EmuCtx {
+  EmuBlock* blk;
   EmuWarp* w;
-  int lane_;
+  int role_, lane_;
+  int seen[wf::kSignals] = {0, 0, 0, 0, 0, 0, 0, 0};
   int lane() const { return lane_; }
+  int role() const { return role_; }
   int atomic_add(int* p, int v) {
     return __atomic_fetch_add(p, v, __ATOMIC_ACQ_REL);
   }
@@ -46,7 +59,23 @@ struct EmuCtx {
     w->bar.arrive_and_wait();
     return r;
   }
-  int bcast(int v) { return (int)exchange((uint64_t)(uint32_t)v, 0); }
+  int block_bcast(int v) {
+    if (role_ == 0 && lane_ == 0) blk->slot = v;
+    blk->bar.arrive_and_wait();
+    const int r = blk->slot;
+    blk->bar.arrive_and_wait();
+    return r;
+  }
+  void block_sync() { blk->bar.arrive_and_wait(); }
+  void signal(int id) {
+    w->bar.arrive_and_wait();
+    if (lane_ == 0) blk->sig[id].fetch_add(1, std::memory_order_release);
+  }
+  void wait(int id) {
+    while (blk->sig[id].load(std::memory_order_acquire) <= seen[id])
+      std::this_thread::yield();
+    ++seen[id];
+  }
   template <class T>
   T shfl_up1(T v) {
     return (T)exchange((uint64_t)v, lane_ - 1);
@@ -73,45 +102,45 @@ struct EmuCtx {
     memcpy(dst, src, (size_t)bytes);
   }
   void cp_commit() {}
-  void cp_wait_all_but_one() {}
   void cp_wait_all() {}
 };
 
 template <class P>
-void run_emulated(const P& prob, int n_warps, int max_w) {
+void run_emulated(const P& prob, int n_blocks, int max_w) {
   if (prob.n_bands <= 0) return;
-  if (n_warps > prob.n_bands) n_warps = prob.n_bands;
+  if (n_blocks > prob.n_bands) n_blocks = prob.n_bands;
   int counter = 0;
   const int flag_pitch = wf::chunks_of(max_w);
   std::vector<uint8_t> flags((size_t)prob.n_bands * flag_pitch, 0);
-  std::vector<std::unique_ptr<EmuWarp>> warps;
-  std::vector<std::vector<unsigned char>> smem(n_warps);
-  for (int i = 0; i < n_warps; ++i) {
-    warps.emplace_back(new EmuWarp());
+  std::vector<std::unique_ptr<EmuBlock>> blocks;
+  std::vector<std::vector<unsigned char>> smem(n_blocks);
+  for (int i = 0; i < n_blocks; ++i) {
+    blocks.emplace_back(new EmuBlock());
     smem[i].resize(wf::tile_bytes<P>());
   }
-  // classification pass: warp wi takes tiles wi, wi + n_warps, ...
+  // classification pass: warp 0 of block bi takes tiles bi, bi + n_blocks, ...
   {
     std::vector<std::thread> threads;
-    for (int wi = 0; wi < n_warps; ++wi)
+    for (int bi = 0; bi < n_blocks; ++bi)
       for (int l = 0; l < 32; ++l)
-        threads.emplace_back([&, wi, l] {
-          EmuCtx ctx{warps[wi].get(), l};
+        threads.emplace_back([&, bi, l] {
+          EmuCtx ctx{blocks[bi].get(), &blocks[bi]->warps[0], 0, l};
           const size_t tiles = (size_t)prob.n_bands * flag_pitch;
-          for (size_t t = wi; t < tiles; t += n_warps)
+          for (size_t t = bi; t < tiles; t += n_blocks)
             wf::classify_tile(ctx, prob, (int)(t / flag_pitch),
                               (int)(t % flag_pitch), flags.data(), flag_pitch);
         });
     for (auto& t : threads) t.join();
   }
   std::vector<std::thread> threads;
-  for (int wi = 0; wi < n_warps; ++wi)
-    for (int l = 0; l < 32; ++l)
-      threads.emplace_back([&, wi, l] {
-        EmuCtx ctx{warps[wi].get(), l};
-        wf::run(ctx, prob, &counter, flags.data(), flag_pitch,
-                smem[wi].data());
-      });
+  for (int bi = 0; bi < n_blocks; ++bi)
+    for (int r = 0; r < wf::kWarpsPerBand; ++r)
+      for (int l = 0; l < 32; ++l)
+        threads.emplace_back([&, bi, r, l] {
+          EmuCtx ctx{blocks[bi].get(), &blocks[bi]->warps[r], r, l};
+          wf::run(ctx, prob, &counter, flags.data(), flag_pitch,
+                  smem[bi].data());
+        });
   for (auto& t : threads) t.join();
 }
 

@@ -42,6 +42,26 @@ namespace xp {
 // ---------------------------------------------------------------------------
 struct DevCtx {
   __device__ __forceinline__ int lane() const { return threadIdx.x & 31; }
+  __device__ __forceinline__ int role() const { return threadIdx.x >> 5; }
+  // whole-block operations (all three warps call them together)
+  __device__ __forceinline__ int block_bcast(int v) {
+    __shared__ int slot;
+    if (threadIdx.x == 0) slot = v;
+    __syncthreads();
+    const int r = slot;
+    __syncthreads();
+    return r;
+  }
+  __device__ __forceinline__ void block_sync() { __syncthreads(); }
+  // hand-over signals between two warps: named barriers 1..8, 64 threads;
+  // the signalling warp arrives without waiting, the waiting warp syncs
+  __device__ __forceinline__ void signal(int id) {
+    __syncwarp();
+    asm volatile("bar.arrive %0, 64;" ::"r"(id + 1) : "memory");
+  }
+  __device__ __forceinline__ void wait(int id) {
+    asm volatile("bar.sync %0, 64;" ::"r"(id + 1) : "memory");
+  }
   __device__ __forceinline__ int atomic_add(int* p, int v) {
     return atomicAdd(p, v);
   }
@@ -103,7 +123,7 @@ struct DevCtx {
 };
 
 template <class P>
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(32 * wf::kWarpsPerBand)
     wavefront_kernel(P prob, int* counter, const uint8_t* flags,
                      int flag_pitch) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -135,7 +155,8 @@ static void launch_wavefront(const P& prob, int* counter, uint8_t* flags,
   XP_LAUNCHED();
   const size_t smem = wf::tile_bytes<P>();
   const int blocks = std::min(prob.n_bands, 148 * 8);
-  wavefront_kernel<P><<<blocks, 32, smem, s>>>(prob, counter, flags,
+  wavefront_kernel<P><<<blocks, 32 * wf::kWarpsPerBand, smem, s>>>(
+      prob, counter, flags,
                                                flag_pitch);
   XP_LAUNCHED();
 }

@@ -8,7 +8,11 @@
 // previously processed row. Nothing about the recurrence is changed here;
 // only the order of evaluation:
 //
-//   * a warp owns a band of 32 consecutive rows, one row per lane;
+//   * a block of three warps owns a band of 32 consecutive rows: the compute
+//     warp carries the recurrence, one row per lane; a loader warp stages the
+//     inputs and a storer warp drains the outputs, so that only the steps
+//     themselves are on the critical path (hand-over through double-buffered
+//     shared tiles and named barriers);
 //   * lane j runs 2 pixels behind lane j-1, so at every step the value it needs
 //     from the row above was produced by its neighbour lane one step earlier
 //     and arrives by a single shuffle; its own-row predecessor is a register;
@@ -75,13 +79,18 @@ XP_HD int chunks_of(int W) {
   return (W + kSkew * (kLanes - 1) + kChunk - 1) / kChunk;
 }
 
-// Shared-memory bytes one warp needs for problem P: two buffers of each input
-// tile, one output tile and one row of hand-over values.
+constexpr int kWarpsPerBand = 3;  // compute, loader, storer
+enum Role { kCompute = 0, kLoader = 1, kStorer = 2 };
+// hand-over signals (one waiter, one signaller each), per buffer parity
+enum Signal { kInFull = 0, kInFree = 2, kOutFull = 4, kOutFree = 6, kSignals = 8 };
+
+// Shared-memory bytes one band (block) needs for problem P: two buffers of
+// each input tile and of the output tile, one row of hand-over values.
 template <class P>
 constexpr size_t tile_bytes() {
-  return (2 * (StreamBytes<typename P::In0>::value +
-               StreamBytes<typename P::In1>::value) +
-          sizeof(typename P::Val)) *
+  return 2 *
+             (StreamBytes<typename P::In0>::value +
+              StreamBytes<typename P::In1>::value + sizeof(typename P::Val)) *
              kTileElems +
          sizeof(typename P::Val) * kChunk;
 }
@@ -122,19 +131,21 @@ XP_HD void classify_tile(Ctx& ctx, const P& prob, int band_idx, int c,
 
 // Runs problem P over all its bands. `counter` is a zero-initialised claim
 // counter; `flags` comes from classify_tile over every tile of the problem.
+// Called by all three warps of a block with the same arguments.
 template <class Ctx, class P>
 XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
-               int flag_pitch, unsigned char* smem_warp) {
+               int flag_pitch, unsigned char* smem_block) {
   using In0 = typename P::In0;
   using In1 = typename P::In1;
   using Val = typename P::Val;
   constexpr size_t kB0 = StreamBytes<In0>::value;
   constexpr size_t kB1 = StreamBytes<In1>::value;
   const int lane = ctx.lane();
+  const int role = ctx.role();
   const Val kSentinel = prob.sentinel();
-  // layout: out tile | hand-over row | in0[2] | in1[2], widest type first
-  Val* out_tile = reinterpret_cast<Val*>(smem_warp);
-  Val* pv_row = out_tile + kTileElems;
+  // layout: out[2] | hand-over row | in0[2] | in1[2], widest type first
+  Val* out_base = reinterpret_cast<Val*>(smem_block);
+  Val* pv_row = out_base + 2 * kTileElems;
   unsigned char* base_a = reinterpret_cast<unsigned char*>(pv_row + kChunk);
   unsigned char* in0_base =
       kB0 >= kB1 ? base_a : base_a + 2 * kB1 * kTileElems;
@@ -143,159 +154,179 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
 
   for (;;) {
     int band_idx = 0;
-    if (lane == 0) band_idx = ctx.atomic_add(counter, 1);
-    band_idx = ctx.bcast(band_idx);
+    if (role == kCompute && lane == 0) band_idx = ctx.atomic_add(counter, 1);
+    band_idx = ctx.block_bcast(band_idx);
     if (band_idx >= prob.n_bands) break;
     const Band B = prob.band(band_idx);
     const int W = B.W;
-    const int rho = B.rho0 + lane;
-    const bool row_ok = rho < B.H;
-    typename P::Row row_state = prob.row_init(B, rho);
     const int n_chunks = chunks_of(W);
     const uint8_t* band_flags = flags + (size_t)band_idx * flag_pitch;
-
-    // stage the inputs of chunk c into buffer c & 1: row r, positions
-    // c*32 - 2r + lane
-    auto prefetch = [&](int c) {
-      const int s0 = c * kChunk;
-      In0* t0 = reinterpret_cast<In0*>(in0_base + (c & 1) * kB0 * kTileElems);
-      In1* t1 = reinterpret_cast<In1*>(in1_base + (c & 1) * kB1 * kTileElems);
-      for (int r = 0; r < kLanes; ++r) {
-        const int q = s0 - kSkew * r + lane;
-        if (B.rho0 + r < B.H && q >= 0 && q < W) {
-          ctx.cp_async(t0 + r * kTilePitch + lane,
-                       prob.in0_ptr(B, B.rho0 + r, q), (int)kB0);
-          if (kB1)
-            ctx.cp_async(t1 + r * kTilePitch + lane,
-                         prob.in1_ptr(B, B.rho0 + r, q), (int)kB1);
-        }
-      }
-      ctx.cp_commit();
-    };
-    // previous band's last row at position pos (lane-private), once final
-    auto poll = [&](bool want, int pos) -> Val {
-      const bool valid = want && pos >= 0 && pos < W;
-      const Val* p = prob.val_ptr(B, B.rho0 - 1, valid ? pos : 0);
-      Val v = 0;
-      for (;;) {
-        if (valid) v = ctx.ld_poll(p);
-        if (ctx.all(!valid || v != kSentinel)) break;
-        ctx.backoff();
-      }
-      return v;
-    };
-
-    Val last = 0, w0 = 0, w1 = 0, w2 = 0;
+    // every role walks the same sequence of unflagged chunks
     unsigned flag_word = 0;  // lane l: flag of chunk (c & ~31) + l
-    int staged = -1;         // chunk whose inputs were requested last
-    bool restore = true;     // lane state must be rebuilt from global memory
-    XP_WF_CLOCK_BEGIN();
-    int n_fast = 0, n_slow = 0;
-    for (int c = 0; c < n_chunks; ++c) {
-      const int s0 = c * kChunk;
-      XP_WF_CLOCK(7);
+    auto skip_chunk = [&](int c) -> bool {
       if ((c & 31) == 0)
         flag_word = c + lane < n_chunks ? band_flags[c + lane] : 0u;
-      // flags of this chunk and the next (the next may sit in the next word)
-      const bool skip = ctx.shfl_idx(flag_word, c & 31) != 0;
-#ifdef XP_WF_STATS
-      if (lane == 0) XP_WF_STATS(skip);
+      return ctx.shfl_idx(flag_word, c & 31) != 0;
+    };
+
+    if (role == kLoader) {
+      // ---- inputs of the k-th unflagged chunk -> buffer k & 1: row r,
+      // positions c*32 - 2r + lane ----
+      int k = 0;
+      for (int c = 0; c < n_chunks; ++c) {
+        if (skip_chunk(c)) continue;
+        if (k >= 2) ctx.wait(kInFree + (k & 1));
+        const int s0 = c * kChunk;
+        In0* t0 = reinterpret_cast<In0*>(in0_base + (k & 1) * kB0 * kTileElems);
+        In1* t1 = reinterpret_cast<In1*>(in1_base + (k & 1) * kB1 * kTileElems);
+#if defined(__CUDA_ARCH__)
+#pragma unroll 8
 #endif
-      n_fast += skip ? 1 : 0;
-      n_slow += skip ? 0 : 1;
-      if (skip) {
-        restore = true;
-        continue;
-      }
-      bool next_slow = false;
-      if (c + 1 < n_chunks) {
-        unsigned nf = ctx.shfl_idx(flag_word, (c + 1) & 31);
-        if (((c + 1) & 31) == 0) nf = band_flags[c + 1];
-        next_slow = nf == 0;
-      }
-      if (staged != c) prefetch(c);
-      if (next_slow) {
-        prefetch(c + 1);
-        staged = c + 1;
-      }
-      XP_WF_CLOCK(0);
-      if (restore) {
-        // state at the end of chunk c-1, all of whose pixels (rows of this
-        // band) were written by the classification pass
-        const int qe = s0 - 1 - kSkew * lane;
-        if (row_ok && qe >= 0 && qe < W) last = prob.load_val(B, rho, qe);
-        if (row_ok && lane > 0) {
-          if (qe >= 0 && qe < W) w1 = prob.load_val(B, rho - 1, qe);
-          if (qe + 1 >= 0 && qe + 1 < W) w2 = prob.load_val(B, rho - 1, qe + 1);
+        for (int r = 0; r < kLanes; ++r) {
+          const int q = s0 - kSkew * r + lane;
+          if (B.rho0 + r < B.H && q >= 0 && q < W) {
+            ctx.cp_async(t0 + r * kTilePitch + lane,
+                         prob.in0_ptr(B, B.rho0 + r, q), (int)kB0);
+            if (kB1)
+              ctx.cp_async(t1 + r * kTilePitch + lane,
+                           prob.in1_ptr(B, B.rho0 + r, q), (int)kB1);
+          }
         }
-        if (B.dep >= 0) {
-          // lane 0's row above belongs to the previous band: lanes 0/1 fetch
-          // positions s0-1 and s0
-          const Val pr = poll(lane < 2, s0 - 1 + lane);
-          const Val p0 = ctx.shfl_idx(pr, 0), p1 = ctx.shfl_idx(pr, 1);
-          if (lane == 0) w1 = p0, w2 = p1;
-        }
-        restore = false;
-      }
-      // previous band's last row, positions s0+1 .. s0+32 (one per lane)
-      Val pv = 0;
-      if (B.dep >= 0) pv = poll(true, s0 + 1 + lane);
-      XP_WF_CLOCK(1);
-      pv_row[lane] = pv;
-      if (next_slow)
-        ctx.cp_wait_all_but_one();
-      else
+        ctx.cp_commit();
         ctx.cp_wait_all();
-      ctx.sync();
-      XP_WF_CLOCK(2);
-      const In0* t0 =
-          reinterpret_cast<const In0*>(in0_base + (c & 1) * kB0 * kTileElems);
-      const In1* t1 =
-          reinterpret_cast<const In1*>(in1_base + (c & 1) * kB1 * kTileElems);
-      {
-        // ---- 32 skewed steps; everything but the chain through `last` and
-        // the shuffle is independent of the previous step ----
-        const In0* r0 = t0 + lane * kTilePitch;
-        const In1* r1 = t1 + lane * kTilePitch;
-        Val* ro = out_tile + lane * kTilePitch;
-        const int q0 = s0 - kSkew * lane;
+        ctx.signal(kInFull + (k & 1));
+        ++k;
+      }
+      // the compute warp frees every buffer; absorb the last two
+      for (int j = k < 2 ? 0 : k - 2; j < k; ++j) ctx.wait(kInFree + (j & 1));
+    } else if (role == kStorer) {
+      // ---- outputs of the k-th unflagged chunk, coalesced per row ----
+      int k = 0;
+      for (int c = 0; c < n_chunks; ++c) {
+        if (skip_chunk(c)) continue;
+        ctx.wait(kOutFull + (k & 1));
+        const int s0 = c * kChunk;
+        const Val* out_tile = out_base + (k & 1) * kTileElems;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 8
+#endif
+        for (int r = 0; r < kLanes; ++r) {
+          const int q = s0 - kSkew * r + lane;
+          if (B.rho0 + r < B.H && q >= 0 && q < W)
+            prob.store(B, B.rho0 + r, q, out_tile[r * kTilePitch + lane]);
+        }
+        ctx.signal(kOutFree + (k & 1));
+        ++k;
+      }
+    } else {
+      // ---- the recurrence ----
+      const int rho = B.rho0 + lane;
+      const bool row_ok = rho < B.H;
+      typename P::Row row_state = prob.row_init(B, rho);
+      // previous band's last row at position pos (lane-private), once final
+      auto poll = [&](bool want, int pos) -> Val {
+        const bool valid = want && pos >= 0 && pos < W;
+        const Val* p = prob.val_ptr(B, B.rho0 - 1, valid ? pos : 0);
+        Val v = 0;
+        for (;;) {
+          if (valid) v = ctx.ld_poll(p);
+          if (ctx.all(!valid || v != kSentinel)) break;
+          ctx.backoff();
+        }
+        return v;
+      };
+      Val last = 0, w0 = 0, w1 = 0, w2 = 0;
+      bool restore = true;  // lane state must be rebuilt from global memory
+      int k = 0;
+      XP_WF_CLOCK_BEGIN();
+      int n_fast = 0, n_slow = 0;
+      for (int c = 0; c < n_chunks; ++c) {
+        const int s0 = c * kChunk;
+        XP_WF_CLOCK(7);
+        const bool skip = skip_chunk(c);
+#ifdef XP_WF_STATS
+        if (lane == 0) XP_WF_STATS(skip);
+#endif
+        n_fast += skip ? 1 : 0;
+        n_slow += skip ? 0 : 1;
+        if (skip) {
+          restore = true;
+          continue;
+        }
+        if (restore) {
+          // state at the end of chunk c-1, all of whose pixels (rows of this
+          // band) were written by the classification pass
+          const int qe = s0 - 1 - kSkew * lane;
+          if (row_ok && qe >= 0 && qe < W) last = prob.load_val(B, rho, qe);
+          if (row_ok && lane > 0) {
+            if (qe >= 0 && qe < W) w1 = prob.load_val(B, rho - 1, qe);
+            if (qe + 1 >= 0 && qe + 1 < W)
+              w2 = prob.load_val(B, rho - 1, qe + 1);
+          }
+          if (B.dep >= 0) {
+            // lane 0's row above belongs to the previous band: lanes 0/1
+            // fetch positions s0-1 and s0
+            const Val pr = poll(lane < 2, s0 - 1 + lane);
+            const Val p0 = ctx.shfl_idx(pr, 0), p1 = ctx.shfl_idx(pr, 1);
+            if (lane == 0) w1 = p0, w2 = p1;
+          }
+          restore = false;
+        }
+        // previous band's last row, positions s0+1 .. s0+32 (one per lane)
+        Val pv = 0;
+        if (B.dep >= 0) pv = poll(true, s0 + 1 + lane);
+        XP_WF_CLOCK(1);
+        pv_row[lane] = pv;
+        ctx.sync();
+        ctx.wait(kInFull + (k & 1));
+        if (k >= 2) ctx.wait(kOutFree + (k & 1));
+        XP_WF_CLOCK(2);
+        {
+          // 32 skewed steps; everything but the chain through `last` and the
+          // shuffle is independent of the previous step
+          const In0* r0 = reinterpret_cast<const In0*>(
+                              in0_base + (k & 1) * kB0 * kTileElems) +
+                          lane * kTilePitch;
+          const In1* r1 = reinterpret_cast<const In1*>(
+                              in1_base + (k & 1) * kB1 * kTileElems) +
+                          lane * kTilePitch;
+          Val* ro = out_base + (k & 1) * kTileElems + lane * kTilePitch;
+          const int q0 = s0 - kSkew * lane;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-        for (int t = 0; t < kChunk; ++t) {
-          const int q = q0 + t;
-          const bool active = row_ok && q >= 0 && q < W;
-          const In0 a = r0[t];
-          In1 b = In1();
-          if (kB1) b = r1[t];
-          const Val hv = pv_row[t];
-          Val up = ctx.shfl_up1(last);
-          if (lane == 0) up = hv;
-          w0 = w1;
-          w1 = w2;
-          w2 = up;
-          const Val nv =
-              prob.step(B, row_state, active, rho, q, a, b, last, w0, w1, w2);
-          if (active) {
-            last = nv;
-            ro[t] = nv;
+          for (int t = 0; t < kChunk; ++t) {
+            const int q = q0 + t;
+            const bool active = row_ok && q >= 0 && q < W;
+            const In0 a = r0[t];
+            In1 b = In1();
+            if (kB1) b = r1[t];
+            const Val hv = pv_row[t];
+            Val up = ctx.shfl_up1(last);
+            if (lane == 0) up = hv;
+            w0 = w1;
+            w1 = w2;
+            w2 = up;
+            const Val nv = prob.step(B, row_state, active, rho, q, a, b, last,
+                                     w0, w1, w2);
+            if (active) {
+              last = nv;
+              ro[t] = nv;
+            }
           }
         }
+        XP_WF_CLOCK(4);
+        ctx.signal(kOutFull + (k & 1));
+        ctx.signal(kInFree + (k & 1));
+        ++k;
       }
-      ctx.sync();
-      XP_WF_CLOCK(4);
-      // ---- flush outputs, coalesced per row ----
-      for (int r = 0; r < kLanes; ++r) {
-        const int q = s0 - kSkew * r + lane;
-        if (B.rho0 + r < B.H && q >= 0 && q < W)
-          prob.store(B, B.rho0 + r, q, out_tile[r * kTilePitch + lane]);
-      }
-      ctx.sync();
-      XP_WF_CLOCK(5);
+      // the storer frees every output tile; absorb the last two
+      for (int j = k < 2 ? 0 : k - 2; j < k; ++j) ctx.wait(kOutFree + (j & 1));
+      (void)n_fast;
+      (void)n_slow;
+      XP_WF_CLOCK_END(band_idx, prob.n_bands, n_fast, n_slow);
     }
-    (void)n_fast;
-    (void)n_slow;
-    XP_WF_CLOCK_END(band_idx, prob.n_bands, n_fast, n_slow);
+    ctx.block_sync();  // tiles and signals are quiet before the next band
   }
 }
 
