@@ -3,9 +3,14 @@
 // panorama size cap (:318-335). Cameras, gain maps and low-resolution seam
 // masks are inputs (registration and seam estimation are outside the path).
 // Sources are uploaded once; warp -> feed -> blend stays on the device.
+#include <chrono>
 #include <climits>
+#include <cstdio>
+#include <cstdlib>
 #include <cmath>
 #include <memory>
+#include <string>
+#include <thread>
 
 #include "blender.h"
 #include "common.h"
@@ -123,9 +128,30 @@ struct Composer {
     const int n = (int)src.size();
     rois.resize(4 * n);
     long x0 = LONG_MAX, y0 = LONG_MAX, x1 = LONG_MIN, y1 = LONG_MIN;
+    // border-walk projections are pure host math (one forward map per
+    // perimeter pixel): one thread per image
+    const bool host_roi = warper.type == XP_PROJ_SPHERICAL ||
+                          warper.type == XP_PROJ_CYLINDRICAL;
+    if (host_roi && n > 1) {
+      std::vector<std::thread> pool;
+      std::vector<std::string> errs(n);
+      for (int i = 0; i < n; ++i)
+        pool.emplace_back([&, i] {
+          try {
+            warper.warp_roi(src[i]->w, src[i]->h, src[i]->K, src[i]->R,
+                            &rois[4 * i]);
+          } catch (const std::exception& e) {
+            errs[i] = e.what();
+          }
+        });
+      for (std::thread& t : pool) t.join();
+      for (int i = 0; i < n; ++i)
+        if (!errs[i].empty()) fail(XP_ERR_INVALID, "%s", errs[i].c_str());
+    }
     for (int i = 0; i < n; ++i) {
       int* r = &rois[4 * i];
-      warper.warp_roi(src[i]->w, src[i]->h, src[i]->K, src[i]->R, r);
+      if (!(host_roi && n > 1))
+        warper.warp_roi(src[i]->w, src[i]->h, src[i]->K, src[i]->R, r);
       x0 = std::min<long>(x0, r[0]);
       y0 = std::min<long>(y0, r[1]);
       x1 = std::max<long>(x1, (long)r[0] + r[2]);
@@ -139,6 +165,13 @@ struct Composer {
 
   void run(xp_compose_info* info) {
     XP_REQUIRE(!src.empty(), "run: set_images first");
+    const bool trace = getenv("XP_TRACE") != nullptr;
+    auto now = [] {
+      return std::chrono::duration<double, std::milli>(
+                 std::chrono::steady_clock::now().time_since_epoch())
+          .count();
+    };
+    const double h0 = now();
     ensure_device();
     float scale = opts.warp_scale;
     std::vector<int> rois;
@@ -152,6 +185,7 @@ struct Composer {
       compute_roi(scale, rois, rect);
       capped = true;
     }
+    const double h1 = now();
     xp_blend_opts bo = opts.blend;
     blender.reset(new Blender(bo));
     blender->stream = stream;
@@ -180,11 +214,17 @@ struct Composer {
       s_w += (double)r[2] * r[3];
     }
     XP_CUDA(cudaEventRecord(ev[1], stream));
+    const double h2 = now();
     xp_timing tm;
     memset(&tm, 0, sizeof(tm));
     blender->blend(&tm);
     XP_CUDA(cudaEventRecord(ev[2], stream));
     XP_CUDA(cudaStreamSynchronize(stream));
+    if (trace)
+      fprintf(stderr,
+              "trace host: roi %.3f ms, new blender + warp launches %.3f ms, "
+              "blend %.3f ms\n",
+              h1 - h0, h2 - h1, now() - h2);
     if (info) {
       memset(info, 0, sizeof(*info));
       float a = 0, b = 0;

@@ -169,16 +169,23 @@ template <int BPP>
 __global__ void trim_kernel(const void* data, int w, int h, int* bbox,
                             unsigned long long* opaque_count) {
   int minx = INT_MAX, miny = INT_MAX, maxx = -1, maxy = -1, cnt = 0;
-  const size_t n = (size_t)w * h;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n;
-       i += (size_t)gridDim.x * blockDim.x) {
-    if (px_opaque<BPP>(data, i)) {
-      const int x = (int)(i % w), y = (int)(i / w);
-      minx = min(minx, x);
-      maxx = max(maxx, x);
+  // a warp scans 32 consecutive x; rows are strided over the grid
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  for (int y = warp; y < h; y += warps) {
+    const size_t row = (size_t)y * w;
+    bool any = false;
+    for (int x = lane; x < w; x += 32)
+      if (px_opaque<BPP>(data, row + x)) {
+        minx = min(minx, x);
+        maxx = max(maxx, x);
+        ++cnt;
+        any = true;
+      }
+    if (any) {
       miny = min(miny, y);
       maxy = max(maxy, y);
-      ++cnt;
     }
   }
   for (int o = 16; o > 0; o >>= 1) {
@@ -188,7 +195,7 @@ __global__ void trim_kernel(const void* data, int w, int h, int* bbox,
     maxx = max(maxx, __shfl_xor_sync(~0u, maxx, o));
     maxy = max(maxy, __shfl_xor_sync(~0u, maxy, o));
   }
-  if ((threadIdx.x & 31) == 0 && maxx >= 0) {
+  if (lane == 0 && maxx >= 0) {
     atomicMin(bbox + 0, minx);
     atomicMin(bbox + 1, miny);
     atomicMax(bbox + 2, maxx);
@@ -199,8 +206,7 @@ __global__ void trim_kernel(const void* data, int w, int h, int* bbox,
 
 void launch_trim(const void* data, int w, int h, int bpp, int* d_bbox,
                  unsigned long long* d_opaque_count, cudaStream_t s) {
-  const int blocks =
-      (int)std::min<size_t>(div_up((size_t)w * h, (size_t)256), 148 * 8);
+  const int blocks = std::min(div_up(h, 8), 148 * 8);
   if (bpp == 8)
     trim_kernel<8><<<blocks, 256, 0, s>>>(data, w, h, d_bbox, d_opaque_count);
   else
@@ -344,7 +350,8 @@ __global__ void canvas_stats_kernel(const C* __restrict__ cover,
   __syncthreads();
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  unsigned long long sum[4] = {0, 0, 0, 0};
+  unsigned sum[4] = {0, 0, 0, 0};
+  int label = -1;
   if (x < W && y < H) {
     const size_t p = (size_t)y * W + x;
     const C bits = cover[p] & ~CoverTraits<C>::rs_bit;
@@ -369,18 +376,25 @@ __global__ void canvas_stats_kernel(const C* __restrict__ cover,
       }
       sum[3] = 1;
     }
-    if (n > 1) {
-      const int l = labels[p];
-      atomicMin(&s_box[l][0], x);
-      atomicMin(&s_box[l][1], y);
-      atomicMax(&s_box[l][2], x);
-      atomicMax(&s_box[l][3], y);
+    if (n > 1) label = labels[p];
+  }
+  // a warp is 32 consecutive x of one row: lanes with the same label elect
+  // one of them to extend that label's box
+  {
+    const unsigned peers = __match_any_sync(~0u, label);
+    const int lane = tid & 31;
+    if (label >= 0 && lane == __ffs(peers) - 1) {
+      const int xb = x - lane;
+      atomicMin(&s_box[label][0], xb + __ffs(peers) - 1);
+      atomicMin(&s_box[label][1], y);
+      atomicMax(&s_box[label][2], xb + 31 - __clz(peers));
+      atomicMax(&s_box[label][3], y);
     }
   }
   for (int k = 0; k < 4; ++k) {
-    unsigned long long v = sum[k];
+    unsigned v = sum[k];  // <= 32 * 65535
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(~0u, v, o);
-    if ((tid & 31) == 0 && v) atomicAdd(&s_sum[k], v);
+    if ((tid & 31) == 0 && v) atomicAdd(&s_sum[k], (unsigned long long)v);
   }
   __syncthreads();
   if (tid < 4 && s_sum[tid]) atomicAdd(&stats->totals[tid], s_sum[tid]);
