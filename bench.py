@@ -78,7 +78,7 @@ def make_image(w, h, seed, bpp=8):
 
 
 def make_workload(cfg, group):
-    import compose_oracle as co
+    from xpano_b200 import synthetic as co
     hfov = 2 * math.atan(cfg["w"] / 2 / cfg["focal"])
     Ks, Rs = co.make_cameras(cfg["n_cols"], cfg["n_rows"], cfg["w"], cfg["h"],
                              cfg["focal"], cfg["step"] * hfov, cfg["pitches"],
@@ -251,6 +251,11 @@ def ncu_traffic(workload):
         return None
 
 
+def sharding_group(world, rank):
+    from xpano_b200 import sharding
+    return sharding.assign_groups(world, world, rank)[0]
+
+
 def run_ours(args, cfg):
     import torch
     import torch.distributed as dist
@@ -267,7 +272,8 @@ def run_ours(args, cfg):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lib = xb._lib.load()
 
-    ims, Ks, Rs = make_workload(cfg, rank)
+    group = sharding_group(world, rank)
+    ims, Ks, Rs = make_workload(cfg, group)
     # host sources in pinned memory (e2e leg copies from here every step)
     pinned = []
     for im in ims:
@@ -288,19 +294,11 @@ def run_ours(args, cfg):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def max_over_ranks(v):
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(v):
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    # N > 1: one panorama group per rank and step (weak scaling), no
+    # data-path collective; only the counters below are reduced
+    from xpano_b200 import sharding
+    max_over_ranks = sharding.reduce_max
+    sum_over_ranks = sharding.reduce_sum
 
     # ---- resident leg ------------------------------------------------------
     comp.set_images(host, Ks, Rs)
