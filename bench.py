@@ -269,7 +269,21 @@ def run_ours(args, cfg):
                          "fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # NCCL announces its version on stdout at communicator creation;
+        # stdout carries exactly one JSON line, so park fd 1 on stderr until
+        # the first collective has run
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl",
+                                    device_id=torch.device("cuda", local))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     lib = xb._lib.load()
 
     group = sharding_group(world, rank)
