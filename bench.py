@@ -340,28 +340,69 @@ def run_ours(args, cfg):
     value = total_mp * args.steps / (ms / 1e3)
 
     # ---- e2e leg: host buffers in, host panorama out, every step -----------
+    # Batch export keeps two panoramas in flight (one composer, stream and
+    # pinned output buffer each, driven by two host threads through the
+    # synchronous public API), so the upload of one overlaps the kernels and
+    # the download of the other. Every step still uploads its own inputs and
+    # downloads its own result inside the timed region.
+    import threading
     W, H = info["width"], info["height"]
     dt = torch.uint8 if info["bpp"] == 8 else torch.uint16
-    pano = torch.empty((H, W, 3), dtype=dt, pin_memory=True)
-    mask = torch.empty((H, W), dtype=torch.uint8, pin_memory=True)
-    pano_np, mask_np = pano.numpy(), mask.numpy()
+    in_flight = 2
+    comps = [comp]
+    for _ in range(in_flight - 1):
+        c2 = xb.Composer(projection=cfg["projection"],
+                         warp_scale=cfg["focal"],
+                         max_pano_mpx=cfg["max_pano_mpx"], depth=cfg["bpp"],
+                         fixed_levels=cfg["fixed_levels"], device=local)
+        comps.append(c2)
+    outs = []
+    for _ in comps:
+        pano = torch.empty((H, W, 3), dtype=dt, pin_memory=True)
+        mask = torch.empty((H, W), dtype=torch.uint8, pin_memory=True)
+        outs.append((pano.numpy(), mask.numpy(), pano, mask))
     h2d = sum(im.nbytes for im in host)
-    d2h = pano_np.nbytes + mask_np.nbytes
-    e2e_steps = max(1, min(args.steps, 5))
-    for _ in range(min(args.warmup, 2)):
-        comp.set_images(host, Ks, Rs)
-        comp.run()
-        comp.fetch(pano_np, mask_np)
+    d2h = outs[0][0].nbytes + outs[0][1].nbytes
+    e2e_steps = min(max(args.steps, 2 * in_flight), 12)
+
+    # one panorama computes while the other uploads / downloads
+    compute_turn = threading.Lock()
+
+    def e2e_worker(j, n_steps, errs):
+        try:
+            torch.cuda.set_device(local)
+            for _ in range(j, n_steps, in_flight):
+                comps[j].set_images(host, Ks, Rs)
+                with compute_turn:
+                    comps[j].run()
+                comps[j].fetch(outs[j][0], outs[j][1])
+        except Exception as e:  # surfaced after join
+            errs.append(e)
+
+    def e2e_pass(n_steps):
+        errs = []
+        ts = [threading.Thread(target=e2e_worker, args=(j, n_steps, errs))
+              for j in range(in_flight)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        if errs:
+            raise errs[0]
+
+    e2e_pass(in_flight * min(args.warmup, 2))
     barrier()
     t0 = time.perf_counter()
     ev0.record()
-    for _ in range(e2e_steps):
-        comp.set_images(host, Ks, Rs)
-        comp.run()
-        comp.fetch(pano_np, mask_np)
+    e2e_pass(e2e_steps)
+    torch.cuda.synchronize()
     ev1.record()
     barrier()
     wall = time.perf_counter() - t0
+    for o in outs[1:]:  # same inputs: the in-flight panoramas must agree
+        if not (np.array_equal(o[0], outs[0][0]) and
+                np.array_equal(o[1], outs[0][1])):
+            raise SystemExit("bench.py: concurrent panoramas differ")
     e2e_ms = max_over_ranks(max(ev0.elapsed_time(ev1), 0.0))
     e2e_value = total_mp * e2e_steps / (e2e_ms / 1e3)
 
@@ -424,7 +465,8 @@ def run_ours(args, cfg):
                    "the 126 MB L2"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / e2e_steps,
-                "steps": e2e_steps, "wall_ms_per_step": 1e3 * wall / e2e_steps},
+                "steps": e2e_steps, "wall_ms_per_step": 1e3 * wall / e2e_steps,
+                "panoramas_in_flight": in_flight},
         "gpu_launches": int(launches), "clocks": clk, "roofline": roof,
         "stages": per_stage, "latency_bound_stages_ms": serial,
         "sizes_mp": {"s_src": info["s_src"] / 1e6, "s_w": info["s_w"] / 1e6,

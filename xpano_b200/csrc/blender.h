@@ -60,6 +60,7 @@ struct Blender {
   double stage_bytes[16] = {0};
   int stage_launches[16] = {0};
   StageTimer timer;
+  Mailbox mbox;
   // workload sizes (pixels)
   double s_t = 0, c_px = 0;
 

@@ -2,6 +2,9 @@
 
 #include <map>
 #include <mutex>
+#include <utility>
+#include <vector>
+#include <cstring>
 
 namespace xp {
 
@@ -37,6 +40,92 @@ Pool& pool() {
   return *p;
 }
 }  // namespace
+
+// ---------------------------------------------------------------------------
+// mailbox
+// ---------------------------------------------------------------------------
+namespace {
+struct MailboxCache {
+  std::mutex mu;
+  std::vector<std::pair<unsigned char*, size_t>> free_list;
+};
+MailboxCache& mailbox_cache() {
+  static MailboxCache* c = new MailboxCache();  // outlives static destructors
+  return *c;
+}
+__global__ void copy_words_kernel(uint32_t* __restrict__ dst,
+                                  const uint32_t* __restrict__ src, size_t n) {
+  for (size_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+}
+}  // namespace
+
+Mailbox::~Mailbox() {
+  if (!host) return;
+  MailboxCache& c = mailbox_cache();
+  std::lock_guard<std::mutex> lk(c.mu);
+  c.free_list.emplace_back(host, cap);
+}
+
+void Mailbox::reset(size_t need) {
+  need = (need + 4095) & ~(size_t)4095;
+  used = 0;
+  if (need <= cap) return;
+  MailboxCache& c = mailbox_cache();
+  {
+    std::lock_guard<std::mutex> lk(c.mu);
+    if (host) c.free_list.emplace_back(host, cap);
+    host = nullptr;
+    cap = 0;
+    for (size_t i = 0; i < c.free_list.size(); ++i)
+      if (c.free_list[i].second >= need) {
+        host = c.free_list[i].first;
+        cap = c.free_list[i].second;
+        c.free_list.erase(c.free_list.begin() + i);
+        break;
+      }
+  }
+  if (!host) {
+    void* p = nullptr;
+    XP_CUDA(cudaHostAlloc(&p, need, cudaHostAllocMapped | cudaHostAllocPortable));
+    host = static_cast<unsigned char*>(p);
+    cap = need;
+  }
+}
+
+void* Mailbox::take(size_t bytes) {
+  const size_t b = (bytes + 15) & ~(size_t)15;
+  XP_REQUIRE(used + b <= cap, "mailbox overflow (%zu + %zu > %zu)", used, b,
+             cap);
+  void* p = host + used;
+  used += b;
+  return p;
+}
+
+void Mailbox::to_device(void* dst, const void* src, size_t bytes,
+                        cudaStream_t s) {
+  if (!bytes) return;
+  XP_REQUIRE(bytes % 4 == 0, "mailbox transfers are whole words");
+  void* slot = take(bytes);
+  memcpy(slot, src, bytes);
+  void* dslot = nullptr;
+  XP_CUDA(cudaHostGetDevicePointer(&dslot, slot, 0));
+  copy_words_kernel<<<1, 256, 0, s>>>(static_cast<uint32_t*>(dst),
+                                      static_cast<const uint32_t*>(dslot),
+                                      bytes / 4);
+  XP_LAUNCHED();
+}
+
+void* Mailbox::to_host(const void* src, size_t bytes, cudaStream_t s) {
+  XP_REQUIRE(bytes % 4 == 0, "mailbox transfers are whole words");
+  void* slot = take(bytes);
+  void* dslot = nullptr;
+  XP_CUDA(cudaHostGetDevicePointer(&dslot, slot, 0));
+  copy_words_kernel<<<1, 256, 0, s>>>(static_cast<uint32_t*>(dslot),
+                                      static_cast<const uint32_t*>(src),
+                                      bytes / 4);
+  XP_LAUNCHED();
+  return slot;
+}
 
 void* pool_alloc(size_t n, size_t* got, int* device) {
   int dev = 0;

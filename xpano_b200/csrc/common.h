@@ -74,6 +74,25 @@ void* pool_alloc(size_t n, size_t* got, int* device);
 void pool_free(void* p, size_t bytes, int device);
 void pool_trim();
 
+// Small control transfers (bounding boxes, counters, job tables) bypass the
+// copy engines: with several panoramas in flight those queues hold bulk PCIe
+// uploads/downloads, and a 100-byte copy would wait milliseconds behind them.
+// The mailbox is pinned, mapped host memory; a one-block kernel moves the words.
+struct Mailbox {
+  unsigned char* host = nullptr;
+  size_t cap = 0, used = 0;
+  Mailbox() = default;
+  Mailbox(const Mailbox&) = delete;
+  Mailbox& operator=(const Mailbox&) = delete;
+  ~Mailbox();
+  void reset(size_t need);  // start a new round with room for `need` bytes
+  void* take(size_t bytes); // 16-byte aligned slot
+  // device <- host bytes (copied into a slot now, moved by a kernel on s)
+  void to_device(void* dst, const void* src, size_t bytes, cudaStream_t s);
+  // host slot <- device bytes; readable after s has been synchronised
+  void* to_host(const void* src, size_t bytes, cudaStream_t s);
+};
+
 struct DevBuf {
   void* p = nullptr;
   size_t bytes = 0;

@@ -409,19 +409,21 @@ __global__ void canvas_stats_kernel(const C* __restrict__ cover,
   }
 }
 
+__global__ void stats_init_kernel(CanvasStats* st) {
+  const int i = threadIdx.x;
+  if (i < 4) st->totals[i] = 0;
+  if (i == 0) st->uncovered = 0, st->pad = 0;
+  st->box[i][0] = st->box[i][1] = INT_MAX;
+  st->box[i][2] = st->box[i][3] = -1;
+}
+
 void launch_canvas_stats(const void* cover, int cover_bytes,
                          const uint8_t* labels, int W, int H,
                          const ImgDev* d_imgs, int n, int bpp,
                          uint8_t* full_mask, uint8_t* xor_mask,
                          CanvasStats* d_stats, cudaStream_t s) {
-  CanvasStats init;
-  memset(&init, 0, sizeof(init));
-  for (int i = 0; i < 64; ++i) {
-    init.box[i][0] = init.box[i][1] = INT_MAX;
-    init.box[i][2] = init.box[i][3] = -1;
-  }
-  XP_CUDA(cudaMemcpyAsync(d_stats, &init, sizeof(init), cudaMemcpyHostToDevice,
-                          s));
+  stats_init_kernel<<<1, 64, 0, s>>>(d_stats);
+  XP_LAUNCHED();
   dim3 b(32, 8);
   dim3 g(div_up(W, 32), div_up(H, 8));
 #define XP_STATS(C, BPP)                                                    \
