@@ -168,20 +168,24 @@ void build_cover(std::vector<C>& cover, int CW, int CH, int n, const int* xpos,
       }
 }
 
-template <class C>
+template <class C, int F>
 void seams_t(int n, const int* xpos, const int* ypos, const int* w,
              const int* h, const uint8_t* const* opaque, int W, int H,
              int reverse, int32_t* labels, uint64_t* bwd, uint64_t* fwd,
              int n_warps) {
   std::vector<C> cover;
   build_cover(cover, W, H, n, xpos, ypos, w, h, opaque);
+  if (F == kCoverDigest)  // mirrors cover_kernel's digest output
+    for (C& c : cover)
+      c = (C)make_digest((u32)(c & ~CoverTraits<C>::rs_bit),
+                         (c & CoverTraits<C>::rs_bit) != 0, reverse);
   std::vector<uint8_t> lab8((size_t)W * H);
   std::vector<u32> b32((size_t)W * H), f32((size_t)W * H);
   const int n_bands = (H + 31) / 32;
-  SeamBwd<C> pb{n_bands, W, H, cover.data(), b32.data()};
+  SeamBwd<C, F> pb{n_bands, W, H, cover.data(), b32.data()};
   run_emulated(pb, n_warps, W);
-  SeamFwd<C> pf{n_bands, W,          H,          reverse,
-                cover.data(), b32.data(), f32.data(), lab8.data()};
+  SeamFwd<C, F> pf{n_bands, W,          H,          reverse,
+                   cover.data(), b32.data(), f32.data(), lab8.data()};
   run_emulated(pf, n_warps, W);
   for (size_t i = 0; i < lab8.size(); ++i) {
     labels[i] = lab8[i];
@@ -204,12 +208,17 @@ void emu_seams(int n, const int* xpos, const int* ypos, const int* w,
                const int* h, const uint8_t* const* opaque, int W, int H,
                int reverse, int wide, int32_t* labels, uint64_t* bwd,
                uint64_t* fwd, int n_warps) {
-  if (wide)
-    seams_t<u64>(n, xpos, ypos, w, h, opaque, W, H, reverse, labels, bwd, fwd,
-                 n_warps);
+  // wide: 0 = u32 digest words (the product's choice up to 24 images),
+  //       1 = u64 bit words, 2 = u32 bit words (25..31 images)
+  if (wide == 1)
+    seams_t<u64, kCoverBits>(n, xpos, ypos, w, h, opaque, W, H, reverse,
+                             labels, bwd, fwd, n_warps);
+  else if (wide == 2)
+    seams_t<u32, kCoverBits>(n, xpos, ypos, w, h, opaque, W, H, reverse,
+                             labels, bwd, fwd, n_warps);
   else
-    seams_t<u32>(n, xpos, ypos, w, h, opaque, W, H, reverse, labels, bwd, fwd,
-                 n_warps);
+    seams_t<u32, kCoverDigest>(n, xpos, ypos, w, h, opaque, W, H, reverse,
+                               labels, bwd, fwd, n_warps);
 }
 
 // Inpaints n images at once (the band table interleaves them like the

@@ -78,6 +78,8 @@ def _emu_seams(lib, ops, tpos, W, H, reverse, wide, n_warps):
     (3, 4, "ellipse", 1, 1, 2),
     (4, 3, "full", 0, 0, 1),
     (5, 5, "blobs", 1, 0, 4),
+    (6, 4, "blobs", 0, 2, 2),
+    (7, 3, "ellipse", 1, 2, 3),
 ])
 def test_emulated_seams_match_oracle(emu, seed, n, mode, reverse, wide,
                                      n_warps):

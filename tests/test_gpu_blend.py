@@ -253,9 +253,11 @@ def test_streaming_path_equals_staged_and_oracle(case):
     assert np.array_equal(ms, mf)
 
 
-def test_many_images_wide_cover():
-    """More than 31 images switches the cover map to 64-bit words."""
-    ims, pos = synth.blend_case(33, n=34, w=60, h=50, mode="ellipse")
+@pytest.mark.parametrize("n", [34, 28])
+def test_many_images_wide_cover(n):
+    """More than 31 images switches the cover map to 64-bit words; 25..31 use
+    32-bit bit words instead of the digest form (scan_problems.h Cov<>)."""
+    ims, pos = synth.blend_case(33, n=n, w=60, h=50, mode="ellipse")
     o = mb_oracle.blend(ims, pos, fixed_levels=3, debug=True)
     b = _gpu_blend(ims, pos, debug=True, fixed_levels=3)
     _diff("labels", b.debug("labels"), o.labels)

@@ -52,10 +52,13 @@ struct MaskLevel {
 // seams.cu
 void launch_trim(const void* data, int w, int h, int bpp, int* d_bbox,
                  unsigned long long* d_opaque_count, cudaStream_t s);
-void launch_cover(void* cover, int cover_bytes, int CW, const ImgDev& im,
-                  int bpp, int bit, cudaStream_t s);
-void launch_seams(const void* cover, int cover_bytes, int W, int H,
-                  int reverse, uint32_t* bwd, uint32_t* fwd, uint8_t* labels,
+// cover word of every canvas pixel in one pass (format chosen by n, see
+// scan_problems.h Cov<>)
+void launch_cover(void* cover, int cover_bytes, int W, int H,
+                  const ImgDev* d_imgs, int n, int bpp, int reverse,
+                  cudaStream_t s);
+void launch_seams(const void* cover, int cover_bytes, int n_images, int W,
+                  int H, int reverse, uint32_t* bwd, uint32_t* fwd, uint8_t* labels,
                   int* counter, uint8_t* flags, cudaStream_t s);
 // bytes of tile flags launch_seams / launch_inpaint need
 size_t wavefront_flag_bytes(int n_bands, int max_w);

@@ -116,14 +116,53 @@ XP_HD u32 mask32(u32 v, C bits) {
 }
 XP_HD u32 min32(u32 a, u32 b) { return a < b ? a : b; }
 
+// Two encodings of the per-pixel cover word.
+//  kCoverBits  : bit i = image i opaque, top bit = run start (u32: <= 31
+//                images, u64: <= 63).
+//  kCoverDigest: u32, <= 24 images; what a step would otherwise recompute
+//                for every pixel is stored ready-made:
+//                [23:0] bits, [28:24] image an arbitrary seam picks (lowest,
+//                or highest with `reverse`), [29] run start, [30] exactly one
+//                image covers, [31] some image covers.
+enum { kCoverBits = 0, kCoverDigest = 1 };
+constexpr int kDigestMaxImages = 24;
+
+template <class C, int F>
+struct Cov {
+  static XP_HD C bits(C c) { return c & ~CoverTraits<C>::rs_bit; }
+  static XP_HD bool rs(C c) { return (c & CoverTraits<C>::rs_bit) != 0; }
+  static XP_HD bool seed(C c) { return popc_c(bits(c)) == 1; }
+  static XP_HD bool any(C c) { return bits(c) != 0; }
+  static XP_HD int low(C c) { return ctz_c((C)(c | CoverTraits<C>::rs_bit)); }
+  static XP_HD int pick(C c, int reverse) {
+    return reverse ? clz_top((C)(bits(c) | 1)) : low(c);
+  }
+};
+template <>
+struct Cov<u32, kCoverDigest> {
+  static XP_HD u32 bits(u32 c) { return c & 0xffffffu; }
+  static XP_HD bool rs(u32 c) { return (c & (1u << 29)) != 0; }
+  static XP_HD bool seed(u32 c) { return (c & (1u << 30)) != 0; }
+  static XP_HD bool any(u32 c) { return (c >> 31) != 0; }
+  static XP_HD int low(u32 c) { return (int)((c >> 24) & 31u); }
+  static XP_HD int pick(u32 c, int) { return (int)((c >> 24) & 31u); }
+};
+XP_HD u32 make_digest(u32 bits, bool run_start, int reverse) {
+  const int cnt = popc_c(bits);
+  const int pick = bits ? (reverse ? clz_top(bits) : ctz_c(bits)) : 0;
+  return bits | ((u32)pick << 24) | (run_start ? 1u << 29 : 0u) |
+         (cnt == 1 ? 1u << 30 : 0u) | (cnt != 0 ? 1u << 31 : 0u);
+}
+
 struct NoRow {};
 
 // ---------------------------------------------------------------------------
 // Seams, backward pass: rows bottom -> top, x right -> left.
 // Processing coordinates: q = W-1-x, rho = H-1-y.
 // ---------------------------------------------------------------------------
-template <class C>
+template <class C, int F = kCoverBits>
 struct SeamBwd {
+  typedef Cov<C, F> Cv;
   typedef u32 Val;
   typedef C In0;
   typedef wf::NoInput In1;
@@ -158,31 +197,34 @@ struct SeamBwd {
   // chunks made of seeds only skip the recurrence; not on the bottom band,
   // whose first row carries the first_run state
   XP_HD bool allow_trivial(const wf::Band& B) const { return B.rho0 != 0; }
-  XP_HD bool trivial(C cov, In1) const {
-    return popc_c((C)(cov & ~CoverTraits<C>::rs_bit)) == 1;
-  }
+  XP_HD bool trivial(C cov, In1) const { return Cv::seed(cov); }
   XP_HD u32 trivial_value(const wf::Band&, const Row&, int, int, C cov,
                           In1) const {
-    return (u32)ctz_c((C)(cov | CoverTraits<C>::rs_bit));
+    return (u32)Cv::low(cov);
   }
-  // last = (x+1, y); w0 = (x+1, y+1); w1 = (x, y+1); w2 = (x-1, y+1)
+  // last = (x+1, y); w0 = (x+1, y+1); w1 = (x, y+1); w2 = (x-1, y+1).
+  // kEdge = false: the caller guarantees rho > 0 and 0 < q < W-1.
+  template <bool kEdge>
   XP_HD u32 step(const wf::Band&, Row& row, bool active, int rho, int q, C cov,
                  In1, u32 last, u32 w0, u32 w1, u32 w2) const {
-    const C bits = cov & ~CoverTraits<C>::rs_bit;
-    const bool was_first = row.first_run;
-    if (active && (cov & CoverTraits<C>::rs_bit)) row.first_run = false;
-    // bottom row :333-346
-    const u32 bottom = was_first ? kDtMax32 : mask32(last, bits) + kD3;
+    const C bits = Cv::bits(cov);
     u32 cl = mask32(last + kD3, bits);
     u32 c0 = mask32(w0 + kD4, bits);
     const u32 c1 = mask32(w1 + kD3, bits);
     u32 c2 = mask32(w2 + kD4, bits);
-    if (q <= 0) cl = kInf32, c0 = kInf32;
-    if (q >= W - 1) c2 = kInf32;
+    if (kEdge) {
+      if (q <= 0) cl = kInf32, c0 = kInf32;
+      if (q >= W - 1) c2 = kInf32;
+    }
     u32 d = min32(min32(cl, c0), min32(c1, c2));
-    if (rho == 0) d = bottom;
-    if (popc_c(bits) == 1)  // :327-331
-      d = (u32)ctz_c((C)(cov | CoverTraits<C>::rs_bit));
+    if (kEdge) {
+      const bool was_first = row.first_run;
+      if (active && Cv::rs(cov)) row.first_run = false;
+      // bottom row :333-346
+      const u32 bottom = was_first ? kDtMax32 : mask32(last, bits) + kD3;
+      if (rho == 0) d = bottom;
+    }
+    if (Cv::seed(cov)) d = (u32)Cv::low(cov);  // :327-331
     return d;
   }
 };
@@ -190,8 +232,9 @@ struct SeamBwd {
 // ---------------------------------------------------------------------------
 // Seams, forward pass: rows top -> bottom, x left -> right. q = x, rho = y.
 // ---------------------------------------------------------------------------
-template <class C>
+template <class C, int F = kCoverBits>
 struct SeamFwd {
+  typedef Cov<C, F> Cv;
   typedef u32 Val;
   typedef u32 In0;  // packed backward value of this pixel
   typedef C In1;    // cover word
@@ -225,19 +268,17 @@ struct SeamFwd {
     labels[p] = (uint8_t)(v & 0xffu);
   }
   XP_HD bool allow_trivial(const wf::Band&) const { return true; }
-  XP_HD bool trivial(u32, C cov) const {
-    return popc_c((C)(cov & ~CoverTraits<C>::rs_bit)) == 1;
-  }
+  XP_HD bool trivial(u32, C cov) const { return Cv::seed(cov); }
   XP_HD u32 trivial_value(const wf::Band&, const Row&, int, int, u32,
                           C cov) const {
-    return (u32)ctz_c((C)(cov | CoverTraits<C>::rs_bit));
+    return (u32)Cv::low(cov);
   }
-  // last = (x-1, y); w0 = (x-1, y-1); w1 = (x, y-1); w2 = (x+1, y-1)
+  // last = (x-1, y); w0 = (x-1, y-1); w1 = (x, y-1); w2 = (x+1, y-1).
+  // kEdge = false: the caller guarantees y > 0 and 1 < x < W-1.
+  template <bool kEdge>
   XP_HD u32 step(const wf::Band&, Row&, bool, int y, int x, u32 bw, C cov,
                  u32 last, u32 w0, u32 w1, u32 w2) const {
-    const C bits = cov & ~CoverTraits<C>::rs_bit;
-    const bool rs = (cov & CoverTraits<C>::rs_bit) != 0;
-    const int cnt = popc_c(bits);
+    const C bits = Cv::bits(cov);
     u32 c0 = mask32(w0 + kD4, bits);
     u32 c1 = mask32(w1 + kD3, bits);
     u32 c2 = mask32(w2 + kD4, bits);
@@ -245,18 +286,18 @@ struct SeamFwd {
     // a run start (:629-630, :704-705); raw inside a run (:750)
     u32 cl = last + kD3;
     const u32 clm = mask32(cl, bits);
-    if (y == 0 || x == 1 || rs) cl = clm;
-    if (x <= 0) cl = kInf32;
-    if (y == 0 || x <= 0) c0 = kInf32;
-    if (y == 0) c1 = kInf32;
-    if (y == 0 || x >= W - 1) c2 = kInf32;
+    if (Cv::rs(cov) || (kEdge && (y == 0 || x == 1))) cl = clm;
+    if (kEdge) {
+      if (x <= 0) cl = kInf32;
+      if (y == 0 || x <= 0) c0 = kInf32;
+      if (y == 0) c1 = kInf32;
+      if (y == 0 || x >= W - 1) c2 = kInf32;
+    }
     // ReadSeamDT value enters unmasked
     u32 best = min32(min32(min32(bw, c0), min32(c1, c2)), cl);
-    const int low = ctz_c((C)(cov | CoverTraits<C>::rs_bit));
-    const int pick = reverse ? clz_top((C)(bits | 1)) : low;
-    if ((best & kTop32) && cnt != 0)  // arbitrary seam :732-742
-      best = kTop32 | (u32)pick;
-    if (cnt == 1) best = (u32)low;  // :607-616
+    if ((best & kTop32) && Cv::any(cov))  // arbitrary seam :732-742
+      best = kTop32 | (u32)Cv::pick(cov, reverse);
+    if (Cv::seed(cov)) best = (u32)Cv::low(cov);  // :607-616
     return best;
   }
 };
@@ -346,21 +387,25 @@ struct InpaintFwd {
                           In0, In1) const {
     return (u64)(row.base + (u32)(dy * jobs[B.job].tiff_w) + (u32)x);
   }
-  // last = (x-1, y); w0 = (x-1, y-1); w1 = (x, y-1); w2 = (x+1, y-1)
+  // last = (x-1, y); w0 = (x-1, y-1); w1 = (x, y-1); w2 = (x+1, y-1).
+  // kEdge = false: the caller guarantees y > 0 and 0 < x < W-1.
+  template <bool kEdge>
   XP_HD u64 step(const wf::Band& B, Row& row, bool, int y, int x, In0 px, In1,
                  u64 last, u64 w0, u64 w1, u64 w2) const {
     const u32 me = row.base + (u32)x;
     // own row :573-583 / :609-641; the very first pixel seeds 0x80000000
     u32 d = hi32(last) + 3, s = lo32(last);
-    if (x == 0) d = y == 0 ? 0x80000000u : kInf32, s = me;
     u32 a = hi32(w0) + 4, b = hi32(w1) + 3, c = hi32(w2) + 4;
-    if (y == 0 || x == 0) a = kInf32;
-    if (y == 0) b = kInf32;
-    if (y == 0 || x >= B.W - 1) c = kInf32;
+    if (kEdge) {
+      if (x == 0) d = y == 0 ? 0x80000000u : kInf32, s = me;
+      if (y == 0 || x == 0) a = kInf32;
+      if (y == 0) b = kInf32;
+      if (y == 0 || x >= B.W - 1) c = kInf32;
+    }
     if (a < d) d = a, s = lo32(w0);
     if (b < d) d = b, s = lo32(w1);
     // in column 0 a tie between up and up-right goes to up-right (:585-603)
-    if (c < d || (x == 0 && c == d)) d = c, s = lo32(w2);
+    if (c < d || (kEdge && x == 0 && c == d)) d = c, s = lo32(w2);
     if (pixel_opaque(px)) d = 0, s = me;  // :659-662
     return d32(d) | s;
   }
@@ -405,19 +450,25 @@ struct InpaintBwd {
                           In1) const {
     return fwd;
   }
-  // last = (x+1, y); w0 = (x+1, y+1); w1 = (x, y+1); w2 = (x-1, y+1)
+  // last = (x+1, y); w0 = (x+1, y+1); w1 = (x, y+1); w2 = (x-1, y+1).
+  // kEdge = false: the caller guarantees rho > 0 and 0 < q < W-1.
+  template <bool kEdge>
   XP_HD u64 step(const wf::Band& B, Row&, bool, int rho, int q, u64 fwd, In1,
                  u64 last, u64 w0, u64 w1, u64 w2) const {
     u32 best = hi32(fwd), src = lo32(fwd);
     const bool opaque = best == 0;  // cur = 0, d = 3
-    const bool bottom = rho == 0;   // last line :711-747: right neighbour only
     // at the row start the reference seeds the running distance with
     // 0x80000000 (nothing on the last line)
-    u32 a = q < B.W - 1 ? hi32(w2) + 4 : 0x80000000u;  // x-1
+    u32 a = hi32(w2) + 4;  // x-1
     u32 b = hi32(w1) + 3;
-    u32 c = q > 0 ? hi32(w0) + 4 : 0x80000000u;        // x+1
-    u32 d = q > 0 ? hi32(last) + 3 : (bottom ? kInf32 : 0x80000000u);
-    if (bottom) a = kInf32, b = kInf32, c = kInf32;
+    u32 c = hi32(w0) + 4;  // x+1
+    u32 d = hi32(last) + 3;
+    if (kEdge) {
+      const bool bottom = rho == 0;  // last line :711-747: right neighbour only
+      if (q >= B.W - 1) a = 0x80000000u;
+      if (q <= 0) c = 0x80000000u, d = bottom ? kInf32 : 0x80000000u;
+      if (bottom) a = kInf32, b = kInf32, c = kInf32;
+    }
     if (a < best) best = a, src = lo32(w2);
     if (b < best) best = b, src = lo32(w1);
     if (c < best) best = c, src = lo32(w0);

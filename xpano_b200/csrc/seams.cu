@@ -219,44 +219,72 @@ void launch_trim(const void* data, int w, int h, int bpp, int* d_bbox,
 // RLE walk starts here (bbox edges and opacity changes of any image,
 // multiblend.cpp:509-534).
 // ---------------------------------------------------------------------------
-template <class C, int BPP>
-__global__ void cover_kernel(C* cover, int CW, ImgDev im, int bit) {
-  const int lx = blockIdx.x * blockDim.x + threadIdx.x;
-  const int ly = blockIdx.y * blockDim.y + threadIdx.y;
-  if (lx <= im.w && ly < im.h) {
-    const int cx = im.xpos + lx, cy = im.ypos + ly;
-    if (cx < CW) {
-      C add = 0;
-      if (lx < im.w) {
-        const size_t p = (size_t)(im.top + ly) * im.tiff_w + im.left + lx;
-        const bool op = px_opaque<BPP>(im.data, p);
-        if (op) add |= (C)1 << bit;
-        if (lx == 0 || op != px_opaque<BPP>(im.data, p - 1))
-          add |= CoverTraits<C>::rs_bit;
-      } else {
-        add |= CoverTraits<C>::rs_bit;
-      }
-      if (add) cover[(size_t)cy * CW + cx] |= add;
+template <class C, int F, int BPP>
+__global__ void __launch_bounds__(256)
+    cover_kernel(C* __restrict__ cover, int W, int H,
+                 const ImgDev* __restrict__ imgs, int n, int reverse) {
+  // one pass over the canvas: every pixel looks at the images whose bounding
+  // box (plus the column right of it, where the reference's walk starts a new
+  // run) contains it
+  extern __shared__ ImgDev s_img[];
+  for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < n;
+       i += blockDim.x * blockDim.y)
+    s_img[i] = imgs[i];
+  __syncthreads();
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= W || y >= H) return;
+  C bits = 0;
+  bool run_start = false;
+  for (int i = 0; i < n; ++i) {
+    const ImgDev& im = s_img[i];
+    const int lx = x - im.xpos, ly = y - im.ypos;
+    if ((unsigned)ly >= (unsigned)im.h || (unsigned)lx > (unsigned)im.w) continue;
+    if (lx < im.w) {
+      const size_t p = (size_t)(im.top + ly) * im.tiff_w + im.left + lx;
+      const bool op = px_opaque<BPP>(im.data, p);
+      if (op) bits |= (C)1 << i;
+      if (lx == 0 || op != px_opaque<BPP>(im.data, p - 1)) run_start = true;
+    } else {
+      run_start = true;
     }
   }
+  C out;
+  if (F == kCoverDigest)
+    out = (C)make_digest((u32)bits, run_start, reverse);
+  else
+    out = bits | (run_start ? CoverTraits<C>::rs_bit : (C)0);
+  cover[(size_t)y * W + x] = out;
 }
 
-void launch_cover(void* cover, int cover_bytes, int CW, const ImgDev& im,
-                  int bpp, int bit, cudaStream_t s) {
+int cover_format(int n) {
+  return n <= kDigestMaxImages ? kCoverDigest : kCoverBits;
+}
+
+void launch_cover(void* cover, int cover_bytes, int W, int H,
+                  const ImgDev* d_imgs, int n, int bpp, int reverse,
+                  cudaStream_t s) {
   dim3 b(32, 8);
-  dim3 g(div_up(im.w + 1, 32), div_up(im.h, 8));
-#define XP_COVER(C, BPP)                                                  \
-  cover_kernel<C, BPP><<<g, b, 0, s>>>((C*)cover, CW, im, bit)
-  if (cover_bytes == 4) {
+  dim3 g(div_up(W, 32), div_up(H, 8));
+  const size_t sm = sizeof(ImgDev) * (size_t)n;
+#define XP_COVER(C, F, BPP)                                        \
+  cover_kernel<C, F, BPP><<<g, b, sm, s>>>((C*)cover, W, H, d_imgs, n, \
+                                           reverse)
+  if (cover_bytes == 8) {
     if (bpp == 8)
-      XP_COVER(u32, 8);
+      XP_COVER(u64, kCoverBits, 8);
     else
-      XP_COVER(u32, 16);
+      XP_COVER(u64, kCoverBits, 16);
+  } else if (cover_format(n) == kCoverDigest) {
+    if (bpp == 8)
+      XP_COVER(u32, kCoverDigest, 8);
+    else
+      XP_COVER(u32, kCoverDigest, 16);
   } else {
     if (bpp == 8)
-      XP_COVER(u64, 8);
+      XP_COVER(u32, kCoverBits, 8);
     else
-      XP_COVER(u64, 16);
+      XP_COVER(u32, kCoverBits, 16);
   }
 #undef XP_COVER
   XP_LAUNCHED();
@@ -283,26 +311,32 @@ void launch_seam_unpack(const u32* in, size_t n, u64* out, cudaStream_t s) {
   XP_LAUNCHED();
 }
 
-void launch_seams(const void* cover, int cover_bytes, int W, int H,
-                  int reverse, u32* bwd, u32* fwd, uint8_t* labels,
+template <class C, int F>
+static void seams_t(const void* cover, int W, int H, int reverse, u32* bwd,
+                    u32* fwd, uint8_t* labels, int* counter, uint8_t* flags,
+                    cudaStream_t s) {
+  const int n_bands = div_up(H, wf::kLanes);
+  const int fp = wf::chunks_of(W);
+  SeamBwd<C, F> pb{n_bands, W, H, (const C*)cover, bwd};
+  launch_wavefront(pb, counter, flags, fp, s);
+  SeamFwd<C, F> pf{n_bands, W, H, reverse, (const C*)cover, bwd, fwd, labels};
+  launch_wavefront(pf, counter, flags, fp, s);
+}
+
+void launch_seams(const void* cover, int cover_bytes, int n_images, int W,
+                  int H, int reverse, u32* bwd, u32* fwd, uint8_t* labels,
                   int* counter, uint8_t* flags, cudaStream_t s) {
   XP_REQUIRE((long)W + H < kSeamMaxExtent,
              "canvas %d x %d exceeds the seam distance range", W, H);
-  const int n_bands = div_up(H, wf::kLanes);
-  const int fp = wf::chunks_of(W);
-  if (cover_bytes == 4) {
-    SeamBwd<u32> pb{n_bands, W, H, (const u32*)cover, bwd};
-    launch_wavefront(pb, counter, flags, fp, s);
-    SeamFwd<u32> pf{n_bands, W, H, reverse, (const u32*)cover, bwd, fwd,
-                    labels};
-    launch_wavefront(pf, counter, flags, fp, s);
-  } else {
-    SeamBwd<u64> pb{n_bands, W, H, (const u64*)cover, bwd};
-    launch_wavefront(pb, counter, flags, fp, s);
-    SeamFwd<u64> pf{n_bands, W, H, reverse, (const u64*)cover, bwd, fwd,
-                    labels};
-    launch_wavefront(pf, counter, flags, fp, s);
-  }
+  if (cover_bytes == 8)
+    seams_t<u64, kCoverBits>(cover, W, H, reverse, bwd, fwd, labels, counter,
+                             flags, s);
+  else if (cover_format(n_images) == kCoverDigest)
+    seams_t<u32, kCoverDigest>(cover, W, H, reverse, bwd, fwd, labels, counter,
+                               flags, s);
+  else
+    seams_t<u32, kCoverBits>(cover, W, H, reverse, bwd, fwd, labels, counter,
+                             flags, s);
 }
 
 // ---------------------------------------------------------------------------
@@ -328,7 +362,7 @@ void launch_inpaint(const InpaintJob* d_jobs, const InpaintBandRef* d_bands,
 // per-channel sums of the inputs over exclusively covered pixels, whether any
 // pixel is uncovered, and the bounding box of every image's owner region.
 // ---------------------------------------------------------------------------
-template <class C, int BPP>
+template <class C, int F, int BPP>
 __global__ void canvas_stats_kernel(const C* __restrict__ cover,
                                     const uint8_t* __restrict__ labels, int W,
                                     int H, const ImgDev* __restrict__ imgs,
@@ -354,13 +388,14 @@ __global__ void canvas_stats_kernel(const C* __restrict__ cover,
   int label = -1;
   if (x < W && y < H) {
     const size_t p = (size_t)y * W + x;
-    const C bits = cover[p] & ~CoverTraits<C>::rs_bit;
-    const int cnt = popc_c(bits);
-    full_mask[p] = cnt ? 255 : 0;
-    xor_mask[p] = cnt == 1 ? 1 : 0;
-    if (cnt == 0) s_uncovered = 1;
-    if (cnt == 1) {
-      const ImgDev im = imgs[ctz_c(bits)];
+    typedef Cov<C, F> Cv;
+    const C cov = cover[p];
+    const bool any = Cv::any(cov), one = Cv::seed(cov);
+    full_mask[p] = any ? 255 : 0;
+    xor_mask[p] = one ? 1 : 0;
+    if (!any) s_uncovered = 1;
+    if (one) {
+      const ImgDev im = imgs[Cv::low(cov)];
       const size_t q =
           (size_t)(im.top + y - im.ypos) * im.tiff_w + im.left + x - im.xpos;
       if (BPP == 8) {
@@ -426,20 +461,26 @@ void launch_canvas_stats(const void* cover, int cover_bytes,
   XP_LAUNCHED();
   dim3 b(32, 8);
   dim3 g(div_up(W, 32), div_up(H, 8));
-#define XP_STATS(C, BPP)                                                    \
-  canvas_stats_kernel<C, BPP><<<g, b, 0, s>>>((const C*)cover, labels, W, H, \
-                                              d_imgs, n, full_mask,          \
-                                              xor_mask, d_stats)
-  if (cover_bytes == 4) {
+#define XP_STATS(C, F, BPP)                                            \
+  canvas_stats_kernel<C, F, BPP><<<g, b, 0, s>>>((const C*)cover, labels, \
+                                                 W, H, d_imgs, n,         \
+                                                 full_mask, xor_mask,     \
+                                                 d_stats)
+  if (cover_bytes == 8) {
     if (bpp == 8)
-      XP_STATS(u32, 8);
+      XP_STATS(u64, kCoverBits, 8);
     else
-      XP_STATS(u32, 16);
+      XP_STATS(u64, kCoverBits, 16);
+  } else if (cover_format(n) == kCoverDigest) {
+    if (bpp == 8)
+      XP_STATS(u32, kCoverDigest, 8);
+    else
+      XP_STATS(u32, kCoverDigest, 16);
   } else {
     if (bpp == 8)
-      XP_STATS(u64, 8);
+      XP_STATS(u32, kCoverBits, 8);
     else
-      XP_STATS(u64, 16);
+      XP_STATS(u32, kCoverBits, 16);
   }
 #undef XP_STATS
   XP_LAUNCHED();

@@ -283,7 +283,9 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
         XP_WF_CLOCK(2);
         {
           // 32 skewed steps; everything but the chain through `last` and the
-          // shuffle is independent of the previous step
+          // shuffle is independent of the previous step. Chunks that touch
+          // no border of the job (first/last column, first row, rows past H)
+          // run the step variant without the border selects.
           const In0* r0 = reinterpret_cast<const In0*>(
                               in0_base + (k & 1) * kB0 * kTileElems) +
                           lane * kTilePitch;
@@ -292,26 +294,49 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
                           lane * kTilePitch;
           Val* ro = out_base + (k & 1) * kTileElems + lane * kTilePitch;
           const int q0 = s0 - kSkew * lane;
+          const bool interior = B.rho0 > 0 && B.rho0 + kLanes <= B.H &&
+                                s0 - kSkew * (kLanes - 1) >= 2 &&
+                                s0 + kChunk - 1 <= W - 2;
+          if (interior) {
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-          for (int t = 0; t < kChunk; ++t) {
-            const int q = q0 + t;
-            const bool active = row_ok && q >= 0 && q < W;
-            const In0 a = r0[t];
-            In1 b = In1();
-            if (kB1) b = r1[t];
-            const Val hv = pv_row[t];
-            Val up = ctx.shfl_up1(last);
-            if (lane == 0) up = hv;
-            w0 = w1;
-            w1 = w2;
-            w2 = up;
-            const Val nv = prob.step(B, row_state, active, rho, q, a, b, last,
-                                     w0, w1, w2);
-            if (active) {
-              last = nv;
-              ro[t] = nv;
+            for (int t = 0; t < kChunk; ++t) {
+              const In0 a = r0[t];
+              In1 b = In1();
+              if (kB1) b = r1[t];
+              const Val hv = pv_row[t];
+              Val up = ctx.shfl_up1(last);
+              if (lane == 0) up = hv;
+              w0 = w1;
+              w1 = w2;
+              w2 = up;
+              last = prob.template step<false>(B, row_state, true, rho, q0 + t,
+                                               a, b, last, w0, w1, w2);
+              ro[t] = last;
+            }
+          } else {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (int t = 0; t < kChunk; ++t) {
+              const int q = q0 + t;
+              const bool active = row_ok && q >= 0 && q < W;
+              const In0 a = r0[t];
+              In1 b = In1();
+              if (kB1) b = r1[t];
+              const Val hv = pv_row[t];
+              Val up = ctx.shfl_up1(last);
+              if (lane == 0) up = hv;
+              w0 = w1;
+              w1 = w2;
+              w2 = up;
+              const Val nv = prob.template step<true>(
+                  B, row_state, active, rho, q, a, b, last, w0, w1, w2);
+              if (active) {
+                last = nv;
+                ro[t] = nv;
+              }
             }
           }
         }
