@@ -203,8 +203,9 @@ struct SeamBwd {
     return (u32)Cv::low(cov);
   }
   // last = (x+1, y); w0 = (x+1, y+1); w1 = (x, y+1); w2 = (x-1, y+1).
-  // kEdge = false: the caller guarantees rho > 0 and 0 < q < W-1.
-  template <bool kEdge>
+  // kEdgeX = false: the caller guarantees 0 < q < W-1;
+  // kEdgeY = false: the caller guarantees rho > 0.
+  template <bool kEdgeX, bool kEdgeY>
   XP_HD u32 step(const wf::Band&, Row& row, bool active, int rho, int q, C cov,
                  In1, u32 last, u32 w0, u32 w1, u32 w2) const {
     const C bits = Cv::bits(cov);
@@ -212,12 +213,12 @@ struct SeamBwd {
     u32 c0 = mask32(w0 + kD4, bits);
     const u32 c1 = mask32(w1 + kD3, bits);
     u32 c2 = mask32(w2 + kD4, bits);
-    if (kEdge) {
+    if (kEdgeX) {
       if (q <= 0) cl = kInf32, c0 = kInf32;
       if (q >= W - 1) c2 = kInf32;
     }
     u32 d = min32(min32(cl, c0), min32(c1, c2));
-    if (kEdge) {
+    if (kEdgeY) {
       const bool was_first = row.first_run;
       if (active && Cv::rs(cov)) row.first_run = false;
       // bottom row :333-346
@@ -274,8 +275,9 @@ struct SeamFwd {
     return (u32)Cv::low(cov);
   }
   // last = (x-1, y); w0 = (x-1, y-1); w1 = (x, y-1); w2 = (x+1, y-1).
-  // kEdge = false: the caller guarantees y > 0 and 1 < x < W-1.
-  template <bool kEdge>
+  // kEdgeX = false: the caller guarantees 1 < x < W-1;
+  // kEdgeY = false: the caller guarantees y > 0.
+  template <bool kEdgeX, bool kEdgeY>
   XP_HD u32 step(const wf::Band&, Row&, bool, int y, int x, u32 bw, C cov,
                  u32 last, u32 w0, u32 w1, u32 w2) const {
     const C bits = Cv::bits(cov);
@@ -286,12 +288,13 @@ struct SeamFwd {
     // a run start (:629-630, :704-705); raw inside a run (:750)
     u32 cl = last + kD3;
     const u32 clm = mask32(cl, bits);
-    if (Cv::rs(cov) || (kEdge && (y == 0 || x == 1))) cl = clm;
-    if (kEdge) {
-      if (x <= 0) cl = kInf32;
-      if (y == 0 || x <= 0) c0 = kInf32;
-      if (y == 0) c1 = kInf32;
-      if (y == 0 || x >= W - 1) c2 = kInf32;
+    if (Cv::rs(cov) || (kEdgeY && y == 0) || (kEdgeX && x == 1)) cl = clm;
+    if (kEdgeX) {
+      if (x <= 0) cl = kInf32, c0 = kInf32;
+      if (x >= W - 1) c2 = kInf32;
+    }
+    if (kEdgeY) {
+      if (y == 0) c0 = kInf32, c1 = kInf32, c2 = kInf32;
     }
     // ReadSeamDT value enters unmasked
     u32 best = min32(min32(min32(bw, c0), min32(c1, c2)), cl);
@@ -388,24 +391,27 @@ struct InpaintFwd {
     return (u64)(row.base + (u32)(dy * jobs[B.job].tiff_w) + (u32)x);
   }
   // last = (x-1, y); w0 = (x-1, y-1); w1 = (x, y-1); w2 = (x+1, y-1).
-  // kEdge = false: the caller guarantees y > 0 and 0 < x < W-1.
-  template <bool kEdge>
+  // kEdgeX = false: the caller guarantees 0 < x < W-1;
+  // kEdgeY = false: the caller guarantees y > 0.
+  template <bool kEdgeX, bool kEdgeY>
   XP_HD u64 step(const wf::Band& B, Row& row, bool, int y, int x, In0 px, In1,
                  u64 last, u64 w0, u64 w1, u64 w2) const {
     const u32 me = row.base + (u32)x;
     // own row :573-583 / :609-641; the very first pixel seeds 0x80000000
     u32 d = hi32(last) + 3, s = lo32(last);
     u32 a = hi32(w0) + 4, b = hi32(w1) + 3, c = hi32(w2) + 4;
-    if (kEdge) {
-      if (x == 0) d = y == 0 ? 0x80000000u : kInf32, s = me;
-      if (y == 0 || x == 0) a = kInf32;
-      if (y == 0) b = kInf32;
-      if (y == 0 || x >= B.W - 1) c = kInf32;
+    if (kEdgeX) {
+      if (x == 0) d = (kEdgeY && y == 0) ? 0x80000000u : kInf32, s = me;
+      if (x == 0) a = kInf32;
+      if (x >= B.W - 1) c = kInf32;
+    }
+    if (kEdgeY) {
+      if (y == 0) a = kInf32, b = kInf32, c = kInf32;
     }
     if (a < d) d = a, s = lo32(w0);
     if (b < d) d = b, s = lo32(w1);
     // in column 0 a tie between up and up-right goes to up-right (:585-603)
-    if (c < d || (kEdge && x == 0 && c == d)) d = c, s = lo32(w2);
+    if (c < d || (kEdgeX && x == 0 && c == d)) d = c, s = lo32(w2);
     if (pixel_opaque(px)) d = 0, s = me;  // :659-662
     return d32(d) | s;
   }
@@ -451,8 +457,9 @@ struct InpaintBwd {
     return fwd;
   }
   // last = (x+1, y); w0 = (x+1, y+1); w1 = (x, y+1); w2 = (x-1, y+1).
-  // kEdge = false: the caller guarantees rho > 0 and 0 < q < W-1.
-  template <bool kEdge>
+  // kEdgeX = false: the caller guarantees 0 < q < W-1;
+  // kEdgeY = false: the caller guarantees rho > 0.
+  template <bool kEdgeX, bool kEdgeY>
   XP_HD u64 step(const wf::Band& B, Row&, bool, int rho, int q, u64 fwd, In1,
                  u64 last, u64 w0, u64 w1, u64 w2) const {
     u32 best = hi32(fwd), src = lo32(fwd);
@@ -463,10 +470,13 @@ struct InpaintBwd {
     u32 b = hi32(w1) + 3;
     u32 c = hi32(w0) + 4;  // x+1
     u32 d = hi32(last) + 3;
-    if (kEdge) {
-      const bool bottom = rho == 0;  // last line :711-747: right neighbour only
+    const bool bottom = kEdgeY && rho == 0;  // last line :711-747: right
+                                             // neighbour only
+    if (kEdgeX) {
       if (q >= B.W - 1) a = 0x80000000u;
       if (q <= 0) c = 0x80000000u, d = bottom ? kInf32 : 0x80000000u;
+    }
+    if (kEdgeY) {
       if (bottom) a = kInf32, b = kInf32, c = kInf32;
     }
     if (a < best) best = a, src = lo32(w2);

@@ -38,6 +38,7 @@
 
 #include <cstddef>
 #include <cstdint>
+#include <type_traits>
 
 #include "hd.h"
 
@@ -294,10 +295,12 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
                           lane * kTilePitch;
           Val* ro = out_base + (k & 1) * kTileElems + lane * kTilePitch;
           const int q0 = s0 - kSkew * lane;
-          const bool interior = B.rho0 > 0 && B.rho0 + kLanes <= B.H &&
-                                s0 - kSkew * (kLanes - 1) >= 2 &&
-                                s0 + kChunk - 1 <= W - 2;
-          if (interior) {
+          // rows past H (lanes below the job) may run the border-free step
+          // too: nothing depends on them and the storer never writes them
+          const bool interior_x = s0 - kSkew * (kLanes - 1) >= 2 &&
+                                  s0 + kChunk - 1 <= W - 2;
+          auto steps = [&](auto edge_y) {
+            constexpr bool kEdgeY = decltype(edge_y)::value;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
@@ -311,10 +314,15 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
               w0 = w1;
               w1 = w2;
               w2 = up;
-              last = prob.template step<false>(B, row_state, true, rho, q0 + t,
-                                               a, b, last, w0, w1, w2);
+              last = prob.template step<false, kEdgeY>(
+                  B, row_state, true, rho, q0 + t, a, b, last, w0, w1, w2);
               ro[t] = last;
             }
+          };
+          if (interior_x && B.rho0 > 0) {
+            steps(std::false_type());
+          } else if (interior_x) {
+            steps(std::true_type());
           } else {
 #if defined(__CUDA_ARCH__)
 #pragma unroll
@@ -331,7 +339,7 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
               w0 = w1;
               w1 = w2;
               w2 = up;
-              const Val nv = prob.template step<true>(
+              const Val nv = prob.template step<true, true>(
                   B, row_state, active, rho, q, a, b, last, w0, w1, w2);
               if (active) {
                 last = nv;
