@@ -103,6 +103,7 @@ Blender::~Blender() {
   if (stream) cudaStreamSynchronize(stream);
   if (ev_fork) cudaEventDestroy(ev_fork);
   if (ev_join) cudaEventDestroy(ev_join);
+  if (ev_cover) cudaEventDestroy(ev_cover);
   if (side_stream) cudaStreamDestroy(side_stream);
   if (own_stream) cudaStreamDestroy(own_stream);
 }
@@ -117,6 +118,7 @@ void Blender::ensure_device() {
     XP_CUDA(cudaStreamCreateWithFlags(&side_stream, cudaStreamNonBlocking));
     XP_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
     XP_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+    XP_CUDA(cudaEventCreateWithFlags(&ev_cover, cudaEventDisableTiming));
   }
 }
 

@@ -71,7 +71,8 @@ void launch_canvas_stats(const void* cover, int cover_bytes,
                          const uint8_t* labels, int W, int H,
                          const ImgDev* d_imgs, int n, int bpp,
                          uint8_t* full_mask, uint8_t* xor_mask,
-                         CanvasStats* d_stats, cudaStream_t s);
+                         CanvasStats* d_stats, int mode, cudaStream_t s);
+void launch_stats_init(CanvasStats* d_stats, cudaStream_t s);
 
 // pyramid.cu
 // level 0 of an image pyramid from the (inpainted) source pixels.

@@ -362,7 +362,9 @@ void launch_inpaint(const InpaintJob* d_jobs, const InpaintBandRef* d_bands,
 // per-channel sums of the inputs over exclusively covered pixels, whether any
 // pixel is uncovered, and the bounding box of every image's owner region.
 // ---------------------------------------------------------------------------
-template <class C, int F, int BPP>
+// kMode bit 0: masks, exclusive-pixel sums, uncovered flag (needs the cover
+// map only); bit 1: owner-region boxes (needs the labels).
+template <class C, int F, int BPP, int kMode>
 __global__ void canvas_stats_kernel(const C* __restrict__ cover,
                                     const uint8_t* __restrict__ labels, int W,
                                     int H, const ImgDev* __restrict__ imgs,
@@ -382,54 +384,61 @@ __global__ void canvas_stats_kernel(const C* __restrict__ cover,
   if (tid < 4) s_sum[tid] = 0;
   if (tid == 0) s_uncovered = 0;
   __syncthreads();
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  unsigned sum[4] = {0, 0, 0, 0};
-  int label = -1;
-  if (x < W && y < H) {
-    const size_t p = (size_t)y * W + x;
-    typedef Cov<C, F> Cv;
-    const C cov = cover[p];
-    const bool any = Cv::any(cov), one = Cv::seed(cov);
-    full_mask[p] = any ? 255 : 0;
-    xor_mask[p] = one ? 1 : 0;
-    if (!any) s_uncovered = 1;
-    if (one) {
-      const ImgDev im = imgs[Cv::low(cov)];
-      const size_t q =
-          (size_t)(im.top + y - im.ypos) * im.tiff_w + im.left + x - im.xpos;
-      if (BPP == 8) {
-        const u32 v = static_cast<const u32*>(im.data)[q];
-        sum[0] = v & 0xff;
-        sum[1] = (v >> 8) & 0xff;
-        sum[2] = (v >> 16) & 0xff;
-      } else {
-        const u64 v = static_cast<const u64*>(im.data)[q];
-        sum[0] = v & 0xffff;
-        sum[1] = (v >> 16) & 0xffff;
-        sum[2] = (v >> 32) & 0xffff;
+  // persistent blocks: tiles of 32 x 8 pixels are strided over the grid and
+  // the block's partial results leave through a handful of global atomics at
+  // the end (one block per tile would serialise ~10^6 atomics on 36 words)
+  const int tiles_x = (W + 31) / 32, tiles_y = (H + 7) / 8;
+  for (int tile = blockIdx.x; tile < tiles_x * tiles_y; tile += gridDim.x) {
+    const int x = (tile % tiles_x) * 32 + threadIdx.x;
+    const int y = (tile / tiles_x) * 8 + threadIdx.y;
+    unsigned sum[4] = {0, 0, 0, 0};
+    int label = -1;
+    if (x < W && y < H && (kMode & 1)) {
+      const size_t p = (size_t)y * W + x;
+      typedef Cov<C, F> Cv;
+      const C cov = cover[p];
+      const bool any = Cv::any(cov), one = Cv::seed(cov);
+      full_mask[p] = any ? 255 : 0;
+      xor_mask[p] = one ? 1 : 0;
+      if (!any) s_uncovered = 1;
+      if (one) {
+        const ImgDev im = imgs[Cv::low(cov)];
+        const size_t q =
+            (size_t)(im.top + y - im.ypos) * im.tiff_w + im.left + x - im.xpos;
+        if (BPP == 8) {
+          const u32 v = static_cast<const u32*>(im.data)[q];
+          sum[0] = v & 0xff;
+          sum[1] = (v >> 8) & 0xff;
+          sum[2] = (v >> 16) & 0xff;
+        } else {
+          const u64 v = static_cast<const u64*>(im.data)[q];
+          sum[0] = v & 0xffff;
+          sum[1] = (v >> 16) & 0xffff;
+          sum[2] = (v >> 32) & 0xffff;
+        }
+        sum[3] = 1;
       }
-      sum[3] = 1;
     }
-    if (n > 1) label = labels[p];
-  }
-  // a warp is 32 consecutive x of one row: lanes with the same label elect
-  // one of them to extend that label's box
-  {
-    const unsigned peers = __match_any_sync(~0u, label);
-    const int lane = tid & 31;
-    if (label >= 0 && lane == __ffs(peers) - 1) {
-      const int xb = x - lane;
-      atomicMin(&s_box[label][0], xb + __ffs(peers) - 1);
-      atomicMin(&s_box[label][1], y);
-      atomicMax(&s_box[label][2], xb + 31 - __clz(peers));
-      atomicMax(&s_box[label][3], y);
+    if (x < W && y < H && (kMode & 2) && n > 1)
+      label = labels[(size_t)y * W + x];
+    // a warp is 32 consecutive x of one row: lanes with the same label elect
+    // one of them to extend that label's box
+    if (kMode & 2) {
+      const unsigned peers = __match_any_sync(~0u, label);
+      const int lane = tid & 31;
+      if (label >= 0 && lane == __ffs(peers) - 1) {
+        const int xb = x - lane;
+        atomicMin(&s_box[label][0], xb + __ffs(peers) - 1);
+        atomicMin(&s_box[label][1], y);
+        atomicMax(&s_box[label][2], xb + 31 - __clz(peers));
+        atomicMax(&s_box[label][3], y);
+      }
     }
-  }
-  for (int k = 0; k < 4; ++k) {
-    unsigned v = sum[k];  // <= 32 * 65535
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(~0u, v, o);
-    if ((tid & 31) == 0 && v) atomicAdd(&s_sum[k], (unsigned long long)v);
+    for (int k = 0; k < ((kMode & 1) ? 4 : 0); ++k) {
+      unsigned v = sum[k];  // <= 32 * 65535
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(~0u, v, o);
+      if ((tid & 31) == 0 && v) atomicAdd(&s_sum[k], (unsigned long long)v);
+    }
   }
   __syncthreads();
   if (tid < 4 && s_sum[tid]) atomicAdd(&stats->totals[tid], s_sum[tid]);
@@ -452,37 +461,51 @@ __global__ void stats_init_kernel(CanvasStats* st) {
   st->box[i][2] = st->box[i][3] = -1;
 }
 
+void launch_stats_init(CanvasStats* d_stats, cudaStream_t s) {
+  stats_init_kernel<<<1, 64, 0, s>>>(d_stats);
+  XP_LAUNCHED();
+}
+
 void launch_canvas_stats(const void* cover, int cover_bytes,
                          const uint8_t* labels, int W, int H,
                          const ImgDev* d_imgs, int n, int bpp,
                          uint8_t* full_mask, uint8_t* xor_mask,
-                         CanvasStats* d_stats, cudaStream_t s) {
-  stats_init_kernel<<<1, 64, 0, s>>>(d_stats);
-  XP_LAUNCHED();
+                         CanvasStats* d_stats, int mode, cudaStream_t s) {
   dim3 b(32, 8);
-  dim3 g(div_up(W, 32), div_up(H, 8));
-#define XP_STATS(C, F, BPP)                                            \
-  canvas_stats_kernel<C, F, BPP><<<g, b, 0, s>>>((const C*)cover, labels, \
-                                                 W, H, d_imgs, n,         \
-                                                 full_mask, xor_mask,     \
-                                                 d_stats)
+  const int g = std::min(div_up(W, 32) * div_up(H, 8), 148 * 8);
+#define XP_STATS3(C, F, BPP, M)                                               \
+  canvas_stats_kernel<C, F, BPP, M><<<g, b, 0, s>>>((const C*)cover, labels, \
+                                                    W, H, d_imgs, n,         \
+                                                    full_mask, xor_mask,     \
+                                                    d_stats)
+#define XP_STATS(C, F, BPP)    \
+  if (mode == 1)               \
+    XP_STATS3(C, F, BPP, 1);   \
+  else if (mode == 2)          \
+    XP_STATS3(C, F, BPP, 2);   \
+  else                         \
+    XP_STATS3(C, F, BPP, 3)
   if (cover_bytes == 8) {
-    if (bpp == 8)
+    if (bpp == 8) {
       XP_STATS(u64, kCoverBits, 8);
-    else
+    } else {
       XP_STATS(u64, kCoverBits, 16);
+    }
   } else if (cover_format(n) == kCoverDigest) {
-    if (bpp == 8)
+    if (bpp == 8) {
       XP_STATS(u32, kCoverDigest, 8);
-    else
+    } else {
       XP_STATS(u32, kCoverDigest, 16);
+    }
   } else {
-    if (bpp == 8)
+    if (bpp == 8) {
       XP_STATS(u32, kCoverBits, 8);
-    else
+    } else {
       XP_STATS(u32, kCoverBits, 16);
+    }
   }
 #undef XP_STATS
+#undef XP_STATS3
   XP_LAUNCHED();
 }
 
