@@ -12,6 +12,7 @@
 #include "blend_impl.h"
 #include "common.h"
 #include "pyramid_dev.h"
+#include "shrink_tiled.h"
 #include "pyramid_math.h"
 
 namespace xp {
@@ -115,64 +116,15 @@ __device__ __forceinline__ float4 ldg4(const float* p) {
   return __ldg(reinterpret_cast<const float4*>(p));
 }
 
-__global__ void __launch_bounds__(256)
-    shrink_kernel(const float* __restrict__ hi, int hh, int hp, int xs, int ys,
-                  float* __restrict__ lo, int lo_h, int lo_pitch,
-                  size_t chan_stride) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  if (4 * i >= lo_pitch || y >= lo_h) return;
-  const size_t co = (size_t)blockIdx.z * chan_stride;
-  const float* h = hi + co;
-  float out[4];
-  if (i >= 1 && 8 * i + 6 <= hp - 1) {
-    const pm::VForm f = pm::shrink_vform(hh, ys, lo_h, y);
-    // v[c] = vertical form at hi column 8i - 8 + c, c = 0..15
-    float v[16];
-    const int c0 = xs ? 0 : 1;
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      if (c < c0) continue;
-      const float* col = h + 8 * i - 8 + 4 * c;
-      float4 r[5];
-      const int taps = f.kind == 3 ? 5 : (f.kind == 1 ? 3 : (f.kind == 0 ? 1 : 2));
-#pragma unroll
-      for (int k = 0; k < 5; ++k)
-        r[k] = k < taps ? ldg4(col + (size_t)f.r[k] * hp)
-                        : make_float4(0.f, 0.f, 0.f, 0.f);
-      v[4 * c + 0] = pm::shrink_vcombine(f.kind, r[0].x, r[1].x, r[2].x, r[3].x, r[4].x);
-      v[4 * c + 1] = pm::shrink_vcombine(f.kind, r[0].y, r[1].y, r[2].y, r[3].y, r[4].y);
-      v[4 * c + 2] = pm::shrink_vcombine(f.kind, r[0].z, r[1].z, r[2].z, r[3].z, r[4].z);
-      v[4 * c + 3] = pm::shrink_vcombine(f.kind, r[0].w, r[1].w, r[2].w, r[3].w, r[4].w);
-    }
-    // sample j = 4i + k reads hi columns 2j - 4 - xs + (0..4)
-    //   = 8i - 8 + (4 - xs + 2k) + (0..4)
-    const int base = 4 - xs;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      float t[5];
-#pragma unroll
-      for (int m = 0; m < 5; ++m) t[m] = xs ? v[3 + 2 * k + m] : v[4 + 2 * k + m];
-      out[k] = pm::squeeze_combine(t, f.mul);
-    }
-    (void)base;
-  } else {
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-      out[k] = pm::shrink_sample(h, hh, hp, xs, ys, lo_h, 4 * i + k, y);
-  }
-  *reinterpret_cast<float4*>(lo + co + (size_t)y * lo_pitch + 4 * i) =
-      make_float4(out[0], out[1], out[2], out[3]);
-}
-
 void launch_shrink(const PyrGeom& g, float* pyr, int level, int channels,
                    cudaStream_t s) {
   const LevelGeom& H = g.lv[level];
   const LevelGeom& L = g.lv[level + 1];
-  dim3 b(32, 8);
-  shrink_kernel<<<grid3(L.pitch / 4, L.h, channels, b), b, 0, s>>>(
-      pyr + H.offset, H.h, H.pitch, H.xs, H.ys, pyr + L.offset, L.h, L.pitch,
-      g.channel_floats);
+  PlaneSrc src{pyr + H.offset, H.pitch, g.channel_floats};
+  dim3 gr(div_up(L.pitch, kShrinkTileW), div_up(L.h, kShrinkTileH), channels);
+  shrink_tiled_kernel<<<gr, 256, 0, s>>>(src, H.h, H.pitch, H.xs, H.ys,
+                                         pyr + L.offset, L.h, L.pitch,
+                                         g.channel_floats);
   XP_LAUNCHED();
 }
 

@@ -15,6 +15,7 @@
 #include "blend_impl.h"
 #include "common.h"
 #include "pyramid_dev.h"
+#include "shrink_tiled.h"
 #include "pyramid_math.h"
 
 namespace xp {
@@ -85,90 +86,38 @@ void launch_inpaint_gather(const ImgDev& im, int bpp, const u64* src_index,
 }
 
 // ---------------------------------------------------------------------------
-// shrink level 0 -> 1 straight from the source pixels, 3 channels together,
-// four lo samples per thread
+// shrink level 0 -> 1 straight from the source pixels, 3 channels together
 // ---------------------------------------------------------------------------
 template <int BPP>
-__global__ void __launch_bounds__(256)
-    shrink0_kernel(Level0<BPP> L0, int hh, int hp, int xs, int ys,
-                   float* __restrict__ lo, int lo_h, int lo_pitch,
-                   size_t chan_stride) {
-  typedef typename PixelOf<BPP>::type Px;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  if (4 * i >= lo_pitch || y >= lo_h) return;
-  const pm::VForm f = pm::shrink_vform(hh, ys, lo_h, y);
-  float out[3][4];
-  // interior: no horizontal clamp, and every form row is a real image row
-  bool fast = i >= 1 && 8 * i + 6 <= hp - 1;
-#pragma unroll
-  for (int k = 0; k < 5; ++k) fast = fast && f.r[k] < L0.h;
-  if (fast) {
-    const int taps =
-        f.kind == 3 ? 5 : (f.kind == 1 ? 3 : (f.kind == 0 ? 1 : 2));
-    // v[c][m] = vertical form of channel c at hi column 8i - 4 - xs + m
-    float v[3][11];
-    const int col0 = 8 * i - 4 - xs;
-#pragma unroll
-    for (int m = 0; m < 11; ++m) {
-      Px r[5];
-#pragma unroll
-      for (int k = 0; k < 5; ++k) r[k] = k < taps ? L0.px(f.r[k], col0 + m) : 0;
-#pragma unroll
-      for (int c = 0; c < 3; ++c)
-        v[c][m] = pm::shrink_vcombine(
-            f.kind, L0.chan(r[0], c) * L0.mul, L0.chan(r[1], c) * L0.mul,
-            L0.chan(r[2], c) * L0.mul, L0.chan(r[3], c) * L0.mul,
-            L0.chan(r[4], c) * L0.mul);
-    }
-#pragma unroll
-    for (int c = 0; c < 3; ++c)
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        float t[5];
-#pragma unroll
-        for (int m = 0; m < 5; ++m) t[m] = v[c][2 * k + m];
-        out[c][k] = pm::squeeze_combine(t, f.mul);
-      }
-  } else {
-#pragma unroll
-    for (int c = 0; c < 3; ++c)
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        float t[5];
-#pragma unroll
-        for (int m = 0; m < 5; ++m) {
-          const int col = pm::squeeze_col(4 * i + k, m, hp, xs);
-          t[m] = pm::shrink_vcombine(f.kind, L0.at(c, f.r[0], col),
-                                     L0.at(c, f.r[1], col),
-                                     L0.at(c, f.r[2], col),
-                                     L0.at(c, f.r[3], col),
-                                     L0.at(c, f.r[4], col));
-        }
-        out[c][k] = pm::squeeze_combine(t, f.mul);
-      }
+struct PixelSrc : Level0<BPP> {
+  typedef typename Level0<BPP>::Px Raw;
+  static constexpr int kChannels = 3;
+  __device__ __forceinline__ Raw raw(int, int row, int col) const {
+    return row < this->h ? this->px(row, col) : (Raw)0;  // zeroed rows
   }
-#pragma unroll
-  for (int c = 0; c < 3; ++c)
-    *reinterpret_cast<float4*>(lo + c * chan_stride + (size_t)y * lo_pitch +
-                               4 * i) =
-        make_float4(out[c][0], out[c][1], out[c][2], out[c][3]);
-}
+  __device__ __forceinline__ float value(Raw v, int c) const {
+    return this->chan(v, c) * this->mul;
+  }
+};
 
 void launch_shrink0(const ImgDev& im, int bpp, float mul, const PyrGeom& g,
                     float* pyr, cudaStream_t s) {
   const LevelGeom& H = g.lv[0];
   const LevelGeom& L = g.lv[1];
-  dim3 b(32, 8);
-  dim3 gr(div_up(L.pitch / 4, 32), div_up(L.h, 8));
-  if (bpp == 8)
-    shrink0_kernel<8><<<gr, b, 0, s>>>(make_level0<8>(im, mul), H.h, H.pitch,
-                                       H.xs, H.ys, pyr + L.offset, L.h,
-                                       L.pitch, g.channel_floats);
-  else
-    shrink0_kernel<16><<<gr, b, 0, s>>>(make_level0<16>(im, mul), H.h, H.pitch,
-                                        H.xs, H.ys, pyr + L.offset, L.h,
-                                        L.pitch, g.channel_floats);
+  dim3 gr(div_up(L.pitch, kShrinkTileW), div_up(L.h, kShrinkTileH), 1);
+  if (bpp == 8) {
+    PixelSrc<8> src;
+    static_cast<Level0<8>&>(src) = make_level0<8>(im, mul);
+    shrink_tiled_kernel<<<gr, 256, 0, s>>>(src, H.h, H.pitch, H.xs, H.ys,
+                                           pyr + L.offset, L.h, L.pitch,
+                                           g.channel_floats);
+  } else {
+    PixelSrc<16> src;
+    static_cast<Level0<16>&>(src) = make_level0<16>(im, mul);
+    shrink_tiled_kernel<<<gr, 256, 0, s>>>(src, H.h, H.pitch, H.xs, H.ys,
+                                           pyr + L.offset, L.h, L.pitch,
+                                           g.channel_floats);
+  }
   XP_LAUNCHED();
 }
 

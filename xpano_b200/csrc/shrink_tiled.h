@@ -1,0 +1,110 @@
+// Tiled Shrink (pyramid.cpp:584-823): a block produces 64 x 8 lo samples.
+// The hi rows and columns they reference are staged in shared memory once
+// (coalesced loads), the vertical form is applied per column into a second
+// shared tile, then the five horizontal taps are combined. All border rules
+// (row forms, column clamps, parity shifts) come from pyramid_math.h index
+// functions, so there is no separate border path.
+//
+// `Src` is the hi level: raw(row, col) loads one stored element, value(raw, c)
+// converts it to the float sample of channel c (kChannels channels per
+// element: 3 for interleaved source pixels, 1 for a float plane).
+#pragma once
+
+#include "pyramid_math.h"
+
+namespace xp {
+
+constexpr int kShrinkTileW = 64, kShrinkTileH = 8;
+constexpr int kShrinkMaxCols = 2 * kShrinkTileW + 6;  // 2*(W-1) + 4 + 1 (+xs)
+constexpr int kShrinkMaxRows = 2 * kShrinkTileH + 4;
+
+template <class Src>
+__global__ void __launch_bounds__(256)
+    shrink_tiled_kernel(Src hi, int hh, int hp, int xs, int ys,
+                        float* __restrict__ lo, int lo_h, int lo_pitch,
+                        size_t chan_stride) {
+  typedef typename Src::Raw Raw;
+  constexpr int NC = Src::kChannels;
+  __shared__ Raw tile[kShrinkMaxRows * kShrinkMaxCols];
+  __shared__ float vert[NC][kShrinkTileH][kShrinkMaxCols];
+  __shared__ pm::VForm forms[kShrinkTileH];
+  __shared__ int s_rmin, s_rmax;
+  const int tid = threadIdx.x;
+  const int j0 = blockIdx.x * kShrinkTileW, y0 = blockIdx.y * kShrinkTileH;
+  const int ny = min(kShrinkTileH, lo_h - y0);
+  const int z = blockIdx.z;  // plane for single-channel sources
+  if (tid == 0) s_rmin = 1 << 30, s_rmax = -1;
+  __syncthreads();
+  if (tid < ny) {
+    const pm::VForm f = pm::shrink_vform(hh, ys, lo_h, y0 + tid);
+    forms[tid] = f;
+    const int taps = f.kind == 3 ? 5 : (f.kind == 1 ? 3 : (f.kind == 0 ? 1 : 2));
+    int lo_r = f.r[0], hi_r = f.r[0];
+    for (int k = 1; k < taps; ++k) lo_r = min(lo_r, f.r[k]), hi_r = max(hi_r, f.r[k]);
+    atomicMin(&s_rmin, lo_r);
+    atomicMax(&s_rmax, hi_r);
+  }
+  __syncthreads();
+  const int rmin = s_rmin, nrows = s_rmax - rmin + 1;
+  const int jl = min(j0 + kShrinkTileW - 1, lo_pitch - 1);
+  const int cmin = pm::squeeze_col(j0, 0, hp, xs);
+  const int ncols = pm::squeeze_col(jl, 4, hp, xs) - cmin + 1;
+  // ---- stage the hi window ----
+  for (int i = tid; i < nrows * ncols; i += 256) {
+    const int r = i / ncols, c = i - r * ncols;
+    tile[r * kShrinkMaxCols + c] = hi.raw(z, rmin + r, cmin + c);
+  }
+  __syncthreads();
+  // ---- vertical forms, one (lo row, hi column) per item ----
+  for (int i = tid; i < ny * ncols; i += 256) {
+    const int yy = i / ncols, c = i - yy * ncols;
+    const pm::VForm& f = forms[yy];
+    Raw r[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      // rows of unused taps alias a staged row; their value is ignored
+      int rr = f.r[k] - rmin;
+      rr = rr < 0 ? 0 : (rr >= nrows ? nrows - 1 : rr);
+      r[k] = tile[rr * kShrinkMaxCols + c];
+    }
+#pragma unroll
+    for (int ch = 0; ch < NC; ++ch)
+      vert[ch][yy][c] = pm::shrink_vcombine(
+          f.kind, hi.value(r[0], ch), hi.value(r[1], ch), hi.value(r[2], ch),
+          hi.value(r[3], ch), hi.value(r[4], ch));
+  }
+  __syncthreads();
+  // ---- horizontal taps ----
+  for (int i = tid; i < ny * kShrinkTileW; i += 256) {
+    const int yy = i / kShrinkTileW, jj = i - yy * kShrinkTileW;
+    const int j = j0 + jj;
+    if (j >= lo_pitch) continue;
+    int col[5];
+#pragma unroll
+    for (int m = 0; m < 5; ++m) col[m] = pm::squeeze_col(j, m, hp, xs) - cmin;
+    const float mul = forms[yy].mul;
+#pragma unroll
+    for (int ch = 0; ch < NC; ++ch) {
+      float t[5];
+#pragma unroll
+      for (int m = 0; m < 5; ++m) t[m] = vert[ch][yy][col[m]];
+      lo[(size_t)(NC == 1 ? z : ch) * chan_stride +
+         (size_t)(y0 + yy) * lo_pitch + j] = pm::squeeze_combine(t, mul);
+    }
+  }
+}
+
+// float plane(s) as the hi level
+struct PlaneSrc {
+  typedef float Raw;
+  static constexpr int kChannels = 1;
+  const float* p;  // channel 0
+  int pitch;
+  size_t cs;
+  __device__ __forceinline__ float raw(int z, int row, int col) const {
+    return __ldg(p + z * cs + (size_t)row * pitch + col);
+  }
+  __device__ __forceinline__ float value(float v, int) const { return v; }
+};
+
+}  // namespace xp
