@@ -145,10 +145,13 @@ typedef struct {
   int keep_debug;   /* keep intermediates for xp_blender_debug_fetch        */
 } xp_blend_opts;
 
-/* multiblend::TimingResult (mb/multiblend.h:16-27), milliseconds on device */
+/* multiblend::TimingResult (mb/multiblend.h:16-27), milliseconds on device.
+ * Stages may overlap (side stream), so they need not add up to `total`;
+ * `pyramid_tail` is the wall time from the end of the seam stage to the end
+ * of `out` (mask pyramids, composite, collapse, out). */
 typedef struct {
   double images, seam, shrink_mask, copy, shrink, laplace, blend, collapse,
-      out, total;
+      out, total, pyramid_tail;
 } xp_timing;
 
 void xp_blend_opts_default(xp_blend_opts* o);

@@ -38,7 +38,7 @@ class BlendOpts(ctypes.Structure):
 class Timing(ctypes.Structure):
     _fields_ = [(k, ctypes.c_double) for k in
                 ("images", "seam", "shrink_mask", "copy", "shrink", "laplace",
-                 "blend", "collapse", "out", "total")]
+                 "blend", "collapse", "out", "total", "pyramid_tail")]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -80,7 +80,7 @@ void StageTimer::collect(double out[16]) {
 
 enum {
   ST_IMAGES = 0, ST_SEAM, ST_SHRINK_MASK, ST_COPY, ST_SHRINK, ST_LAPLACE,
-  ST_BLEND, ST_COLLAPSE, ST_OUT, ST_TOTAL
+  ST_BLEND, ST_COLLAPSE, ST_OUT, ST_TOTAL, ST_TAIL
 };
 
 struct Scope {

@@ -100,12 +100,18 @@ void launch_pad_level(const PyrGeom& g, float* pyr, int level, int channels,
 void launch_xor_sum(const PyrGeom& g, const float* pyr,
                     const uint8_t* xor_mask, int W, int H, double* d_partials,
                     double* d_sums, cudaStream_t s);
+// last collapse step fused with the xor sums; d_partials needs
+// collapse0_partials(g) doubles
+size_t collapse0_partials(const PyrGeom& g);
+void launch_collapse0_sum(const PyrGeom& g, float* pyr,
+                          const uint8_t* xor_mask, int W, double* d_partials,
+                          double* d_sums, cudaStream_t s);
 // offset add (from device scalars) + dither + clamp + round + planar/BGR pack
 void launch_out(const PyrGeom& g, const float* pyr, int W, int H, int out_bpp,
                 int dither, int apply_add, const CanvasStats* d_stats,
                 const double* d_sums, int in_bpp,
-                const uint8_t* full_mask, void* planes, void* bgr,
-                cudaStream_t s);
+                const uint8_t* full_mask, float* d_offset /* 4 floats */,
+                void* planes, void* bgr, cudaStream_t s);
 // pyramid_fused.cu: streaming path (level 0 and the Laplacian stay virtual)
 void launch_inpaint_gather(const ImgDev& im, int bpp, const u64* src_index,
                            cudaStream_t s);

@@ -55,6 +55,7 @@ struct Blender {
   DevBuf cover, seam_bwd, seam_fwd, labels, full_mask, xor_mask;
   std::vector<DevBuf> inp_fwd, inp_bwd;  // per image (empty if no holes)
   DevBuf img_pyr, mask_buf, out_pyr, planes, bgr;
+  std::vector<DevBuf> mask_bufs;     // streaming path: mask pyramid per image
   std::vector<DevBuf> img_pyrs;      // streaming path: levels >= 1 per image
   std::vector<PyrGeom> img_geoms;    // ... their geometry (compact stride)
   std::vector<float*> img_bases;     // ... base pointers for level offsets

@@ -131,19 +131,43 @@ void launch_shrink(const PyrGeom& g, float* pyr, int level, int channels,
 // ---------------------------------------------------------------------------
 // laplace / collapse: hi <- expand(lo) - hi, four hi samples per thread
 // ---------------------------------------------------------------------------
+// kSum: also accumulate, in double, the new hi values over the pixels of the
+// xor mask (offset correction, multiblend.cpp:1232-1258) -- used on the last
+// collapse step so level 0 is not read again for the sum. One partial per
+// block, combined in a fixed order by xor_sum_final_kernel: deterministic.
+template <bool kSum>
 __global__ void __launch_bounds__(256)
     laplace_kernel(float* __restrict__ hi, int hh, int hp, int xs, int ys,
                    const float* __restrict__ lo, int lo_pitch,
-                   size_t chan_stride) {
+                   size_t chan_stride, const uint8_t* __restrict__ xor_mask,
+                   int W, double* __restrict__ partials) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  if (4 * i >= hp || y >= hh) return;
-  const size_t co = (size_t)blockIdx.z * chan_stride;
-  float e[4];
-  expand4(lo + co, lo_pitch, xs, ys, i, y, e);
-  float4* dst = reinterpret_cast<float4*>(hi + co + (size_t)y * hp + 4 * i);
-  const float4 h = *dst;
-  *dst = make_float4(e[0] - h.x, e[1] - h.y, e[2] - h.z, e[3] - h.w);
+  double acc = 0.0;
+  if (4 * i < hp && y < hh) {
+    const size_t co = (size_t)blockIdx.z * chan_stride;
+    float e[4];
+    expand4(lo + co, lo_pitch, xs, ys, i, y, e);
+    float4* dst = reinterpret_cast<float4*>(hi + co + (size_t)y * hp + 4 * i);
+    const float4 h = *dst;
+    const float4 r = make_float4(e[0] - h.x, e[1] - h.y, e[2] - h.z, e[3] - h.w);
+    *dst = r;
+    if (kSum) {
+      const uint8_t* m = xor_mask + (size_t)y * W;
+      const int x = 4 * i;
+      if (x < W && m[x]) acc += r.x;
+      if (x + 1 < W && m[x + 1]) acc += r.y;
+      if (x + 2 < W && m[x + 2]) acc += r.z;
+      if (x + 3 < W && m[x + 3]) acc += r.w;
+    }
+  }
+  if (kSum) {
+    // one partial per warp (a warp is one row of the block): no block barrier
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(~0u, acc, o);
+    if (threadIdx.x == 0)
+      partials[(((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x +
+                blockIdx.x) * blockDim.y + threadIdx.y] = acc;
+  }
 }
 
 void launch_laplace(const PyrGeom& g, float* pyr, int level, int channels,
@@ -151,9 +175,9 @@ void launch_laplace(const PyrGeom& g, float* pyr, int level, int channels,
   const LevelGeom& H = g.lv[level];
   const LevelGeom& L = g.lv[level + 1];
   dim3 b(32, 8);
-  laplace_kernel<<<grid3(H.pitch / 4, H.h, channels, b), b, 0, s>>>(
+  laplace_kernel<false><<<grid3(H.pitch / 4, H.h, channels, b), b, 0, s>>>(
       pyr + H.offset, H.h, H.pitch, H.xs, H.ys, pyr + L.offset, L.pitch,
-      g.channel_floats);
+      g.channel_floats, nullptr, 0, nullptr);
   XP_LAUNCHED();
 }
 
@@ -336,14 +360,44 @@ __global__ void xor_sum_kernel(const float* __restrict__ lvl0, int pitch,
   }
 }
 
-__global__ void xor_sum_final_kernel(const double* __restrict__ partials,
-                                     int n, double* sums) {
-  // one warp per channel, fixed order
-  const int c = threadIdx.x >> 5, lane = threadIdx.x & 31;
+__global__ void __launch_bounds__(1024)
+    xor_sum_final_kernel(const double* __restrict__ partials, int n,
+                         double* sums) {
+  // one block per channel; fixed assignment and a fixed tree: deterministic
+  __shared__ double sh[1024];
+  const int c = blockIdx.x, t = threadIdx.x;
   double v = 0;
-  for (int i = lane; i < n; i += 32) v += partials[c * n + i];
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(~0u, v, o);
-  if (lane == 0) sums[c] = v;
+  for (int i = t; i < n; i += 1024) v += partials[(size_t)c * n + i];
+  sh[t] = v;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if (t < o) sh[t] += sh[t + o];
+    __syncthreads();
+  }
+  if (t == 0) sums[c] = sh[0];
+}
+
+size_t collapse0_partials(const PyrGeom& g) {
+  const LevelGeom& H = g.lv[0];
+  return (size_t)3 * div_up(H.pitch / 4, 32) * div_up(H.h, 8) * 8;
+}
+
+// last collapse step (level 1 -> 0 of the canvas pyramid) + the xor sums
+void launch_collapse0_sum(const PyrGeom& g, float* pyr,
+                          const uint8_t* xor_mask, int W, double* d_partials,
+                          double* d_sums, cudaStream_t s) {
+  const LevelGeom& H = g.lv[0];
+  const LevelGeom& L = g.lv[1];
+  dim3 b(32, 8);
+  dim3 gr = grid3(H.pitch / 4, H.h, 3, b);
+  laplace_kernel<true><<<gr, b, 0, s>>>(pyr + H.offset, H.h, H.pitch, H.xs,
+                                        H.ys, pyr + L.offset, L.pitch,
+                                        g.channel_floats, xor_mask, W,
+                                        d_partials);
+  XP_LAUNCHED();
+  xor_sum_final_kernel<<<3, 1024, 0, s>>>(d_partials, (int)(gr.x * gr.y * 8),
+                                        d_sums);
+  XP_LAUNCHED();
 }
 
 void launch_xor_sum(const PyrGeom& g, const float* pyr,
@@ -354,7 +408,7 @@ void launch_xor_sum(const PyrGeom& g, const float* pyr,
                                             g.channel_floats, xor_mask, W, H,
                                             d_partials);
   XP_LAUNCHED();
-  xor_sum_final_kernel<<<1, 96, 0, s>>>(d_partials, kSumBlocks, d_sums);
+  xor_sum_final_kernel<<<3, 1024, 0, s>>>(d_partials, kSumBlocks, d_sums);
   XP_LAUNCHED();
 }
 
@@ -363,61 +417,150 @@ void launch_xor_sum(const PyrGeom& g, const float* pyr,
 // with pixels outside the mask zeroed (pyramid.cpp:1563-1794,
 // blenders.cc:64-77,151-154)
 // ---------------------------------------------------------------------------
+// Four consecutive pixels of the flat H*W output per thread: the plane and
+// BGR stores are aligned vectors whatever W is; the level-0 rows (pitch != W)
+// are read as scalars.
 template <typename T>
-__global__ void out_kernel(const float* __restrict__ lvl0, int pitch,
-                           size_t chan_stride, int W, int H, int dither,
-                           int apply_add, const CanvasStats* __restrict__ stats,
-                           const double* __restrict__ sums, int in_bpp,
-                           const uint8_t* __restrict__ full_mask,
-                           T* __restrict__ planes, T* __restrict__ bgr) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  if (x >= W || y >= H) return;
-  const float maxv = sizeof(T) == 1 ? 255.0f : 65535.0f;
-  const int out_bpp = sizeof(T) * 8;
-  const size_t p = (size_t)y * W + x;
-  const unsigned long long total_px = stats->totals[3];
-  const bool masked = full_mask[p] != 0;
-  const float dv = dither ? pm::dither_value(y, x) : 0.0f;
+struct OutVec;
+template <>
+struct OutVec<uint8_t> {
+  static __device__ __forceinline__ void plane4(uint8_t* p, const uint8_t q[4]) {
+    *reinterpret_cast<uchar4*>(p) = make_uchar4(q[0], q[1], q[2], q[3]);
+  }
+  static __device__ __forceinline__ void bgr12(uint8_t* p, const uint8_t v[12]) {
+    uint32_t w[3];
 #pragma unroll
-  for (int c = 0; c < 3; ++c) {
-    float v = lvl0[(size_t)y * pitch + x + c * chan_stride];
-    if (apply_add && total_px != 0) {
+    for (int k = 0; k < 3; ++k)
+      w[k] = v[4 * k] | (v[4 * k + 1] << 8) | (v[4 * k + 2] << 16) |
+             ((uint32_t)v[4 * k + 3] << 24);
+    uint32_t* d = reinterpret_cast<uint32_t*>(p);
+    d[0] = w[0], d[1] = w[1], d[2] = w[2];
+  }
+};
+template <>
+struct OutVec<uint16_t> {
+  static __device__ __forceinline__ void plane4(uint16_t* p,
+                                                const uint16_t q[4]) {
+    *reinterpret_cast<ushort4*>(p) = make_ushort4(q[0], q[1], q[2], q[3]);
+  }
+  static __device__ __forceinline__ void bgr12(uint16_t* p,
+                                               const uint16_t v[12]) {
+    uint2* d = reinterpret_cast<uint2*>(p);
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      d[k] = make_uint2(v[4 * k] | ((uint32_t)v[4 * k + 1] << 16),
+                        v[4 * k + 2] | ((uint32_t)v[4 * k + 3] << 16));
+  }
+};
+
+// offset correction (multiblend.cpp:1259-1267): mean of the inputs minus mean
+// of the collapsed level 0 over the exclusively covered pixels, per channel;
+// out[3] != 0 tells the out kernel to apply it
+__global__ void offset_kernel(const CanvasStats* __restrict__ stats,
+                              const double* __restrict__ sums, int apply_add,
+                              int in_bpp, int out_bpp, float* out) {
+  const int c = threadIdx.x;
+  const unsigned long long total_px = stats->totals[3];
+  const bool on = apply_add && total_px != 0;
+  if (c < 3) {
+    float add = 0.0f;
+    if (on) {
       float avg = __ull2float_rn(stats->totals[c]) / __ull2float_rn(total_px);
       if (out_bpp != in_bpp) avg = out_bpp == 8 ? avg / 256 : avg * 256;
       const float output_avg =
           __double2float_rn(sums[c]) / __ull2float_rn(total_px);
-      const float add = avg - output_avg;
-      v = add + v;
+      add = avg - output_avg;
     }
-    if (dither) v = v + dv;
-    v = v > 0.0f ? v : 0.0f;
-    v = v < maxv ? v : maxv;
-    const T q = (T)__float2int_rn(v);
-    planes[(size_t)c * W * H + p] = q;
-    bgr[p * 3 + c] = masked ? q : (T)0;
+    out[c] = add;
+  } else if (c == 3) {
+    out[3] = on ? 1.0f : 0.0f;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+    out_kernel(const float* __restrict__ lvl0, int pitch, size_t chan_stride,
+               int W, int H, int dither, const float* __restrict__ offset,
+               const uint8_t* __restrict__ full_mask, T* __restrict__ planes,
+               T* __restrict__ bgr) {
+  const float maxv = sizeof(T) == 1 ? 255.0f : 65535.0f;
+  // offset correction, the same for every pixel: add[3] + "apply" flag
+  const float add0 = __ldg(offset + 0), add1 = __ldg(offset + 1),
+              add2 = __ldg(offset + 2);
+  const bool adding = __ldg(offset + 3) != 0.0f;
+  const float s_add[3] = {add0, add1, add2};
+  const size_t n = (size_t)W * H;
+  const size_t p0 = 4 * (blockIdx.x * (size_t)blockDim.x + threadIdx.x);
+  if (p0 >= n) return;
+  int y = (int)(p0 / W), x = (int)(p0 - (size_t)y * W);
+  T q[3][4];
+  bool masked[4];
+  int cnt = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if (p0 + k < n) {
+      masked[k] = full_mask[p0 + k] != 0;
+      const float dv = dither ? pm::dither_value(y, x) : 0.0f;
+      const size_t o = (size_t)y * pitch + x;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        float v = lvl0[o + c * chan_stride];
+        if (adding) v = s_add[c] + v;
+        if (dither) v = v + dv;
+        v = v > 0.0f ? v : 0.0f;
+        v = v < maxv ? v : maxv;
+        q[c][k] = (T)__float2int_rn(v);
+      }
+      ++cnt;
+      if (++x == W) x = 0, ++y;
+    } else {
+      masked[k] = false;
+      q[0][k] = q[1][k] = q[2][k] = 0;
+    }
+  }
+  if (cnt == 4) {
+    if ((n & 3) == 0) {  // plane bases c*n keep the vector alignment
+#pragma unroll
+      for (int c = 0; c < 3; ++c) OutVec<T>::plane4(planes + c * n + p0, q[c]);
+    } else {
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) planes[c * n + p0 + k] = q[c][k];
+    }
+    T v[12];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[3 * k + c] = masked[k] ? q[c][k] : (T)0;
+    OutVec<T>::bgr12(bgr + 3 * p0, v);
+  } else {
+    for (int k = 0; k < cnt; ++k)
+      for (int c = 0; c < 3; ++c) {
+        planes[c * n + p0 + k] = q[c][k];
+        bgr[3 * (p0 + k) + c] = masked[k] ? q[c][k] : (T)0;
+      }
   }
 }
 
 void launch_out(const PyrGeom& g, const float* pyr, int W, int H, int out_bpp,
                 int dither, int apply_add, const CanvasStats* d_stats,
                 const double* d_sums, int in_bpp, const uint8_t* full_mask,
-                void* planes, void* bgr, cudaStream_t s) {
+                float* d_offset, void* planes, void* bgr, cudaStream_t s) {
   const LevelGeom& L = g.lv[0];
-  dim3 b(32, 8);
-  dim3 gr = grid3(W, H, 1, b);
+  const size_t groups = div_up((size_t)W * H, (size_t)4);
+  const unsigned blocks = (unsigned)div_up(groups, (size_t)256);
+  offset_kernel<<<1, 32, 0, s>>>(d_stats, d_sums, apply_add, in_bpp, out_bpp,
+                                 d_offset);
+  XP_LAUNCHED();
   if (out_bpp == 8)
-    out_kernel<uint8_t><<<gr, b, 0, s>>>(pyr + L.offset, L.pitch,
-                                         g.channel_floats, W, H, dither,
-                                         apply_add, d_stats, d_sums, in_bpp,
-                                         full_mask, (uint8_t*)planes,
-                                         (uint8_t*)bgr);
+    out_kernel<uint8_t><<<blocks, 256, 0, s>>>(
+        pyr + L.offset, L.pitch, g.channel_floats, W, H, dither, d_offset,
+        full_mask, (uint8_t*)planes, (uint8_t*)bgr);
   else
-    out_kernel<uint16_t><<<gr, b, 0, s>>>(pyr + L.offset, L.pitch,
-                                          g.channel_floats, W, H, dither,
-                                          apply_add, d_stats, d_sums, in_bpp,
-                                          full_mask, (uint16_t*)planes,
-                                          (uint16_t*)bgr);
+    out_kernel<uint16_t><<<blocks, 256, 0, s>>>(
+        pyr + L.offset, L.pitch, g.channel_floats, W, H, dither, d_offset,
+        full_mask, (uint16_t*)planes, (uint16_t*)bgr);
   XP_LAUNCHED();
 }
 
