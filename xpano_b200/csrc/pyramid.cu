@@ -453,6 +453,11 @@ struct OutVec<uint16_t> {
   }
 };
 
+// pm::dither_value as a constant table (pyramid.cpp:1621-1634)
+__constant__ float kDitherTable[16] = {
+    -0.125f, 0.375f,  0.0f,     0.4999f, 0.125f,  -0.375f,  0.25f,   -0.25f,
+    -0.0625f, 0.4375f, -0.1875f, 0.3125f, 0.1875f, -0.3125f, 0.0625f, -0.4375f};
+
 // offset correction (multiblend.cpp:1259-1267): mean of the inputs minus mean
 // of the collapsed level 0 over the exclusively covered pixels, per channel;
 // out[3] != 0 tells the out kernel to apply it
@@ -489,10 +494,12 @@ __global__ void __launch_bounds__(256)
               add2 = __ldg(offset + 2);
   const bool adding = __ldg(offset + 3) != 0.0f;
   const float s_add[3] = {add0, add1, add2};
-  const size_t n = (size_t)W * H;
-  const size_t p0 = 4 * (blockIdx.x * (size_t)blockDim.x + threadIdx.x);
+  // the canvas has fewer than 2^32 pixels (checked by the blender)
+  const unsigned n = (unsigned)W * (unsigned)H;
+  const unsigned p0 = 4u * (blockIdx.x * blockDim.x + threadIdx.x);
   if (p0 >= n) return;
-  int y = (int)(p0 / W), x = (int)(p0 - (size_t)y * W);
+  int y = (int)(p0 / (unsigned)W), x = (int)(p0 - (unsigned)y * (unsigned)W);
+  const unsigned cs = (unsigned)chan_stride;
   T q[3][4];
   bool masked[4];
   int cnt = 0;
@@ -500,11 +507,11 @@ __global__ void __launch_bounds__(256)
   for (int k = 0; k < 4; ++k) {
     if (p0 + k < n) {
       masked[k] = full_mask[p0 + k] != 0;
-      const float dv = dither ? pm::dither_value(y, x) : 0.0f;
-      const size_t o = (size_t)y * pitch + x;
+      const float dv = dither ? kDitherTable[(y & 3) * 4 + (x & 3)] : 0.0f;
+      const unsigned o = (unsigned)y * (unsigned)pitch + (unsigned)x;
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        float v = lvl0[o + c * chan_stride];
+        float v = lvl0[o + c * cs];
         if (adding) v = s_add[c] + v;
         if (dither) v = v + dv;
         v = v > 0.0f ? v : 0.0f;
@@ -521,24 +528,25 @@ __global__ void __launch_bounds__(256)
   if (cnt == 4) {
     if ((n & 3) == 0) {  // plane bases c*n keep the vector alignment
 #pragma unroll
-      for (int c = 0; c < 3; ++c) OutVec<T>::plane4(planes + c * n + p0, q[c]);
+      for (int c = 0; c < 3; ++c)
+        OutVec<T>::plane4(planes + ((size_t)c * n + p0), q[c]);
     } else {
 #pragma unroll
       for (int c = 0; c < 3; ++c)
 #pragma unroll
-        for (int k = 0; k < 4; ++k) planes[c * n + p0 + k] = q[c][k];
+        for (int k = 0; k < 4; ++k) planes[(size_t)c * n + p0 + k] = q[c][k];
     }
     T v[12];
 #pragma unroll
     for (int k = 0; k < 4; ++k)
 #pragma unroll
       for (int c = 0; c < 3; ++c) v[3 * k + c] = masked[k] ? q[c][k] : (T)0;
-    OutVec<T>::bgr12(bgr + 3 * p0, v);
+    OutVec<T>::bgr12(bgr + 3 * (size_t)p0, v);
   } else {
     for (int k = 0; k < cnt; ++k)
       for (int c = 0; c < 3; ++c) {
-        planes[c * n + p0 + k] = q[c][k];
-        bgr[3 * (p0 + k) + c] = masked[k] ? q[c][k] : (T)0;
+        planes[(size_t)c * n + p0 + k] = q[c][k];
+        bgr[3 * ((size_t)p0 + k) + c] = masked[k] ? q[c][k] : (T)0;
       }
   }
 }

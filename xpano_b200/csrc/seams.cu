@@ -226,24 +226,40 @@ __global__ void __launch_bounds__(256)
   // one pass over the canvas: every pixel looks at the images whose bounding
   // box (plus the column right of it, where the reference's walk starts a new
   // run) contains it
+  // images whose box (plus the run-start column right of it) meets this
+  // block's 32 x 8 tile, in image order
   extern __shared__ ImgDev s_img[];
-  for (int i = threadIdx.y * blockDim.x + threadIdx.x; i < n;
-       i += blockDim.x * blockDim.y)
-    s_img[i] = imgs[i];
+  __shared__ int s_count;
+  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+  const int bx0 = blockIdx.x * blockDim.x, by0 = blockIdx.y * blockDim.y;
+  if (tid == 0) {
+    int m = 0;
+    for (int i = 0; i < n; ++i) {
+      const ImgDev im = imgs[i];
+      if (bx0 + 31 >= im.xpos && bx0 <= im.xpos + im.w &&
+          by0 + 7 >= im.ypos && by0 < im.ypos + im.h) {
+        s_img[m] = im;
+        s_img[m].tiff_h = i;  // the image's bit position
+        ++m;
+      }
+    }
+    s_count = m;
+  }
   __syncthreads();
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  const int x = bx0 + threadIdx.x;
+  const int y = by0 + threadIdx.y;
   if (x >= W || y >= H) return;
   C bits = 0;
   bool run_start = false;
-  for (int i = 0; i < n; ++i) {
-    const ImgDev& im = s_img[i];
+  const int m = s_count;
+  for (int k = 0; k < m; ++k) {
+    const ImgDev& im = s_img[k];
     const int lx = x - im.xpos, ly = y - im.ypos;
     if ((unsigned)ly >= (unsigned)im.h || (unsigned)lx > (unsigned)im.w) continue;
     if (lx < im.w) {
       const size_t p = (size_t)(im.top + ly) * im.tiff_w + im.left + lx;
       const bool op = px_opaque<BPP>(im.data, p);
-      if (op) bits |= (C)1 << i;
+      if (op) bits |= (C)1 << im.tiff_h;
       if (lx == 0 || op != px_opaque<BPP>(im.data, p - 1)) run_start = true;
     } else {
       run_start = true;
