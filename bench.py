@@ -50,6 +50,23 @@ CONFIGS = {
                                      math.radians(25)],
                  projection=2, fixed_levels=7, bpp=8, max_pano_mpx=100.0,
                  name="24x24MP u8 -> 100MP spherical (capped), 7 levels"),
+    # BASELINE.json configs[3]: 16-bit, cylindrical / Mercator, with the
+    # pitch/yaw/roll adjustment R <- M R (algorithm.cc:362-369), auto levels
+    "cfg4c": dict(n_cols=8, n_rows=2, w=5472, h=3648, focal=4000.0, step=0.6,
+                  pitches=[-math.radians(12), math.radians(12)], projection=1,
+                  fixed_levels=0, bpp=16, max_pano_mpx=1000.0,
+                  extra_rot=(10.0, 5.0, 3.0),
+                  name="16x20MP u16 cylindrical + rotation, auto levels"),
+    "cfg4m": dict(n_cols=8, n_rows=2, w=5472, h=3648, focal=4000.0, step=0.6,
+                  pitches=[-math.radians(12), math.radians(12)], projection=7,
+                  fixed_levels=0, bpp=16, max_pano_mpx=1000.0,
+                  extra_rot=(10.0, 5.0, 3.0),
+                  name="16x20MP u16 Mercator + rotation, auto levels"),
+    # BASELINE.json configs[4]: one group of the 64-group batch export
+    "cfg5": dict(n_cols=6, n_rows=1, w=4000, h=3000, focal=3600.0, step=0.66,
+                 pitches=[0.0], projection=2, fixed_levels=0, bpp=8,
+                 max_pano_mpx=100.0,
+                 name="6x12MP u8 spherical group (batch export), auto levels"),
     # reduced shapes for smoke runs
     "small": dict(n_cols=4, n_rows=1, w=800, h=600, focal=700.0, step=0.62,
                   pitches=[0.0], projection=2, fixed_levels=5, bpp=8,
@@ -80,9 +97,13 @@ def make_image(w, h, seed, bpp=8):
 def make_workload(cfg, group):
     from xpano_b200 import synthetic as co
     hfov = 2 * math.atan(cfg["w"] / 2 / cfg["focal"])
+    extra = None
+    if cfg.get("extra_rot"):
+        yaw, pitch, roll = (math.radians(v) for v in cfg["extra_rot"])
+        extra = co.rot(yaw, pitch, roll)
     Ks, Rs = co.make_cameras(cfg["n_cols"], cfg["n_rows"], cfg["w"], cfg["h"],
                              cfg["focal"], cfg["step"] * hfov, cfg["pitches"],
-                             2000 + 10 * group)
+                             2000 + 10 * group, extra=extra)
     ims = [make_image(cfg["w"], cfg["h"], 2000 + 10 * group + i, cfg["bpp"])
            for i in range(len(Ks))]
     return ims, Ks, Rs
