@@ -369,7 +369,7 @@ def run_ours(args, cfg):
     import threading
     W, H = info["width"], info["height"]
     dt = torch.uint8 if info["bpp"] == 8 else torch.uint16
-    in_flight = 2
+    in_flight = 3
     comps = [comp]
     for _ in range(in_flight - 1):
         c2 = xb.Composer(projection=cfg["projection"],

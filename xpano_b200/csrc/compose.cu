@@ -8,7 +8,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cmath>
+#include <condition_variable>
+#include <functional>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <thread>
 
@@ -28,7 +31,83 @@ struct SrcImage {
   float K[9], R[9];
 };
 
+// A few host threads that stay parked between panoramas: the per-image ROI
+// walk is ~0.25 ms of scalar trig per image and nothing else can start before
+// it, so it is spread over the images without paying thread creation per run.
+class HostPool {
+ public:
+  ~HostPool() {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      stop_ = true;
+    }
+    cv_.notify_all();
+    for (std::thread& t : threads_) t.join();
+  }
+  // runs fn(i) for i in [0, n) on the pool and the calling thread
+  void parallel_for(int n, const std::function<void(int)>& fn) {
+    if (n <= 1) {
+      for (int i = 0; i < n; ++i) fn(i);
+      return;
+    }
+    ensure(std::min(n - 1, 7));
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      fn_ = &fn;
+      next_ = 0;
+      total_ = n;
+      pending_ = n;
+      ++generation_;
+    }
+    cv_.notify_all();
+    work();
+    std::unique_lock<std::mutex> lk(mu_);
+    done_.wait(lk, [&] { return pending_ == 0; });
+    fn_ = nullptr;
+  }
+
+ private:
+  void ensure(int k) {
+    while ((int)threads_.size() < k)
+      threads_.emplace_back([this] {
+        unsigned long long seen = 0;
+        for (;;) {
+          {
+            std::unique_lock<std::mutex> lk(mu_);
+            cv_.wait(lk, [&] { return stop_ || generation_ != seen; });
+            if (stop_) return;
+            seen = generation_;
+          }
+          work();
+        }
+      });
+  }
+  void work() {
+    for (;;) {
+      const std::function<void(int)>* fn;
+      int i;
+      {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (!fn_ || next_ >= total_) return;
+        i = next_++;
+        fn = fn_;
+      }
+      (*fn)(i);
+      std::lock_guard<std::mutex> lk(mu_);
+      if (--pending_ == 0) done_.notify_all();
+    }
+  }
+  std::mutex mu_;
+  std::condition_variable cv_, done_;
+  std::vector<std::thread> threads_;
+  const std::function<void(int)>* fn_ = nullptr;
+  int next_ = 0, total_ = 0, pending_ = 0;
+  unsigned long long generation_ = 0;
+  bool stop_ = false;
+};
+
 struct Composer {
+  HostPool pool;
   xp_compose_opts opts;
   Warper warper;
   std::unique_ptr<Blender> blender;
@@ -132,25 +211,40 @@ struct Composer {
     // perimeter pixel): one thread per image
     const bool host_roi = warper.type == XP_PROJ_SPHERICAL ||
                           warper.type == XP_PROJ_CYLINDRICAL;
-    if (host_roi && n > 1) {
-      std::vector<std::thread> pool;
-      std::vector<std::string> errs(n);
-      for (int i = 0; i < n; ++i)
-        pool.emplace_back([&, i] {
-          try {
-            warper.warp_roi(src[i]->w, src[i]->h, src[i]->K, src[i]->R,
-                            &rois[4 * i]);
-          } catch (const std::exception& e) {
-            errs[i] = e.what();
-          }
-        });
-      for (std::thread& t : pool) t.join();
-      for (int i = 0; i < n; ++i)
-        if (!errs[i].empty()) fail(XP_ERR_INVALID, "%s", errs[i].c_str());
+    if (host_roi) {
+      // the walk of every image is cut in kParts pieces; merging the
+      // pieces' min/max is exact
+      constexpr int kParts = 4;
+      std::vector<Projector> proj(n);
+      std::vector<float> ext(4 * kParts * (size_t)n);
+      for (int i = 0; i < n; ++i) proj[i] = warper.projector(src[i]->K, src[i]->R);
+      pool.parallel_for(n * kParts, [&](int t) {
+        const int i = t / kParts, part = t % kParts;
+        Warper::border_extent(proj[i], src[i]->w, src[i]->h, part, kParts,
+                              &ext[4 * (size_t)t]);
+      });
+      for (int i = 0; i < n; ++i) {
+        float m[4] = {3.402823466e+38f, 3.402823466e+38f, -3.402823466e+38f,
+                      -3.402823466e+38f};
+        for (int k = 0; k < kParts; ++k) {
+          const float* e = &ext[4 * ((size_t)i * kParts + k)];
+          m[0] = e[0] < m[0] ? e[0] : m[0];
+          m[1] = e[1] < m[1] ? e[1] : m[1];
+          m[2] = m[2] < e[2] ? e[2] : m[2];
+          m[3] = m[3] < e[3] ? e[3] : m[3];
+        }
+        int roi[4];
+        warper.detect_roi(proj[i], src[i]->w, src[i]->h, roi, m);
+        int* r = &rois[4 * i];
+        r[0] = roi[0];
+        r[1] = roi[1];
+        r[2] = roi[2] - roi[0] + 1;
+        r[3] = roi[3] - roi[1] + 1;
+      }
     }
     for (int i = 0; i < n; ++i) {
       int* r = &rois[4 * i];
-      if (!(host_roi && n > 1))
+      if (!host_roi)
         warper.warp_roi(src[i]->w, src[i]->h, src[i]->K, src[i]->R, r);
       x0 = std::min<long>(x0, r[0]);
       y0 = std::min<long>(y0, r[1]);

@@ -145,14 +145,22 @@ __global__ void __launch_bounds__(128)
 // `flags` needs n_bands * flag_pitch bytes, flag_pitch >= chunks of the
 // widest band
 template <class P>
-static void launch_wavefront(const P& prob, int* counter, uint8_t* flags,
-                             int flag_pitch, cudaStream_t s) {
+static void launch_classify(const P& prob, uint8_t* flags, int flag_pitch,
+                            cudaStream_t s) {
   if (prob.n_bands <= 0) return;
-  XP_CUDA(cudaMemsetAsync(counter, 0, sizeof(int), s));
   const size_t tiles = (size_t)prob.n_bands * flag_pitch;
   classify_kernel<P><<<(unsigned)div_up(tiles, (size_t)4), 128, 0, s>>>(
       prob, flags, flag_pitch);
   XP_LAUNCHED();
+}
+
+template <class P>
+static void launch_wavefront(const P& prob, int* counter, uint8_t* flags,
+                             int flag_pitch, cudaStream_t s,
+                             bool classified = false) {
+  if (prob.n_bands <= 0) return;
+  XP_CUDA(cudaMemsetAsync(counter, 0, sizeof(int), s));
+  if (!classified) launch_classify(prob, flags, flag_pitch, s);
   const size_t smem = wf::tile_bytes<P>();
   const int blocks = std::min(prob.n_bands, 148 * 8);
   wavefront_kernel<P><<<blocks, 32 * wf::kWarpsPerBand, smem, s>>>(
@@ -333,10 +341,15 @@ static void seams_t(const void* cover, int W, int H, int reverse, u32* bwd,
                     cudaStream_t s) {
   const int n_bands = div_up(H, wf::kLanes);
   const int fp = wf::chunks_of(W);
+  // both classification passes depend on the cover map only: run them back
+  // to back, then the two dependent wavefronts (separate flag arrays)
+  uint8_t* flags_fwd = flags + (size_t)n_bands * fp;
   SeamBwd<C, F> pb{n_bands, W, H, (const C*)cover, bwd};
-  launch_wavefront(pb, counter, flags, fp, s);
   SeamFwd<C, F> pf{n_bands, W, H, reverse, (const C*)cover, bwd, fwd, labels};
-  launch_wavefront(pf, counter, flags, fp, s);
+  launch_classify(pb, flags, fp, s);
+  launch_classify(pf, flags_fwd, fp, s);
+  launch_wavefront(pb, counter, flags, fp, s, true);
+  launch_wavefront(pf, counter, flags_fwd, fp, s, true);
 }
 
 void launch_seams(const void* cover, int cover_bytes, int n_images, int W,

@@ -123,7 +123,34 @@ __global__ void roi_all_pixels_kernel(Projector p, int w, int h,
   }
 }
 
-void Warper::detect_roi(const Projector& p, int w, int h, int out[4]) {
+// part `part` of `parts` of the border walk (pure host math, thread-safe);
+// min/max merging of the parts is exact
+void Warper::border_extent(const Projector& p, int w, int h, int part,
+                           int parts, float ext[4]) {
+  Ext e;
+  float u, v;
+  const int n = w + h;
+  const int beg = (int)((long)n * part / parts),
+            end = (int)((long)n * (part + 1) / parts);
+  for (int k = beg; k < end; ++k) {
+    if (k < w) {
+      map_forward(p, (float)k, 0, u, v);
+      e.add(u, v);
+      map_forward(p, (float)k, (float)(h - 1), u, v);
+      e.add(u, v);
+    } else {
+      const int i = k - w;
+      map_forward(p, 0, (float)i, u, v);
+      e.add(u, v);
+      map_forward(p, (float)(w - 1), (float)i, u, v);
+      e.add(u, v);
+    }
+  }
+  ext[0] = e.tl_u, ext[1] = e.tl_v, ext[2] = e.br_u, ext[3] = e.br_v;
+}
+
+void Warper::detect_roi(const Projector& p, int w, int h, int out[4],
+                        const float* border_ext) {
   Ext e;
   float u, v;
   const bool by_border =
@@ -138,18 +165,13 @@ void Warper::detect_roi(const Projector& p, int w, int h, int out[4]) {
     map_forward(p, (float)(w - 1), (float)(h - 1), u, v);
     e.add(u, v);
   } else if (by_border) {
-    for (int i = 0; i < w; ++i) {
-      map_forward(p, (float)i, 0, u, v);
-      e.add(u, v);
-      map_forward(p, (float)i, (float)(h - 1), u, v);
-      e.add(u, v);
+    float ext[4];
+    if (!border_ext) {
+      border_extent(p, w, h, 0, 1, ext);
+      border_ext = ext;
     }
-    for (int i = 0; i < h; ++i) {
-      map_forward(p, 0, (float)i, u, v);
-      e.add(u, v);
-      map_forward(p, (float)(w - 1), (float)i, u, v);
-      e.add(u, v);
-    }
+    e.tl_u = border_ext[0], e.tl_v = border_ext[1];
+    e.br_u = border_ext[2], e.br_v = border_ext[3];
   } else {
     // O(area) forward map: data-parallel, done on the device
     ensure_device();

@@ -20,7 +20,11 @@ struct Warper {
   void ensure_device();
   Projector projector(const float* K, const float* R) const;
   // {tl.x, tl.y, br.x, br.y}, inclusive
-  void detect_roi(const Projector& p, int w, int h, int out[4]);
+  // border_ext: extent of the border walk if the caller already has it
+  void detect_roi(const Projector& p, int w, int h, int out[4],
+                  const float* border_ext = nullptr);
+  static void border_extent(const Projector& p, int w, int h, int part,
+                            int parts, float ext[4]);
   MapSrc prepare_map(const Projector& p, const int roi[4]);
   const void* stage_src(const void* src, int sw, int sh, size_t stride,
                         size_t row_bytes, int mem, size_t* dev_pitch);
