@@ -121,14 +121,17 @@ XP_HD u32 min32(u32 a, u32 b) { return a < b ? a : b; }
 //                images, u64: <= 63).
 //  kCoverDigest: u32, <= 24 images; what a step would otherwise recompute
 //                for every pixel is stored ready-made:
-//                [23:0] bits, [28:24] image an arbitrary seam picks (lowest,
-//                or highest with `reverse`), [29] run start, [30] exactly one
-//                image covers, [31] some image covers.
+//                [31:8] cover bits, reversed (image i at bit 31 - i, so that
+//                `word << label` brings the label's bit to the top: maskval
+//                is one funnel shift and one LOP3), [4:0] image an arbitrary
+//                seam picks (lowest, or highest with `reverse`), [5] run
+//                start, [6] exactly one image covers, [7] some image covers.
 enum { kCoverBits = 0, kCoverDigest = 1 };
 constexpr int kDigestMaxImages = 24;
 
 template <class C, int F>
 struct Cov {
+  static XP_HD u32 mask(u32 v, C c) { return mask32(v, bits(c)); }
   static XP_HD C bits(C c) { return c & ~CoverTraits<C>::rs_bit; }
   static XP_HD bool rs(C c) { return (c & CoverTraits<C>::rs_bit) != 0; }
   static XP_HD bool seed(C c) { return popc_c(bits(c)) == 1; }
@@ -140,18 +143,46 @@ struct Cov {
 };
 template <>
 struct Cov<u32, kCoverDigest> {
-  static XP_HD u32 bits(u32 c) { return c & 0xffffffu; }
-  static XP_HD bool rs(u32 c) { return (c & (1u << 29)) != 0; }
-  static XP_HD bool seed(u32 c) { return (c & (1u << 30)) != 0; }
-  static XP_HD bool any(u32 c) { return (c >> 31) != 0; }
-  static XP_HD int low(u32 c) { return (int)((c >> 24) & 31u); }
-  static XP_HD int pick(u32 c, int) { return (int)((c >> 24) & 31u); }
+  // maskval: the label's (reversed) cover bit shifted to the top, inverted,
+  // replaces v's flag. Labels of live values are < 24; bits 7..0 of the word
+  // can only reach the top for labels >= 24.
+  static XP_HD u32 mask(u32 v, u32 c) {
+#if defined(__CUDA_ARCH__)
+    // two instructions on the step's dependent chain: funnel shift with a
+    // wrapped amount, then (v & ~m) | (~top & m) as one LOP3 (LUT 0x72)
+    u32 top, r;
+    asm("shf.l.wrap.b32 %0, %1, %2, %3;" : "=r"(top) : "r"(0u), "r"(c), "r"(v));
+    asm("lop3.b32 %0, %1, %2, %3, 0x72;"
+        : "=r"(r)
+        : "r"(v), "r"(top), "r"(0x80000000u));
+    return r;
+#else
+    const u32 top = c << (v & 31u);
+    return (v & 0x7fffffffu) | (~top & kTop32);
+#endif
+  }
+  static XP_HD bool rs(u32 c) { return (c & (1u << 5)) != 0; }
+  static XP_HD bool seed(u32 c) { return (c & (1u << 6)) != 0; }
+  static XP_HD bool any(u32 c) { return (c & (1u << 7)) != 0; }
+  static XP_HD int low(u32 c) { return (int)(c & 31u); }
+  static XP_HD int pick(u32 c, int) { return (int)(c & 31u); }
 };
+XP_HD u32 brev32(u32 v) {
+#if defined(__CUDA_ARCH__)
+  return __brev(v);
+#else
+  v = ((v >> 1) & 0x55555555u) | ((v & 0x55555555u) << 1);
+  v = ((v >> 2) & 0x33333333u) | ((v & 0x33333333u) << 2);
+  v = ((v >> 4) & 0x0f0f0f0fu) | ((v & 0x0f0f0f0fu) << 4);
+  v = ((v >> 8) & 0x00ff00ffu) | ((v & 0x00ff00ffu) << 8);
+  return (v >> 16) | (v << 16);
+#endif
+}
 XP_HD u32 make_digest(u32 bits, bool run_start, int reverse) {
   const int cnt = popc_c(bits);
   const int pick = bits ? (reverse ? clz_top(bits) : ctz_c(bits)) : 0;
-  return bits | ((u32)pick << 24) | (run_start ? 1u << 29 : 0u) |
-         (cnt == 1 ? 1u << 30 : 0u) | (cnt != 0 ? 1u << 31 : 0u);
+  return brev32(bits) | (u32)pick | (run_start ? 1u << 5 : 0u) |
+         (cnt == 1 ? 1u << 6 : 0u) | (cnt != 0 ? 1u << 7 : 0u);
 }
 
 struct NoRow {};
@@ -208,11 +239,10 @@ struct SeamBwd {
   template <bool kEdgeX, bool kEdgeY>
   XP_HD u32 step(const wf::Band&, Row& row, bool active, int rho, int q, C cov,
                  In1, u32 last, u32 w0, u32 w1, u32 w2) const {
-    const C bits = Cv::bits(cov);
-    u32 cl = mask32(last + kD3, bits);
-    u32 c0 = mask32(w0 + kD4, bits);
-    const u32 c1 = mask32(w1 + kD3, bits);
-    u32 c2 = mask32(w2 + kD4, bits);
+    u32 cl = Cv::mask(last + kD3, cov);
+    u32 c0 = Cv::mask(w0 + kD4, cov);
+    const u32 c1 = Cv::mask(w1 + kD3, cov);
+    u32 c2 = Cv::mask(w2 + kD4, cov);
     if (kEdgeX) {
       if (q <= 0) cl = kInf32, c0 = kInf32;
       if (q >= W - 1) c2 = kInf32;
@@ -222,7 +252,7 @@ struct SeamBwd {
       const bool was_first = row.first_run;
       if (active && Cv::rs(cov)) row.first_run = false;
       // bottom row :333-346
-      const u32 bottom = was_first ? kDtMax32 : mask32(last, bits) + kD3;
+      const u32 bottom = was_first ? kDtMax32 : Cv::mask(last, cov) + kD3;
       if (rho == 0) d = bottom;
     }
     if (Cv::seed(cov)) d = (u32)Cv::low(cov);  // :327-331
@@ -280,14 +310,13 @@ struct SeamFwd {
   template <bool kEdgeX, bool kEdgeY>
   XP_HD u32 step(const wf::Band&, Row&, bool, int y, int x, u32 bw, C cov,
                  u32 last, u32 w0, u32 w1, u32 w2) const {
-    const C bits = Cv::bits(cov);
-    u32 c0 = mask32(w0 + kD4, bits);
-    u32 c1 = mask32(w1 + kD3, bits);
-    u32 c2 = mask32(w2 + kD4, bits);
+    u32 c0 = Cv::mask(w0 + kD4, cov);
+    u32 c1 = Cv::mask(w1 + kD3, cov);
+    u32 c2 = Cv::mask(w2 + kD4, cov);
     // the left neighbour is re-masked only on the top row, at x == 1 and at
     // a run start (:629-630, :704-705); raw inside a run (:750)
     u32 cl = last + kD3;
-    const u32 clm = mask32(cl, bits);
+    const u32 clm = Cv::mask(cl, cov);
     if (Cv::rs(cov) || (kEdgeY && y == 0) || (kEdgeX && x == 1)) cl = clm;
     if (kEdgeX) {
       if (x <= 0) cl = kInf32, c0 = kInf32;

@@ -98,7 +98,7 @@ struct DevCtx {
                  : "memory");
     return v;
   }
-  __device__ __forceinline__ void backoff() { __nanosleep(20); }
+  __device__ __forceinline__ void backoff() { __nanosleep(200); }
   __device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc,
                                            int bytes) {
     const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
