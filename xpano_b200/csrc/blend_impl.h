@@ -2,6 +2,7 @@
 #pragma once
 
 #include <cstdint>
+#include <vector>
 
 #include "common.h"
 #include "scan_problems.h"
@@ -87,6 +88,13 @@ void launch_laplace(const PyrGeom& g, float* pyr, int level, int channels,
                     cudaStream_t s);
 void launch_mask_level1(const uint8_t* labels, int CW, int CH, int image,
                         const MaskLevel& out, float* mask, cudaStream_t s);
+// all images, one launch per level
+size_t mask_batch_bytes(int n);
+void launch_mask_pyramids(const uint8_t* labels, int CW, int CH, int n,
+                          int n_levels,
+                          const std::vector<std::vector<MaskLevel>>& levels,
+                          const std::vector<float*>& masks, void* d_jobs,
+                          Mailbox& mbox, cudaStream_t s);
 void launch_mask_shrink(const MaskLevel& in, const MaskLevel& out, float* mask,
                         cudaStream_t s);
 // out level (+)= in level * mask (functions.cpp:319-411)

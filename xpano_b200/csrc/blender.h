@@ -51,7 +51,7 @@ struct Blender {
   std::vector<unsigned long long> transparent;
   PyrGeom out_g;
   DevBuf d_bbox, d_transparent, d_imgs, d_stats, d_jobs, d_bands, d_counter,
-      d_progress, d_flags_inp, d_partials, d_sums;
+      d_progress, d_flags_inp, d_partials, d_sums, d_mask_jobs;
   DevBuf cover, seam_bwd, seam_fwd, labels, full_mask, xor_mask;
   std::vector<DevBuf> inp_fwd, inp_bwd;  // per image (empty if no holes)
   DevBuf img_pyr, mask_buf, out_pyr, planes, bgr;

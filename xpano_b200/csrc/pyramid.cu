@@ -206,33 +206,124 @@ struct RectSrc {
   __device__ __forceinline__ int height() const { return ch; }
 };
 
-template <class Src>
-__device__ __forceinline__ float mask_squish(const Src& s, int r, int X) {
-  const int wmax = s.width() - 1;
-  float t[5];
-#pragma unroll
-  for (int k = 0; k < 5; ++k) t[k] = s.at(r, pm::clampi(2 * X - 4 + k, 0, wmax));
-  return pm::mask_h_combine(t[0], t[1], t[2], t[3], t[4]);
-}
+// A block produces 32 x 8 mask samples: the source window (19 rows x 67
+// columns after clamping) is staged in shared memory once, squished
+// horizontally per row, then combined vertically. The first line of a level
+// is the squished first source line verbatim (functions.cpp:195-214).
+constexpr int kMaskTileRows = 2 * 8 + 4, kMaskTileCols = 2 * 32 + 4;
 
 template <class Src>
-__global__ void mask_shrink_kernel(Src src, MaskLevel out, float* dst) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  if (x >= out.w || y >= out.h) return;
-  const int X = out.x0 + x, Y = out.y0 + y;
-  float v;
-  if (Y == 0) {  // functions.cpp:195-214: squished first line verbatim
-    v = mask_squish(src, 0, X);
-  } else {
-    const int hmax = src.height() - 1;
+__device__ __forceinline__ void mask_shrink_tile(const Src& src,
+                                                 const MaskLevel& out,
+                                                 float* dst) {
+  __shared__ float tile[kMaskTileRows][kMaskTileCols + 1];
+  __shared__ float hs[kMaskTileRows][32];
+  const int tid = threadIdx.y * 32 + threadIdx.x;
+  const int X0 = out.x0 + blockIdx.x * 32, Y0 = out.y0 + blockIdx.y * 8;
+  const int wmax = src.width() - 1, hmax = src.height() - 1;
+  const int rmin = pm::clampi(2 * Y0 - 4, 0, hmax);
+  const int rmax = pm::clampi(2 * (Y0 + 7), 0, hmax);
+  const int cmin = pm::clampi(2 * X0 - 4, 0, wmax);
+  const int cmax = pm::clampi(2 * (X0 + 31), 0, wmax);
+  const int nrows = rmax - rmin + 1, ncols = cmax - cmin + 1;
+  for (int i = tid; i < nrows * kMaskTileCols; i += 256) {
+    const int r = i / kMaskTileCols, c = i - r * kMaskTileCols;
+    if (c < ncols) tile[r][c] = src.at(rmin + r, cmin + c);
+  }
+  __syncthreads();
+  for (int i = tid; i < nrows * 32; i += 256) {
+    const int r = i >> 5, x = i & 31;
+    const int X = X0 + x;
     float t[5];
 #pragma unroll
     for (int k = 0; k < 5; ++k)
-      t[k] = mask_squish(src, pm::clampi(2 * Y - 4 + k, 0, hmax), X);
+      t[k] = tile[r][pm::clampi(2 * X - 4 + k, 0, wmax) - cmin];
+    hs[r][x] = pm::mask_h_combine(t[0], t[1], t[2], t[3], t[4]);
+  }
+  __syncthreads();
+  const int x = blockIdx.x * 32 + threadIdx.x;
+  const int y = blockIdx.y * 8 + threadIdx.y;
+  if (x >= out.w || y >= out.h) return;
+  const int Y = out.y0 + y;
+  float v;
+  if (Y == 0) {
+    v = hs[0 - rmin][threadIdx.x];
+  } else {
+    float t[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k)
+      t[k] = hs[pm::clampi(2 * Y - 4 + k, 0, hmax) - rmin][threadIdx.x];
     v = pm::mask_v_combine(t[0], t[1], t[2], t[3], t[4]);
   }
   dst[(size_t)y * out.w + x] = v;
+}
+
+template <class Src>
+__global__ void __launch_bounds__(256)
+    mask_shrink_kernel(Src src, MaskLevel out, float* dst) {
+  mask_shrink_tile(src, out, dst);
+}
+
+// one level of every image's mask pyramid in one launch (blockIdx.z = image)
+template <class Src>
+struct MaskJob {
+  Src src;
+  MaskLevel out;
+  float* dst;
+};
+
+template <class Src>
+__global__ void __launch_bounds__(256)
+    mask_shrink_batch_kernel(const MaskJob<Src>* __restrict__ jobs) {
+  const MaskJob<Src> j = jobs[blockIdx.z];
+  if ((int)blockIdx.x * 32 >= j.out.w || (int)blockIdx.y * 8 >= j.out.h) return;
+  mask_shrink_tile(j.src, j.out, j.dst);
+}
+
+size_t mask_batch_bytes(int n) {
+  return (size_t)n * std::max(sizeof(MaskJob<LabelSrc>), sizeof(MaskJob<RectSrc>));
+}
+
+// levels[i] / masks[i]: mask levels and buffer of image i. `d_jobs` is device
+// scratch of mask_batch_bytes(n) bytes per level, filled through the mailbox.
+void launch_mask_pyramids(const uint8_t* labels, int CW, int CH, int n,
+                          int n_levels,
+                          const std::vector<std::vector<MaskLevel>>& levels,
+                          const std::vector<float*>& masks, void* d_jobs,
+                          Mailbox& mbox, cudaStream_t s) {
+  for (int l = 1; l < n_levels; ++l) {
+    int gx = 0, gy = 0;
+    for (int i = 0; i < n; ++i) {
+      gx = std::max(gx, div_up(levels[i][l].w, 32));
+      gy = std::max(gy, div_up(levels[i][l].h, 8));
+    }
+    if (gx == 0 || gy == 0) continue;
+    unsigned char* slot =
+        static_cast<unsigned char*>(d_jobs) + (size_t)(l - 1) * mask_batch_bytes(n);
+    dim3 b(32, 8), g(gx, gy, n);
+    if (l == 1) {
+      std::vector<MaskJob<LabelSrc>> jobs(n);
+      for (int i = 0; i < n; ++i)
+        jobs[i] = MaskJob<LabelSrc>{LabelSrc{labels, CW, CH, i}, levels[i][1],
+                                    masks[i] + levels[i][1].offset};
+      mbox.to_device(slot, jobs.data(), sizeof(jobs[0]) * n, s);
+      mask_shrink_batch_kernel<<<g, b, 0, s>>>(
+          reinterpret_cast<const MaskJob<LabelSrc>*>(slot));
+    } else {
+      std::vector<MaskJob<RectSrc>> jobs(n);
+      for (int i = 0; i < n; ++i) {
+        const MaskLevel& in = levels[i][l - 1];
+        jobs[i] = MaskJob<RectSrc>{
+            RectSrc{masks[i] + in.offset, in.x0, in.y0, in.w, in.h, in.cw,
+                    in.ch},
+            levels[i][l], masks[i] + levels[i][l].offset};
+      }
+      mbox.to_device(slot, jobs.data(), sizeof(jobs[0]) * n, s);
+      mask_shrink_batch_kernel<<<g, b, 0, s>>>(
+          reinterpret_cast<const MaskJob<RectSrc>*>(slot));
+    }
+    XP_LAUNCHED();
+  }
 }
 
 void launch_mask_level1(const uint8_t* labels, int CW, int CH, int image,
