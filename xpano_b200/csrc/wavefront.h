@@ -13,9 +13,11 @@
 //     inputs and a storer warp drains the outputs, so that only the steps
 //     themselves are on the critical path (hand-over through double-buffered
 //     shared tiles and named barriers);
-//   * lane j runs 2 pixels behind lane j-1, so at every step the value it needs
-//     from the row above was produced by its neighbour lane one step earlier
-//     and arrives by a single shuffle; its own-row predecessor is a register;
+//   * lane j runs 3 pixels behind lane j-1, so at every step the value it needs
+//     from the row above was produced by its neighbour lane two steps earlier
+//     and arrives by a single shuffle that overlaps the step in between (2
+//     pixels would do, but put the shuffle latency on the chain of every
+//     step); its own-row predecessor is a register;
 //   * bands are claimed in order from an atomic counter; lane 0 of a band
 //     reads the last row of the previous band from global memory, polling
 //     the values themselves: outputs start as a sentinel no recurrence can
@@ -56,7 +58,7 @@ constexpr int kLanes = 32;
 constexpr int kChunk = 32;          // steps per tile
 constexpr int kTilePitch = kChunk + 1;
 constexpr int kTileElems = kLanes * kTilePitch;
-constexpr int kSkew = 2;            // pixels a lane trails the lane above it
+constexpr int kSkew = 3;            // pixels a lane trails the lane above it
 
 struct Band {
   int job;    // which image (inpaint) / 0 (seams)
@@ -172,7 +174,7 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
 
     if (role == kLoader) {
       // ---- inputs of the k-th unflagged chunk -> buffer k & 1: row r,
-      // positions c*32 - 2r + lane ----
+      // positions c*32 - kSkew*r + lane ----
       int k = 0;
       for (int c = 0; c < n_chunks; ++c) {
         if (skip_chunk(c)) continue;
@@ -211,7 +213,7 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
 #if defined(__CUDA_ARCH__)
 #pragma unroll 8
 #endif
-        for (int r = 0; r < kLanes; ++r) {
+        for (int r = kLanes - 1; r >= 0; --r) {  // hand-over row first
           const int q = s0 - kSkew * r + lane;
           if (B.rho0 + r < B.H && q >= 0 && q < W)
             prob.store(B, B.rho0 + r, q, out_tile[r * kTilePitch + lane]);
@@ -236,7 +238,9 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
         }
         return v;
       };
-      Val last = 0, w0 = 0, w1 = 0, w2 = 0;
+      // `older` is `last` one step back: with a skew of 3 the lane below needs
+      // it a full step after it was formed, so the shuffle is off the chain
+      Val last = 0, older = 0, w0 = 0, w1 = 0, w2 = 0;
       bool restore = true;  // lane state must be rebuilt from global memory
       int k = 0;
       XP_WF_CLOCK_BEGIN();
@@ -259,6 +263,8 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
           // band) were written by the classification pass
           const int qe = s0 - 1 - kSkew * lane;
           if (row_ok && qe >= 0 && qe < W) last = prob.load_val(B, rho, qe);
+          if (row_ok && qe >= 1 && qe - 1 < W)
+            older = prob.load_val(B, rho, qe - 1);
           if (row_ok && lane > 0) {
             if (qe >= 0 && qe < W) w1 = prob.load_val(B, rho - 1, qe);
             if (qe + 1 >= 0 && qe + 1 < W)
@@ -283,10 +289,12 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
         if (k >= 2) ctx.wait(kOutFree + (k & 1));
         XP_WF_CLOCK(2);
         {
-          // 32 skewed steps; everything but the chain through `last` and the
-          // shuffle is independent of the previous step. Chunks that touch
-          // no border of the job (first/last column, first row, rows past H)
-          // run the step variant without the border selects.
+          // 32 skewed steps. Chunks that touch no border of the job (first /
+          // last column, first row) run the step variant without the border
+          // selects. Inputs are read from the shared tiles a group of steps
+          // ahead and outputs are written a group at a time: a shared store
+          // between two loads would pin every load behind it and put its
+          // latency on the chain of every step.
           const In0* r0 = reinterpret_cast<const In0*>(
                               in0_base + (k & 1) * kB0 * kTileElems) +
                           lane * kTilePitch;
@@ -299,53 +307,69 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
           // too: nothing depends on them and the storer never writes them
           const bool interior_x = s0 - kSkew * (kLanes - 1) >= 2 &&
                                   s0 + kChunk - 1 <= W - 2;
-          auto steps = [&](auto edge_y) {
+          auto steps = [&](auto interior_tag, auto edge_y) {
+            constexpr bool kInterior = decltype(interior_tag)::value;
             constexpr bool kEdgeY = decltype(edge_y)::value;
+            constexpr int kGroup = 8;
+            constexpr int kGroups = kChunk / kGroup;
+            In0 ga[2][kGroup];
+            In1 gb[2][kGroup];
+            Val gh[2][kGroup];
+            auto fetch = [&](int g, int slot) {
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-            for (int t = 0; t < kChunk; ++t) {
-              const In0 a = r0[t];
-              In1 b = In1();
-              if (kB1) b = r1[t];
-              const Val hv = pv_row[t];
-              Val up = ctx.shfl_up1(last);
-              if (lane == 0) up = hv;
-              w0 = w1;
-              w1 = w2;
-              w2 = up;
-              last = prob.template step<false, kEdgeY>(
-                  B, row_state, true, rho, q0 + t, a, b, last, w0, w1, w2);
-              ro[t] = last;
+              for (int i = 0; i < kGroup; ++i) {
+                ga[slot][i] = r0[g * kGroup + i];
+                if (kB1) gb[slot][i] = r1[g * kGroup + i];
+                gh[slot][i] = pv_row[g * kGroup + i];
+              }
+            };
+            fetch(0, 0);
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (int g = 0; g < kGroups; ++g) {
+              if (g + 1 < kGroups) fetch(g + 1, (g + 1) & 1);
+              Val go[kGroup];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+              for (int i = 0; i < kGroup; ++i) {
+                const int t = g * kGroup + i;
+                const In0 a = ga[g & 1][i];
+                In1 b = In1();
+                if (kB1) b = gb[g & 1][i];
+                Val up = ctx.shfl_up1(older);
+                if (lane == 0) up = gh[g & 1][i];
+                older = last;
+                w0 = w1;
+                w1 = w2;
+                w2 = up;
+                if (kInterior) {
+                  last = prob.template step<false, kEdgeY>(
+                      B, row_state, true, rho, q0 + t, a, b, last, w0, w1, w2);
+                } else {
+                  const int q = q0 + t;
+                  const bool active = row_ok && q >= 0 && q < W;
+                  const Val nv = prob.template step<true, true>(
+                      B, row_state, active, rho, q, a, b, last, w0, w1, w2);
+                  if (active) last = nv;
+                }
+                go[i] = last;  // inactive positions are never stored
+              }
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+              for (int i = 0; i < kGroup; ++i) ro[g * kGroup + i] = go[i];
             }
           };
           if (interior_x && B.rho0 > 0) {
-            steps(std::false_type());
+            steps(std::true_type(), std::false_type());
           } else if (interior_x) {
-            steps(std::true_type());
+            steps(std::true_type(), std::true_type());
           } else {
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-            for (int t = 0; t < kChunk; ++t) {
-              const int q = q0 + t;
-              const bool active = row_ok && q >= 0 && q < W;
-              const In0 a = r0[t];
-              In1 b = In1();
-              if (kB1) b = r1[t];
-              const Val hv = pv_row[t];
-              Val up = ctx.shfl_up1(last);
-              if (lane == 0) up = hv;
-              w0 = w1;
-              w1 = w2;
-              w2 = up;
-              const Val nv = prob.template step<true, true>(
-                  B, row_state, active, rho, q, a, b, last, w0, w1, w2);
-              if (active) {
-                last = nv;
-                ro[t] = nv;
-              }
-            }
+            steps(std::false_type(), std::true_type());
           }
         }
         XP_WF_CLOCK(4);
