@@ -115,6 +115,14 @@ XP_HD u32 mask32(u32 v, C bits) {
   return (v & 0x7fffffffu) | ((covered ^ 1u) << 31);
 }
 XP_HD u32 min32(u32 a, u32 b) { return a < b ? a : b; }
+// min(a + b, c): one instruction (VIADDMNMX) on the device
+XP_HD u32 add_min32(u32 a, u32 b, u32 c) {
+#if defined(__CUDA_ARCH__)
+  return __viaddmin_u32(a, b, c);
+#else
+  return min32(a + b, c);
+#endif
+}
 
 // Two encodings of the per-pixel cover word.
 //  kCoverBits  : bit i = image i opaque, top bit = run start (u32: <= 31
@@ -132,6 +140,7 @@ constexpr int kDigestMaxImages = 24;
 template <class C, int F>
 struct Cov {
   static XP_HD u32 mask(u32 v, C c) { return mask32(v, bits(c)); }
+  static XP_HD u32 mask_if(u32 v, C c, bool on) { return on ? mask(v, c) : v; }
   static XP_HD C bits(C c) { return c & ~CoverTraits<C>::rs_bit; }
   static XP_HD bool rs(C c) { return (c & CoverTraits<C>::rs_bit) != 0; }
   static XP_HD bool seed(C c) { return popc_c(bits(c)) == 1; }
@@ -159,6 +168,19 @@ struct Cov<u32, kCoverDigest> {
 #else
     const u32 top = c << (v & 31u);
     return (v & 0x7fffffffu) | (~top & kTop32);
+#endif
+  }
+  // maskval when `on`, v otherwise: the LOP3's select mask carries the choice
+  static XP_HD u32 mask_if(u32 v, u32 c, bool on) {
+#if defined(__CUDA_ARCH__)
+    u32 top, r;
+    asm("shf.l.wrap.b32 %0, %1, %2, %3;" : "=r"(top) : "r"(0u), "r"(c), "r"(v));
+    asm("lop3.b32 %0, %1, %2, %3, 0x72;"
+        : "=r"(r)
+        : "r"(v), "r"(top), "r"(on ? 0x80000000u : 0u));
+    return r;
+#else
+    return on ? mask(v, c) : v;
 #endif
   }
   static XP_HD bool rs(u32 c) { return (c & (1u << 5)) != 0; }
@@ -239,23 +261,31 @@ struct SeamBwd {
   template <bool kEdgeX, bool kEdgeY>
   XP_HD u32 step(const wf::Band&, Row& row, bool active, int rho, int q, C cov,
                  In1, u32 last, u32 w0, u32 w1, u32 w2) const {
-    u32 cl = Cv::mask(last + kD3, cov);
+    // Everything but `last` is two steps old when it is needed, so all of
+    // it is folded into `pre` off the chain; the chain through `last` is
+    // maskval (2 instructions) and one add-min. The add commutes with
+    // maskval: it cannot carry into the label or the flag.
     u32 c0 = Cv::mask(w0 + kD4, cov);
     const u32 c1 = Cv::mask(w1 + kD3, cov);
     u32 c2 = Cv::mask(w2 + kD4, cov);
+    bool left = true;  // the (x+1, y) neighbour exists
     if (kEdgeX) {
-      if (q <= 0) cl = kInf32, c0 = kInf32;
+      if (q <= 0) left = false, c0 = kInf32;
       if (q >= W - 1) c2 = kInf32;
     }
-    u32 d = min32(min32(cl, c0), min32(c1, c2));
+    u32 pre = min32(c0, min32(c1, c2));
+    bool bottom_first = false;
     if (kEdgeY) {
       const bool was_first = row.first_run;
       if (active && Cv::rs(cov)) row.first_run = false;
-      // bottom row :333-346
-      const u32 bottom = was_first ? kDtMax32 : Cv::mask(last, cov) + kD3;
-      if (rho == 0) d = bottom;
+      // bottom row :333-346: the left neighbour alone, or DT_MAX
+      if (rho == 0) pre = kInf32, bottom_first = was_first;
     }
-    if (Cv::seed(cov)) d = (u32)Cv::low(cov);  // :327-331
+    // a seed's value is below anything a neighbour can offer :327-331
+    if (Cv::seed(cov)) pre = (u32)Cv::low(cov);
+    u32 d = add_min32(Cv::mask(last, cov), kD3, pre);
+    if (kEdgeX && !left) d = pre;
+    if (kEdgeY && bottom_first && !Cv::seed(cov)) d = kDtMax32;
     return d;
   }
 };
@@ -315,21 +345,29 @@ struct SeamFwd {
     u32 c2 = Cv::mask(w2 + kD4, cov);
     // the left neighbour is re-masked only on the top row, at x == 1 and at
     // a run start (:629-630, :704-705); raw inside a run (:750)
-    u32 cl = last + kD3;
-    const u32 clm = Cv::mask(cl, cov);
-    if (Cv::rs(cov) || (kEdgeY && y == 0) || (kEdgeX && x == 1)) cl = clm;
+    const bool remask =
+        Cv::rs(cov) || (kEdgeY && y == 0) || (kEdgeX && x == 1);
+    bool left = true;
     if (kEdgeX) {
-      if (x <= 0) cl = kInf32, c0 = kInf32;
+      if (x <= 0) left = false, c0 = kInf32;
       if (x >= W - 1) c2 = kInf32;
     }
     if (kEdgeY) {
       if (y == 0) c0 = kInf32, c1 = kInf32, c2 = kInf32;
     }
-    // ReadSeamDT value enters unmasked
-    u32 best = min32(min32(min32(bw, c0), min32(c1, c2)), cl);
-    if ((best & kTop32) && Cv::any(cov))  // arbitrary seam :732-742
-      best = kTop32 | (u32)Cv::pick(cov, reverse);
-    if (Cv::seed(cov)) best = (u32)Cv::low(cov);  // :607-616
+    // ReadSeamDT value enters unmasked. Everything but `last` is folded into
+    // `pre` off the chain (see SeamBwd::step):
+    //  * arbitrary seam :732-742 -- the minimum is flagged iff every
+    //    candidate is; flag|pick is below every other flagged value and above
+    //    every unflagged one, so substituting it for a flagged `pre` makes
+    //    the minimum come out right whatever the left neighbour is;
+    //  * a seed's value :607-616 is below anything a neighbour can offer.
+    u32 pre = min32(min32(bw, c0), min32(c1, c2));
+    if ((pre & kTop32) && Cv::any(cov))
+      pre = kTop32 | (u32)Cv::pick(cov, reverse);
+    if (Cv::seed(cov)) pre = (u32)Cv::low(cov);
+    u32 best = add_min32(Cv::mask_if(last, cov, remask), kD3, pre);
+    if (kEdgeX && !left) best = pre;
     return best;
   }
 };

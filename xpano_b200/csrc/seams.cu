@@ -14,8 +14,18 @@ static __host__ __device__ inline long long wf_now() {
   return 0;
 #endif
 }
-#define XP_WF_CLOCK_BEGIN() \
-  long long wf_prof[8] = {0, 0, 0, 0, 0, 0, 0, 0}, wf_prev = wf_now()
+static __host__ __device__ inline unsigned long long wf_ns() {
+#ifdef __CUDA_ARCH__
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+#else
+  return 0;
+#endif
+}
+#define XP_WF_CLOCK_BEGIN()                                             \
+  long long wf_prof[8] = {0, 0, 0, 0, 0, 0, 0, 0}, wf_prev = wf_now(); \
+  const unsigned long long wf_t0 = wf_ns()
 #define XP_WF_CLOCK(i)                \
   {                                   \
     const long long now = wf_now();   \
@@ -23,11 +33,11 @@ static __host__ __device__ inline long long wf_now() {
     wf_prev = now;                    \
   }
 #define XP_WF_CLOCK_END(band, nb, fast, slow)                                 \
-  if (lane == 0 && (band == (nb) / 2 || band == (nb)-1))                      \
-  printf("band %d/%d fast %d slow %d | prefetch %lld dep %lld cpwait %lld "   \
-         "check %lld steps %lld flush %lld publish %lld loop %lld\n",         \
-         band, nb, fast, slow, wf_prof[0], wf_prof[1], wf_prof[2],            \
-         wf_prof[3], wf_prof[4], wf_prof[5], wf_prof[6], wf_prof[7])
+  if (lane == 0 && (nb) < 200 && (band % 4 == 0 || band == (nb)-1))           \
+  printf("band %d/%d fast %d slow %d | t0 %llu t1 %llu dep %lld cpwait %lld " \
+         "steps %lld loop %lld\n",                                            \
+         band, nb, fast, slow, wf_t0 % 100000000ull, wf_ns() % 100000000ull,  \
+         wf_prof[1], wf_prof[2], wf_prof[4], wf_prof[7])
 #endif
 
 #include "blend_impl.h"
