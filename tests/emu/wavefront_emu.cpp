@@ -17,8 +17,10 @@
 #include <thread>
 #include <vector>
 
-static std::atomic<long> g_fast_chunks{0}, g_slow_chunks{0};
-#define XP_WF_STATS(fast) ((fast) ? ++g_fast_chunks : ++g_slow_chunks)
+static std::atomic<long> g_fast_chunks{0}, g_slow_chunks{0}, g_uncovered_chunks{0};
+// stepped chunks are reported per work item by wf::run; flagged chunks (never
+// visited by the wavefront) are counted by run_emulated
+#define XP_WF_STATS(stepped) (g_slow_chunks += (stepped))
 
 #include "../../xpano_b200/csrc/scan_problems.h"
 #include "../../xpano_b200/csrc/wavefront.h"
@@ -93,6 +95,14 @@ struct EmuCtx {
     w->bar.arrive_and_wait();
     return r;
   }
+  unsigned ballot(bool v) {
+    w->x[lane_] = v ? 1 : 0;
+    w->bar.arrive_and_wait();
+    unsigned r = 0;
+    for (int i = 0; i < 32; ++i) r |= w->x[i] ? 1u << i : 0u;
+    w->bar.arrive_and_wait();
+    return r;
+  }
   template <class T>
   T ld_poll(const T* p) {
     return __atomic_load_n(p, __ATOMIC_RELAXED);
@@ -132,14 +142,43 @@ void run_emulated(const P& prob, int n_blocks, int max_w) {
         });
     for (auto& t : threads) t.join();
   }
+  // work items, as segment_kernel builds them (one emulated warp)
+  std::vector<int> first(prob.n_bands + 1, 0);
+  std::vector<wf::Item> items(wf::max_items(prob.n_bands, flag_pitch));
+  {
+    std::vector<std::thread> threads;
+    for (int l = 0; l < 32; ++l)
+      threads.emplace_back([&, l] {
+        EmuCtx ctx{blocks[0].get(), &blocks[0]->warps[0], 0, l};
+        int total = 0;
+        for (int b = 0; b < prob.n_bands; ++b) {
+          const int nc = wf::chunks_of(prob.band(b).W);
+          if (l == 0) first[b] = total;
+          total += wf::segment_band(ctx, flags.data() + (size_t)b * flag_pitch,
+                                    nc, b, items.data() + total);
+        }
+        if (l == 0) first[prob.n_bands] = total;
+      });
+    for (auto& t : threads) t.join();
+    for (int b = 0; b < prob.n_bands; ++b) {
+      const int nc = wf::chunks_of(prob.band(b).W);
+      for (int c = 0; c < nc; ++c)
+      {
+        const uint8_t f = flags[(size_t)b * flag_pitch + c];
+        if (f == wf::kTileTrivial) ++g_fast_chunks;
+        if (f == wf::kTileUncovered) ++g_uncovered_chunks;
+      }
+    }
+  }
+  const int n_items = first[prob.n_bands];
   std::vector<std::thread> threads;
   for (int bi = 0; bi < n_blocks; ++bi)
     for (int r = 0; r < wf::kWarpsPerBand; ++r)
       for (int l = 0; l < 32; ++l)
         threads.emplace_back([&, bi, r, l] {
           EmuCtx ctx{blocks[bi].get(), &blocks[bi]->warps[r], r, l};
-          wf::run(ctx, prob, &counter, flags.data(), flag_pitch,
-                  smem[bi].data());
+          wf::run(ctx, prob, &counter, items.data(), &n_items, flags.data(),
+                  flag_pitch, smem[bi].data());
         });
   for (auto& t : threads) t.join();
 }
@@ -203,6 +242,9 @@ void emu_chunk_stats(long* fast, long* slow) {
   *fast = g_fast_chunks.exchange(0);
   *slow = g_slow_chunks.exchange(0);
 }
+
+// chunks classified as uncovered (cheaper step variant) since last call
+long emu_uncovered_chunks() { return g_uncovered_chunks.exchange(0); }
 
 void emu_seams(int n, const int* xpos, const int* ypos, const int* w,
                const int* h, const uint8_t* const* opaque, int W, int H,

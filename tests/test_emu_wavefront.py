@@ -101,6 +101,36 @@ def test_emulated_seams_seed_only_chunks(emu, seed, n, mode, reverse, wide,
     assert fast > 0 and slow > 0, (fast, slow)
 
 
+@pytest.mark.parametrize("reverse,wide,n_warps", [(0, 0, 3), (1, 0, 2),
+                                                  (0, 1, 2), (1, 2, 4)])
+def test_emulated_seams_uncovered_tiles(emu, reverse, wide, n_warps):
+    """Sparse placement: most 32x32 skewed tiles of the canvas are covered by
+    no image and take the wavefront's uncovered step variant (first band,
+    which keeps the border selects, and the bands below it). One image has a
+    mostly transparent bounding box, so run-start bits fall into such tiles
+    too."""
+    rng = np.random.default_rng(77)
+    W, H = 520, 150
+    frame = np.zeros((H - 10, W - 20), np.uint8)   # opaque corners only
+    frame[:12, :15] = 1
+    frame[-9:, -14:] = 1
+    frame[60:75, 240:262] = 1
+    blob = (rng.random((40, 60)) < 0.85).astype(np.uint8)
+    blob[0, :] = blob[-1, :] = blob[:, 0] = blob[:, -1] = 1
+    small = np.ones((25, 30), np.uint8)
+    ops = [frame, blob, small]
+    tpos = [(0, 0), (W - 60, H - 40), (200, 50)]
+    ref_l, ref_b, ref_f = mb_oracle.seams(ops, tpos, W, H,
+                                          reverse=bool(reverse), debug=True)
+    emu.emu_uncovered_chunks.restype = ctypes.c_long
+    emu.emu_uncovered_chunks()
+    l, b, f = _emu_seams(emu, ops, tpos, W, H, reverse, wide, n_warps)
+    assert emu.emu_uncovered_chunks() >= 20
+    assert np.array_equal(b, ref_b), "backward seam DT differs"
+    assert np.array_equal(f, ref_f), "forward seam DT differs"
+    assert np.array_equal(l, ref_l)
+
+
 def _chunk_stats(emu):
     fast, slow = ctypes.c_long(), ctypes.c_long()
     emu.emu_chunk_stats(ctypes.byref(fast), ctypes.byref(slow))

@@ -255,6 +255,28 @@ struct SeamBwd {
                           In1) const {
     return (u32)Cv::low(cov);
   }
+  // Tiles no image covers: maskval flags every candidate, so the step is a
+  // plain 3-4 chamfer minimum. The flag of the carried state is recomputed
+  // by every consumer (all of them go through maskval), so it may be set on
+  // entry and the chain through `last` is the add-min alone.
+  static constexpr bool kHasUncovered = true;
+  XP_HD bool uncovered(C cov, In1) const { return !Cv::any(cov); }
+  XP_HD u32 uncovered_up(u32 up) const { return up | kTop32; }
+  XP_HD u32 uncovered_last(u32 last) const { return last | kTop32; }
+  template <bool kEdgeY>
+  XP_HD u32 step_uncovered(Row& row, int rho, C cov, In1, u32 last, u32 w0,
+                           u32 w1, u32 w2) const {
+    u32 pre = add_min32(w2, kD4, add_min32(w1, kD3, w0 + kD4));
+    bool bottom_first = false;
+    if (kEdgeY) {
+      const bool was_first = row.first_run;
+      if (Cv::rs(cov)) row.first_run = false;
+      if (rho == 0) pre = kInf32, bottom_first = was_first;
+    }
+    u32 d = add_min32(last, kD3, pre);
+    if (kEdgeY && bottom_first) d = kDtMax32;
+    return d;
+  }
   // last = (x+1, y); w0 = (x+1, y+1); w1 = (x, y+1); w2 = (x-1, y+1).
   // kEdgeX = false: the caller guarantees 0 < q < W-1;
   // kEdgeY = false: the caller guarantees rho > 0.
@@ -333,6 +355,24 @@ struct SeamFwd {
   XP_HD u32 trivial_value(const wf::Band&, const Row&, int, int, u32,
                           C cov) const {
     return (u32)Cv::low(cov);
+  }
+  // Tiles no image covers (see SeamBwd): the row above is always re-masked,
+  // i.e. flagged; the left neighbour enters raw inside a run (:750), so its
+  // flag is kept as it is.
+  static constexpr bool kHasUncovered = true;
+  XP_HD bool uncovered(u32, C cov) const { return !Cv::any(cov); }
+  XP_HD u32 uncovered_up(u32 up) const { return up | kTop32; }
+  XP_HD u32 uncovered_last(u32 last) const { return last; }
+  template <bool kEdgeY>
+  XP_HD u32 step_uncovered(Row&, int y, u32 bw, C cov, u32 last, u32 w0,
+                           u32 w1, u32 w2) const {
+    u32 pre = add_min32(w2, kD4, add_min32(w1, kD3, w0 + kD4));
+    pre = min32(pre, bw);
+    bool remask = Cv::rs(cov);
+    if (kEdgeY) {
+      if (y == 0) pre = bw, remask = true;
+    }
+    return add_min32(last | (remask ? kTop32 : 0u), kD3, pre);
   }
   // last = (x-1, y); w0 = (x-1, y-1); w1 = (x, y-1); w2 = (x+1, y-1).
   // kEdgeX = false: the caller guarantees 1 < x < W-1;
@@ -449,6 +489,16 @@ struct InpaintFwd {
   XP_HD void store(const wf::Band& B, int y, int x, u64 v) const {
     jobs[B.job].fwd[(size_t)y * B.W + x] = v;
   }
+  // no uncovered-tile variant (wavefront.h); never called
+  static constexpr bool kHasUncovered = false;
+  XP_HD bool uncovered(In0, In1) const { return false; }
+  XP_HD u64 uncovered_up(u64 v) const { return v; }
+  XP_HD u64 uncovered_last(u64 v) const { return v; }
+  template <bool kEdgeY>
+  XP_HD u64 step_uncovered(Row&, int, In0, In1, u64 last, u64, u64,
+                           u64) const {
+    return last;
+  }
   XP_HD bool allow_trivial(const wf::Band&) const { return true; }
   XP_HD bool trivial(In0 px, In1) const { return pixel_opaque(px); }
   // `row` is the calling lane's; the wavefront asks for other rows of the
@@ -516,6 +566,16 @@ struct InpaintBwd {
   XP_HD u64 sentinel() const { return ~0ull; }
   XP_HD void store(const wf::Band& B, int rho, int q, u64 v) const {
     jobs[B.job].bwd[at(B, rho, q)] = v;
+  }
+  // no uncovered-tile variant (wavefront.h); never called
+  static constexpr bool kHasUncovered = false;
+  XP_HD bool uncovered(In0, In1) const { return false; }
+  XP_HD u64 uncovered_up(u64 v) const { return v; }
+  XP_HD u64 uncovered_last(u64 v) const { return v; }
+  template <bool kEdgeY>
+  XP_HD u64 step_uncovered(Row&, int, In0, In1, u64 last, u64, u64,
+                           u64) const {
+    return last;
   }
   XP_HD bool allow_trivial(const wf::Band&) const { return true; }
   XP_HD bool trivial(u64 fwd, In1) const { return (fwd >> 32) == 0; }

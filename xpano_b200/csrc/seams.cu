@@ -90,6 +90,9 @@ struct DevCtx {
   __device__ __forceinline__ bool all(bool v) {
     return __all_sync(0xffffffffu, v);
   }
+  __device__ __forceinline__ unsigned ballot(bool v) {
+    return __ballot_sync(0xffffffffu, v);
+  }
   // polling loads go to L2 every time (values are published by plain stores
   // of whole words; a word that is not the sentinel is final)
   __device__ __forceinline__ u32 ld_poll(const u32* p) {
@@ -132,13 +135,40 @@ struct DevCtx {
   }
 };
 
+// Scratch of one wavefront problem: the tile flags of the classification
+// pass, the first item of every band (+ the item count) and the item list.
+struct WfScratch {
+  uint8_t* flags;
+  int* first;       // n_bands + 1
+  wf::Item* items;  // wf::max_items(n_bands, flag_pitch)
+};
+static size_t wf_flag_bytes(int n_bands, int fp) {
+  return ((size_t)n_bands * fp + 15) & ~(size_t)15;
+}
+static size_t wf_first_bytes(int n_bands) {
+  return (sizeof(int) * ((size_t)n_bands + 1) + 15) & ~(size_t)15;
+}
+static size_t wf_scratch_bytes(int n_bands, int fp) {
+  return wf_flag_bytes(n_bands, fp) + wf_first_bytes(n_bands) +
+         ((sizeof(wf::Item) * wf::max_items(n_bands, fp) + 15) & ~(size_t)15);
+}
+static WfScratch wf_scratch(uint8_t* base, int n_bands, int fp) {
+  WfScratch w;
+  w.flags = base;
+  w.first = reinterpret_cast<int*>(base + wf_flag_bytes(n_bands, fp));
+  w.items = reinterpret_cast<wf::Item*>(base + wf_flag_bytes(n_bands, fp) +
+                                        wf_first_bytes(n_bands));
+  return w;
+}
+
 template <class P>
 __global__ void __launch_bounds__(32 * wf::kWarpsPerBand)
-    wavefront_kernel(P prob, int* counter, const uint8_t* flags,
+    wavefront_kernel(P prob, int* counter, const wf::Item* items,
+                     const int* n_items, const uint8_t* flags,
                      int flag_pitch) {
   extern __shared__ __align__(16) unsigned char smem[];
   DevCtx ctx;
-  wf::run(ctx, prob, counter, flags, flag_pitch, smem);
+  wf::run(ctx, prob, counter, items, n_items, flags, flag_pitch, smem);
 }
 
 template <class P>
@@ -152,30 +182,75 @@ __global__ void __launch_bounds__(128)
                     flag_pitch);
 }
 
-// `flags` needs n_bands * flag_pitch bytes, flag_pitch >= chunks of the
-// widest band
+// Work items of a classified problem (wavefront.h): one block; a warp per
+// band counts the runs of unflagged chunks, warp 0 turns the counts into
+// first-item indices (band-major order), then the runs are written.
 template <class P>
-static void launch_classify(const P& prob, uint8_t* flags, int flag_pitch,
+__global__ void __launch_bounds__(1024)
+    segment_kernel(P prob, const uint8_t* flags, int flag_pitch, int* first,
+                   wf::Item* items) {
+  DevCtx ctx;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warps = blockDim.x >> 5;
+  const int nb = prob.n_bands;
+  for (int b = warp; b < nb; b += warps) {
+    const int n = wf::segment_band(ctx, flags + (size_t)b * flag_pitch,
+                                   wf::chunks_of(prob.band(b).W), b,
+                                   (wf::Item*)nullptr);
+    if (lane == 0) first[b] = n;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    int carry = 0;
+    for (int base = 0; base < nb; base += 32) {
+      const int b = base + lane;
+      const int v = b < nb ? first[b] : 0;
+      int incl = v;
+      for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+      }
+      if (b < nb) first[b] = carry + incl - v;
+      carry += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (lane == 0) first[nb] = carry;
+  }
+  __syncthreads();
+  for (int b = warp; b < nb; b += warps)
+    wf::segment_band(ctx, flags + (size_t)b * flag_pitch,
+                     wf::chunks_of(prob.band(b).W), b, items + first[b]);
+}
+
+// `scratch` needs wavefront_flag_bytes(n_bands, widest band) bytes
+template <class P>
+static void launch_classify(const P& prob, uint8_t* scratch, int flag_pitch,
                             cudaStream_t s) {
   if (prob.n_bands <= 0) return;
+  const WfScratch w = wf_scratch(scratch, prob.n_bands, flag_pitch);
   const size_t tiles = (size_t)prob.n_bands * flag_pitch;
   classify_kernel<P><<<(unsigned)div_up(tiles, (size_t)4), 128, 0, s>>>(
-      prob, flags, flag_pitch);
+      prob, w.flags, flag_pitch);
+  XP_LAUNCHED();
+  segment_kernel<P><<<1, 1024, 0, s>>>(prob, w.flags, flag_pitch, w.first,
+                                       w.items);
   XP_LAUNCHED();
 }
 
 template <class P>
-static void launch_wavefront(const P& prob, int* counter, uint8_t* flags,
+static void launch_wavefront(const P& prob, int* counter, uint8_t* scratch,
                              int flag_pitch, cudaStream_t s,
                              bool classified = false) {
   if (prob.n_bands <= 0) return;
   XP_CUDA(cudaMemsetAsync(counter, 0, sizeof(int), s));
-  if (!classified) launch_classify(prob, flags, flag_pitch, s);
+  if (!classified) launch_classify(prob, scratch, flag_pitch, s);
+  const WfScratch w = wf_scratch(scratch, prob.n_bands, flag_pitch);
   const size_t smem = wf::tile_bytes<P>();
-  const int blocks = std::min(prob.n_bands, 148 * 8);
+  // the item count lives on the device: launch what can be resident, blocks
+  // without an item leave at once
+  const int blocks = (int)std::min<size_t>(
+      wf::max_items(prob.n_bands, flag_pitch), (size_t)148 * 8);
   wavefront_kernel<P><<<blocks, 32 * wf::kWarpsPerBand, smem, s>>>(
-      prob, counter, flags,
-                                               flag_pitch);
+      prob, counter, w.items, w.first + prob.n_bands, w.flags, flag_pitch);
   XP_LAUNCHED();
 }
 
@@ -328,7 +403,7 @@ void launch_cover(void* cover, int cover_bytes, int W, int H,
 // seams
 // ---------------------------------------------------------------------------
 size_t wavefront_flag_bytes(int n_bands, int max_w) {
-  return (size_t)n_bands * wf::chunks_of(max_w);
+  return wf_scratch_bytes(n_bands, wf::chunks_of(max_w));
 }
 
 __global__ void seam_unpack_kernel(const u32* __restrict__ in, size_t n,
@@ -353,7 +428,7 @@ static void seams_t(const void* cover, int W, int H, int reverse, u32* bwd,
   const int fp = wf::chunks_of(W);
   // both classification passes depend on the cover map only: run them back
   // to back, then the two dependent wavefronts (separate flag arrays)
-  uint8_t* flags_fwd = flags + (size_t)n_bands * fp;
+  uint8_t* flags_fwd = flags + wf_scratch_bytes(n_bands, fp);
   SeamBwd<C, F> pb{n_bands, W, H, (const C*)cover, bwd};
   SeamFwd<C, F> pf{n_bands, W, H, reverse, (const C*)cover, bwd, fwd, labels};
   launch_classify(pb, flags, fp, s);

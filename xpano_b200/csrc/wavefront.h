@@ -29,9 +29,14 @@
 //   * a fully parallel classification pass (classify_tile) runs first: pixels
 //     whose value follows from their own input alone (a seam seed, an opaque
 //     pixel) are written there, every other output becomes the sentinel, and
-//     each 32x32 skewed tile that consists of such pixels only is flagged. The
-//     wavefront skips flagged tiles and rebuilds its lane state from global
-//     memory when the next unflagged tile starts.
+//     each 32x32 skewed tile that consists of such pixels only is flagged;
+//   * nothing propagates through a flagged tile, so every maximal run of
+//     unflagged tiles of a band is a work item of its own (segment_count /
+//     segment_emit build the list, band-major): its lane state comes from
+//     global memory (all of it written by the classification pass) and it
+//     depends only on items of the previous band, which have smaller indices.
+//     Items are claimed in order from an atomic counter, so whatever an item
+//     waits for is running or done.
 //
 // Total depth is at most (W + 3H) steps instead of W*H. The code is written against a
 // small warp-context interface so the identical source runs on the device and
@@ -82,6 +87,14 @@ XP_HD int chunks_of(int W) {
   return (W + kSkew * (kLanes - 1) + kChunk - 1) / kChunk;
 }
 
+XP_HD int popc32(unsigned v) {
+#if defined(__CUDA_ARCH__)
+  return __popc(v);
+#else
+  return __builtin_popcount(v);
+#endif
+}
+
 constexpr int kWarpsPerBand = 3;  // compute, loader, storer
 enum Role { kCompute = 0, kLoader = 1, kStorer = 2 };
 // hand-over signals (one waiter, one signaller each), per buffer parity
@@ -98,6 +111,58 @@ constexpr size_t tile_bytes() {
          sizeof(typename P::Val) * kChunk;
 }
 
+// tile flags of the classification pass
+enum TileKind : uint8_t {
+  kTileGeneral = 0,
+  kTileTrivial = 1,    // every pixel follows from its own input: skipped
+  kTileUncovered = 2,  // P::uncovered() for every pixel: cheaper step variant
+};
+
+// A work item of the wavefront: the unflagged chunks [c0, c1) of one band.
+struct Item {
+  int band, c0, c1;
+};
+
+// Upper bound of the number of items of a problem with `n_bands` bands of at
+// most `flag_pitch` chunks (runs are separated by at least one flagged chunk).
+XP_HD size_t max_items(int n_bands, int flag_pitch) {
+  return (size_t)n_bands * (size_t)((flag_pitch + 1) / 2);
+}
+
+// Runs of unflagged chunks in one band, called by a whole warp. With
+// items == nullptr it only counts; otherwise item k of the band is written
+// to items[k] (starts and ends are ranked separately: the k-th end closes
+// the k-th start).
+template <class Ctx>
+XP_HD int segment_band(Ctx& ctx, const uint8_t* band_flags, int n_chunks,
+                       int band_idx, Item* items) {
+  const int lane = ctx.lane();
+  int n_start = 0, n_end = 0;
+  for (int base = 0; base < n_chunks; base += 32) {
+    const int c = base + lane;
+    const bool in = c < n_chunks;
+    const bool open = in && band_flags[c] != kTileTrivial;
+    const bool prev_closed =
+        c == 0 || (in && band_flags[c - 1] == kTileTrivial);
+    const bool next_closed =
+        c + 1 >= n_chunks || band_flags[c + 1] == kTileTrivial;
+    const unsigned bs = ctx.ballot(open && prev_closed);
+    const unsigned be = ctx.ballot(open && next_closed);
+    const unsigned below = (1u << lane) - 1u;
+    if (items) {
+      if (open && prev_closed) {
+        Item& it = items[n_start + popc32(bs & below)];
+        it.band = band_idx;
+        it.c0 = c;
+      }
+      if (open && next_closed) items[n_end + popc32(be & below)].c1 = c + 1;
+    }
+    n_start += popc32(bs);
+    n_end += popc32(be);
+  }
+  return n_start;
+}
+
 // Classification pass, one warp per (band, chunk) tile: writes the value of
 // every self-determined pixel, the sentinel everywhere else, and the tile's
 // "nothing to propagate here" flag.
@@ -112,7 +177,7 @@ XP_HD void classify_tile(Ctx& ctx, const P& prob, int band_idx, int c,
   if (c >= chunks_of(B.W)) return;
   const typename P::Row row = prob.row_init(B, B.rho0 + lane);
   const int s0 = c * kChunk;
-  bool all_trivial = true;
+  bool all_trivial = true, all_uncovered = P::kHasUncovered;
   for (int r = 0; r < kLanes; ++r) {
     const int q = s0 - kSkew * r + lane;
     if (B.rho0 + r < B.H && q >= 0 && q < B.W) {
@@ -124,20 +189,27 @@ XP_HD void classify_tile(Ctx& ctx, const P& prob, int band_idx, int c,
                  t ? prob.trivial_value(B, row, r - lane, q, a, b)
                    : prob.sentinel());
       all_trivial = all_trivial && t;
+      if constexpr (P::kHasUncovered)
+        all_uncovered = all_uncovered && prob.uncovered(a, b);
     }
   }
   all_trivial = ctx.all(all_trivial);
+  all_uncovered = ctx.all(all_uncovered);
   if (lane == 0)
     flags[(size_t)band_idx * flag_pitch + c] =
-        all_trivial && prob.allow_trivial(B) ? 1 : 0;
+        all_trivial && prob.allow_trivial(B) ? kTileTrivial
+        : all_uncovered                      ? kTileUncovered
+                                             : kTileGeneral;
 }
 
-// Runs problem P over all its bands. `counter` is a zero-initialised claim
-// counter; `flags` comes from classify_tile over every tile of the problem.
-// Called by all three warps of a block with the same arguments.
+// Runs problem P over all its work items. `counter` is a zero-initialised
+// claim counter; `items` / `*n_items` come from segment_band over `flags`,
+// the tile flags of classify_tile (flag_pitch per band). Called by all three warps of a block with the same
+// arguments.
 template <class Ctx, class P>
-XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
-               int flag_pitch, unsigned char* smem_block) {
+XP_HD void run(Ctx& ctx, const P& prob, int* counter, const Item* items,
+               const int* n_items, const uint8_t* flags, int flag_pitch,
+               unsigned char* smem_block) {
   using In0 = typename P::In0;
   using In1 = typename P::In1;
   using Val = typename P::Val;
@@ -154,30 +226,22 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
       kB0 >= kB1 ? base_a : base_a + 2 * kB1 * kTileElems;
   unsigned char* in1_base =
       kB0 >= kB1 ? base_a + 2 * kB0 * kTileElems : base_a;
+  const int total_items = *n_items;
 
   for (;;) {
-    int band_idx = 0;
-    if (role == kCompute && lane == 0) band_idx = ctx.atomic_add(counter, 1);
-    band_idx = ctx.block_bcast(band_idx);
-    if (band_idx >= prob.n_bands) break;
-    const Band B = prob.band(band_idx);
+    int item_idx = 0;
+    if (role == kCompute && lane == 0) item_idx = ctx.atomic_add(counter, 1);
+    item_idx = ctx.block_bcast(item_idx);
+    if (item_idx >= total_items) break;
+    const Item item = items[item_idx];
+    const Band B = prob.band(item.band);
     const int W = B.W;
-    const int n_chunks = chunks_of(W);
-    const uint8_t* band_flags = flags + (size_t)band_idx * flag_pitch;
-    // every role walks the same sequence of unflagged chunks
-    unsigned flag_word = 0;  // lane l: flag of chunk (c & ~31) + l
-    auto skip_chunk = [&](int c) -> bool {
-      if ((c & 31) == 0)
-        flag_word = c + lane < n_chunks ? band_flags[c + lane] : 0u;
-      return ctx.shfl_idx(flag_word, c & 31) != 0;
-    };
 
     if (role == kLoader) {
-      // ---- inputs of the k-th unflagged chunk -> buffer k & 1: row r,
+      // ---- inputs of the k-th chunk of the item -> buffer k & 1: row r,
       // positions c*32 - kSkew*r + lane ----
       int k = 0;
-      for (int c = 0; c < n_chunks; ++c) {
-        if (skip_chunk(c)) continue;
+      for (int c = item.c0; c < item.c1; ++c) {
         if (k >= 2) ctx.wait(kInFree + (k & 1));
         const int s0 = c * kChunk;
         In0* t0 = reinterpret_cast<In0*>(in0_base + (k & 1) * kB0 * kTileElems);
@@ -203,10 +267,9 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
       // the compute warp frees every buffer; absorb the last two
       for (int j = k < 2 ? 0 : k - 2; j < k; ++j) ctx.wait(kInFree + (j & 1));
     } else if (role == kStorer) {
-      // ---- outputs of the k-th unflagged chunk, coalesced per row ----
+      // ---- outputs of the k-th chunk, coalesced per row ----
       int k = 0;
-      for (int c = 0; c < n_chunks; ++c) {
-        if (skip_chunk(c)) continue;
+      for (int c = item.c0; c < item.c1; ++c) {
         ctx.wait(kOutFull + (k & 1));
         const int s0 = c * kChunk;
         const Val* out_tile = out_base + (k & 1) * kTileElems;
@@ -241,43 +304,45 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
       // `older` is `last` one step back: with a skew of 3 the lane below needs
       // it a full step after it was formed, so the shuffle is off the chain
       Val last = 0, older = 0, w0 = 0, w1 = 0, w2 = 0;
-      bool restore = true;  // lane state must be rebuilt from global memory
-      int k = 0;
       XP_WF_CLOCK_BEGIN();
-      int n_fast = 0, n_slow = 0;
-      for (int c = 0; c < n_chunks; ++c) {
+#ifdef XP_WF_STATS
+      if (lane == 0) XP_WF_STATS(item.c1 - item.c0);
+#endif
+      {
+        // Lane state at the end of chunk c0-1: all of its pixels in the rows
+        // of this band were written by the classification pass (the chunk is
+        // flagged, or lies before the first column). A row state that evolves
+        // along the row (P::Row) is only kept by problems whose first band
+        // is never flagged, i.e. starts at chunk 0.
+        const int s0 = item.c0 * kChunk;
+        const int qe = s0 - 1 - kSkew * lane;
+        if (row_ok && qe >= 0 && qe < W) last = prob.load_val(B, rho, qe);
+        if (row_ok && qe >= 1 && qe - 1 < W)
+          older = prob.load_val(B, rho, qe - 1);
+        if (row_ok && lane > 0) {
+          if (qe >= 0 && qe < W) w1 = prob.load_val(B, rho - 1, qe);
+          if (qe + 1 >= 0 && qe + 1 < W)
+            w2 = prob.load_val(B, rho - 1, qe + 1);
+        }
+        if (B.dep >= 0) {
+          // lane 0's row above belongs to the previous band: lanes 0/1
+          // fetch positions s0-1 and s0
+          const Val pr = poll(lane < 2, s0 - 1 + lane);
+          const Val p0 = ctx.shfl_idx(pr, 0), p1 = ctx.shfl_idx(pr, 1);
+          if (lane == 0) w1 = p0, w2 = p1;
+        }
+      }
+      int k = 0;
+      const uint8_t* band_flags = flags + (size_t)item.band * flag_pitch;
+      unsigned kind_word = 0;  // lane l: kind of chunk c0 + (k & ~31) + l
+      for (int c = item.c0; c < item.c1; ++c) {
         const int s0 = c * kChunk;
         XP_WF_CLOCK(7);
-        const bool skip = skip_chunk(c);
-#ifdef XP_WF_STATS
-        if (lane == 0) XP_WF_STATS(skip);
-#endif
-        n_fast += skip ? 1 : 0;
-        n_slow += skip ? 0 : 1;
-        if (skip) {
-          restore = true;
-          continue;
-        }
-        if (restore) {
-          // state at the end of chunk c-1, all of whose pixels (rows of this
-          // band) were written by the classification pass
-          const int qe = s0 - 1 - kSkew * lane;
-          if (row_ok && qe >= 0 && qe < W) last = prob.load_val(B, rho, qe);
-          if (row_ok && qe >= 1 && qe - 1 < W)
-            older = prob.load_val(B, rho, qe - 1);
-          if (row_ok && lane > 0) {
-            if (qe >= 0 && qe < W) w1 = prob.load_val(B, rho - 1, qe);
-            if (qe + 1 >= 0 && qe + 1 < W)
-              w2 = prob.load_val(B, rho - 1, qe + 1);
-          }
-          if (B.dep >= 0) {
-            // lane 0's row above belongs to the previous band: lanes 0/1
-            // fetch positions s0-1 and s0
-            const Val pr = poll(lane < 2, s0 - 1 + lane);
-            const Val p0 = ctx.shfl_idx(pr, 0), p1 = ctx.shfl_idx(pr, 1);
-            if (lane == 0) w1 = p0, w2 = p1;
-          }
-          restore = false;
+        bool uncovered = false;
+        if constexpr (P::kHasUncovered) {
+          if ((k & 31) == 0)
+            kind_word = c + lane < item.c1 ? band_flags[c + lane] : 0u;
+          uncovered = ctx.shfl_idx(kind_word, k & 31) == kTileUncovered;
         }
         // previous band's last row, positions s0+1 .. s0+32 (one per lane)
         Val pv = 0;
@@ -307,9 +372,15 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
           // too: nothing depends on them and the storer never writes them
           const bool interior_x = s0 - kSkew * (kLanes - 1) >= 2 &&
                                   s0 + kChunk - 1 <= W - 2;
-          auto steps = [&](auto interior_tag, auto edge_y) {
+          auto steps = [&](auto interior_tag, auto edge_y, auto uncov_tag) {
             constexpr bool kInterior = decltype(interior_tag)::value;
             constexpr bool kEdgeY = decltype(edge_y)::value;
+            constexpr bool kUncovered = decltype(uncov_tag)::value;
+            if constexpr (kUncovered) {
+              w1 = prob.uncovered_up(w1);
+              w2 = prob.uncovered_up(w2);
+              last = prob.uncovered_last(last);
+            }
             constexpr int kGroup = 8;
             constexpr int kGroups = kChunk / kGroup;
             In0 ga[2][kGroup];
@@ -342,11 +413,15 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
                 if (kB1) b = gb[g & 1][i];
                 Val up = ctx.shfl_up1(older);
                 if (lane == 0) up = gh[g & 1][i];
+                if constexpr (kUncovered) up = prob.uncovered_up(up);
                 older = last;
                 w0 = w1;
                 w1 = w2;
                 w2 = up;
-                if (kInterior) {
+                if constexpr (kUncovered) {
+                  last = prob.template step_uncovered<kEdgeY>(
+                      row_state, rho, a, b, last, w0, w1, w2);
+                } else if (kInterior) {
                   last = prob.template step<false, kEdgeY>(
                       B, row_state, true, rho, q0 + t, a, b, last, w0, w1, w2);
                 } else {
@@ -364,12 +439,21 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
               for (int i = 0; i < kGroup; ++i) ro[g * kGroup + i] = go[i];
             }
           };
+          auto interior_steps = [&](auto edge_y) {
+            if constexpr (P::kHasUncovered) {
+              if (uncovered) {
+                steps(std::true_type(), edge_y, std::true_type());
+                return;
+              }
+            }
+            steps(std::true_type(), edge_y, std::false_type());
+          };
           if (interior_x && B.rho0 > 0) {
-            steps(std::true_type(), std::false_type());
+            interior_steps(std::false_type());
           } else if (interior_x) {
-            steps(std::true_type(), std::true_type());
+            interior_steps(std::true_type());
           } else {
-            steps(std::false_type(), std::true_type());
+            steps(std::false_type(), std::true_type(), std::false_type());
           }
         }
         XP_WF_CLOCK(4);
@@ -379,11 +463,9 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const uint8_t* flags,
       }
       // the storer frees every output tile; absorb the last two
       for (int j = k < 2 ? 0 : k - 2; j < k; ++j) ctx.wait(kOutFree + (j & 1));
-      (void)n_fast;
-      (void)n_slow;
-      XP_WF_CLOCK_END(band_idx, prob.n_bands, n_fast, n_slow);
+      XP_WF_CLOCK_END(item.band, prob.n_bands, item.c0, item.c1);
     }
-    ctx.block_sync();  // tiles and signals are quiet before the next band
+    ctx.block_sync();  // tiles and signals are quiet before the next item
   }
 }
 
