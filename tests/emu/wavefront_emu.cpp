@@ -48,7 +48,7 @@ struct EmuCtx {
   EmuBlock* blk;
   EmuWarp* w;
   int role_, lane_;
-  int seen[wf::kSignals] = {0, 0, 0, 0, 0, 0, 0, 0};
+  int seen[wf::kSignals] = {};
   int lane() const { return lane_; }
   int role() const { return role_; }
   int atomic_add(int* p, int v) {
@@ -112,7 +112,8 @@ struct EmuCtx {
     memcpy(dst, src, (size_t)bytes);
   }
   void cp_commit() {}
-  void cp_wait_all() {}
+  template <int kPending>
+  void cp_wait_pending() {}
 };
 
 template <class P>

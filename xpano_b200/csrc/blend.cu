@@ -100,11 +100,14 @@ struct Scope {
 Blender::~Blender() {
   // buffers go back to the caching pool: nothing may still be using them
   if (side_stream) cudaStreamSynchronize(side_stream);
+  if (aux_stream) cudaStreamSynchronize(aux_stream);
   if (stream) cudaStreamSynchronize(stream);
   if (ev_fork) cudaEventDestroy(ev_fork);
   if (ev_join) cudaEventDestroy(ev_join);
   if (ev_cover) cudaEventDestroy(ev_cover);
+  if (ev_aux) cudaEventDestroy(ev_aux);
   if (side_stream) cudaStreamDestroy(side_stream);
+  if (aux_stream) cudaStreamDestroy(aux_stream);
   if (own_stream) cudaStreamDestroy(own_stream);
 }
 
@@ -119,6 +122,8 @@ void Blender::ensure_device() {
     XP_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
     XP_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
     XP_CUDA(cudaEventCreateWithFlags(&ev_cover, cudaEventDisableTiming));
+    XP_CUDA(cudaStreamCreateWithFlags(&aux_stream, cudaStreamNonBlocking));
+    XP_CUDA(cudaEventCreateWithFlags(&ev_aux, cudaEventDisableTiming));
   }
 }
 

@@ -121,8 +121,12 @@ void launch_out(const PyrGeom& g, const float* pyr, int W, int H, int out_bpp,
                 const uint8_t* full_mask, float* d_offset /* 4 floats */,
                 void* planes, void* bgr, cudaStream_t s);
 // pyramid_fused.cu: streaming path (level 0 and the Laplacian stay virtual)
-void launch_inpaint_gather(const ImgDev& im, int bpp, const u64* src_index,
-                           cudaStream_t s);
+// gather of the inpaint fill over the unflagged tiles of the backward pass
+// (`scratch` as passed to launch_inpaint)
+void launch_inpaint_gather_tiles(const InpaintJob* d_jobs,
+                                 const InpaintBandRef* d_bands, int n_bands,
+                                 int max_w, int bpp, const uint8_t* scratch,
+                                 cudaStream_t s);
 void launch_shrink0(const ImgDev& im, int bpp, float mul, const PyrGeom& g,
                     float* pyr, cudaStream_t s);
 void launch_lapcomp(const ImgDev& im, int bpp, float mul, const PyrGeom& in_g,

@@ -36,7 +36,9 @@ struct Blender {
   xp_blend_opts opts;
   cudaStream_t stream = nullptr, own_stream = nullptr;
   cudaStream_t side_stream = nullptr;  // inpaint runs beside the seam passes
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_cover = nullptr;
+  cudaStream_t aux_stream = nullptr;   // cover-only statistics
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_cover = nullptr,
+              ev_aux = nullptr;
   bool external_stream = false;
   int roi[4] = {0, 0, 0, 0};
   std::vector<std::unique_ptr<Fed>> fed;

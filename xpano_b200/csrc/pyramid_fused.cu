@@ -2,7 +2,8 @@
 //
 //   * level 0 of an image pyramid is never materialised as floats: the
 //     inpainted pixels stay in the interleaved source buffer (the inpaint
-//     result is gathered into it in place) and are converted on the fly;
+//     result is gathered into it in place, seams.cu) and are converted on the
+//     fly;
 //   * the Laplacian is never materialised either: expand(lo) - hi is formed in
 //     registers and multiplied straight into the canvas pyramid, and only
 //     where the image's mask is non-zero.
@@ -49,40 +50,6 @@ template <int BPP>
 static Level0<BPP> make_level0(const ImgDev& im, float mul) {
   return Level0<BPP>{static_cast<const typename PixelOf<BPP>::type*>(im.data),
                      im.tiff_w, im.left, im.top, im.w, im.h, mul};
-}
-
-// ---------------------------------------------------------------------------
-// inpaint gather, in place: every non-opaque bbox pixel takes the colour of
-// its source (always an opaque pixel, never written here); alpha is kept so
-// the cover map, which may be read concurrently, is unaffected
-// ---------------------------------------------------------------------------
-template <int BPP>
-__global__ void inpaint_gather_kernel(ImgDev im, const u64* __restrict__ src) {
-  typedef typename PixelOf<BPP>::type Px;
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  if (x >= im.w || y >= im.h) return;
-  Px* data = static_cast<Px*>(const_cast<void*>(im.data));
-  const size_t me = (size_t)(im.top + y) * im.tiff_w + im.left + x;
-  const Px mine = data[me];
-  if (pixel_opaque(mine)) return;
-  const u32 from = (u32)src[(size_t)y * im.w + x];
-  if (from == (u32)me) return;
-  const Px colour = data[from];
-  const int ab = BPP == 8 ? 24 : 48;
-  const Px amask = (Px)(BPP == 8 ? 0xffull : 0xffffull) << ab;
-  data[me] = (colour & ~amask) | (mine & amask);
-}
-
-void launch_inpaint_gather(const ImgDev& im, int bpp, const u64* src_index,
-                           cudaStream_t s) {
-  dim3 b(32, 8);
-  dim3 g(div_up(im.w, 32), div_up(im.h, 8));
-  if (bpp == 8)
-    inpaint_gather_kernel<8><<<g, b, 0, s>>>(im, src_index);
-  else
-    inpaint_gather_kernel<16><<<g, b, 0, s>>>(im, src_index);
-  XP_LAUNCHED();
 }
 
 // ---------------------------------------------------------------------------
@@ -161,7 +128,10 @@ __device__ __forceinline__ int floor_div4(int a) {
   return a >= 0 ? a >> 2 : -((-a + 3) >> 2);
 }
 
-template <class Hi>
+// kFirstTouch (level 0): the label map gives every canvas pixel to exactly
+// one image with weight 1, so the level is written once instead of zeroed
+// and accumulated into (0 + x, as the reference computes it).
+template <class Hi, bool kFirstTouch>
 __global__ void __launch_bounds__(256)
     lapcomp_kernel(Hi hi, int in_w, int in_h, int xs, int ys,
                    const float* __restrict__ lo, int lo_pitch, size_t in_cs,
@@ -220,7 +190,8 @@ __global__ void __launch_bounds__(256)
     float* row = out + c * out_cs + (size_t)Y * out_pitch + X0;
 #pragma unroll
     for (int k = 0; k < 4; ++k)
-      if (mv[k] != 0.0f) row[k] = row[k] + lap[c][k] * mv[k];
+      if (mv[k] != 0.0f)
+        row[k] = (kFirstTouch ? 0.0f : row[k]) + lap[c][k] * mv[k];
   }
 }
 
@@ -244,22 +215,21 @@ void launch_lapcomp(const ImgDev& im, int bpp, float mul, const PyrGeom& in_g,
   float* out = out_pyr + O.offset;
   const float* mk = level == 0 ? nullptr : mask + m.offset;
   const uint8_t* lb = level == 0 ? labels : nullptr;
-#define XP_LAPCOMP(HI)                                                       \
-  lapcomp_kernel<<<gr, b, 0, s>>>(HI, I.w, I.h, I.xs, I.ys, lo, Lo.pitch,    \
-                                  in_g.channel_floats, out, O.pitch,         \
-                                  out_g.channel_floats, x_off, y_off, m, mk, \
-                                  lb, image)
+#define XP_LAPCOMP(HI, FIRST)                                                \
+  lapcomp_kernel<decltype(HI), FIRST><<<gr, b, 0, s>>>(                      \
+      HI, I.w, I.h, I.xs, I.ys, lo, Lo.pitch, in_g.channel_floats, out,      \
+      O.pitch, out_g.channel_floats, x_off, y_off, m, mk, lb, image)
   if (level > 0) {
     FloatLevel hi{in_pyr + I.offset, I.pitch, in_g.channel_floats};
-    XP_LAPCOMP(hi);
+    XP_LAPCOMP(hi, false);
   } else if (bpp == 8) {
     PixelLevel<8> hi;
     static_cast<Level0<8>&>(hi) = make_level0<8>(im, mul);
-    XP_LAPCOMP(hi);
+    XP_LAPCOMP(hi, true);
   } else {
     PixelLevel<16> hi;
     static_cast<Level0<16>&>(hi) = make_level0<16>(im, mul);
-    XP_LAPCOMP(hi);
+    XP_LAPCOMP(hi, true);
   }
 #undef XP_LAPCOMP
   XP_LAUNCHED();

@@ -283,10 +283,12 @@ struct SeamBwd {
   template <bool kEdgeX, bool kEdgeY>
   XP_HD u32 step(const wf::Band&, Row& row, bool active, int rho, int q, C cov,
                  In1, u32 last, u32 w0, u32 w1, u32 w2) const {
-    // Everything but `last` is two steps old when it is needed, so all of
-    // it is folded into `pre` off the chain; the chain through `last` is
-    // maskval (2 instructions) and one add-min. The add commutes with
-    // maskval: it cannot carry into the label or the flag.
+    // w2 arrives by shuffle from the lane above and depends on that lane's
+    // value two steps back: over the whole warp, `last` -> shuffle -> c2 ->
+    // pre -> `last` is the loop-carried cycle, so everything that does not
+    // need w2 is folded into `early` first. The chain through `last` itself
+    // is maskval (2 instructions) and one add-min; the add commutes with
+    // maskval (it cannot carry into the label or the flag).
     u32 c0 = Cv::mask(w0 + kD4, cov);
     const u32 c1 = Cv::mask(w1 + kD3, cov);
     u32 c2 = Cv::mask(w2 + kD4, cov);
@@ -295,16 +297,17 @@ struct SeamBwd {
       if (q <= 0) left = false, c0 = kInf32;
       if (q >= W - 1) c2 = kInf32;
     }
-    u32 pre = min32(c0, min32(c1, c2));
+    u32 early = min32(c0, c1);
     bool bottom_first = false;
     if (kEdgeY) {
       const bool was_first = row.first_run;
       if (active && Cv::rs(cov)) row.first_run = false;
       // bottom row :333-346: the left neighbour alone, or DT_MAX
-      if (rho == 0) pre = kInf32, bottom_first = was_first;
+      if (rho == 0) early = kInf32, c2 = kInf32, bottom_first = was_first;
     }
     // a seed's value is below anything a neighbour can offer :327-331
-    if (Cv::seed(cov)) pre = (u32)Cv::low(cov);
+    if (Cv::seed(cov)) early = (u32)Cv::low(cov);
+    const u32 pre = min32(early, c2);
     u32 d = add_min32(Cv::mask(last, cov), kD3, pre);
     if (kEdgeX && !left) d = pre;
     if (kEdgeY && bottom_first && !Cv::seed(cov)) d = kDtMax32;
@@ -395,17 +398,19 @@ struct SeamFwd {
     if (kEdgeY) {
       if (y == 0) c0 = kInf32, c1 = kInf32, c2 = kInf32;
     }
-    // ReadSeamDT value enters unmasked. Everything but `last` is folded into
-    // `pre` off the chain (see SeamBwd::step):
+    // ReadSeamDT value enters unmasked. Everything that does not need w2 is
+    // folded into `early` (see SeamBwd::step):
     //  * arbitrary seam :732-742 -- the minimum is flagged iff every
-    //    candidate is; flag|pick is below every other flagged value and above
-    //    every unflagged one, so substituting it for a flagged `pre` makes
-    //    the minimum come out right whatever the left neighbour is;
+    //    candidate is; flag|pick (distance 0) is below every other flagged
+    //    value (those are at distance >= 3) and above every unflagged one, so
+    //    taking the minimum with it makes the result come out right whatever
+    //    w2 and the left neighbour are;
     //  * a seed's value :607-616 is below anything a neighbour can offer.
-    u32 pre = min32(min32(bw, c0), min32(c1, c2));
-    if ((pre & kTop32) && Cv::any(cov))
-      pre = kTop32 | (u32)Cv::pick(cov, reverse);
-    if (Cv::seed(cov)) pre = (u32)Cv::low(cov);
+    u32 early = min32(min32(bw, c0), c1);
+    if (Cv::any(cov))
+      early = min32(early, kTop32 | (u32)Cv::pick(cov, reverse));
+    if (Cv::seed(cov)) early = (u32)Cv::low(cov);
+    const u32 pre = min32(early, c2);
     u32 best = add_min32(Cv::mask_if(last, cov, remask), kD3, pre);
     if (kEdgeX && !left) best = pre;
     return best;

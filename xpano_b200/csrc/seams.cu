@@ -63,7 +63,8 @@ struct DevCtx {
     return r;
   }
   __device__ __forceinline__ void block_sync() { __syncthreads(); }
-  // hand-over signals between two warps: named barriers 1..8, 64 threads;
+  // hand-over signals between two warps: named barriers 1..kSignals, 64
+  // threads;
   // the signalling warp arrives without waiting, the waiting warp syncs
   __device__ __forceinline__ void signal(int id) {
     __syncwarp();
@@ -127,11 +128,9 @@ struct DevCtx {
   __device__ __forceinline__ void cp_commit() {
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
-  __device__ __forceinline__ void cp_wait_all_but_one() {
-    asm volatile("cp.async.wait_group 1;" ::: "memory");
-  }
-  __device__ __forceinline__ void cp_wait_all() {
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  template <int kPending>
+  __device__ __forceinline__ void cp_wait_pending() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory");
   }
 };
 
@@ -245,10 +244,18 @@ static void launch_wavefront(const P& prob, int* counter, uint8_t* scratch,
   if (!classified) launch_classify(prob, scratch, flag_pitch, s);
   const WfScratch w = wf_scratch(scratch, prob.n_bands, flag_pitch);
   const size_t smem = wf::tile_bytes<P>();
-  // the item count lives on the device: launch what can be resident, blocks
-  // without an item leave at once
+  static_assert(wf::kSignals <= 15, "named barriers 1..15");
+  // more than 48 KB of dynamic shared memory needs the opt-in (per device)
+  XP_CUDA(cudaFuncSetAttribute(wavefront_kernel<P>,
+                               cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)smem));
+  // The item count lives on the device; blocks without an item leave at
+  // once. One block per SM: its three warps then sit on three different
+  // schedulers, whereas a second block's loader or storer warp would share a
+  // scheduler with the first block's compute warp and slow every step of it.
+  // Items are short, so 148 of them in flight cover the active front.
   const int blocks = (int)std::min<size_t>(
-      wf::max_items(prob.n_bands, flag_pitch), (size_t)148 * 8);
+      wf::max_items(prob.n_bands, flag_pitch), (size_t)148);
   wavefront_kernel<P><<<blocks, 32 * wf::kWarpsPerBand, smem, s>>>(
       prob, counter, w.items, w.first + prob.n_bands, w.flags, flag_pitch);
   XP_LAUNCHED();
@@ -471,6 +478,58 @@ void launch_inpaint(const InpaintJob* d_jobs, const InpaintBandRef* d_bands,
   launch_wavefront(pb, counter, flags, fp, s);
 }
 
+// Inpaint gather, in place, over the tiles the backward pass did not flag
+// (a flagged tile consists of opaque pixels: nothing to fill): every
+// non-opaque bbox pixel takes the colour of its source -- always an opaque
+// pixel, never written here; alpha is kept, so the cover map and the
+// exclusive-pixel sums, which may be read concurrently, are unaffected.
+// One warp per tile of the InpaintBwd problem.
+template <int BPP>
+__global__ void __launch_bounds__(128)
+    inpaint_gather_tiles_kernel(InpaintBwd prob, const uint8_t* flags,
+                                int flag_pitch) {
+  typedef typename PixelOf<BPP>::type Px;
+  const size_t tile = blockIdx.x * (size_t)(blockDim.x / 32) + threadIdx.x / 32;
+  const int band = (int)(tile / flag_pitch), c = (int)(tile % flag_pitch);
+  if (band >= prob.n_bands) return;
+  if (flags[(size_t)band * flag_pitch + c] == wf::kTileTrivial) return;
+  const wf::Band B = prob.band(band);
+  if (c >= wf::chunks_of(B.W)) return;
+  const InpaintJob& j = prob.jobs[B.job];
+  Px* data = static_cast<Px*>(const_cast<void*>(j.data));
+  const int lane = threadIdx.x & 31;
+  const int ab = BPP == 8 ? 24 : 48;
+  const Px amask = (Px)(BPP == 8 ? 0xffull : 0xffffull) << ab;
+  for (int r = 0; r < wf::kLanes; ++r) {
+    const int rho = B.rho0 + r, q = c * wf::kChunk - wf::kSkew * r + lane;
+    if (rho >= B.H || q < 0 || q >= B.W) continue;
+    const int x = B.W - 1 - q, y = B.H - 1 - rho;
+    const size_t me = (size_t)(j.top + y) * j.tiff_w + j.left + x;
+    const Px mine = data[me];
+    if (pixel_opaque(mine)) continue;
+    const u32 from = (u32)j.bwd[(size_t)y * B.W + x];
+    if (from == (u32)me) continue;
+    data[me] = (data[from] & ~amask) | (mine & amask);
+  }
+}
+
+void launch_inpaint_gather_tiles(const InpaintJob* d_jobs,
+                                 const InpaintBandRef* d_bands, int n_bands,
+                                 int max_w, int bpp, const uint8_t* scratch,
+                                 cudaStream_t s) {
+  if (n_bands <= 0) return;
+  const int fp = wf::chunks_of(max_w);
+  InpaintBwd pb{n_bands, d_jobs, d_bands};
+  const WfScratch w = wf_scratch(const_cast<uint8_t*>(scratch), n_bands, fp);
+  const size_t tiles = (size_t)n_bands * fp;
+  const unsigned g = (unsigned)div_up(tiles, (size_t)4);
+  if (bpp == 8)
+    inpaint_gather_tiles_kernel<8><<<g, 128, 0, s>>>(pb, w.flags, fp);
+  else
+    inpaint_gather_tiles_kernel<16><<<g, 128, 0, s>>>(pb, w.flags, fp);
+  XP_LAUNCHED();
+}
+
 // ---------------------------------------------------------------------------
 // canvas statistics (multiblend.cpp:536-616, 821-823): full / xor masks,
 // per-channel sums of the inputs over exclusively covered pixels, whether any
@@ -567,6 +626,94 @@ __global__ void canvas_stats_kernel(const C* __restrict__ cover,
   }
 }
 
+// The cover-only part (kMode 1) as a streaming pass: four consecutive pixels
+// of the linear canvas per thread (one 16/32-byte load of cover words, one
+// 4-byte store to each mask), sums kept in registers over the whole grid
+// stride and reduced once per block.
+template <class C, int F, int BPP>
+__global__ void __launch_bounds__(256)
+    canvas_masks_kernel(const C* __restrict__ cover, int W, size_t n_px,
+                        const ImgDev* __restrict__ imgs, int n,
+                        uint8_t* __restrict__ full_mask,
+                        uint8_t* __restrict__ xor_mask, CanvasStats* stats) {
+  typedef Cov<C, F> Cv;
+  __shared__ ImgDev s_img[64];
+  __shared__ unsigned long long s_sum[4];
+  __shared__ int s_uncovered;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) s_img[i] = imgs[i];
+  if (threadIdx.x < 4) s_sum[threadIdx.x] = 0;
+  if (threadIdx.x == 0) s_uncovered = 0;
+  __syncthreads();
+  unsigned long long sum[4] = {0, 0, 0, 0};
+  bool uncovered = false;
+  const size_t groups = (n_px + 3) / 4;
+  for (size_t g = blockIdx.x * (size_t)blockDim.x + threadIdx.x; g < groups;
+       g += (size_t)gridDim.x * blockDim.x) {
+    const size_t p0 = 4 * g;
+    C cv[4];
+    if (p0 + 3 < n_px) {
+      if (sizeof(C) == 4) {
+        const uint4 v = *reinterpret_cast<const uint4*>(cover + p0);
+        cv[0] = v.x, cv[1] = v.y, cv[2] = v.z, cv[3] = v.w;
+      } else {
+        const ulonglong2 a = *reinterpret_cast<const ulonglong2*>(cover + p0);
+        const ulonglong2 b =
+            *reinterpret_cast<const ulonglong2*>(cover + p0 + 2);
+        cv[0] = (C)a.x, cv[1] = (C)a.y, cv[2] = (C)b.x, cv[3] = (C)b.y;
+      }
+    } else {
+      for (int k = 0; k < 4; ++k) cv[k] = p0 + k < n_px ? cover[p0 + k] : (C)0;
+    }
+    unsigned fm = 0, xm = 0;
+    int y = (int)(p0 / W), x = (int)(p0 - (size_t)y * W);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const bool in = p0 + k < n_px;
+      const bool any = Cv::any(cv[k]), one = Cv::seed(cv[k]);
+      fm |= any ? 255u << (8 * k) : 0u;
+      xm |= one ? 1u << (8 * k) : 0u;
+      uncovered = uncovered || (in && !any);
+      if (in && one) {
+        const ImgDev& im = s_img[Cv::low(cv[k])];
+        const size_t q =
+            (size_t)(im.top + y - im.ypos) * im.tiff_w + im.left + x - im.xpos;
+        if (BPP == 8) {
+          const u32 v = static_cast<const u32*>(im.data)[q];
+          sum[0] += v & 0xff;
+          sum[1] += (v >> 8) & 0xff;
+          sum[2] += (v >> 16) & 0xff;
+        } else {
+          const u64 v = static_cast<const u64*>(im.data)[q];
+          sum[0] += v & 0xffff;
+          sum[1] += (v >> 16) & 0xffff;
+          sum[2] += (v >> 32) & 0xffff;
+        }
+        sum[3] += 1;
+      }
+      if (++x == W) x = 0, ++y;
+    }
+    if (p0 + 3 < n_px) {
+      *reinterpret_cast<unsigned*>(full_mask + p0) = fm;
+      *reinterpret_cast<unsigned*>(xor_mask + p0) = xm;
+    } else {
+      for (int k = 0; p0 + k < n_px; ++k) {
+        full_mask[p0 + k] = (uint8_t)(fm >> (8 * k));
+        xor_mask[p0 + k] = (uint8_t)(xm >> (8 * k));
+      }
+    }
+  }
+  for (int k = 0; k < 4; ++k) {
+    unsigned long long v = sum[k];
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(~0u, v, o);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_sum[k], v);
+  }
+  if (uncovered) s_uncovered = 1;
+  __syncthreads();
+  if (threadIdx.x < 4 && s_sum[threadIdx.x])
+    atomicAdd(&stats->totals[threadIdx.x], s_sum[threadIdx.x]);
+  if (threadIdx.x == 0 && s_uncovered) stats->uncovered = 1;
+}
+
 __global__ void stats_init_kernel(CanvasStats* st) {
   const int i = threadIdx.x;
   if (i < 4) st->totals[i] = 0;
@@ -592,9 +739,11 @@ void launch_canvas_stats(const void* cover, int cover_bytes,
                                                     W, H, d_imgs, n,         \
                                                     full_mask, xor_mask,     \
                                                     d_stats)
-#define XP_STATS(C, F, BPP)    \
-  if (mode == 1)               \
-    XP_STATS3(C, F, BPP, 1);   \
+#define XP_STATS(C, F, BPP)                                                 \
+  if (mode == 1)                                                            \
+    canvas_masks_kernel<C, F, BPP><<<148 * 8, 256, 0, s>>>(                 \
+        (const C*)cover, W, (size_t)W * H, d_imgs, n, full_mask, xor_mask, \
+        d_stats);                                                           \
   else if (mode == 2)          \
     XP_STATS3(C, F, BPP, 2);   \
   else                         \

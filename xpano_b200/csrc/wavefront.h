@@ -98,15 +98,27 @@ XP_HD int popc32(unsigned v) {
 constexpr int kWarpsPerBand = 3;  // compute, loader, storer
 enum Role { kCompute = 0, kLoader = 1, kStorer = 2 };
 // hand-over signals (one waiter, one signaller each), per buffer parity
-enum Signal { kInFull = 0, kInFree = 2, kOutFull = 4, kOutFree = 6, kSignals = 8 };
+// input tiles are staged kInBufs deep: one tile load (32-64 cp.async and a
+// trip to L2 / HBM) takes longer than the steps of a chunk, so a band that
+// waits for nobody (the first one, which every other band trails) would run
+// at the loader's pace with two buffers
+constexpr int kInBufs = 4;
+constexpr int kFlight = 2;  // tile loads in flight behind the newest one
+enum Signal {
+  kInFull = 0,
+  kInFree = kInBufs,
+  kOutFull = 2 * kInBufs,
+  kOutFree = 2 * kInBufs + 2,
+  kSignals = 2 * kInBufs + 4
+};
 
-// Shared-memory bytes one band (block) needs for problem P: two buffers of
-// each input tile and of the output tile, one row of hand-over values.
+// Shared-memory bytes one band (block) needs for problem P: kInBufs buffers
+// of each input tile, two of the output tile, one row of hand-over values.
 template <class P>
 constexpr size_t tile_bytes() {
-  return 2 *
-             (StreamBytes<typename P::In0>::value +
-              StreamBytes<typename P::In1>::value + sizeof(typename P::Val)) *
+  return (kInBufs * (StreamBytes<typename P::In0>::value +
+                     StreamBytes<typename P::In1>::value) +
+          2 * sizeof(typename P::Val)) *
              kTileElems +
          sizeof(typename P::Val) * kChunk;
 }
@@ -218,14 +230,15 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const Item* items,
   const int lane = ctx.lane();
   const int role = ctx.role();
   const Val kSentinel = prob.sentinel();
-  // layout: out[2] | hand-over row | in0[2] | in1[2], widest type first
+  // layout: out[2] | hand-over row | in0[kInBufs] | in1[kInBufs], widest
+  // type first
   Val* out_base = reinterpret_cast<Val*>(smem_block);
   Val* pv_row = out_base + 2 * kTileElems;
   unsigned char* base_a = reinterpret_cast<unsigned char*>(pv_row + kChunk);
   unsigned char* in0_base =
-      kB0 >= kB1 ? base_a : base_a + 2 * kB1 * kTileElems;
+      kB0 >= kB1 ? base_a : base_a + kInBufs * kB1 * kTileElems;
   unsigned char* in1_base =
-      kB0 >= kB1 ? base_a + 2 * kB0 * kTileElems : base_a;
+      kB0 >= kB1 ? base_a + kInBufs * kB0 * kTileElems : base_a;
   const int total_items = *n_items;
 
   for (;;) {
@@ -238,14 +251,16 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const Item* items,
     const int W = B.W;
 
     if (role == kLoader) {
-      // ---- inputs of the k-th chunk of the item -> buffer k & 1: row r,
+      // ---- inputs of the k-th chunk of the item -> buffer k % kInBufs: row r,
       // positions c*32 - kSkew*r + lane ----
       int k = 0;
       for (int c = item.c0; c < item.c1; ++c) {
-        if (k >= 2) ctx.wait(kInFree + (k & 1));
+        if (k >= kInBufs) ctx.wait(kInFree + (k % kInBufs));
         const int s0 = c * kChunk;
-        In0* t0 = reinterpret_cast<In0*>(in0_base + (k & 1) * kB0 * kTileElems);
-        In1* t1 = reinterpret_cast<In1*>(in1_base + (k & 1) * kB1 * kTileElems);
+        In0* t0 = reinterpret_cast<In0*>(in0_base +
+                                        (k % kInBufs) * kB0 * kTileElems);
+        In1* t1 = reinterpret_cast<In1*>(in1_base +
+                                        (k % kInBufs) * kB1 * kTileElems);
 #if defined(__CUDA_ARCH__)
 #pragma unroll 8
 #endif
@@ -260,12 +275,19 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const Item* items,
           }
         }
         ctx.cp_commit();
-        ctx.cp_wait_all();
-        ctx.signal(kInFull + (k & 1));
+        // kFlight tiles stay in flight behind the one just issued
+        if (k >= kFlight) {
+          ctx.template cp_wait_pending<kFlight>();
+          ctx.signal(kInFull + ((k - kFlight) % kInBufs));
+        }
         ++k;
       }
-      // the compute warp frees every buffer; absorb the last two
-      for (int j = k < 2 ? 0 : k - 2; j < k; ++j) ctx.wait(kInFree + (j & 1));
+      ctx.template cp_wait_pending<0>();
+      for (int j = k < kFlight ? 0 : k - kFlight; j < k; ++j)
+        ctx.signal(kInFull + (j % kInBufs));
+      // the compute warp frees every buffer; absorb the last kInBufs
+      for (int j = k < kInBufs ? 0 : k - kInBufs; j < k; ++j)
+        ctx.wait(kInFree + (j % kInBufs));
     } else if (role == kStorer) {
       // ---- outputs of the k-th chunk, coalesced per row ----
       int k = 0;
@@ -350,7 +372,7 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const Item* items,
         XP_WF_CLOCK(1);
         pv_row[lane] = pv;
         ctx.sync();
-        ctx.wait(kInFull + (k & 1));
+        ctx.wait(kInFull + (k % kInBufs));
         if (k >= 2) ctx.wait(kOutFree + (k & 1));
         XP_WF_CLOCK(2);
         {
@@ -361,10 +383,10 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const Item* items,
           // between two loads would pin every load behind it and put its
           // latency on the chain of every step.
           const In0* r0 = reinterpret_cast<const In0*>(
-                              in0_base + (k & 1) * kB0 * kTileElems) +
+                              in0_base + (k % kInBufs) * kB0 * kTileElems) +
                           lane * kTilePitch;
           const In1* r1 = reinterpret_cast<const In1*>(
-                              in1_base + (k & 1) * kB1 * kTileElems) +
+                              in1_base + (k % kInBufs) * kB1 * kTileElems) +
                           lane * kTilePitch;
           Val* ro = out_base + (k & 1) * kTileElems + lane * kTilePitch;
           const int q0 = s0 - kSkew * lane;
@@ -458,7 +480,7 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const Item* items,
         }
         XP_WF_CLOCK(4);
         ctx.signal(kOutFull + (k & 1));
-        ctx.signal(kInFree + (k & 1));
+        ctx.signal(kInFree + (k % kInBufs));
         ++k;
       }
       // the storer frees every output tile; absorb the last two
