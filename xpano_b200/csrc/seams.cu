@@ -319,58 +319,89 @@ void launch_trim(const void* data, int w, int h, int bpp, int* d_bbox,
 // RLE walk starts here (bbox edges and opacity changes of any image,
 // multiblend.cpp:509-534).
 // ---------------------------------------------------------------------------
+constexpr int kCoverTileW = 128, kCoverTileH = 8;
+
 template <class C, int F, int BPP>
 __global__ void __launch_bounds__(256)
     cover_kernel(C* __restrict__ cover, int W, int H,
                  const ImgDev* __restrict__ imgs, int n, int reverse) {
-  // one pass over the canvas: every pixel looks at the images whose bounding
-  // box (plus the column right of it, where the reference's walk starts a new
-  // run) contains it
-  // images whose box (plus the run-start column right of it) meets this
-  // block's 32 x 8 tile, in image order
+  // One pass over the canvas, a 128 x 8 tile per block. Every pixel looks at
+  // the images whose bounding box (plus the column right of it, where the
+  // reference's walk starts a new run) meets the tile; warp 0 compacts that
+  // list, in image order. A thread owns the four pixels x0 + 32 j of its row,
+  // so every load and store of a warp is one contiguous run, and the pixel
+  // left of it -- whose opacity decides whether a run starts here -- is the
+  // neighbour lane's.
   extern __shared__ ImgDev s_img[];
   __shared__ int s_count;
-  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
-  const int bx0 = blockIdx.x * blockDim.x, by0 = blockIdx.y * blockDim.y;
-  if (tid == 0) {
+  const int lane = threadIdx.x;
+  const int bx0 = blockIdx.x * kCoverTileW, by0 = blockIdx.y * kCoverTileH;
+  if (threadIdx.y == 0) {
     int m = 0;
-    for (int i = 0; i < n; ++i) {
-      const ImgDev im = imgs[i];
-      if (bx0 + 31 >= im.xpos && bx0 <= im.xpos + im.w &&
-          by0 + 7 >= im.ypos && by0 < im.ypos + im.h) {
-        s_img[m] = im;
-        s_img[m].tiff_h = i;  // the image's bit position
-        ++m;
+    for (int base = 0; base < n; base += 32) {
+      const int i = base + lane;
+      ImgDev im;
+      bool hit = false;
+      if (i < n) {
+        im = imgs[i];
+        hit = bx0 + kCoverTileW - 1 >= im.xpos && bx0 <= im.xpos + im.w &&
+              by0 + kCoverTileH - 1 >= im.ypos && by0 < im.ypos + im.h;
       }
+      const unsigned hits = __ballot_sync(~0u, hit);
+      if (hit) {
+        im.tiff_h = i;  // the image's bit position
+        s_img[m + __popc(hits & ((1u << lane) - 1u))] = im;
+      }
+      m += __popc(hits);
     }
-    s_count = m;
+    if (lane == 0) s_count = m;
   }
   __syncthreads();
-  const int x = bx0 + threadIdx.x;
   const int y = by0 + threadIdx.y;
-  if (x >= W || y >= H) return;
-  C bits = 0;
-  bool run_start = false;
+  const int x0 = bx0 + lane;
+  C bits[4] = {0, 0, 0, 0};
+  bool rs[4] = {false, false, false, false};
   const int m = s_count;
   for (int k = 0; k < m; ++k) {
     const ImgDev& im = s_img[k];
-    const int lx = x - im.xpos, ly = y - im.ypos;
-    if ((unsigned)ly >= (unsigned)im.h || (unsigned)lx > (unsigned)im.w) continue;
-    if (lx < im.w) {
-      const size_t p = (size_t)(im.top + ly) * im.tiff_w + im.left + lx;
-      const bool op = px_opaque<BPP>(im.data, p);
-      if (op) bits |= (C)1 << im.tiff_h;
-      if (lx == 0 || op != px_opaque<BPP>(im.data, p - 1)) run_start = true;
-    } else {
-      run_start = true;
+    const int ly = y - im.ypos;
+    const bool row_in = y < H && (unsigned)ly < (unsigned)im.h;
+    const size_t row = (size_t)(im.top + (row_in ? ly : 0)) * im.tiff_w + im.left;
+    const int lx0 = x0 - im.xpos;
+    bool op[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int lx = lx0 + 32 * j;
+      op[j] = row_in && (unsigned)lx < (unsigned)im.w &&
+              px_opaque<BPP>(im.data, row + lx);
+    }
+    // opacity of the pixel left of the tile's first column
+    bool carry = row_in && lane == 0 && lx0 >= 1 && lx0 - 1 < im.w &&
+                 px_opaque<BPP>(im.data, row + lx0 - 1);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int lx = lx0 + 32 * j;
+      bool prev = __shfl_up_sync(~0u, op[j], 1);
+      if (lane == 0) prev = carry;
+      carry = __shfl_sync(~0u, op[j], 31);
+      if (row_in && (unsigned)lx <= (unsigned)im.w) {
+        if (op[j]) bits[j] |= (C)1 << im.tiff_h;
+        if (lx == 0 || lx == im.w || op[j] != prev) rs[j] = true;
+      }
     }
   }
-  C out;
-  if (F == kCoverDigest)
-    out = (C)make_digest((u32)bits, run_start, reverse);
-  else
-    out = bits | (run_start ? CoverTraits<C>::rs_bit : (C)0);
-  cover[(size_t)y * W + x] = out;
+  if (y >= H) return;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int x = x0 + 32 * j;
+    if (x >= W) break;
+    C out;
+    if (F == kCoverDigest)
+      out = (C)make_digest((u32)bits[j], rs[j], reverse);
+    else
+      out = bits[j] | (rs[j] ? CoverTraits<C>::rs_bit : (C)0);
+    cover[(size_t)y * W + x] = out;
+  }
 }
 
 int cover_format(int n) {
@@ -380,8 +411,8 @@ int cover_format(int n) {
 void launch_cover(void* cover, int cover_bytes, int W, int H,
                   const ImgDev* d_imgs, int n, int bpp, int reverse,
                   cudaStream_t s) {
-  dim3 b(32, 8);
-  dim3 g(div_up(W, 32), div_up(H, 8));
+  dim3 b(32, kCoverTileH);
+  dim3 g(div_up(W, kCoverTileW), div_up(H, kCoverTileH));
   const size_t sm = sizeof(ImgDev) * (size_t)n;
 #define XP_COVER(C, F, BPP)                                        \
   cover_kernel<C, F, BPP><<<g, b, sm, s>>>((C*)cover, W, H, d_imgs, n, \

@@ -61,7 +61,12 @@ namespace wf {
 
 constexpr int kLanes = 32;
 constexpr int kChunk = 32;          // steps per tile
-constexpr int kTilePitch = kChunk + 1;
+// Row pitch of the shared tiles: a multiple of four 32-bit words, so a lane
+// reads / writes its row 16 bytes at a time, and 4 mod 32 words, so that the
+// eight lanes of a quarter warp hit distinct 16-byte bank groups (4-byte
+// elements; two-way conflicts for 8-byte ones) while the loader and storer
+// warps, which walk rows, stay conflict-free.
+constexpr int kTilePitch = kChunk + 4;
 constexpr int kTileElems = kLanes * kTilePitch;
 constexpr int kSkew = 3;            // pixels a lane trails the lane above it
 
@@ -85,6 +90,34 @@ struct StreamBytes<NoInput> {
 
 XP_HD int chunks_of(int W) {
   return (W + kSkew * (kLanes - 1) + kChunk - 1) / kChunk;
+}
+
+// 16-byte shared-memory accesses of a lane's run of tile elements (src / dst
+// 16-byte aligned, N * sizeof(T) a multiple of 16)
+struct alignas(16) Quad {
+  uint32_t w[4];
+};
+template <class T, int N>
+XP_HD void load_group(const T* src, T (&dst)[N]) {
+  constexpr int kQuads = (int)(N * sizeof(T) / 16);
+  static_assert(kQuads * 16 == N * sizeof(T), "whole quads");
+  union {
+    Quad q[kQuads];
+    T v[N];
+  } u;
+  for (int i = 0; i < kQuads; ++i)
+    u.q[i] = reinterpret_cast<const Quad*>(src)[i];
+  for (int i = 0; i < N; ++i) dst[i] = u.v[i];
+}
+template <class T, int N>
+XP_HD void store_group(T* dst, const T (&src)[N]) {
+  constexpr int kQuads = (int)(N * sizeof(T) / 16);
+  union {
+    Quad q[kQuads];
+    T v[N];
+  } u;
+  for (int i = 0; i < N; ++i) u.v[i] = src[i];
+  for (int i = 0; i < kQuads; ++i) reinterpret_cast<Quad*>(dst)[i] = u.q[i];
 }
 
 XP_HD int popc32(unsigned v) {
@@ -409,14 +442,9 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const Item* items,
             In1 gb[2][kGroup];
             Val gh[2][kGroup];
             auto fetch = [&](int g, int slot) {
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-              for (int i = 0; i < kGroup; ++i) {
-                ga[slot][i] = r0[g * kGroup + i];
-                if (kB1) gb[slot][i] = r1[g * kGroup + i];
-                gh[slot][i] = pv_row[g * kGroup + i];
-              }
+              load_group(r0 + g * kGroup, ga[slot]);
+              if constexpr (kB1 > 0) load_group(r1 + g * kGroup, gb[slot]);
+              load_group(pv_row + g * kGroup, gh[slot]);
             };
             fetch(0, 0);
 #if defined(__CUDA_ARCH__)
@@ -455,10 +483,7 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const Item* items,
                 }
                 go[i] = last;  // inactive positions are never stored
               }
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-              for (int i = 0; i < kGroup; ++i) ro[g * kGroup + i] = go[i];
+              store_group(ro + g * kGroup, go);
             }
           };
           auto interior_steps = [&](auto edge_y) {
