@@ -3,7 +3,10 @@
 // (coalesced loads), the vertical form is applied per column into a second
 // shared tile, then the five horizontal taps are combined. All border rules
 // (row forms, column clamps, parity shifts) come from pyramid_math.h index
-// functions, so there is no separate border path.
+// functions. Blocks whose window touches no border (every row the five-tap
+// form on consecutive hi rows, no column clamped) take a path with fixed
+// loop shapes that converts each hi sample once; the same arithmetic per
+// sample, so both paths agree bit for bit.
 //
 // `Src` is the hi level: raw(row, col) loads one stored element, value(raw, c)
 // converts it to the float sample of channel c (kChannels channels per
@@ -25,7 +28,13 @@ __global__ void __launch_bounds__(256)
                         size_t chan_stride) {
   typedef typename Src::Raw Raw;
   constexpr int NC = Src::kChannels;
-  __shared__ Raw tile[kShrinkMaxRows * kShrinkMaxCols];
+  constexpr int kFastRows = 2 * kShrinkTileH + 3, kFastCols = 2 * kShrinkTileW + 3;
+  constexpr int kFastPitch = kFastCols + 1;
+  constexpr size_t kRawBytes = sizeof(Raw) * kShrinkMaxRows * kShrinkMaxCols;
+  constexpr size_t kFastBytes = sizeof(float) * NC * kFastRows * kFastPitch;
+  __shared__ __align__(16) unsigned char
+      stage[kRawBytes > kFastBytes ? kRawBytes : kFastBytes];
+  Raw* tile = reinterpret_cast<Raw*>(stage);
   __shared__ float vert[NC][kShrinkTileH][kShrinkMaxCols];
   __shared__ pm::VForm forms[kShrinkTileH];
   __shared__ int s_rmin, s_rmax;
@@ -44,8 +53,70 @@ __global__ void __launch_bounds__(256)
     atomicMin(&s_rmin, lo_r);
     atomicMax(&s_rmax, hi_r);
   }
-  __syncthreads();
+  // interior block: full tile, five consecutive unclamped rows per lo row,
+  // no clamped column
+  bool mine_ok = true;
+  if (tid < kShrinkTileH) {
+    mine_ok = false;
+    if (tid < ny) {
+      const pm::VForm& f = forms[tid];
+      mine_ok = f.kind == 3 && f.r[0] == f.r[2] - 2 && f.r[1] == f.r[2] - 1 &&
+                f.r[3] == f.r[2] + 1 && f.r[4] == f.r[2] + 2;
+    }
+  }
+  const bool cols_ok = 2 * j0 - 4 - xs >= 0 &&
+                       2 * (j0 + kShrinkTileW - 1) <= hp - 1 &&
+                       j0 + kShrinkTileW <= lo_pitch;
+  const bool fast = __syncthreads_and(mine_ok && cols_ok && ny == kShrinkTileH);
   const int rmin = s_rmin, nrows = s_rmax - rmin + 1;
+  if (fast) {
+    float(*S)[kFastRows][kFastPitch] =
+        reinterpret_cast<float(*)[kFastRows][kFastPitch]>(stage);
+    const int c0 = 2 * j0 - 4 - xs;
+    // all loads of a thread are issued before the first conversion
+    constexpr int kPer = (kFastRows * kFastCols + 255) / 256;
+    Raw v[kPer];
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int i = tid + 256 * k;
+      const int r = i / kFastCols, c = i - r * kFastCols;
+      if (i < kFastRows * kFastCols) v[k] = hi.raw(z, rmin + r, c0 + c);
+    }
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int i = tid + 256 * k;
+      const int r = i / kFastCols, c = i - r * kFastCols;
+      if (i < kFastRows * kFastCols) {
+#pragma unroll
+        for (int ch = 0; ch < NC; ++ch) S[ch][r][c] = hi.value(v[k], ch);
+      }
+    }
+    __syncthreads();
+    for (int i = tid; i < kShrinkTileH * kFastCols; i += 256) {
+      const int yy = i / kFastCols, c = i - yy * kFastCols;
+#pragma unroll
+      for (int ch = 0; ch < NC; ++ch)
+        vert[ch][yy][c] = pm::shrink_vcombine(
+            3, S[ch][2 * yy][c], S[ch][2 * yy + 1][c], S[ch][2 * yy + 2][c],
+            S[ch][2 * yy + 3][c], S[ch][2 * yy + 4][c]);
+    }
+    __syncthreads();
+    const int jj = tid & (kShrinkTileW - 1);
+#pragma unroll
+    for (int it = 0; it < kShrinkTileH * kShrinkTileW / 256; ++it) {
+      const int yy = (tid / kShrinkTileW) + it * (256 / kShrinkTileW);
+#pragma unroll
+      for (int ch = 0; ch < NC; ++ch) {
+        float t[5];
+#pragma unroll
+        for (int m = 0; m < 5; ++m) t[m] = vert[ch][yy][2 * jj + m];
+        lo[(size_t)(NC == 1 ? z : ch) * chan_stride +
+           (size_t)(y0 + yy) * lo_pitch + j0 + jj] =
+            pm::squeeze_combine(t, 1.0f / 256);
+      }
+    }
+    return;
+  }
   const int jl = min(j0 + kShrinkTileW - 1, lo_pitch - 1);
   const int cmin = pm::squeeze_col(j0, 0, hp, xs);
   const int ncols = pm::squeeze_col(jl, 4, hp, xs) - cmin + 1;
