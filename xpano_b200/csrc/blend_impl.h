@@ -51,8 +51,12 @@ struct MaskLevel {
 };
 
 // seams.cu
-void launch_trim(const void* data, int w, int h, int bpp, int* d_bbox,
-                 unsigned long long* d_opaque_count, cudaStream_t s);
+// box = (INT_MAX, INT_MAX, -1, -1), count = 0 for n images
+void launch_trim_init(int* d_bbox, unsigned long long* d_opaque, int n,
+                      cudaStream_t s);
+void launch_trim(const void* const* data, const int* w, const int* h, int n,
+                 int bpp, int* d_bbox, unsigned long long* d_opaque_count,
+                 cudaStream_t s);
 // cover word of every canvas pixel in one pass (format chosen by n, see
 // scan_problems.h Cov<>)
 void launch_cover(void* cover, int cover_bytes, int W, int H,

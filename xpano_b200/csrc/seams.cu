@@ -181,43 +181,37 @@ __global__ void __launch_bounds__(128)
                     flag_pitch);
 }
 
-// Work items of a classified problem (wavefront.h): one block; a warp per
-// band counts the runs of unflagged chunks, warp 0 turns the counts into
-// first-item indices (band-major order), then the runs are written.
-template <class P>
-__global__ void __launch_bounds__(1024)
+// Work items of a classified problem (wavefront.h), band-major: a warp per
+// band counts the runs of unflagged chunks, one warp turns the counts into
+// first-item indices, then a warp per band writes its runs.
+template <class P, bool kEmit>
+__global__ void __launch_bounds__(256)
     segment_kernel(P prob, const uint8_t* flags, int flag_pitch, int* first,
                    wf::Item* items) {
   DevCtx ctx;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int warps = blockDim.x >> 5;
-  const int nb = prob.n_bands;
-  for (int b = warp; b < nb; b += warps) {
-    const int n = wf::segment_band(ctx, flags + (size_t)b * flag_pitch,
-                                   wf::chunks_of(prob.band(b).W), b,
-                                   (wf::Item*)nullptr);
-    if (lane == 0) first[b] = n;
-  }
-  __syncthreads();
-  if (warp == 0) {
-    int carry = 0;
-    for (int base = 0; base < nb; base += 32) {
-      const int b = base + lane;
-      const int v = b < nb ? first[b] : 0;
-      int incl = v;
-      for (int d = 1; d < 32; d <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += t;
-      }
-      if (b < nb) first[b] = carry + incl - v;
-      carry += __shfl_sync(0xffffffffu, incl, 31);
+  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= prob.n_bands) return;
+  const int n = wf::segment_band(ctx, flags + (size_t)b * flag_pitch,
+                                 wf::chunks_of(prob.band(b).W), b,
+                                 kEmit ? items + first[b] : (wf::Item*)nullptr);
+  if (!kEmit && (threadIdx.x & 31) == 0) first[b] = n;
+}
+
+__global__ void segment_scan_kernel(int* first, int nb) {
+  const int lane = threadIdx.x;
+  int carry = 0;
+  for (int base = 0; base < nb; base += 32) {
+    const int b = base + lane;
+    const int v = b < nb ? first[b] : 0;
+    int incl = v;
+    for (int d = 1; d < 32; d <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
     }
-    if (lane == 0) first[nb] = carry;
+    if (b < nb) first[b] = carry + incl - v;
+    carry += __shfl_sync(0xffffffffu, incl, 31);
   }
-  __syncthreads();
-  for (int b = warp; b < nb; b += warps)
-    wf::segment_band(ctx, flags + (size_t)b * flag_pitch,
-                     wf::chunks_of(prob.band(b).W), b, items + first[b]);
+  if (lane == 0) first[nb] = carry;
 }
 
 // `scratch` needs wavefront_flag_bytes(n_bands, widest band) bytes
@@ -230,8 +224,14 @@ static void launch_classify(const P& prob, uint8_t* scratch, int flag_pitch,
   classify_kernel<P><<<(unsigned)div_up(tiles, (size_t)4), 128, 0, s>>>(
       prob, w.flags, flag_pitch);
   XP_LAUNCHED();
-  segment_kernel<P><<<1, 1024, 0, s>>>(prob, w.flags, flag_pitch, w.first,
-                                       w.items);
+  const int sb = div_up(prob.n_bands, 8);
+  segment_kernel<P, false><<<sb, 256, 0, s>>>(prob, w.flags, flag_pitch,
+                                              w.first, w.items);
+  XP_LAUNCHED();
+  segment_scan_kernel<<<1, 32, 0, s>>>(w.first, prob.n_bands);
+  XP_LAUNCHED();
+  segment_kernel<P, true><<<sb, 256, 0, s>>>(prob, w.flags, flag_pitch,
+                                             w.first, w.items);
   XP_LAUNCHED();
 }
 
@@ -265,9 +265,20 @@ static void launch_wavefront(const P& prob, int* counter, uint8_t* scratch,
 // trim: bbox of alpha == max (image.cpp:396-447; the widening loops make the
 // result the exact bounding box of the opaque pixels)
 // ---------------------------------------------------------------------------
+// all images of a blend in one launch: blockIdx.y = image
+struct TrimBatch {
+  const void* data[kMaxImages + 1];
+  int w[kMaxImages + 1], h[kMaxImages + 1];
+};
+
 template <int BPP>
-__global__ void trim_kernel(const void* data, int w, int h, int* bbox,
-                            unsigned long long* opaque_count) {
+__global__ void trim_kernel(const __grid_constant__ TrimBatch batch,
+                            int* bbox_all,
+                            unsigned long long* opaque_count_all) {
+  const void* data = batch.data[blockIdx.y];
+  const int w = batch.w[blockIdx.y], h = batch.h[blockIdx.y];
+  int* bbox = bbox_all + 4 * blockIdx.y;
+  unsigned long long* opaque_count = opaque_count_all + blockIdx.y;
   int minx = INT_MAX, miny = INT_MAX, maxx = -1, maxy = -1, cnt = 0;
   // a warp scans 32 consecutive x; rows are strided over the grid
   const int lane = threadIdx.x & 31;
@@ -276,13 +287,24 @@ __global__ void trim_kernel(const void* data, int w, int h, int* bbox,
   for (int y = warp; y < h; y += warps) {
     const size_t row = (size_t)y * w;
     bool any = false;
-    for (int x = lane; x < w; x += 32)
-      if (px_opaque<BPP>(data, row + x)) {
-        minx = min(minx, x);
-        maxx = max(maxx, x);
-        ++cnt;
-        any = true;
+    // eight independent loads per lane in flight
+    for (int x0 = lane; x0 < w; x0 += 32 * 8) {
+      bool op[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int x = x0 + 32 * k;
+        op[k] = x < w && px_opaque<BPP>(data, row + x);
       }
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (op[k]) {
+          const int x = x0 + 32 * k;
+          minx = min(minx, x);
+          maxx = max(maxx, x);
+          ++cnt;
+          any = true;
+        }
+    }
     if (any) {
       miny = min(miny, y);
       maxy = max(maxy, y);
@@ -304,13 +326,39 @@ __global__ void trim_kernel(const void* data, int w, int h, int* bbox,
   }
 }
 
-void launch_trim(const void* data, int w, int h, int bpp, int* d_bbox,
-                 unsigned long long* d_opaque_count, cudaStream_t s) {
-  const int blocks = std::min(div_up(h, 8), 148 * 8);
+__global__ void trim_init_kernel(int* bbox, unsigned long long* opaque, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  bbox[4 * i] = bbox[4 * i + 1] = INT_MAX;
+  bbox[4 * i + 2] = bbox[4 * i + 3] = -1;
+  opaque[i] = 0;
+}
+
+void launch_trim_init(int* d_bbox, unsigned long long* d_opaque, int n,
+                      cudaStream_t s) {
+  trim_init_kernel<<<div_up(n, 64), 64, 0, s>>>(d_bbox, d_opaque, n);
+  XP_LAUNCHED();
+}
+
+// trim boxes and opaque counts of n images (d_bbox: 4 ints, d_opaque_count:
+// one word per image; both initialised by launch_trim_init)
+void launch_trim(const void* const* data, const int* w, const int* h, int n,
+                 int bpp, int* d_bbox, unsigned long long* d_opaque_count,
+                 cudaStream_t s) {
+  TrimBatch batch;
+  int max_h = 0;
+  for (int i = 0; i < n; ++i) {
+    batch.data[i] = data[i];
+    batch.w[i] = w[i];
+    batch.h[i] = h[i];
+    max_h = std::max(max_h, h[i]);
+  }
+  // rows are strided over gridDim.x blocks of eight warps
+  dim3 g(std::min(div_up(max_h, 8), 148 * 4), n);
   if (bpp == 8)
-    trim_kernel<8><<<blocks, 256, 0, s>>>(data, w, h, d_bbox, d_opaque_count);
+    trim_kernel<8><<<g, 256, 0, s>>>(batch, d_bbox, d_opaque_count);
   else
-    trim_kernel<16><<<blocks, 256, 0, s>>>(data, w, h, d_bbox, d_opaque_count);
+    trim_kernel<16><<<g, 256, 0, s>>>(batch, d_bbox, d_opaque_count);
   XP_LAUNCHED();
 }
 

@@ -177,33 +177,50 @@ XP_HD size_t max_items(int n_bands, int flag_pitch) {
 // Runs of unflagged chunks in one band, called by a whole warp. With
 // items == nullptr it only counts; otherwise item k of the band is written
 // to items[k] (starts and ends are ranked separately: the k-th end closes
-// the k-th start).
+// the k-th start). A lane reads each flag once; its neighbours' flags come by
+// shuffle, the flags across a 32-chunk window boundary as carried bits.
 template <class Ctx>
 XP_HD int segment_band(Ctx& ctx, const uint8_t* band_flags, int n_chunks,
                        int band_idx, Item* items) {
   const int lane = ctx.lane();
   int n_start = 0, n_end = 0;
-  for (int base = 0; base < n_chunks; base += 32) {
+  // closed = trivial or outside the band; window w + 1 is loaded one ahead
+  auto closed_mask = [&](int base) -> unsigned {
     const int c = base + lane;
-    const bool in = c < n_chunks;
-    const bool open = in && band_flags[c] != kTileTrivial;
-    const bool prev_closed =
-        c == 0 || (in && band_flags[c - 1] == kTileTrivial);
-    const bool next_closed =
-        c + 1 >= n_chunks || band_flags[c + 1] == kTileTrivial;
-    const unsigned bs = ctx.ballot(open && prev_closed);
-    const unsigned be = ctx.ballot(open && next_closed);
-    const unsigned below = (1u << lane) - 1u;
-    if (items) {
-      if (open && prev_closed) {
-        Item& it = items[n_start + popc32(bs & below)];
-        it.band = band_idx;
-        it.c0 = c;
-      }
-      if (open && next_closed) items[n_end + popc32(be & below)].c1 = c + 1;
+    return ctx.ballot(c >= n_chunks || band_flags[c] == kTileTrivial);
+  };
+  unsigned prev_last = 1;  // chunk -1 counts as closed
+  constexpr int kBatch = 8;  // windows whose flags are loaded together
+  unsigned cur = closed_mask(0);
+  for (int b0 = 0; b0 < n_chunks; b0 += 32 * kBatch) {
+    bool closed[kBatch];
+    for (int w = 0; w < kBatch; ++w) {  // independent loads, one latency
+      const int c = b0 + 32 * (w + 1) + lane;
+      closed[w] = c >= n_chunks || band_flags[c] == kTileTrivial;
     }
-    n_start += popc32(bs);
-    n_end += popc32(be);
+    for (int w = 0; w < kBatch; ++w) {
+      const int base = b0 + 32 * w;
+      const unsigned next = ctx.ballot(closed[w]);
+      if (base >= n_chunks) continue;
+      const unsigned open = ~cur;
+      const unsigned prev_closed = (cur << 1) | prev_last;
+      const unsigned next_closed = (cur >> 1) | (next << 31);
+      const unsigned bs = open & prev_closed, be = open & next_closed;
+      const unsigned below = (1u << lane) - 1u, me = 1u << lane;
+      if (items) {
+        const int c = base + lane;
+        if (bs & me) {
+          Item& it = items[n_start + popc32(bs & below)];
+          it.band = band_idx;
+          it.c0 = c;
+        }
+        if (be & me) items[n_end + popc32(be & below)].c1 = c + 1;
+      }
+      n_start += popc32(bs);
+      n_end += popc32(be);
+      prev_last = cur >> 31;
+      cur = next;
+    }
   }
   return n_start;
 }
