@@ -135,6 +135,9 @@ void launch_shrink(const PyrGeom& g, float* pyr, int level, int channels,
 // xor mask (offset correction, multiblend.cpp:1232-1258) -- used on the last
 // collapse step so level 0 is not read again for the sum. One partial per
 // block, combined in a fixed order by xor_sum_final_kernel: deterministic.
+// A thread owns four samples of two consecutive hi rows that share their lo
+// rows: t = y + ys even (lo rows p, p+1, p+2) and t + 1 (lo rows p+1, p+2),
+// so every horizontally expanded lo row is formed once for both.
 template <bool kSum>
 __global__ void __launch_bounds__(256)
     laplace_kernel(float* __restrict__ hi, int hh, int hp, int xs, int ys,
@@ -142,27 +145,62 @@ __global__ void __launch_bounds__(256)
                    size_t chan_stride, const uint8_t* __restrict__ xor_mask,
                    int W, double* __restrict__ partials) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  const int p = blockIdx.y * blockDim.y + threadIdx.y;  // row pair
+  const int ya = 2 * p - ys, yb = ya + 1;               // ya + ys is even
   double acc = 0.0;
-  if (4 * i < hp && y < hh) {
+  if (4 * i < hp && ya < hh) {
     const size_t co = (size_t)blockIdx.z * chan_stride;
-    float e[4];
-    expand4(lo + co, lo_pitch, xs, ys, i, y, e);
-    float4* dst = reinterpret_cast<float4*>(hi + co + (size_t)y * hp + 4 * i);
-    const float4 h = *dst;
-    const float4 r = make_float4(e[0] - h.x, e[1] - h.y, e[2] - h.z, e[3] - h.w);
-    *dst = r;
+    const bool has_a = ya >= 0, has_b = yb < hh;
+    float ea[4], eb[4];
+    if (2 * i + 4 < lo_pitch) {
+      const float* r0 = lo + co + (size_t)p * lo_pitch;
+      float e0[4], e1[4], e2[4];
+      expand_row4(r0, i, xs, e0);
+      expand_row4(r0 + lo_pitch, i, xs, e1);
+      expand_row4(r0 + 2 * (size_t)lo_pitch, i, xs, e2);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        ea[k] = pm::expand_v(1, e0[k], e1[k], e2[k]);
+        eb[k] = pm::expand_v(0, e0[k], e1[k], e2[k]);
+      }
+    } else {
+      if (has_a) expand4(lo + co, lo_pitch, xs, ys, i, ya, ea);
+      if (has_b) expand4(lo + co, lo_pitch, xs, ys, i, yb, eb);
+    }
+    float4* da = reinterpret_cast<float4*>(hi + co +
+                                           (size_t)(has_a ? ya : 0) * hp + 4 * i);
+    float4* db = reinterpret_cast<float4*>(hi + co +
+                                           (size_t)(has_b ? yb : 0) * hp + 4 * i);
+    float4 ha = make_float4(0, 0, 0, 0), hb = ha;
+    if (has_a) ha = *da;
+    if (has_b) hb = *db;
+    const float4 ra =
+        make_float4(ea[0] - ha.x, ea[1] - ha.y, ea[2] - ha.z, ea[3] - ha.w);
+    const float4 rb =
+        make_float4(eb[0] - hb.x, eb[1] - hb.y, eb[2] - hb.z, eb[3] - hb.w);
+    if (has_a) *da = ra;
+    if (has_b) *db = rb;
     if (kSum) {
-      const uint8_t* m = xor_mask + (size_t)y * W;
       const int x = 4 * i;
-      if (x < W && m[x]) acc += r.x;
-      if (x + 1 < W && m[x + 1]) acc += r.y;
-      if (x + 2 < W && m[x + 2]) acc += r.z;
-      if (x + 3 < W && m[x + 3]) acc += r.w;
+      if (has_a) {
+        const uint8_t* m = xor_mask + (size_t)ya * W;
+        if (x < W && m[x]) acc += ra.x;
+        if (x + 1 < W && m[x + 1]) acc += ra.y;
+        if (x + 2 < W && m[x + 2]) acc += ra.z;
+        if (x + 3 < W && m[x + 3]) acc += ra.w;
+      }
+      if (has_b) {
+        const uint8_t* m = xor_mask + (size_t)yb * W;
+        if (x < W && m[x]) acc += rb.x;
+        if (x + 1 < W && m[x + 1]) acc += rb.y;
+        if (x + 2 < W && m[x + 2]) acc += rb.z;
+        if (x + 3 < W && m[x + 3]) acc += rb.w;
+      }
     }
   }
   if (kSum) {
-    // one partial per warp (a warp is one row of the block): no block barrier
+    // one partial per warp (a warp is one row pair of the block): no block
+    // barrier
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(~0u, acc, o);
     if (threadIdx.x == 0)
       partials[(((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x +
@@ -170,12 +208,17 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// row pairs of a level with h rows and parity shift ys: pair p holds rows
+// 2p - ys and 2p - ys + 1
+static int laplace_pairs(int h, int ys) { return (h - 1 + ys) / 2 + 1; }
+
 void launch_laplace(const PyrGeom& g, float* pyr, int level, int channels,
                     cudaStream_t s) {
   const LevelGeom& H = g.lv[level];
   const LevelGeom& L = g.lv[level + 1];
   dim3 b(32, 8);
-  laplace_kernel<false><<<grid3(H.pitch / 4, H.h, channels, b), b, 0, s>>>(
+  laplace_kernel<false><<<grid3(H.pitch / 4, laplace_pairs(H.h, H.ys),
+                                channels, b), b, 0, s>>>(
       pyr + H.offset, H.h, H.pitch, H.xs, H.ys, pyr + L.offset, L.pitch,
       g.channel_floats, nullptr, 0, nullptr);
   XP_LAUNCHED();
@@ -226,11 +269,28 @@ __device__ __forceinline__ void mask_shrink_tile(const Src& src,
   const int cmin = pm::clampi(2 * X0 - 4, 0, wmax);
   const int cmax = pm::clampi(2 * (X0 + 31), 0, wmax);
   const int nrows = rmax - rmin + 1, ncols = cmax - cmin + 1;
+  bool all_one = true, all_zero = true;
   for (int i = tid; i < nrows * kMaskTileCols; i += 256) {
     const int r = i / kMaskTileCols, c = i - r * kMaskTileCols;
-    if (c < ncols) tile[r][c] = src.at(rmin + r, cmin + c);
+    if (c < ncols) {
+      const float v = src.at(rmin + r, cmin + c);
+      tile[r][c] = v;
+      all_one = all_one && v == 1.0f;
+      all_zero = all_zero && v == 0.0f;
+    }
   }
-  __syncthreads();
+  // A window of equal weights (inside or outside the owner region: nearly
+  // every tile) gives that weight for every sample: the horizontal rule
+  // copies it, the vertical taps sum to one exactly for 0 and 1.
+  all_one = __syncthreads_and(all_one);
+  all_zero = __syncthreads_and(all_zero);
+  if (all_one || all_zero) {
+    const int x = blockIdx.x * 32 + threadIdx.x;
+    const int y = blockIdx.y * 8 + threadIdx.y;
+    if (x < out.w && y < out.h)
+      dst[(size_t)y * out.w + x] = all_one ? 1.0f : 0.0f;
+    return;
+  }
   for (int i = tid; i < nrows * 32; i += 256) {
     const int r = i >> 5, x = i & 31;
     const int X = X0 + x;
@@ -470,7 +530,8 @@ __global__ void __launch_bounds__(1024)
 
 size_t collapse0_partials(const PyrGeom& g) {
   const LevelGeom& H = g.lv[0];
-  return (size_t)3 * div_up(H.pitch / 4, 32) * div_up(H.h, 8) * 8;
+  return (size_t)3 * div_up(H.pitch / 4, 32) *
+         div_up(laplace_pairs(H.h, H.ys), 8) * 8;
 }
 
 // last collapse step (level 1 -> 0 of the canvas pyramid) + the xor sums
@@ -480,7 +541,7 @@ void launch_collapse0_sum(const PyrGeom& g, float* pyr,
   const LevelGeom& H = g.lv[0];
   const LevelGeom& L = g.lv[1];
   dim3 b(32, 8);
-  dim3 gr = grid3(H.pitch / 4, H.h, 3, b);
+  dim3 gr = grid3(H.pitch / 4, laplace_pairs(H.h, H.ys), 3, b);
   laplace_kernel<true><<<gr, b, 0, s>>>(pyr + H.offset, H.h, H.pitch, H.xs,
                                         H.ys, pyr + L.offset, L.pitch,
                                         g.channel_floats, xor_mask, W,
