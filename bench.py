@@ -386,7 +386,10 @@ def run_ours(args, cfg):
     d2h = outs[0][0].nbytes + outs[0][1].nbytes
     e2e_steps = min(max(args.steps, 2 * in_flight), 12)
 
-    # one panorama computes while the other uploads / downloads
+    # one panorama computes while the others upload / download. Letting two
+    # compute at once is slower (measured: 11.3 -> 13.0 ms per panorama): the
+    # seam wavefronts are latency chains and every co-resident warp on their
+    # SMs stretches each step.
     compute_turn = threading.Lock()
 
     def e2e_worker(j, n_steps, errs):

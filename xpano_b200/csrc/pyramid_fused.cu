@@ -161,37 +161,41 @@ __global__ void __launch_bounds__(256)
   }
   if (!any) return;  // functions.cpp:347-351 (skip)
   const int iy = pm::clampi(Y - y_off, 0, in_h - 1);
-  float lap[3][4];
+  // one channel at a time, stored as soon as it is formed (fewer live
+  // registers, stores issue early)
+  auto put = [&](int c, const float lap[4]) {
+    float* row = out + c * out_cs + (size_t)Y * out_pitch + X0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (mv[k] != 0.0f)
+        row[k] = (kFirstTouch ? 0.0f : row[k]) + lap[k] * mv[k];
+  };
   if (g >= 0 && 4 * g + 3 <= in_w - 1) {
     float h[3][4];
     hi.load4(iy, g, h);
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      float e[4];
+      float e[4], lap[4];
       expand4(lo + c * in_cs, lo_pitch, xs, ys, g, iy, e);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) lap[c][k] = e[k] - h[c][k];
+      for (int k = 0; k < 4; ++k) lap[k] = e[k] - h[c][k];
+      put(c, lap);
     }
   } else {
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int ix = pm::clampi(4 * g + k, 0, in_w - 1);
+    for (int c = 0; c < 3; ++c) {
+      float lap[4];
 #pragma unroll
-      for (int c = 0; c < 3; ++c)
-        lap[c][k] = mv[k] != 0.0f
-                        ? pm::expand_sample(lo + c * in_cs, lo_pitch, xs, ys,
-                                            ix, iy) -
-                              hi.at(c, iy, ix)
-                        : 0.0f;
+      for (int k = 0; k < 4; ++k) {
+        const int ix = pm::clampi(4 * g + k, 0, in_w - 1);
+        lap[k] = mv[k] != 0.0f
+                     ? pm::expand_sample(lo + c * in_cs, lo_pitch, xs, ys, ix,
+                                         iy) -
+                           hi.at(c, iy, ix)
+                     : 0.0f;
+      }
+      put(c, lap);
     }
-  }
-#pragma unroll
-  for (int c = 0; c < 3; ++c) {
-    float* row = out + c * out_cs + (size_t)Y * out_pitch + X0;
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-      if (mv[k] != 0.0f)
-        row[k] = (kFirstTouch ? 0.0f : row[k]) + lap[c][k] * mv[k];
   }
 }
 
