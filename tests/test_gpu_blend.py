@@ -171,6 +171,55 @@ def test_stages_against_oracle(case):
                                np.moveaxis(planes, 0, 2), 0))
 
 
+def _sparse_case(bpp=8):
+    """Images far apart on a wide canvas, one of them with a mostly
+    transparent bounding box: most 32x32 skewed tiles of the canvas are
+    covered by no image (the wavefront's uncovered step variant, first band
+    included) and run-start bits fall into such tiles."""
+    rng = np.random.default_rng(5)
+    dt = np.uint8 if bpp == 8 else np.uint16
+    amax = 255 if bpp == 8 else 65535
+
+    def img(h, w, opaque):
+        a = np.zeros((h, w, 4), dt)
+        a[..., :3] = rng.integers(0, amax + 1, (h, w, 3), dtype=np.uint32)
+        a[..., 3] = np.where(opaque, amax, 0)
+        return a
+
+    W, H = 900, 400
+    frame = np.zeros((H - 10, W - 20), bool)
+    frame[:14, :17] = True
+    frame[-11:, -15:] = True
+    frame[150:170, 420:450] = True
+    blob = rng.random((160, 220)) < 0.9
+    blob[0, :] = blob[-1, :] = blob[:, 0] = blob[:, -1] = True
+    ims = [img(*frame.shape, frame), img(160, 220, blob),
+           img(100, 150, np.ones((100, 150), bool)),
+           img(150, 200, np.ones((150, 200), bool))]
+    pos = [(0, 0), (W - 220, H - 160), (330, 120), (5, 200)]
+    return ims, pos
+
+
+@pytest.mark.parametrize("bpp,reverse", [(8, False), (16, True)])
+def test_sparse_canvas_uncovered_tiles(bpp, reverse):
+    ims, pos = _sparse_case(bpp)
+    kw = dict(fixed_levels=4, reverse=reverse)
+    o, _ = _oracle_dump(ims, pos, **kw)
+    b = _gpu_blend(ims, pos, **kw)
+    assert b.size == (o.width, o.height)
+    _diff("seam_bwd", b.debug("seam_bwd"), o.seam_bwd)
+    _diff("seam_fwd", b.debug("seam_fwd"), o.seam_fwd)
+    _diff("labels", b.debug("labels"), o.labels)
+    _diff("full_mask", b.debug("full_mask"), o.mask)
+    d = np.abs(b.planes().astype(np.int64) - o.planes.astype(np.int64))
+    assert d.max() <= 1 and float((d > 0).mean()) < 1e-4
+    # the streaming path (what xpano's export runs) gives the same planes
+    s2 = _gpu_blend(ims, pos, debug=False, **kw)
+    _diff("planes", s2.planes(), b.planes())
+    _note(f"sparse_{bpp}", plane_max_diff=int(d.max()),
+          uncovered_fraction=float((o.mask == 0).mean()))
+
+
 def test_single_image_and_spp3():
     ims, pos = synth.blend_case(9, n=1, mode="ellipse", bpp=8)
     o = mb_oracle.blend(ims, pos)
