@@ -23,9 +23,9 @@ def worker(j, n):
         a = time.perf_counter(); comps[j].set_images(host, Ks, Rs)
         b = time.perf_counter()
         with turn:
-            comps[j].run()
+            b2 = time.perf_counter(); comps[j].run()
         c = time.perf_counter(); comps[j].fetch(outs[j][0].numpy(), outs[j][1].numpy())
-        d = time.perf_counter(); log.append((j, k, a, b, c, d))
+        d = time.perf_counter(); log.append((j, k, a, b, c, d, b2))
 for rep in range(2):
     log.clear()
     torch.cuda.synchronize(); t0 = time.perf_counter()
@@ -33,5 +33,5 @@ for rep in range(2):
     [t.start() for t in ts]; [t.join() for t in ts]
     torch.cuda.synchronize(); t1 = time.perf_counter()
 print("in flight", NF, "ms per pano", 1e3 * (t1 - t0) / (4 * NF))
-for j, k, a, b, c, d in sorted(log, key=lambda r: r[2]):
-    print(f"thr {j} step {k}: start {1e3*(a-t0):7.2f} upload {1e3*(b-a):6.2f} run {1e3*(c-b):6.2f} fetch {1e3*(d-c):6.2f}")
+for j, k, a, b, c, d, b2 in sorted(log, key=lambda r: r[2]):
+    print(f"thr {j} step {k}: start {1e3*(a-t0):7.2f} upload {1e3*(b-a):6.2f} wait {1e3*(b2-b):6.2f} run {1e3*(c-b2):6.2f} fetch {1e3*(d-c):6.2f}")

@@ -219,6 +219,23 @@ void copy_out_2d(void* user, size_t user_pitch, const void* dev,
       s));
 }
 
+void sync_blocking(cudaStream_t s) {
+  // one event per thread and device; blocking-sync events make
+  // cudaEventSynchronize yield the core
+  struct Ev {
+    cudaEvent_t e[16] = {};
+  };
+  static thread_local Ev evs;
+  int dev = 0;
+  XP_CUDA(cudaGetDevice(&dev));
+  cudaEvent_t& e = evs.e[dev & 15];
+  if (!e)
+    XP_CUDA(cudaEventCreateWithFlags(
+        &e, cudaEventBlockingSync | cudaEventDisableTiming));
+  XP_CUDA(cudaEventRecord(e, s));
+  XP_CUDA(cudaEventSynchronize(e));
+}
+
 }  // namespace xp
 
 extern "C" {

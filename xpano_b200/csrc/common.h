@@ -136,6 +136,11 @@ struct DevBuf {
   }
 };
 
+// Wait for a stream with the calling thread blocked in the OS instead of
+// spinning in the driver: for the long waits on bulk copies (uploads,
+// downloads) that overlap another thread's kernel launches.
+void sync_blocking(cudaStream_t s);
+
 inline int div_up(int a, int b) { return (a + b - 1) / b; }
 inline size_t div_up(size_t a, size_t b) { return (a + b - 1) / b; }
 

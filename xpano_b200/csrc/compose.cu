@@ -195,7 +195,7 @@ struct Composer {
       src.push_back(std::move(s));
     }
     XP_CUDA(cudaEventRecord(ev[1], stream));
-    XP_CUDA(cudaStreamSynchronize(stream));
+    sync_blocking(stream);
     float ms = 0;
     cudaEventElapsedTime(&ms, ev[0], ev[1]);
     h2d_ms = ms;

@@ -131,71 +131,134 @@ __device__ __forceinline__ int floor_div4(int a) {
 // kFirstTouch (level 0): the label map gives every canvas pixel to exactly
 // one image with weight 1, so the level is written once instead of zeroed
 // and accumulated into (0 + x, as the reference computes it).
+//
+// A thread owns four samples of two consecutive canvas rows whose image rows
+// t = iy + ys (even) and t + 1 share their lo rows, so every horizontally
+// expanded lo row is formed once for both (as in laplace_kernel); rows that
+// are clamped to the image, lie outside the mask rectangle or touch the
+// image's right edge take the one-row path.
 template <class Hi, bool kFirstTouch>
-__global__ void __launch_bounds__(256)
-    lapcomp_kernel(Hi hi, int in_w, int in_h, int xs, int ys,
-                   const float* __restrict__ lo, int lo_pitch, size_t in_cs,
-                   float* __restrict__ out, int out_pitch, size_t out_cs,
-                   int x_off, int y_off, MaskLevel m,
-                   const float* __restrict__ mask,
-                   const uint8_t* __restrict__ labels, int image) {
-  const int g = floor_div4(m.x0 - x_off) + blockIdx.x * blockDim.x + threadIdx.x;
-  const int Y = m.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  if (Y >= m.y0 + m.h) return;
-  const int X0 = 4 * g + x_off;
-  if (X0 >= m.x0 + m.w) return;
-  float mv[4];
-  bool any = false;
+struct LapComp {
+  Hi hi;
+  int in_w, in_h, xs, ys;
+  const float* __restrict__ lo;
+  int lo_pitch;
+  size_t in_cs;
+  float* __restrict__ out;
+  int out_pitch;
+  size_t out_cs;
+  int x_off, y_off;
+  MaskLevel m;
+  const float* __restrict__ mask;
+  const uint8_t* __restrict__ labels;
+  int image;
+
+  // weights of samples X0 .. X0+3 of canvas row Y; false if all are zero
+  __device__ __forceinline__ bool weights(int X0, int Y, float mv[4]) const {
+    bool any = false;
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int X = X0 + k;
-    float v = 0.0f;
-    if (X >= m.x0 && X < m.x0 + m.w) {
-      if (labels)
-        v = labels[(size_t)Y * m.cw + X] == image ? 1.0f : 0.0f;
-      else
-        v = mask[(size_t)(Y - m.y0) * m.w + (X - m.x0)];
+    for (int k = 0; k < 4; ++k) {
+      const int X = X0 + k;
+      float v = 0.0f;
+      if (X >= m.x0 && X < m.x0 + m.w) {
+        if (labels)
+          v = labels[(size_t)Y * m.cw + X] == image ? 1.0f : 0.0f;
+        else
+          v = mask[(size_t)(Y - m.y0) * m.w + (X - m.x0)];
+      }
+      mv[k] = v;
+      any = any || v != 0.0f;
     }
-    mv[k] = v;
-    any = any || v != 0.0f;
+    return any;
   }
-  if (!any) return;  // functions.cpp:347-351 (skip)
-  const int iy = pm::clampi(Y - y_off, 0, in_h - 1);
-  // one channel at a time, stored as soon as it is formed (fewer live
-  // registers, stores issue early)
-  auto put = [&](int c, const float lap[4]) {
+  __device__ __forceinline__ void put(int c, int X0, int Y, const float mv[4],
+                                      const float lap[4]) const {
     float* row = out + c * out_cs + (size_t)Y * out_pitch + X0;
 #pragma unroll
     for (int k = 0; k < 4; ++k)
       if (mv[k] != 0.0f)
         row[k] = (kFirstTouch ? 0.0f : row[k]) + lap[k] * mv[k];
-  };
-  if (g >= 0 && 4 * g + 3 <= in_w - 1) {
-    float h[3][4];
-    hi.load4(iy, g, h);
+  }
+  // one canvas row (any position: clamped addressing, functions.cpp:319-411)
+  __device__ __forceinline__ void row(int g, int X0, int Y) const {
+    float mv[4];
+    if (!weights(X0, Y, mv)) return;  // functions.cpp:347-351 (skip)
+    const int iy = pm::clampi(Y - y_off, 0, in_h - 1);
+    if (g >= 0 && 4 * g + 3 <= in_w - 1) {
+      float h[3][4];
+      hi.load4(iy, g, h);
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      float e[4], lap[4];
-      expand4(lo + c * in_cs, lo_pitch, xs, ys, g, iy, e);
+      for (int c = 0; c < 3; ++c) {
+        float e[4], lap[4];
+        expand4(lo + c * in_cs, lo_pitch, xs, ys, g, iy, e);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) lap[k] = e[k] - h[c][k];
-      put(c, lap);
+        for (int k = 0; k < 4; ++k) lap[k] = e[k] - h[c][k];
+        put(c, X0, Y, mv, lap);
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        float lap[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int ix = pm::clampi(4 * g + k, 0, in_w - 1);
+          lap[k] = mv[k] != 0.0f
+                       ? pm::expand_sample(lo + c * in_cs, lo_pitch, xs, ys,
+                                           ix, iy) -
+                             hi.at(c, iy, ix)
+                       : 0.0f;
+        }
+        put(c, X0, Y, mv, lap);
+      }
     }
-  } else {
+  }
+  // canvas rows Ya, Ya + 1 with image rows iya (iya + ys even), iya + 1, both
+  // inside the image and the rectangle, group g inside the image
+  __device__ __forceinline__ void pair(int g, int X0, int Ya, int iya) const {
+    float ma[4], mb[4];
+    const bool any_a = weights(X0, Ya, ma), any_b = weights(X0, Ya + 1, mb);
+    if (!any_a && !any_b) return;
+    float ha[3][4], hb[3][4];
+    hi.load4(iya, g, ha);
+    hi.load4(iya + 1, g, hb);
+    const int j = ((iya + ys) >> 1) + 1;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      float lap[4];
+      const float* r1 = lo + c * in_cs + (size_t)j * lo_pitch;
+      float e0[4], e1[4], e2[4], la[4], lb[4];
+      expand_row4(r1 - lo_pitch, g, xs, e0);
+      expand_row4(r1, g, xs, e1);
+      expand_row4(r1 + lo_pitch, g, xs, e2);
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const int ix = pm::clampi(4 * g + k, 0, in_w - 1);
-        lap[k] = mv[k] != 0.0f
-                     ? pm::expand_sample(lo + c * in_cs, lo_pitch, xs, ys, ix,
-                                         iy) -
-                           hi.at(c, iy, ix)
-                     : 0.0f;
+        la[k] = pm::expand_v(1, e0[k], e1[k], e2[k]) - ha[c][k];
+        lb[k] = pm::expand_v(0, e0[k], e1[k], e2[k]) - hb[c][k];
       }
-      put(c, lap);
+      if (any_a) put(c, X0, Ya, ma, la);
+      if (any_b) put(c, X0, Ya + 1, mb, lb);
     }
+  }
+};
+
+template <class Hi, bool kFirstTouch>
+__global__ void __launch_bounds__(256)
+    lapcomp_kernel(const LapComp<Hi, kFirstTouch> k, int y_first) {
+  const int g =
+      floor_div4(k.m.x0 - k.x_off) + blockIdx.x * blockDim.x + threadIdx.x;
+  // row pairs start at y_first (<= m.y0), chosen so that image row
+  // y_first - y_off + ys is even
+  const int Ya = y_first + 2 * (blockIdx.y * blockDim.y + threadIdx.y);
+  const int y_end = k.m.y0 + k.m.h;
+  if (Ya >= y_end) return;
+  const int X0 = 4 * g + k.x_off;
+  if (X0 >= k.m.x0 + k.m.w) return;
+  const int iya = Ya - k.y_off;
+  if (Ya >= k.m.y0 && Ya + 1 < y_end && iya >= 0 && iya + 1 <= k.in_h - 1 &&
+      g >= 0 && 4 * g + 3 <= k.in_w - 1 && 2 * g + 4 < k.lo_pitch) {
+    k.pair(g, X0, Ya, iya);
+  } else {
+    if (Ya >= k.m.y0) k.row(g, X0, Ya);
+    if (Ya + 1 < y_end) k.row(g, X0, Ya + 1);
   }
 }
 
@@ -213,16 +276,23 @@ void launch_lapcomp(const ImgDev& im, int bpp, float mul, const PyrGeom& in_g,
                                      : -((-(m.x0 - x_off) + 3) >> 2);
   const int last = m.x0 + m.w - 1 - x_off;
   const int g1 = last >= 0 ? last >> 2 : -((-last + 3) >> 2);
+  // row pairs: the first one starts on an image row of even t = iy + ys
+  const int y_first = m.y0 - ((m.y0 - y_off + I.ys) & 1);
+  const int pairs = (m.y0 + m.h - y_first + 1) / 2;
   dim3 b(32, 8);
-  dim3 gr(div_up(g1 - g0 + 1, 32), div_up(m.h, 8));
+  dim3 gr(div_up(g1 - g0 + 1, 32), div_up(pairs, 8));
   const float* lo = in_pyr + Lo.offset;
   float* out = out_pyr + O.offset;
   const float* mk = level == 0 ? nullptr : mask + m.offset;
   const uint8_t* lb = level == 0 ? labels : nullptr;
-#define XP_LAPCOMP(HI, FIRST)                                                \
-  lapcomp_kernel<decltype(HI), FIRST><<<gr, b, 0, s>>>(                      \
-      HI, I.w, I.h, I.xs, I.ys, lo, Lo.pitch, in_g.channel_floats, out,      \
-      O.pitch, out_g.channel_floats, x_off, y_off, m, mk, lb, image)
+#define XP_LAPCOMP(HI, FIRST)                                                 \
+  {                                                                           \
+    const LapComp<decltype(HI), FIRST> k{                                     \
+        HI,       I.w,     I.h,    I.xs, I.ys, lo, Lo.pitch,                  \
+        in_g.channel_floats, out,  O.pitch, out_g.channel_floats, x_off,      \
+        y_off,    m,       mk,     lb,   image};                              \
+    lapcomp_kernel<decltype(HI), FIRST><<<gr, b, 0, s>>>(k, y_first);         \
+  }
   if (level > 0) {
     FloatLevel hi{in_pyr + I.offset, I.pitch, in_g.channel_floats};
     XP_LAPCOMP(hi, false);
