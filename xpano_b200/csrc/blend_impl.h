@@ -131,6 +131,11 @@ void launch_inpaint_gather_tiles(const InpaintJob* d_jobs,
                                  const InpaintBandRef* d_bands, int n_bands,
                                  int max_w, int bpp, const uint8_t* scratch,
                                  cudaStream_t s);
+void launch_shrink0_batch(const ImgDev* im, int bpp, float mul,
+                          const PyrGeom* g, float* const* pyr, int n,
+                          cudaStream_t s);
+void launch_shrink_batch(const PyrGeom* g, float* const* pyr, int n, int level,
+                         int channels, cudaStream_t s);
 void launch_shrink0(const ImgDev& im, int bpp, float mul, const PyrGeom& g,
                     float* pyr, cudaStream_t s);
 void launch_lapcomp(const ImgDev& im, int bpp, float mul, const PyrGeom& in_g,

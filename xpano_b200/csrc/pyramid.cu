@@ -116,6 +116,32 @@ __device__ __forceinline__ float4 ldg4(const float* p) {
   return __ldg(reinterpret_cast<const float4*>(p));
 }
 
+// level -> level + 1 of n pyramids (geometry g[i], base pointer pyr[i]), in
+// launches of up to kShrinkBatch pyramids
+void launch_shrink_batch(const PyrGeom* g, float* const* pyr, int n, int level,
+                         int channels, cudaStream_t s) {
+  for (int i0 = 0; i0 < n; i0 += kShrinkBatch) {
+    const int m = std::min(kShrinkBatch, n - i0);
+    ShrinkBatch<PlaneSrc> batch;
+    int gx = 0, gy = 0;
+    for (int k = 0; k < m; ++k) {
+      const PyrGeom& G = g[i0 + k];
+      const LevelGeom& H = G.lv[level];
+      const LevelGeom& L = G.lv[level + 1];
+      batch.job[k] = ShrinkJob<PlaneSrc>{
+          PlaneSrc{pyr[i0 + k] + H.offset, H.pitch, G.channel_floats},
+          H.h, H.pitch, H.xs, H.ys, pyr[i0 + k] + L.offset, L.h, L.pitch,
+          G.channel_floats};
+      gx = std::max(gx, div_up(L.pitch, kShrinkTileW));
+      gy = std::max(gy, div_up(L.h, kShrinkTileH));
+    }
+    for (int k = m; k < kShrinkBatch; ++k) batch.job[k] = batch.job[0];
+    shrink_batch_kernel<<<dim3(gx, gy, m * channels), 256, 0, s>>>(batch,
+                                                                  channels);
+    XP_LAUNCHED();
+  }
+}
+
 void launch_shrink(const PyrGeom& g, float* pyr, int level, int channels,
                    cudaStream_t s) {
   const LevelGeom& H = g.lv[level];

@@ -67,6 +67,42 @@ struct PixelSrc : Level0<BPP> {
   }
 };
 
+// level 0 -> 1 of n images straight from their source pixels, in launches of
+// up to kShrinkBatch images
+template <int BPP>
+static void shrink0_batch_t(const ImgDev* im, float mul, const PyrGeom* g,
+                            float* const* pyr, int n, cudaStream_t s) {
+  for (int i0 = 0; i0 < n; i0 += kShrinkBatch) {
+    const int m = std::min(kShrinkBatch, n - i0);
+    ShrinkBatch<PixelSrc<BPP>> batch;
+    int gx = 0, gy = 0;
+    for (int k = 0; k < m; ++k) {
+      const PyrGeom& G = g[i0 + k];
+      const LevelGeom& H = G.lv[0];
+      const LevelGeom& L = G.lv[1];
+      PixelSrc<BPP> src;
+      static_cast<Level0<BPP>&>(src) = make_level0<BPP>(im[i0 + k], mul);
+      batch.job[k] = ShrinkJob<PixelSrc<BPP>>{
+          src, H.h, H.pitch, H.xs, H.ys, pyr[i0 + k] + L.offset, L.h, L.pitch,
+          G.channel_floats};
+      gx = std::max(gx, div_up(L.pitch, kShrinkTileW));
+      gy = std::max(gy, div_up(L.h, kShrinkTileH));
+    }
+    for (int k = m; k < kShrinkBatch; ++k) batch.job[k] = batch.job[0];
+    shrink_batch_kernel<<<dim3(gx, gy, m), 256, 0, s>>>(batch, 1);
+    XP_LAUNCHED();
+  }
+}
+
+void launch_shrink0_batch(const ImgDev* im, int bpp, float mul,
+                          const PyrGeom* g, float* const* pyr, int n,
+                          cudaStream_t s) {
+  if (bpp == 8)
+    shrink0_batch_t<8>(im, mul, g, pyr, n, s);
+  else
+    shrink0_batch_t<16>(im, mul, g, pyr, n, s);
+}
+
 void launch_shrink0(const ImgDev& im, int bpp, float mul, const PyrGeom& g,
                     float* pyr, cudaStream_t s) {
   const LevelGeom& H = g.lv[0];

@@ -22,10 +22,11 @@ constexpr int kShrinkMaxCols = 2 * kShrinkTileW + 6;  // 2*(W-1) + 4 + 1 (+xs)
 constexpr int kShrinkMaxRows = 2 * kShrinkTileH + 4;
 
 template <class Src>
-__global__ void __launch_bounds__(256)
-    shrink_tiled_kernel(Src hi, int hh, int hp, int xs, int ys,
-                        float* __restrict__ lo, int lo_h, int lo_pitch,
-                        size_t chan_stride) {
+__device__ __forceinline__ void shrink_tile(const Src& hi, int hh, int hp,
+                                            int xs, int ys,
+                                            float* __restrict__ lo, int lo_h,
+                                            int lo_pitch, size_t chan_stride,
+                                            int bx, int by, int z) {
   typedef typename Src::Raw Raw;
   constexpr int NC = Src::kChannels;
   constexpr int kFastRows = 2 * kShrinkTileH + 3, kFastCols = 2 * kShrinkTileW + 3;
@@ -39,9 +40,9 @@ __global__ void __launch_bounds__(256)
   __shared__ pm::VForm forms[kShrinkTileH];
   __shared__ int s_rmin, s_rmax;
   const int tid = threadIdx.x;
-  const int j0 = blockIdx.x * kShrinkTileW, y0 = blockIdx.y * kShrinkTileH;
+  const int j0 = bx * kShrinkTileW, y0 = by * kShrinkTileH;
   const int ny = min(kShrinkTileH, lo_h - y0);
-  const int z = blockIdx.z;  // plane for single-channel sources
+  // z: plane for single-channel sources
   if (tid == 0) s_rmin = 1 << 30, s_rmax = -1;
   __syncthreads();
   if (tid < ny) {
@@ -163,6 +164,45 @@ __global__ void __launch_bounds__(256)
          (size_t)(y0 + yy) * lo_pitch + j] = pm::squeeze_combine(t, mul);
     }
   }
+}
+
+template <class Src>
+__global__ void __launch_bounds__(256)
+    shrink_tiled_kernel(Src hi, int hh, int hp, int xs, int ys,
+                        float* __restrict__ lo, int lo_h, int lo_pitch,
+                        size_t chan_stride) {
+  shrink_tile(hi, hh, hp, xs, ys, lo, lo_h, lo_pitch, chan_stride,
+              (int)blockIdx.x, (int)blockIdx.y, (int)blockIdx.z);
+}
+
+// The same level of several pyramids in one launch (the upper levels of an
+// image pyramid are a few hundred blocks each): blockIdx.z = job * planes +
+// plane, blocks beyond a job's own extent leave at once.
+template <class Src>
+struct ShrinkJob {
+  Src hi;
+  int hh, hp, xs, ys;
+  float* lo;
+  int lo_h, lo_pitch;
+  size_t chan_stride;
+};
+constexpr int kShrinkBatch = 16;
+template <class Src>
+struct ShrinkBatch {
+  ShrinkJob<Src> job[kShrinkBatch];
+};
+
+template <class Src>
+__global__ void __launch_bounds__(256)
+    shrink_batch_kernel(const __grid_constant__ ShrinkBatch<Src> batch,
+                        int planes) {
+  const ShrinkJob<Src>& j = batch.job[blockIdx.z / planes];
+  if ((int)blockIdx.x * kShrinkTileW >= j.lo_pitch ||
+      (int)blockIdx.y * kShrinkTileH >= j.lo_h)
+    return;
+  shrink_tile(j.hi, j.hh, j.hp, j.xs, j.ys, j.lo, j.lo_h, j.lo_pitch,
+              j.chan_stride, (int)blockIdx.x, (int)blockIdx.y,
+              (int)(blockIdx.z % planes));
 }
 
 // float plane(s) as the hi level

@@ -269,8 +269,31 @@ __device__ __forceinline__ void sample_linear_reflect(
   const int sx = round_q5(mx), sy = round_q5(my);
   const int fx = sx & 31, fy = sy & 31;
   const int ix = sat_short(sx >> 5), iy = sat_short(sy >> 5);
-  const int x0 = reflect_idx(ix, sw), x1 = reflect_idx(ix + 1, sw);
-  const int y0 = reflect_idx(iy, sh), y1 = reflect_idx(iy + 1, sh);
+  if (sizeof(T) == 1 && (unsigned)ix < (unsigned)(sw - 1) &&
+      (unsigned)iy < (unsigned)(sh - 1)) {
+    // interior (nearly every pixel): the four taps are two runs of 2 * CN
+    // consecutive bytes, one base pointer, no border arithmetic
+    const T* p0 = src + (size_t)iy * pitch_elems + ix * CN;
+    const T* p1 = p0 + pitch_elems;
+    const int w00 = (32 - fy) * (32 - fx) * 32, w01 = (32 - fy) * fx * 32,
+              w10 = fy * (32 - fx) * 32, w11 = fy * fx * 32;
+#pragma unroll
+    for (int c = 0; c < CN; ++c) {
+      int p00 = __ldg(p0 + c), p01 = __ldg(p0 + CN + c), p10 = __ldg(p1 + c),
+          p11 = __ldg(p1 + CN + c);
+      int v = (p00 * w00 + p01 * w01 + p10 * w10 + p11 * w11 + (1 << 14)) >> 15;
+      out[c] = (T)(v > 255 ? 255 : v);
+    }
+    return;
+  }
+  // border pixels: BORDER_REFLECT indices; interior 16-bit pixels take the
+  // same path with x1 = x0 + 1, y1 = y0 + 1 and no reflection arithmetic
+  const bool inner = (unsigned)ix < (unsigned)(sw - 1) &&
+                     (unsigned)iy < (unsigned)(sh - 1);
+  const int x0 = inner ? ix : reflect_idx(ix, sw),
+            x1 = inner ? ix + 1 : reflect_idx(ix + 1, sw);
+  const int y0 = inner ? iy : reflect_idx(iy, sh),
+            y1 = inner ? iy + 1 : reflect_idx(iy + 1, sh);
   const T* r0 = src + (size_t)y0 * pitch_elems;
   const T* r1 = src + (size_t)y1 * pitch_elems;
   if (sizeof(T) == 1) {
