@@ -106,6 +106,7 @@ Blender::~Blender() {
   if (ev_join) cudaEventDestroy(ev_join);
   if (ev_cover) cudaEventDestroy(ev_cover);
   if (ev_aux) cudaEventDestroy(ev_aux);
+  if (ev_cls) cudaEventDestroy(ev_cls);
   if (side_stream) cudaStreamDestroy(side_stream);
   if (aux_stream) cudaStreamDestroy(aux_stream);
   if (own_stream) cudaStreamDestroy(own_stream);
@@ -114,16 +115,17 @@ Blender::~Blender() {
 void Blender::ensure_device() {
   select_device(opts.device);
   if (!stream && !external_stream) {
-    XP_CUDA(cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
+    own_stream = create_stream(true);
     stream = own_stream;
   }
   if (!side_stream) {
-    XP_CUDA(cudaStreamCreateWithFlags(&side_stream, cudaStreamNonBlocking));
+    side_stream = create_stream(false);
     XP_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
     XP_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
     XP_CUDA(cudaEventCreateWithFlags(&ev_cover, cudaEventDisableTiming));
-    XP_CUDA(cudaStreamCreateWithFlags(&aux_stream, cudaStreamNonBlocking));
+    aux_stream = create_stream(false);
     XP_CUDA(cudaEventCreateWithFlags(&ev_aux, cudaEventDisableTiming));
+    XP_CUDA(cudaEventCreateWithFlags(&ev_cls, cudaEventDisableTiming));
   }
 }
 

@@ -64,7 +64,8 @@ void launch_cover(void* cover, int cover_bytes, int W, int H,
                   cudaStream_t s);
 void launch_seams(const void* cover, int cover_bytes, int n_images, int W,
                   int H, int reverse, uint32_t* bwd, uint32_t* fwd, uint8_t* labels,
-                  int* counter, uint8_t* flags, cudaStream_t s);
+                  int* counter, uint8_t* flags, cudaStream_t s,
+                  cudaStream_t beside = nullptr, cudaEvent_t ev = nullptr);
 // bytes of tile flags launch_seams / launch_inpaint need
 size_t wavefront_flag_bytes(int n_bands, int max_w);
 void launch_seam_unpack(const uint32_t* in, size_t n, uint64_t* out,

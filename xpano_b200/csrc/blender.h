@@ -38,7 +38,7 @@ struct Blender {
   cudaStream_t side_stream = nullptr;  // inpaint runs beside the seam passes
   cudaStream_t aux_stream = nullptr;   // cover-only statistics
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_cover = nullptr,
-              ev_aux = nullptr;
+              ev_aux = nullptr, ev_cls = nullptr;
   bool external_stream = false;
   int roi[4] = {0, 0, 0, 0};
   std::vector<std::unique_ptr<Fed>> fed;

@@ -219,6 +219,15 @@ void copy_out_2d(void* user, size_t user_pitch, const void* dev,
       s));
 }
 
+cudaStream_t create_stream(bool high_priority) {
+  int least = 0, greatest = 0;
+  XP_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+  cudaStream_t s = nullptr;
+  XP_CUDA(cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking,
+                                       high_priority ? greatest : least));
+  return s;
+}
+
 void sync_blocking(cudaStream_t s) {
   // one event per thread and device; blocking-sync events make
   // cudaEventSynchronize yield the core

@@ -136,6 +136,11 @@ struct DevBuf {
   }
 };
 
+// Non-blocking stream of the highest (main chain: seams, pyramid tail) or
+// lowest (work that runs beside it) priority the device offers: when both
+// have blocks pending, the main chain's are placed first.
+cudaStream_t create_stream(bool high_priority);
+
 // Wait for a stream with the calling thread blocked in the OS instead of
 // spinning in the driver: for the long waits on bulk copies (uploads,
 // downloads) that overlap another thread's kernel launches.

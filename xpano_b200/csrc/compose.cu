@@ -131,7 +131,7 @@ struct Composer {
   void ensure_device() {
     select_device(opts.blend.device);
     if (!stream && !external_stream) {
-      XP_CUDA(cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
+      own_stream = create_stream(true);
       stream = own_stream;
     }
     for (cudaEvent_t& e : ev)

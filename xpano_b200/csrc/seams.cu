@@ -509,34 +509,43 @@ void launch_seam_unpack(const u32* in, size_t n, u64* out, cudaStream_t s) {
 template <class C, int F>
 static void seams_t(const void* cover, int W, int H, int reverse, u32* bwd,
                     u32* fwd, uint8_t* labels, int* counter, uint8_t* flags,
-                    cudaStream_t s) {
+                    cudaStream_t s, cudaStream_t beside, cudaEvent_t ev) {
   const int n_bands = div_up(H, wf::kLanes);
   const int fp = wf::chunks_of(W);
-  // both classification passes depend on the cover map only: run them back
-  // to back, then the two dependent wavefronts (separate flag arrays)
+  // Both classification passes depend on the cover map only (the forward
+  // one loads the backward value of each pixel but never looks at it). The
+  // forward one leaves the critical chain: it runs on `beside`, which the
+  // caller has made wait for the cover map, under the backward wavefront.
   uint8_t* flags_fwd = flags + wf_scratch_bytes(n_bands, fp);
   SeamBwd<C, F> pb{n_bands, W, H, (const C*)cover, bwd};
   SeamFwd<C, F> pf{n_bands, W, H, reverse, (const C*)cover, bwd, fwd, labels};
   launch_classify(pb, flags, fp, s);
-  launch_classify(pf, flags_fwd, fp, s);
+  if (beside) {
+    launch_classify(pf, flags_fwd, fp, beside);
+    XP_CUDA(cudaEventRecord(ev, beside));
+  } else {
+    launch_classify(pf, flags_fwd, fp, s);
+  }
   launch_wavefront(pb, counter, flags, fp, s, true);
+  if (beside) XP_CUDA(cudaStreamWaitEvent(s, ev, 0));
   launch_wavefront(pf, counter, flags_fwd, fp, s, true);
 }
 
 void launch_seams(const void* cover, int cover_bytes, int n_images, int W,
                   int H, int reverse, u32* bwd, u32* fwd, uint8_t* labels,
-                  int* counter, uint8_t* flags, cudaStream_t s) {
+                  int* counter, uint8_t* flags, cudaStream_t s,
+                  cudaStream_t beside, cudaEvent_t ev) {
   XP_REQUIRE((long)W + H < kSeamMaxExtent,
              "canvas %d x %d exceeds the seam distance range", W, H);
   if (cover_bytes == 8)
     seams_t<u64, kCoverBits>(cover, W, H, reverse, bwd, fwd, labels, counter,
-                             flags, s);
+                             flags, s, beside, ev);
   else if (cover_format(n_images) == kCoverDigest)
     seams_t<u32, kCoverDigest>(cover, W, H, reverse, bwd, fwd, labels, counter,
-                               flags, s);
+                               flags, s, beside, ev);
   else
     seams_t<u32, kCoverBits>(cover, W, H, reverse, bwd, fwd, labels, counter,
-                             flags, s);
+                             flags, s, beside, ev);
 }
 
 // ---------------------------------------------------------------------------
