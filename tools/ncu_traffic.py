@@ -19,7 +19,7 @@ import os
 import re
 import sys
 
-GROUP = ("shrink_tiled_kernel", "mask_shrink", "lapcomp_kernel",
+GROUP = ("shrink_tiled_kernel", "shrink_batch_kernel", "mask_shrink", "lapcomp_kernel",
          "composite_kernel", "pad_kernel", "laplace_kernel",
          "xor_sum", "offset_kernel", "out_kernel")
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9,
@@ -31,17 +31,19 @@ def main():
     out = sys.argv[3] if len(sys.argv) > 3 else os.path.join(
         os.path.dirname(os.path.abspath(__file__)), "..", "profiles",
         "traffic.json")
+    rows = [r for r in csv.reader(open(path))
+            if len(r) >= 15 and r[0].isdigit()]
+    short = lambda r: re.sub(r"^void ", "", re.sub(r"[<(].*", "", r[4]))
+    # whole steps only: a step ends with its out_kernel launch
+    ends = sorted({int(r[0]) for r in rows if short(r) == "out_kernel"})
+    last = ends[-1] if ends else -1
+    steps = len(ends)
     per = collections.OrderedDict()
-    steps = 0
-    seen = set()
-    for r in csv.reader(open(path)):
-        if len(r) < 15 or not r[0].isdigit():
+    for r in rows:
+        if int(r[0]) > last:
             continue
-        name = re.sub(r"^void ", "", re.sub(r"[<(].*", "", r[4]))
+        name = short(r)
         metric, unit, val = r[12], r[13], float(r[14].replace(",", ""))
-        if name == "out_kernel" and r[0] not in seen:
-            seen.add(r[0])
-            steps += 1
         if not name.startswith(GROUP):
             continue
         k = per.setdefault(name, {"launches": set(), "dram_bytes": 0.0,

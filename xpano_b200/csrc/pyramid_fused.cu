@@ -276,15 +276,24 @@ struct LapComp {
   }
 };
 
-template <class Hi, bool kFirstTouch>
+// kPairs: two rows per thread (level 0, tens of thousands of blocks); the
+// upper levels are a few hundred blocks each and keep one row per thread --
+// halving their grids costs more in parallelism than the shared rows save.
+template <class Hi, bool kFirstTouch, bool kPairs>
 __global__ void __launch_bounds__(256)
     lapcomp_kernel(const LapComp<Hi, kFirstTouch> k, int y_first) {
   const int g =
       floor_div4(k.m.x0 - k.x_off) + blockIdx.x * blockDim.x + threadIdx.x;
+  const int y_end = k.m.y0 + k.m.h;
+  if (!kPairs) {
+    const int Y = k.m.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+    const int X0 = 4 * g + k.x_off;
+    if (Y < y_end && X0 < k.m.x0 + k.m.w) k.row(g, X0, Y);
+    return;
+  }
   // row pairs start at y_first (<= m.y0), chosen so that image row
   // y_first - y_off + ys is even
   const int Ya = y_first + 2 * (blockIdx.y * blockDim.y + threadIdx.y);
-  const int y_end = k.m.y0 + k.m.h;
   if (Ya >= y_end) return;
   const int X0 = 4 * g + k.x_off;
   if (X0 >= k.m.x0 + k.m.w) return;
@@ -316,7 +325,7 @@ void launch_lapcomp(const ImgDev& im, int bpp, float mul, const PyrGeom& in_g,
   const int y_first = m.y0 - ((m.y0 - y_off + I.ys) & 1);
   const int pairs = (m.y0 + m.h - y_first + 1) / 2;
   dim3 b(32, 8);
-  dim3 gr(div_up(g1 - g0 + 1, 32), div_up(pairs, 8));
+  dim3 gr(div_up(g1 - g0 + 1, 32), div_up(level == 0 ? pairs : m.h, 8));
   const float* lo = in_pyr + Lo.offset;
   float* out = out_pyr + O.offset;
   const float* mk = level == 0 ? nullptr : mask + m.offset;
@@ -327,7 +336,7 @@ void launch_lapcomp(const ImgDev& im, int bpp, float mul, const PyrGeom& in_g,
         HI,       I.w,     I.h,    I.xs, I.ys, lo, Lo.pitch,                  \
         in_g.channel_floats, out,  O.pitch, out_g.channel_floats, x_off,      \
         y_off,    m,       mk,     lb,   image};                              \
-    lapcomp_kernel<decltype(HI), FIRST><<<gr, b, 0, s>>>(k, y_first);         \
+    lapcomp_kernel<decltype(HI), FIRST, FIRST><<<gr, b, 0, s>>>(k, y_first);  \
   }
   if (level > 0) {
     FloatLevel hi{in_pyr + I.offset, I.pitch, in_g.channel_floats};
