@@ -802,6 +802,73 @@ __global__ void __launch_bounds__(256)
   if (threadIdx.x == 0 && s_uncovered) stats->uncovered = 1;
 }
 
+// Owner-region boxes (kMode 2) as a streaming pass over the label map: four
+// consecutive pixels of the linear canvas per thread. Nearly every thread
+// sees one label; the lanes of a warp that share (row, label) elect their
+// lowest lane, which extends that label's box by the span of all of them.
+__global__ void __launch_bounds__(256)
+    label_boxes_kernel(const uint8_t* __restrict__ labels, int W, size_t n_px,
+                       int n, CanvasStats* stats) {
+  __shared__ int s_box[64][4];
+  for (int i = threadIdx.x; i < 64; i += blockDim.x) {
+    s_box[i][0] = s_box[i][1] = INT_MAX;
+    s_box[i][2] = s_box[i][3] = -1;
+  }
+  __syncthreads();
+  auto extend = [&](int label, int xa, int xb, int y) {
+    if (label >= 64) return;
+    atomicMin(&s_box[label][0], xa);
+    atomicMin(&s_box[label][1], y);
+    atomicMax(&s_box[label][2], xb);
+    atomicMax(&s_box[label][3], y);
+  };
+  const int lane = threadIdx.x & 31;
+  const size_t groups = (n_px + 3) / 4;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  // whole warps iterate together (the vote below needs every lane)
+  const size_t rounds = (groups + stride - 1) / stride;
+  for (size_t r = 0; r < rounds; ++r) {
+    const size_t g = r * stride + blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    const size_t p0 = 4 * g;
+    unsigned key = 0x80000000u | (unsigned)lane;  // no peers
+    int x = 0, y = 0;
+    if (g < groups) {
+      y = (int)(p0 / W);
+      x = (int)(p0 - (size_t)y * W);
+      if (p0 + 3 < n_px && x + 3 < W) {
+        const unsigned v = *reinterpret_cast<const unsigned*>(labels + p0);
+        if (v == (v & 0xffu) * 0x01010101u) {
+          key = ((unsigned)y << 6) | (v & 63u);
+          if ((v & 0xffu) >= 64u) key = 0x80000000u | (unsigned)lane;
+        } else {
+          for (int k = 0; k < 4; ++k)
+            extend((int)((v >> (8 * k)) & 0xffu), x + k, x + k, y);
+        }
+      } else {
+        int xx = x, yy = y;
+        for (int k = 0; k < 4 && p0 + k < n_px; ++k) {
+          extend(labels[p0 + k], xx, xx, yy);
+          if (++xx == W) xx = 0, ++yy;
+        }
+      }
+    }
+    const unsigned peers = __match_any_sync(~0u, key);
+    const int hi_lane = 31 - __clz(peers);
+    const int x_hi = __shfl_sync(~0u, x + 3, hi_lane);
+    if (!(key & 0x80000000u) && lane == __ffs(peers) - 1)
+      extend((int)(key & 63u), x, x_hi, y);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    if (s_box[i][2] >= 0) {
+      atomicMin(&stats->box[i][0], s_box[i][0]);
+      atomicMin(&stats->box[i][1], s_box[i][1]);
+      atomicMax(&stats->box[i][2], s_box[i][2]);
+      atomicMax(&stats->box[i][3], s_box[i][3]);
+    }
+  }
+}
+
 __global__ void stats_init_kernel(CanvasStats* st) {
   const int i = threadIdx.x;
   if (i < 4) st->totals[i] = 0;
@@ -820,6 +887,14 @@ void launch_canvas_stats(const void* cover, int cover_bytes,
                          const ImgDev* d_imgs, int n, int bpp,
                          uint8_t* full_mask, uint8_t* xor_mask,
                          CanvasStats* d_stats, int mode, cudaStream_t s) {
+  if (mode == 2) {  // needs the labels only
+    if (n > 1) {
+      label_boxes_kernel<<<148 * 8, 256, 0, s>>>(labels, W, (size_t)W * H, n,
+                                                 d_stats);
+      XP_LAUNCHED();
+    }
+    return;
+  }
   dim3 b(32, 8);
   const int g = std::min(div_up(W, 32) * div_up(H, 8), 148 * 8);
 #define XP_STATS3(C, F, BPP, M)                                               \
