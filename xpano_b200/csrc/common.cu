@@ -2,6 +2,10 @@
 
 #include <map>
 #include <mutex>
+#include <thread>
+#include <algorithm>
+#include <cstdlib>
+#include <sched.h>
 #include <utility>
 #include <vector>
 #include <cstring>
@@ -226,6 +230,42 @@ cudaStream_t create_stream(bool high_priority) {
   XP_CUDA(cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking,
                                        high_priority ? greatest : least));
   return s;
+}
+
+namespace {
+struct HostShare {
+  int threads;  // cap of worker threads per process
+  bool block;   // waits yield the core
+  HostShare() {
+    const unsigned hc = std::thread::hardware_concurrency();
+    int cores = hc ? (int)hc : 8;
+    cpu_set_t set;
+    if (sched_getaffinity(0, sizeof(set), &set) == 0)
+      cores = std::max(1, CPU_COUNT(&set));
+    int ranks = 1;
+    if (const char* e = getenv("LOCAL_WORLD_SIZE")) ranks = std::max(1, atoi(e));
+    const int per_rank = std::max(1, cores / ranks);
+    threads = per_rank;
+    block = per_rank < 8;
+    if (const char* e = getenv("XP_HOST_THREADS")) threads = std::max(1, atoi(e));
+    if (const char* e = getenv("XP_SYNC_BLOCK")) block = atoi(e) != 0;
+  }
+};
+const HostShare& host_share() {
+  static const HostShare h;
+  return h;
+}
+}  // namespace
+
+int host_worker_threads(int wanted) {
+  return std::max(0, std::min(wanted, host_share().threads - 1));
+}
+
+void sync_stream(cudaStream_t s) {
+  if (host_share().block)
+    sync_blocking(s);
+  else
+    XP_CUDA(cudaStreamSynchronize(s));
 }
 
 void sync_blocking(cudaStream_t s) {

@@ -146,6 +146,14 @@ cudaStream_t create_stream(bool high_priority);
 // downloads) that overlap another thread's kernel launches.
 void sync_blocking(cudaStream_t s);
 
+// Host threads this process should use for short parallel host work, and
+// whether its stream waits should yield the core: several ranks of one job
+// share the box's cores (torchrun exports LOCAL_WORLD_SIZE), and a rank that
+// spins in the driver or wakes eight workers takes them from its peers.
+// Overrides: XP_HOST_THREADS, XP_SYNC_BLOCK.
+int host_worker_threads(int wanted);
+void sync_stream(cudaStream_t s);
+
 inline int div_up(int a, int b) { return (a + b - 1) / b; }
 inline size_t div_up(size_t a, size_t b) { return (a + b - 1) / b; }
 

@@ -50,7 +50,7 @@ class HostPool {
       for (int i = 0; i < n; ++i) fn(i);
       return;
     }
-    ensure(std::min(n - 1, 7));
+    ensure(host_worker_threads(std::min(n - 1, 7)));
     {
       std::lock_guard<std::mutex> lk(mu_);
       fn_ = &fn;
@@ -313,7 +313,7 @@ struct Composer {
     memset(&tm, 0, sizeof(tm));
     blender->blend(&tm);
     XP_CUDA(cudaEventRecord(ev[2], stream));
-    XP_CUDA(cudaStreamSynchronize(stream));
+    sync_stream(stream);
     if (trace)
       fprintf(stderr,
               "trace host: roi %.3f ms, new blender + warp launches %.3f ms, "
