@@ -117,12 +117,14 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
+    def __init__(self, index, interval_ms=20):
+        # every query takes driver locks that kernel launches also need: with
+        # several ranks on one box only a slow poll is harmless
         self.p = None
         try:
             self.p = subprocess.Popen(
                 ["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
-                 "--format=csv,noheader,nounits", "-lms", "20"],
+                 "--format=csv,noheader,nounits", "-lms", str(interval_ms)],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             pass
@@ -341,7 +343,7 @@ def run_ours(args, cfg):
     for _ in range(args.warmup):
         info = comp.run()
     barrier()
-    clocks = ClockSampler(local)
+    clocks = ClockSampler(local, 20 if world == 1 else 250)
     launches0 = lib.xp_kernel_launch_count()
     ev0, ev1 = torch.cuda.Event(True), torch.cuda.Event(True)
     stage_ms = {}
@@ -355,7 +357,11 @@ def run_ours(args, cfg):
     barrier()
     launches = lib.xp_kernel_launch_count() - launches0
     clk = clocks.stop()
-    ms = max_over_ranks(ev0.elapsed_time(ev1))
+    ms_rank = ev0.elapsed_time(ev1)
+    if world > 1:  # per-rank record: the job's time is the slowest rank's
+        print(f"[rank {rank}] {ms_rank / args.steps:.3f} ms/step, "
+              f"{host_cores()} host cores visible", file=sys.stderr)
+    ms = max_over_ranks(ms_rank)
     mp_rank = info["width"] * info["height"] / 1e6
     total_mp = sum_over_ranks(mp_rank)
     value = total_mp * args.steps / (ms / 1e3)

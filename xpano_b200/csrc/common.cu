@@ -246,7 +246,10 @@ struct HostShare {
     if (const char* e = getenv("LOCAL_WORLD_SIZE")) ranks = std::max(1, atoi(e));
     const int per_rank = std::max(1, cores / ranks);
     threads = per_rank;
-    block = per_rank < 8;
+    // spinning waits stay the default even when cores are short: blocking
+    // ones (interrupt-driven) were measured at several ms per wake-up with
+    // eight ranks on one box
+    block = false;
     if (const char* e = getenv("XP_HOST_THREADS")) threads = std::max(1, atoi(e));
     if (const char* e = getenv("XP_SYNC_BLOCK")) block = atoi(e) != 0;
   }
