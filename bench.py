@@ -121,6 +121,8 @@ class ClockSampler:
         # every query takes driver locks that kernel launches also need: with
         # several ranks on one box only a slow poll is harmless
         self.p = None
+        if index is None:
+            return
         try:
             self.p = subprocess.Popen(
                 ["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
@@ -343,7 +345,10 @@ def run_ours(args, cfg):
     for _ in range(args.warmup):
         info = comp.run()
     barrier()
-    clocks = ClockSampler(local, 20 if world == 1 else 250)
+    # one nvidia-smi poller per job: every query takes driver locks on all
+    # GPUs of the box, and kernel launches of every rank wait for them
+    clocks = ClockSampler(local if rank == 0 else None,
+                          20 if world == 1 else 250)
     launches0 = lib.xp_kernel_launch_count()
     ev0, ev1 = torch.cuda.Event(True), torch.cuda.Event(True)
     stage_ms = {}
