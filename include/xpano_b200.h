@@ -229,8 +229,14 @@ typedef struct {
 typedef struct {
   int projection, portrait;
   float a, b;
-  float warp_scale;     /* warped_image_scale * compose_work_aspect         */
-  double max_pano_mpx;  /* StitchUserOptions::max_pano_mpx (constants.h:106)*/
+  float warp_scale;     /* warped_image_scale * compose_work_aspect, used
+                           when warped_image_scale == 0                     */
+  double max_pano_mpx;  /* StitchUserOptions::max_pano_mpx (constants.h:106);
+                           0 = no cap                                       */
+  /* the two doubles of stitcher.cc:306-313 (warped_image_scale_,
+   * 1.0 / work_scale_): given separately, the capped scale is formed exactly
+   * as the reference forms it (xp_compose_capped_scale)                    */
+  double warped_image_scale, compose_work_aspect;
   int depth;            /* 8 or 16                                          */
   xp_blend_opts blend;
 } xp_compose_opts;
@@ -254,6 +260,13 @@ typedef struct {
 } xp_compose_info;
 
 void xp_compose_opts_default(xp_compose_opts* o);
+/* The size cap of stitcher.cc:318-335 as host arithmetic: pano_mpx in float
+ * (utils/opencv.cc:35-38), compared with float(max_pano_mpx), float sqrt,
+ * warped_image_scale (double) *= ratio, then *warp_scale =
+ * float(warped_image_scale * compose_work_aspect). Returns 1 when capped. */
+int xp_compose_capped_scale(double warped_image_scale,
+                            double compose_work_aspect, int roi_w, int roi_h,
+                            double max_pano_mpx, float* warp_scale);
 xp_status xp_composer_create(const xp_compose_opts* opts, xp_composer** out);
 void xp_composer_destroy(xp_composer* c);
 xp_status xp_composer_set_stream(xp_composer* c, void* cuda_stream);

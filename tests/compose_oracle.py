@@ -25,23 +25,42 @@ def compute_roi(warper, sizes, Ks, Rs):
     return rois, (x0, y0, x1 - x0, y1 - y0)
 
 
+def capped_scale(warped_image_scale, compose_work_aspect, roi_w, roi_h,
+                 max_pano_mpx):
+    """stitcher.cc:312-329 + utils/opencv.cc:35-38, type for type: MPx is a
+    float product over 1e6f, max_pano_mpx_ a float (stitcher.h:141-143),
+    std::sqrt(float) the float overload; warped_image_scale_ is a double that
+    is multiplied by the float ratio, and only the product with the (double)
+    aspect is rounded to float. -> (float32 warp scale, capped)."""
+    f32 = np.float32
+    wis = float(warped_image_scale)
+    pano_mpx = f32(f32(f32(roi_w) * f32(roi_h)) / f32(1e6))
+    max_mpx = f32(max_pano_mpx)
+    capped = bool(max_pano_mpx > 0 and pano_mpx > max_mpx)
+    if capped:
+        downscale_ratio = f32(np.sqrt(f32(max_mpx / pano_mpx)))
+        wis = wis * float(downscale_ratio)
+    return f32(wis * float(compose_work_aspect)), capped
+
+
 def compose(images, Ks, Rs, projection=wo.SPHERICAL, warp_scale=1.0,
             portrait=False, a=2.0, b=1.0, max_pano_mpx=100.0, gains=None,
-            seam_masks=None, keep_fed=False, **blend_kw):
+            seam_masks=None, keep_fed=False, warped_image_scale=None,
+            compose_work_aspect=1.0, **blend_kw):
     """-> dict(pano (H, W, 3) zeroed outside mask, mask, planes, min_x, min_y,
     warp_scale, capped, fed=[(bgra, corner)])."""
     sizes = [(im.shape[1], im.shape[0]) for im in images]
-    scale = np.float32(warp_scale)
+    if warped_image_scale is None:
+        warped_image_scale = float(np.float32(warp_scale))
+        compose_work_aspect = 1.0
+    scale = np.float32(warped_image_scale * compose_work_aspect)
     warper = wo.Warper(projection, float(scale), portrait, a, b)
     rois, rect = compute_roi(warper, sizes, Ks, Rs)
-    mpx = rect[2] * rect[3] / 1e6
-    capped = False
-    if max_pano_mpx > 0 and mpx > max_pano_mpx:
-        ratio = np.float32(math.sqrt(max_pano_mpx / mpx))
-        scale = np.float32(float(scale) * float(ratio))
+    scale, capped = capped_scale(warped_image_scale, compose_work_aspect,
+                                 rect[2], rect[3], max_pano_mpx)
+    if capped:
         warper = wo.Warper(projection, float(scale), portrait, a, b)
         rois, rect = compute_roi(warper, sizes, Ks, Rs)
-        capped = True
     fed, posn = [], []
     for i, im in enumerate(images):
         if seam_masks is not None and seam_masks[i] is not None \

@@ -137,3 +137,40 @@ def test_argument_errors(xb):
     b = xb.Multiblend()
     with pytest.raises(ValueError):
         b.feed(np.zeros((4, 4), np.uint8), np.zeros((4, 4), np.uint8), (0, 0))
+
+
+def test_size_cap_arithmetic_matches_the_reference(xb):
+    """stitcher.cc:318-335: the capped warp scale is formed in float/double
+    exactly as the reference mixes them; an all-double evaluation differs in
+    the last bit for part of the inputs, which this test must see."""
+    import ctypes
+    import math
+    import compose_oracle as co
+    lib = xb._lib.load()
+    rng = np.random.default_rng(11)
+    differs_from_double = 0
+    for _ in range(4000):
+        wis = float(rng.uniform(200.0, 9000.0))
+        cwa = float(rng.uniform(1.0, 9.0))
+        w, h = int(rng.integers(500, 40000)), int(rng.integers(300, 12000))
+        cap = float(rng.choice([0.35, 20, 50, 100, 1000]))
+        got = ctypes.c_float()
+        capped = lib.xp_compose_capped_scale(wis, cwa, w, h, cap,
+                                             ctypes.byref(got))
+        want, want_capped = co.capped_scale(wis, cwa, w, h, cap)
+        assert bool(capped) == want_capped
+        assert np.float32(got.value) == want, (wis, cwa, w, h, cap)
+        if want_capped:
+            mpx = w * h / 1e6
+            old = np.float32(float(np.float32(wis * cwa)) *
+                             float(np.float32(math.sqrt(cap / mpx))))
+            differs_from_double += int(old != want)
+    assert differs_from_double > 0
+    # not capped: the scale is just float(wis * cwa); 0 switches the cap off
+    got = ctypes.c_float()
+    assert lib.xp_compose_capped_scale(1234.5678, 3.3, 20000, 5000, 0.0,
+                                       ctypes.byref(got)) == 0
+    assert np.float32(got.value) == np.float32(1234.5678 * 3.3)
+    # exactly at the limit is not capped (pano_mpx > max_pano_mpx_)
+    assert lib.xp_compose_capped_scale(1000.0, 1.0, 10000, 10000, 100.0,
+                                       ctypes.byref(got)) == 0

@@ -53,7 +53,9 @@ class ComposeImage(ctypes.Structure):
 class ComposeOpts(ctypes.Structure):
     _fields_ = [("projection", c_int), ("portrait", c_int), ("a", c_float),
                 ("b", c_float), ("warp_scale", c_float),
-                ("max_pano_mpx", ctypes.c_double), ("depth", c_int),
+                ("max_pano_mpx", ctypes.c_double),
+                ("warped_image_scale", ctypes.c_double),
+                ("compose_work_aspect", ctypes.c_double), ("depth", c_int),
                 ("blend", BlendOpts)]
 
 
@@ -120,6 +122,9 @@ SYMBOLS = {
     "xp_pyramid_geometry": (c_int, [c_int] * 5 + [c_void_p] * 7),
     "xp_blend_levels": (c_int, [c_int, c_void_p, c_void_p, c_int, c_int]),
     "xp_compose_opts_default": (None, [P(ComposeOpts)]),
+    "xp_compose_capped_scale": (c_int, [ctypes.c_double, ctypes.c_double,
+                                        c_int, c_int, ctypes.c_double,
+                                        P(c_float)]),
     "xp_composer_create": (c_int, [P(ComposeOpts), P(c_void_p)]),
     "xp_composer_destroy": (None, [c_void_p]),
     "xp_composer_set_stream": (c_int, [c_void_p, c_void_p]),

@@ -48,17 +48,36 @@ class Multiblend:
                                            int(h)))
 
     def feed(self, img, mask, tl):
-        """img: (h, w, 3) u8/u16, mask: (h, w) u8, tl: (x, y)."""
-        img = np.ascontiguousarray(img)
-        mask = np.ascontiguousarray(mask, np.uint8)
-        if img.ndim != 3 or img.shape[2] != 3:
+        """img: (h, w, 3) u8/u16, mask: (h, w) u8, tl: (x, y). Rows may be
+        strided (a cv::Mat ROI: step != cols * elemSize), as blenders.cc:86-95
+        handles non-continuous inputs."""
+        img, mask = np.asarray(img), np.asarray(mask)
+        if img.ndim != 3 or img.shape[2] != 3 or \
+                img.dtype not in (np.uint8, np.uint16):
             raise ValueError("feed: CV_Assert(img.type() == CV_8UC3)")
+        if mask.dtype != np.uint8 or mask.ndim != 2:
+            raise ValueError("feed: CV_Assert(mask.type() == CV_8U)")
         if mask.shape != img.shape[:2]:
             raise ValueError("feed: mask size differs from the image")
+        it = img.dtype.itemsize
+        if img.strides[1:] != (3 * it, it) or img.strides[0] < 0:
+            img = np.ascontiguousarray(img)
+        if mask.strides[1] != 1 or mask.strides[0] < 0:
+            mask = np.ascontiguousarray(mask)
         h, w = mask.shape
         check(self._lib.xp_blender_feed(
-            self._h, img.ctypes.data, 0, mask.ctypes.data, 0, w, h,
-            8 * img.dtype.itemsize, int(tl[0]), int(tl[1]), _lib.MEM_HOST))
+            self._h, img.ctypes.data, img.strides[0], mask.ctypes.data,
+            mask.strides[0], w, h, 8 * it, int(tl[0]), int(tl[1]),
+            _lib.MEM_HOST))
+
+    def feed_device(self, img_ptr, stride, mask_ptr, mask_stride, w, h,
+                    depth, tl):
+        """feed() of buffers already in device memory (XP_MEM_DEVICE): raw
+        device pointers, strides in bytes."""
+        check(self._lib.xp_blender_feed(
+            self._h, c_void_p(img_ptr), int(stride), c_void_p(mask_ptr),
+            int(mask_stride), int(w), int(h), int(depth), int(tl[0]),
+            int(tl[1]), _lib.MEM_DEVICE))
 
     def feed_interleaved(self, data, tl):
         """multiblend::io::InMemoryImage with spp 3 or 4."""
@@ -93,6 +112,15 @@ class Multiblend:
         check(self._lib.xp_blender_fetch(self._h, dst.ctypes.data, 0,
                                          mask.ctypes.data, 0, _lib.MEM_HOST))
         return dst, mask
+
+    def blend_device(self, dst_ptr, dst_stride, mask_ptr, mask_stride):
+        """blend() into caller-owned device buffers (XP_MEM_DEVICE); either
+        pointer may be 0. -> (W, H)"""
+        size = self.run()
+        check(self._lib.xp_blender_fetch(
+            self._h, c_void_p(dst_ptr or None), int(dst_stride),
+            c_void_p(mask_ptr or None), int(mask_stride), _lib.MEM_DEVICE))
+        return size
 
     def planes(self):
         """Result.output_channels: (3, H, W), not zeroed outside the mask."""

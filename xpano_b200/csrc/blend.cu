@@ -98,10 +98,18 @@ struct Scope {
 // Blender basics
 // ---------------------------------------------------------------------------
 Blender::~Blender() {
-  // buffers go back to the caching pool: nothing may still be using them
-  if (side_stream) cudaStreamSynchronize(side_stream);
-  if (aux_stream) cudaStreamSynchronize(aux_stream);
-  if (stream) cudaStreamSynchronize(stream);
+  // buffers go back to the caching pool: nothing may still be using them.
+  // The main stream may be the caller's legacy default stream (a null
+  // handle), which is synchronised like any other -- on the blender's device.
+  if (device_ready) {
+    int cur = 0;
+    cudaGetDevice(&cur);
+    if (cur != opts.device) cudaSetDevice(opts.device);
+    if (side_stream) cudaStreamSynchronize(side_stream);
+    if (aux_stream) cudaStreamSynchronize(aux_stream);
+    cudaStreamSynchronize(stream);
+    if (cur != opts.device) cudaSetDevice(cur);
+  }
   if (ev_fork) cudaEventDestroy(ev_fork);
   if (ev_join) cudaEventDestroy(ev_join);
   if (ev_cover) cudaEventDestroy(ev_cover);
@@ -114,6 +122,7 @@ Blender::~Blender() {
 
 void Blender::ensure_device() {
   select_device(opts.device);
+  device_ready = true;
   if (!stream && !external_stream) {
     own_stream = create_stream(true);
     stream = own_stream;

@@ -40,6 +40,7 @@ struct Blender {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_cover = nullptr,
               ev_aux = nullptr, ev_cls = nullptr;
   bool external_stream = false;
+  bool device_ready = false;  // ensure_device() ran: streams may hold work
   int roi[4] = {0, 0, 0, 0};
   std::vector<std::unique_ptr<Fed>> fed;
   DevBuf staging, staging_mask;

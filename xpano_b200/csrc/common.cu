@@ -203,6 +203,21 @@ void select_device(int device) {
   XP_CUDA(cudaSetDevice(device));
 }
 
+int sm_count() {
+  static std::atomic<int> cached[16];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  std::atomic<int>& c = cached[dev & 15];
+  int v = c.load(std::memory_order_relaxed);
+  if (v == 0) {
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) !=
+            cudaSuccess || v <= 0)
+      v = 148;
+    c.store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+
 void copy_in_2d(void* dev, size_t dev_pitch, const void* user,
                 size_t user_pitch, size_t row_bytes, size_t rows, int mem,
                 cudaStream_t s) {

@@ -66,10 +66,11 @@ xp_status guard(F&& f) {
 }
 
 // Owning device allocation.
-// caching device allocator (common.cu); blocks are reused only after the
-// owning stream work was synchronised by the caller's own stream order: every
-// user of a block in this library runs on one stream per object and buffers
-// are released at object destruction, after a stream synchronisation.
+// caching device allocator (common.cu). The pool itself is not stream-ordered:
+// an object may queue work on several streams (a blender uses three), and
+// every owner synchronises all of them -- the caller's stream included, also
+// when that is the legacy default stream -- before its buffers are released,
+// on success and on every error path (the destructors do it).
 void* pool_alloc(size_t n, size_t* got, int* device);
 void pool_free(void* p, size_t bytes, int device);
 void pool_trim();
@@ -158,6 +159,9 @@ inline int div_up(int a, int b) { return (a + b - 1) / b; }
 inline size_t div_up(size_t a, size_t b) { return (a + b - 1) / b; }
 
 void select_device(int device);
+// multiprocessors of the current device (cudaDevAttrMultiProcessorCount,
+// queried once per device; 148 on B200): persistent grids are sized from it
+int sm_count();
 
 // 2-D copy helper between host/device according to `mem` of the *user* side.
 void copy_in_2d(void* dev, size_t dev_pitch, const void* user,

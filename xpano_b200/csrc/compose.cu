@@ -113,16 +113,24 @@ struct Composer {
   std::unique_ptr<Blender> blender;
   std::vector<std::unique_ptr<SrcImage>> src;
   cudaStream_t stream = nullptr, own_stream = nullptr;
-  bool external_stream = false;
+  bool external_stream = false, device_ready = false;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double h2d_ms = 0;
 
   ~Composer() {
-    if (stream) cudaStreamSynchronize(stream);
+    // the caller's stream may be the legacy default stream (a null handle)
+    if (device_ready) {
+      int cur = 0;
+      cudaGetDevice(&cur);
+      if (cur != opts.blend.device) cudaSetDevice(opts.blend.device);
+      cudaStreamSynchronize(stream);
+      if (cur != opts.blend.device) cudaSetDevice(cur);
+    }
     // members that remember the stream must go before it is destroyed
     blender.reset();
     src.clear();
     warper.stream = nullptr;
+    warper.detached = true;
     for (cudaEvent_t e : ev)
       if (e) cudaEventDestroy(e);
     if (own_stream) cudaStreamDestroy(own_stream);
@@ -130,6 +138,7 @@ struct Composer {
 
   void ensure_device() {
     select_device(opts.blend.device);
+    device_ready = true;
     if (!stream && !external_stream) {
       own_stream = create_stream(true);
       stream = own_stream;
@@ -267,18 +276,20 @@ struct Composer {
     };
     const double h0 = now();
     ensure_device();
-    float scale = opts.warp_scale;
+    // stitcher.cc:306-313: warp_scale = float(warped_image_scale_ *
+    // compose_work_aspect), both doubles there
+    double wis = opts.warped_image_scale, cwa = opts.compose_work_aspect;
+    if (!(wis > 0)) {
+      wis = (double)opts.warp_scale;
+      cwa = 1.0;
+    }
+    float scale = (float)(wis * cwa);
     std::vector<int> rois;
     int rect[4];
     compute_roi(scale, rois, rect);
-    bool capped = false;
-    const double mpx = (double)rect[2] * rect[3] / 1e6;
-    if (opts.max_pano_mpx > 0 && mpx > opts.max_pano_mpx) {  // :318-335
-      const float ratio = (float)std::sqrt(opts.max_pano_mpx / mpx);
-      scale = (float)((double)scale * ratio);
-      compute_roi(scale, rois, rect);
-      capped = true;
-    }
+    const bool capped = xp_compose_capped_scale(wis, cwa, rect[2], rect[3],
+                                                opts.max_pano_mpx, &scale) != 0;
+    if (capped) compute_roi(scale, rois, rect);
     const double h1 = now();
     xp_blend_opts bo = opts.blend;
     blender.reset(new Blender(bo));
@@ -357,6 +368,25 @@ struct xp_composer : xp::Composer {};
 
 extern "C" {
 
+int xp_compose_capped_scale(double warped_image_scale,
+                            double compose_work_aspect, int roi_w, int roi_h,
+                            double max_pano_mpx, float* warp_scale) {
+  // utils::opencv::MPx (utils/opencv.cc:35-38): float product over 1e6f;
+  // max_pano_mpx_ is a float (stitcher.h:141-143, 282); std::sqrt of a float
+  // is the float overload; warped_image_scale_ (double) *= ratio, and only
+  // then is the product with the aspect rounded to float (stitcher.cc:318-329)
+  const float pano_mpx = (float)roi_w * (float)roi_h / 1e6f;
+  const float max_mpx = (float)max_pano_mpx;
+  int capped = 0;
+  if (max_pano_mpx > 0 && pano_mpx > max_mpx) {
+    const float downscale_ratio = sqrtf(max_mpx / pano_mpx);
+    warped_image_scale *= downscale_ratio;
+    capped = 1;
+  }
+  if (warp_scale) *warp_scale = (float)(warped_image_scale * compose_work_aspect);
+  return capped;
+}
+
 void xp_compose_opts_default(xp_compose_opts* o) {
   if (!o) return;
   memset(o, 0, sizeof(*o));
@@ -364,6 +394,8 @@ void xp_compose_opts_default(xp_compose_opts* o) {
   o->a = 2.0f;
   o->b = 1.0f;
   o->warp_scale = 1.0f;
+  o->warped_image_scale = 0.0;  // 0: use warp_scale as given
+  o->compose_work_aspect = 1.0;
   o->max_pano_mpx = 100.0;  // constants.h:106
   o->depth = 8;
   xp_blend_opts_default(&o->blend);

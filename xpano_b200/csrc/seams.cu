@@ -253,9 +253,9 @@ static void launch_wavefront(const P& prob, int* counter, uint8_t* scratch,
   // once. One block per SM: its three warps then sit on three different
   // schedulers, whereas a second block's loader or storer warp would share a
   // scheduler with the first block's compute warp and slow every step of it.
-  // Items are short, so 148 of them in flight cover the active front.
+  // Items are short, so one per SM (148) in flight cover the active front.
   const int blocks = (int)std::min<size_t>(
-      wf::max_items(prob.n_bands, flag_pitch), (size_t)148);
+      wf::max_items(prob.n_bands, flag_pitch), (size_t)sm_count());
   wavefront_kernel<P><<<blocks, 32 * wf::kWarpsPerBand, smem, s>>>(
       prob, counter, w.items, w.first + prob.n_bands, w.flags, flag_pitch);
   XP_LAUNCHED();
@@ -354,7 +354,7 @@ void launch_trim(const void* const* data, const int* w, const int* h, int n,
     max_h = std::max(max_h, h[i]);
   }
   // rows are strided over gridDim.x blocks of eight warps
-  dim3 g(std::min(div_up(max_h, 8), 148 * 4), n);
+  dim3 g(std::min(div_up(max_h, 8), sm_count() * 4), n);
   if (bpp == 8)
     trim_kernel<8><<<g, 256, 0, s>>>(batch, d_bbox, d_opaque_count);
   else
@@ -501,7 +501,7 @@ __global__ void seam_unpack_kernel(const u32* __restrict__ in, size_t n,
 
 // debug view: the reference's u64 encoding of the packed seam values
 void launch_seam_unpack(const u32* in, size_t n, u64* out, cudaStream_t s) {
-  const int blocks = (int)std::min<size_t>(div_up(n, (size_t)256), 148 * 16);
+  const int blocks = (int)std::min<size_t>(div_up(n, (size_t)256), sm_count() * 16);
   seam_unpack_kernel<<<blocks, 256, 0, s>>>(in, n, out);
   XP_LAUNCHED();
 }
@@ -889,14 +889,14 @@ void launch_canvas_stats(const void* cover, int cover_bytes,
                          CanvasStats* d_stats, int mode, cudaStream_t s) {
   if (mode == 2) {  // needs the labels only
     if (n > 1) {
-      label_boxes_kernel<<<148 * 8, 256, 0, s>>>(labels, W, (size_t)W * H, n,
+      label_boxes_kernel<<<sm_count() * 8, 256, 0, s>>>(labels, W, (size_t)W * H, n,
                                                  d_stats);
       XP_LAUNCHED();
     }
     return;
   }
   dim3 b(32, 8);
-  const int g = std::min(div_up(W, 32) * div_up(H, 8), 148 * 8);
+  const int g = std::min(div_up(W, 32) * div_up(H, 8), sm_count() * 8);
 #define XP_STATS3(C, F, BPP, M)                                               \
   canvas_stats_kernel<C, F, BPP, M><<<g, b, 0, s>>>((const C*)cover, labels, \
                                                     W, H, d_imgs, n,         \
@@ -904,7 +904,7 @@ void launch_canvas_stats(const void* cover, int cover_bytes,
                                                     d_stats)
 #define XP_STATS(C, F, BPP)                                                 \
   if (mode == 1)                                                            \
-    canvas_masks_kernel<C, F, BPP><<<148 * 8, 256, 0, s>>>(                 \
+    canvas_masks_kernel<C, F, BPP><<<sm_count() * 8, 256, 0, s>>>(                 \
         (const C*)cover, W, (size_t)W * H, d_imgs, n, full_mask, xor_mask, \
         d_stats);                                                           \
   else if (mode == 2)          \

@@ -180,7 +180,7 @@ void Warper::detect_roi(const Projector& p, int w, int h, int out[4],
     XP_CUDA(cudaMemcpyAsync(scratch.p, init, 16, cudaMemcpyHostToDevice,
                             stream));
     int blocks = (int)std::min<size_t>(div_up((size_t)w * h, (size_t)256),
-                                       148 * 16);
+                                       sm_count() * 16);
     roi_all_pixels_kernel<<<blocks, 256, 0, stream>>>(
         p, w, h, scratch.as<unsigned>());
     XP_LAUNCHED();
@@ -559,6 +559,7 @@ __global__ void warp_bgra_kernel(MapSrc m, const T* __restrict__ src,
 // ---------------------------------------------------------------------------
 void Warper::ensure_device() {
   select_device(device);
+  device_ready = true;
   if (!stream && !external_stream) {
     XP_CUDA(cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
     stream = own_stream;
@@ -566,7 +567,15 @@ void Warper::ensure_device() {
 }
 
 Warper::~Warper() {
-  if (stream) cudaStreamSynchronize(stream);
+  // scratch buffers return to the pool: the stream (possibly the caller's
+  // legacy default stream, a null handle) must be idle, also after an error
+  if (device_ready && !(external_stream && detached)) {
+    int cur = 0;
+    cudaGetDevice(&cur);
+    if (cur != device) cudaSetDevice(device);
+    cudaStreamSynchronize(stream);
+    if (cur != device) cudaSetDevice(cur);
+  }
   if (own_stream) cudaStreamDestroy(own_stream);
 }
 

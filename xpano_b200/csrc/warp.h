@@ -13,6 +13,8 @@ struct Warper {
   float scale = 1.f, a = 1.f, b = 1.f;
   cudaStream_t stream = nullptr, own_stream = nullptr;
   bool external_stream = false;
+  bool device_ready = false;  // ensure_device() ran: the stream may hold work
+  bool detached = false;      // the owner (composer) synchronised already
   DevBuf scratch, tables, staging_src, staging_dst, dilated, aux_gain,
       aux_seam;
 

@@ -31,13 +31,20 @@ class Composer:
     def __init__(self, projection=2, warp_scale=1.0, portrait=False, a=2.0,
                  b=1.0, max_pano_mpx=100.0, depth=8, output_bpp=0,
                  fixed_levels=0, add_levels=0, dither=True, reverse=False,
-                 device=0, keep_debug=False):
+                 device=0, keep_debug=False, warped_image_scale=0.0,
+                 compose_work_aspect=1.0):
+        """warp_scale: float(warped_image_scale * compose_work_aspect) as
+        stitcher.cc:312-313 forms it; or give the two doubles themselves
+        (warped_image_scale > 0) so that the size cap rounds as the
+        reference's does."""
         self._lib = _lib.load()
         o = _lib.ComposeOpts()
         self._lib.xp_compose_opts_default(ctypes.byref(o))
         o.projection, o.portrait = int(projection), int(bool(portrait))
         o.a, o.b, o.warp_scale = float(a), float(b), float(warp_scale)
         o.max_pano_mpx, o.depth = float(max_pano_mpx), int(depth)
+        o.warped_image_scale = float(warped_image_scale)
+        o.compose_work_aspect = float(compose_work_aspect)
         o.blend = _lib.BlendOpts(int(output_bpp), int(fixed_levels),
                                  int(add_levels), int(bool(dither)),
                                  int(bool(reverse)), int(device),
