@@ -107,6 +107,33 @@ xp_status xp_warper_warp(xp_warper* w, const void* src, int src_w, int src_h,
                          int border, void* dst, size_t dst_stride, int mem,
                          int out_corner[2]);
 
+/* Allocation-free variant of xp_warper_warp. It has NO counterpart in the
+ * reference: it was added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it). Same arithmetic and result as
+ * xp_warper_warp, with these differences:
+ *  - src and dst are DEVICE pointers (the caller's buffers; dst must hold the
+ *    warp_roi rectangle); the work is queued on `cuda_stream` (a cudaStream_t,
+ *    NULL = the default stream) and the call returns without synchronising;
+ *  - no cudaMalloc / cudaFree / stream creation / pool allocation: the only
+ *    scratch of the warp, the per-column and per-row trig table of a separable
+ *    projection, lives in a static device array of
+ *    XP_NOALLOC_MAX_ROI_PERIMETER float2 entries (512 KiB, held by every GPU
+ *    that loads the library until exit);
+ *  - limits: spherical and cylindrical projections only (their ROI is host
+ *    arithmetic); result ROI width + height <= XP_NOALLOC_MAX_ROI_PERIMETER,
+ *    larger ones fail with XP_ERR_INVALID and a message naming the limit;
+ *  - every call on a device shares that array: calls that overlap on the GPU
+ *    (different streams, or graph branches) race. Nothing in it needs to
+ *    start at zero -- each call rewrites every entry it reads. */
+#define XP_NOALLOC_MAX_ROI_PERIMETER 65536
+xp_status xp_warper_warp_noalloc(xp_warper* w, const void* d_src, int src_w,
+                                 int src_h, size_t src_stride, int depth,
+                                 int channels, const float K[9],
+                                 const float R[9], int interp, int border,
+                                 void* d_dst, size_t dst_stride,
+                                 void* cuda_stream, int out_corner[2]);
+
 /* Fused form of stitcher.cc:377-405 + blenders.cc:99-112 for one image: warp
  * image (LINEAR/REFLECT) and all-255 mask (NEAREST/CONSTANT) from one map
  * evaluation, apply the exposure gain map (BlocksCompensator::apply: bilinear

@@ -4,7 +4,8 @@
 # into oracle/_ref/libmb_ref.so. Nothing is copied into the repo; outputs go
 # only into oracle/_ref/ (git-ignored, but shipped to the GPU box by gpurun).
 # Configuration = xpano's: no MULTIBLEND_WITH_{JPEG,PNG,TIFF}, -msse4.1
-# (external/multiblend/CMakeLists.txt:16-18, 89-91).
+# (external/multiblend/CMakeLists.txt:16-18, 89-91), optimisation as a CMake
+# Release build has it (-O3 -DNDEBUG).
 set -euo pipefail
 HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
 REF="${XPANO_REFERENCE:-/root/reference}"
@@ -37,14 +38,14 @@ OBJS=()
 for s in "${SRCS[@]}"; do
   o="$OUT/$s.o"
   if [ ! -f "$o" ] || [ "$MB/src/$s.cpp" -nt "$o" ]; then
-    g++ -std=c++20 -O2 -msse4.1 -fPIC -w -c "$MB/src/$s.cpp" -o "$o" \
+    g++ -std=c++20 -O3 -DNDEBUG -msse4.1 -fPIC -w -c "$MB/src/$s.cpp" -o "$o" \
       -I"$MB/include" -I"$REF/external/simde" \
       -I"$REF/external/thread-pool/include" -I"$SPDLOG" &
   fi
   OBJS+=("$o")
 done
 wait
-g++ -std=c++20 -O2 -msse4.1 -fPIC -w -shared "$HERE/ref_driver.cpp" "${OBJS[@]}" \
+g++ -std=c++20 -O3 -DNDEBUG -msse4.1 -fPIC -w -shared "$HERE/ref_driver.cpp" "${OBJS[@]}" \
   -I"$MB/include" -I"$REF/external/simde" \
   -I"$REF/external/thread-pool/include" -I"$SPDLOG" \
   -lpthread -o "$OUT/libmb_ref.so"

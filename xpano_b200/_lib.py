@@ -96,6 +96,10 @@ SYMBOLS = {
     "xp_warper_warp": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t,
                                c_int, c_int, c_void_p, c_void_p, c_int, c_int,
                                c_void_p, c_size_t, c_int, c_void_p]),
+    "xp_warper_warp_noalloc": (c_int, [c_void_p, c_void_p, c_int, c_int,
+                                       c_size_t, c_int, c_int, c_void_p,
+                                       c_void_p, c_int, c_int, c_void_p,
+                                       c_size_t, c_void_p, c_void_p]),
     "xp_warper_warp_bgra": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t,
                                     c_int, c_void_p, c_void_p, c_void_p, c_int,
                                     c_void_p, c_size_t, c_int, c_void_p]),

@@ -13,6 +13,8 @@
 
 #include "common.h"
 #include "projector.h"
+#include <mutex>
+
 #include "warp.h"
 
 namespace xp {
@@ -836,6 +838,112 @@ void Warper::warp_bgra(const void* src, int sw, int sh, size_t src_stride,
   XP_CUDA(cudaStreamSynchronize(stream));
 }
 
+// ---------------------------------------------------------------------------
+// Allocation-free warp (xp_warper_warp_noalloc). The only scratch of a warp
+// with a separable projection is the per-column / per-row trig table
+// (sep_tables_kernel); here it lives in a file-scope device array that every
+// GPU loading the library holds until exit, so the call needs no cudaMalloc.
+// ---------------------------------------------------------------------------
+constexpr int kNoAllocTableEntries = XP_NOALLOC_MAX_ROI_PERIMETER;  // float2 each
+static __device__ __align__(256) float2 g_noalloc_tables[kNoAllocTableEntries];
+
+// In host code `g_noalloc_tables` is only a handle for the runtime, not a
+// device address: the address is looked up once per device, with that device
+// current, and cached.
+static float2* noalloc_tables(int device) {
+  static std::mutex mu;
+  static float2* ptr[64] = {};
+  XP_REQUIRE(device >= 0 && device < 64, "device %d out of range", device);
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptr[device]) {
+    void* p = nullptr;
+    XP_CUDA(cudaGetSymbolAddress(&p, g_noalloc_tables));
+    XP_REQUIRE(p, "cudaGetSymbolAddress returned a null address");
+    ptr[device] = static_cast<float2*>(p);
+  }
+  return ptr[device];
+}
+
+void warp_noalloc(const Warper& wr, const void* d_src, int sw, int sh,
+                  size_t src_stride, int depth, int channels, const float* K,
+                  const float* R, int interp, int border, void* d_dst,
+                  size_t dst_stride, cudaStream_t stream, int out_corner[2]) {
+  XP_REQUIRE(d_src && d_dst, "warp_noalloc: null buffer");
+  XP_REQUIRE(sw > 0 && sh > 0, "warp_noalloc: empty source size");
+  XP_REQUIRE(depth == 8 || depth == 16, "warp_noalloc: depth must be 8 or 16");
+  XP_REQUIRE(channels == 1 || channels == 3,
+             "warp_noalloc: channels must be 1 or 3");
+  const bool linear = interp == XP_INTER_LINEAR && border == XP_BORDER_REFLECT;
+  const bool nearest =
+      interp == XP_INTER_NEAREST && border == XP_BORDER_CONSTANT;
+  if (!linear && !nearest)
+    fail(XP_ERR_UNSUPPORTED,
+         "warp_noalloc: only INTER_LINEAR+BORDER_REFLECT and "
+         "INTER_NEAREST+BORDER_CONSTANT are on the export path");
+  if (wr.type != XP_PROJ_SPHERICAL && wr.type != XP_PROJ_CYLINDRICAL)
+    fail(XP_ERR_UNSUPPORTED,
+         "warp_noalloc: only the spherical and cylindrical projections (host "
+         "ROI walk, separable maps) run without device allocations");
+  select_device(wr.device);
+  Projector p = wr.projector(K, R);
+  int roi[4];
+  {  // border-walk ROI: host arithmetic only (see Warper::detect_roi)
+    Warper host_only;
+    host_only.type = wr.type;
+    host_only.detect_roi(p, sw, sh, roi);
+  }
+  check_roi(roi);
+  const int W = roi[2] - roi[0] + 1, H = roi[3] - roi[1] + 1;
+  if ((long)W + H > kNoAllocTableEntries)
+    fail(XP_ERR_INVALID,
+         "warp_noalloc: result ROI %dx%d needs %ld table entries, the static "
+         "scratch holds %d (width + height <= XP_NOALLOC_MAX_ROI_PERIMETER)",
+         W, H, (long)W + H, kNoAllocTableEntries);
+  const size_t bs = depth / 8;
+  if (src_stride == 0) src_stride = (size_t)sw * channels * bs;
+  if (dst_stride == 0) dst_stride = (size_t)W * channels * bs;
+  XP_REQUIRE(src_stride % bs == 0 && dst_stride % bs == 0,
+             "warp_noalloc: stride not a multiple of the sample size");
+  MapSrc m;
+  m.p = p;
+  m.tlx = roi[0];
+  m.tly = roi[1];
+  m.separable = 1;
+  float2* col = noalloc_tables(wr.device);
+  float2* row = col + W;
+  // every entry that is read (W + H of them) is written here first: nothing
+  // carried over from the previous call is used
+  sep_tables_kernel<<<div_up(W + H, 256), 256, 0, stream>>>(p, roi[0], roi[1],
+                                                             W, H, col, row);
+  XP_LAUNCHED();
+  m.col = col;
+  m.row = row;
+  dim3 b(32, 8);
+  dim3 g = grid2d(W, H, b);
+#define XP_WARP_CASE(T, CN)                                                  \
+  if (linear)                                                                \
+    warp_linear_kernel<T, CN><<<g, b, 0, stream>>>(                          \
+        m, (const T*)d_src, src_stride / sizeof(T), sw, sh, W, H, (T*)d_dst, \
+        dst_stride / sizeof(T));                                             \
+  else                                                                       \
+    warp_nearest_kernel<T, CN><<<g, b, 0, stream>>>(                         \
+        m, (const T*)d_src, src_stride / sizeof(T), sw, sh, W, H, (T*)d_dst, \
+        dst_stride / sizeof(T));
+  if (depth == 8 && channels == 1) {
+    XP_WARP_CASE(uint8_t, 1)
+  } else if (depth == 8) {
+    XP_WARP_CASE(uint8_t, 3)
+  } else if (channels == 1) {
+    XP_WARP_CASE(uint16_t, 1)
+  } else {
+    XP_WARP_CASE(uint16_t, 3)
+  }
+#undef XP_WARP_CASE
+  XP_LAUNCHED();
+  out_corner[0] = roi[0];
+  out_corner[1] = roi[1];
+}
+
 }  // namespace xp
 
 // ---------------------------------------------------------------------------
@@ -931,6 +1039,20 @@ xp_status xp_warper_warp(xp_warper* w, const void* src, int src_w, int src_h,
     XP_REQUIRE(w && K && R && out_corner, "warp: null argument");
     w->warp(src, src_w, src_h, src_stride, depth, channels, K, R, interp,
             border, dst, dst_stride, mem, out_corner);
+  });
+}
+
+xp_status xp_warper_warp_noalloc(xp_warper* w, const void* d_src, int src_w,
+                                 int src_h, size_t src_stride, int depth,
+                                 int channels, const float K[9],
+                                 const float R[9], int interp, int border,
+                                 void* d_dst, size_t dst_stride,
+                                 void* cuda_stream, int out_corner[2]) {
+  return guard([&] {
+    XP_REQUIRE(w && K && R && out_corner, "warp_noalloc: null argument");
+    xp::warp_noalloc(*w, d_src, src_w, src_h, src_stride, depth, channels, K,
+                     R, interp, border, d_dst, dst_stride,
+                     (cudaStream_t)cuda_stream, out_corner);
   });
 }
 
