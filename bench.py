@@ -94,7 +94,63 @@ def make_image(w, h, seed, bpp=8):
     return out
 
 
-def make_workload(cfg, group):
+PROJ_NAMES = {2: "spherical", 1: "cylindrical", 7: "mercator", 0: "plane"}
+
+
+def estimate_seams(ims, Ks, Rs, cfg, masks):
+    """The path's two small inputs, produced as the reference produces them:
+    Stitcher::EstimateSeams (stitcher.cc:241-296) run once on the CPU with
+    cv2 -- images resized to the seam scale (0.1 MPx, stitcher.cc:182),
+    warped at warped_image_scale * seam_work_aspect, BlocksGainCompensator
+    fed and applied, GraphCutSeamFinder(COST_COLOR) (stitcher.cc:184-185).
+    This step is outside the path and outside every timed
+    region; both arms get the same arrays.
+
+    masks = "graphcut": the seam finder's masks (the reference's default);
+            "full": the warped all-255 masks untouched by a seam finder
+            (isolates multiblend's own seaming).
+    -> (gains | None, seam_masks): per image, low resolution."""
+    import cv2
+    w, h = cfg["w"], cfg["h"]
+    seam_scale = min(1.0, math.sqrt(0.1 * 1e6 / (w * h)))
+    warper = cv2.PyRotationWarper(PROJ_NAMES[cfg["projection"]],
+                                  float(np.float32(cfg["focal"] * seam_scale)))
+    corners, warped, wmasks = [], [], []
+    for im, K, R in zip(ims, Ks, Rs):
+        small = cv2.resize(im, None, fx=seam_scale, fy=seam_scale,
+                           interpolation=cv2.INTER_LINEAR_EXACT)
+        if small.dtype != np.uint8:  # the compensator and finder are 8-bit
+            small = (small >> 8).astype(np.uint8)
+        Ks_ = np.array(K, np.float32)
+        Ks_[0, 0] *= seam_scale
+        Ks_[1, 1] *= seam_scale
+        Ks_[0, 2] *= seam_scale
+        Ks_[1, 2] *= seam_scale
+        c, iw = warper.warp(small, Ks_, R, cv2.INTER_LINEAR,
+                            cv2.BORDER_REFLECT)
+        _, mw = warper.warp(np.full(small.shape[:2], 255, np.uint8), Ks_, R,
+                            cv2.INTER_NEAREST, cv2.BORDER_CONSTANT)
+        corners.append(c)
+        warped.append(iw)
+        wmasks.append(mw)
+    gains = None
+    if cfg["bpp"] == 8:  # BlocksCompensator::apply asserts CV_8UC3
+        comp = cv2.detail_BlocksGainCompensator()
+        comp.feed(corners, warped, wmasks)
+        warped = [comp.apply(i, corners[i], warped[i], wmasks[i])
+                  for i in range(len(ims))]
+        gains = [np.ascontiguousarray(g, np.float32)
+                 for g in comp.getMatGains()]
+    if masks == "graphcut":
+        finder = cv2.detail_GraphCutSeamFinder("COST_COLOR")
+        out = finder.find([iw.astype(np.float32) for iw in warped], corners,
+                          wmasks)
+        wmasks = [m.get() if hasattr(m, "get") else np.asarray(m)
+                  for m in out]
+    return gains, [np.ascontiguousarray(m, np.uint8) for m in wmasks]
+
+
+def make_workload(cfg, group, masks="graphcut"):
     from xpano_b200 import synthetic as co
     hfov = 2 * math.atan(cfg["w"] / 2 / cfg["focal"])
     extra = None
@@ -106,7 +162,11 @@ def make_workload(cfg, group):
                              2000 + 10 * group, extra=extra)
     ims = [make_image(cfg["w"], cfg["h"], 2000 + 10 * group + i, cfg["bpp"])
            for i in range(len(Ks))]
-    return ims, Ks, Rs
+    gains = seams = None
+    if masks != "none":
+        gains, seams = estimate_seams(ims, Ks, Rs, cfg, masks)
+    return {"ims": ims, "Ks": Ks, "Rs": Rs, "gains": gains, "seams": seams,
+            "masks": masks}
 
 
 class ClockSampler:
@@ -167,32 +227,50 @@ def host_cores():
     return len(os.sched_getaffinity(0))
 
 
-def reference_step(ims, Ks, Rs, cfg, cores):
-    """One pass of the CPU path on the given images. Returns (canvas MP,
-    seconds, kind). kind "reference": cv2 RotationWarper.warp twice per image
-    (stitcher.cc:377-385) + unmodified multiblend (oracle/_ref) with
-    max(2, cores-1) threads (stitcher_pipeline.h:148-149); kind "port": the
-    oracle's C restatement (single thread) when either is unavailable."""
+def reference_step(wl, cfg, cores, keep=False):
+    """One pass of the CPU path over the workload. Returns (canvas MP,
+    seconds, kind, result | None). kind "reference": the loop of
+    stitcher.cc:358-419 with cv2 -- RotationWarper.warp twice per image
+    (:377-385), ExposureCompensator::apply (:389-390), dilate + resize
+    INTER_LINEAR_EXACT + bitwise_and (:397-401), Merge (blenders.cc:99-112)
+    -- then the unmodified multiblend (oracle/_ref) with max(2, cores-1)
+    threads (stitcher_pipeline.h:148-149); kind "port": the oracle's C
+    restatement (single thread) when either is unavailable."""
     from oracle import mb_ref
     try:
         import cv2
     except Exception:  # pragma: no cover
         cv2 = None
-    names = {2: "spherical", 1: "cylindrical", 7: "mercator", 0: "plane"}
+    ims, Ks, Rs = wl["ims"], wl["Ks"], wl["Rs"]
+    gains, seams = wl["gains"], wl["seams"]
     use_ref = cv2 is not None and mb_ref.available() \
-        and cfg["projection"] in names
+        and cfg["projection"] in PROJ_NAMES
     t0 = time.perf_counter()
+    result = None
     if use_ref:
         cv2.setNumThreads(cores)
-        warper = cv2.PyRotationWarper(names[cfg["projection"]],
-                                      float(cfg["focal"]))
+        scale, capped = reference_warp_scale(wl, cfg, cv2)
+        warper = cv2.PyRotationWarper(PROJ_NAMES[cfg["projection"]], scale)
+        comp = None
+        if gains is not None:
+            comp = cv2.detail_BlocksGainCompensator()
+            comp.setMatGains(gains)
         fed, pos = [], []
-        for im, K, R in zip(ims, Ks, Rs):
+        for i, (im, K, R) in enumerate(zip(ims, Ks, Rs)):
+            if seams is not None and cv2.countNonZero(seams[i]) == 0:
+                continue
             corner, warped = warper.warp(im, K, R, cv2.INTER_LINEAR,
                                          cv2.BORDER_REFLECT)
             mask = np.full(im.shape[:2], 255, np.uint8)
             _, mw = warper.warp(mask, K, R, cv2.INTER_NEAREST,
                                 cv2.BORDER_CONSTANT)
+            if comp is not None:
+                warped = comp.apply(i, corner, warped, mw)
+            if seams is not None:
+                dil = cv2.dilate(seams[i], None)
+                sm = cv2.resize(dil, (mw.shape[1], mw.shape[0]), 0, 0,
+                                cv2.INTER_LINEAR_EXACT)
+                mw = cv2.bitwise_and(sm, mw)
             alpha = cv2.compare(mw, 0, cv2.CMP_NE)          # blenders.cc:106
             if warped.dtype == np.uint16:
                 alpha = alpha.astype(np.uint16) * 257
@@ -202,22 +280,99 @@ def reference_step(ims, Ks, Rs, cfg, cores):
                            n_threads=max(2, cores - 1))
         mp = res.width * res.height / 1e6
         kind = "reference"
+        if keep:
+            result = {"pano": res.interleaved(True), "mask": res.mask,
+                      "min": (res.min_x, res.min_y), "capped": capped,
+                      "warp_scale": scale}
     else:
         import compose_oracle as co
         res = co.compose(ims, Ks, Rs, projection=cfg["projection"],
                          warp_scale=cfg["focal"],
-                         max_pano_mpx=cfg["max_pano_mpx"],
-                         fixed_levels=cfg["fixed_levels"])
+                         max_pano_mpx=cfg["max_pano_mpx"], gains=gains,
+                         seam_masks=seams, fixed_levels=cfg["fixed_levels"])
         mp = res["pano"].shape[0] * res["pano"].shape[1] / 1e6
         kind = "port"
-    return mp, time.perf_counter() - t0, kind
+        if keep:
+            result = {"pano": res["pano"], "mask": res["mask"],
+                      "min": (res["min_x"], res["min_y"]),
+                      "capped": res["capped"],
+                      "warp_scale": res["warp_scale"]}
+    return mp, time.perf_counter() - t0, kind, result
 
 
-def sample_of(cfg, ims, Ks, Rs, n_sample):
-    n = min(n_sample, len(ims))
-    return ims[:n], Ks[:n], Rs[:n], (
-        f"first {n} of {len(ims)} images of the workload "
-        f"({n} x {cfg['w']}x{cfg['h']})")
+def reference_warp_scale(wl, cfg, cv2):
+    """ComputeRoi + the size cap (stitcher.cc:144-169, 312-335) with cv2's
+    warpRoi; float / double mix as in the reference."""
+    f32 = np.float32
+    wis = float(f32(cfg["focal"]))
+    scale = float(f32(wis))
+    cap = cfg["max_pano_mpx"]
+    warper = cv2.PyRotationWarper(PROJ_NAMES[cfg["projection"]], scale)
+    rois = [warper.warpRoi((im.shape[1], im.shape[0]), K, R)
+            for im, K, R in zip(wl["ims"], wl["Ks"], wl["Rs"])]
+    x0 = min(r[0] for r in rois)
+    y0 = min(r[1] for r in rois)
+    x1 = max(r[0] + r[2] for r in rois)
+    y1 = max(r[1] + r[3] for r in rois)
+    pano_mpx = f32(f32(f32(x1 - x0) * f32(y1 - y0)) / f32(1e6))
+    if cap > 0 and pano_mpx > f32(cap):
+        ratio = f32(np.sqrt(f32(f32(cap) / pano_mpx)))
+        return float(f32(wis * float(ratio))), True
+    return scale, False
+
+
+def parity_check(pano, mask, min_xy, ref, bpp):
+    """North-star bars at full size: masks bit-exact, panorama within 1 LSB
+    (8-bit) / 1e-3 relative (16-bit) at >= 99.9 % of pixels, PSNR >= 50 dB."""
+    out = {"against": "reference CPU arm, all images, same inputs"}
+    if pano.shape != ref["pano"].shape or tuple(min_xy) != tuple(ref["min"]):
+        out.update(ok=False, size=[list(pano.shape), list(ref["pano"].shape)],
+                   min_xy=[list(min_xy), list(ref["min"])])
+        return out
+    nm = int(np.count_nonzero(mask != ref["mask"]))
+    both = (mask > 0) & (ref["mask"] > 0)
+    a = pano[both].astype(np.int32)
+    b = ref["pano"][both].astype(np.int32)
+    d = np.abs(a - b)
+    tol = 1 if bpp == 8 else np.maximum(1, (1e-3 * b).astype(np.int32))
+    within = float((d <= tol).mean())
+    mse = float(np.mean(d.astype(np.float64) ** 2))
+    maxv = 255.0 if bpp == 8 else 65535.0
+    psnr = 200.0 if mse == 0 else 10 * math.log10(maxv * maxv / mse)
+    out.update(mask_equal=nm == 0, mask_diff_pixels=nm,
+               within_tol=within, identical=float((d == 0).mean()),
+               max_diff=int(d.max()), psnr=round(psnr, 2),
+               pixels=int(mask.size),
+               ok=bool(nm <= 1e-6 * mask.size and within >= 0.999
+                       and psnr >= 50.0))
+    return out
+
+
+def sample_of(cfg, wl, n_sample):
+    """The bounded CPU sample: the first n images of the workload (0 = all)."""
+    n_all = len(wl["ims"])
+    n = n_all if n_sample <= 0 else min(n_sample, n_all)
+    if n == n_all:
+        return wl, (f"the whole workload ({n} x {cfg['w']}x{cfg['h']} images,"
+                    f" ratio 1.0)")
+    sub = dict(wl)
+    for k in ("ims", "Ks", "Rs", "gains", "seams"):
+        sub[k] = wl[k][:n] if wl[k] is not None else None
+    return sub, (f"first {n} of {n_all} images of the workload "
+                 f"({n} x {cfg['w']}x{cfg['h']}, ratio {n / n_all:.3f})")
+
+
+def config_of(cfg, wl):
+    """`config` of the JSON line: identical on both arms."""
+    return {"workload": cfg["name"], "images": len(wl["ims"]),
+            "masks": {"graphcut": "cv2 GraphCutSeamFinder(COST_COLOR) at the "
+                      "seam scale, computed once on the CPU",
+                      "full": "warped all-255 masks (no seam finder)",
+                      "none": "no seam masks, no gains"}[wl["masks"]],
+            "gains": "BlocksGainCompensator maps from the seam-scale images"
+            if wl["gains"] is not None else "none",
+            "l2": "inputs and intermediates (>2 GB per step) exceed the "
+            "126 MB L2"}
 
 
 def run_reference(args, cfg):
@@ -225,14 +380,14 @@ def run_reference(args, cfg):
     if rank != 0:
         return
     cores = host_cores()
-    ims, Ks, Rs = make_workload(cfg, 0)
-    ims, Ks, Rs, sample = sample_of(cfg, ims, Ks, Rs, args.ref_images)
+    full = make_workload(cfg, 0, args.masks)
+    wl, sample = sample_of(cfg, full, args.ref_images)
     kind = "port"
     for _ in range(args.warmup):
-        reference_step(ims, Ks, Rs, cfg, cores)
+        reference_step(wl, cfg, cores)
     total_mp, total_s = 0.0, 0.0
     for _ in range(args.steps):
-        mp, s, kind = reference_step(ims, Ks, Rs, cfg, cores)
+        mp, s, kind, _ = reference_step(wl, cfg, cores)
         total_mp += mp
         total_s += s
     value = total_mp / total_s
@@ -241,8 +396,9 @@ def run_reference(args, cfg):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data":
-        "synthetic", "config": {"workload": cfg["name"], "sample": sample},
+        "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8" if cfg["bpp"] == 8 else "u16", "data": "synthetic",
+        "config": config_of(cfg, full),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": used,
                          "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0,
@@ -312,7 +468,8 @@ def run_ours(args, cfg):
     lib = xb._lib.load()
 
     group = sharding_group(world, rank)
-    ims, Ks, Rs = make_workload(cfg, group)
+    wl = make_workload(cfg, group, args.masks)
+    ims, Ks, Rs = wl["ims"], wl["Ks"], wl["Rs"]
     # host sources in pinned memory (e2e leg copies from here every step)
     pinned = []
     for im in ims:
@@ -340,7 +497,7 @@ def run_ours(args, cfg):
     sum_over_ranks = sharding.reduce_sum
 
     # ---- resident leg ------------------------------------------------------
-    comp.set_images(host, Ks, Rs)
+    comp.set_images(host, Ks, Rs, wl["gains"], wl["seams"])
     info = None
     for _ in range(args.warmup):
         info = comp.run()
@@ -393,7 +550,9 @@ def run_ours(args, cfg):
         pano = torch.empty((H, W, 3), dtype=dt, pin_memory=True)
         mask = torch.empty((H, W), dtype=torch.uint8, pin_memory=True)
         outs.append((pano.numpy(), mask.numpy(), pano, mask))
-    h2d = sum(im.nbytes for im in host)
+    h2d = sum(im.nbytes for im in host) + sum(
+        a.nbytes for k in ("gains", "seams") if wl[k] is not None
+        for a in wl[k])
     d2h = outs[0][0].nbytes + outs[0][1].nbytes
     e2e_steps = min(max(args.steps, 2 * in_flight), 12)
 
@@ -407,7 +566,7 @@ def run_ours(args, cfg):
         try:
             torch.cuda.set_device(local)
             for _ in range(j, n_steps, in_flight):
-                comps[j].set_images(host, Ks, Rs)
+                comps[j].set_images(host, Ks, Rs, wl["gains"], wl["seams"])
                 with compute_turn:
                     comps[j].run()
                 comps[j].fetch(outs[j][0], outs[j][1])
@@ -484,8 +643,6 @@ def run_ours(args, cfg):
             "bytes_per_step": b_blend, "ms_per_step": round(blend_ms, 4),
             "ms_tail_after_seams": round(tail_ms, 4),
             "ms_shrink_under_seams": round(shrink_ms, 4),
-            "frac_critical_path": round(
-                b_blend / max(tail_ms, 1e-9) / 1e6 / peak, 4),
             "launches_per_step": blend_launches,
             "warp": {"bytes_per_step": b_warp,
                      "ms_per_step": per_stage.get("warp", {}).get("ms"),
@@ -503,11 +660,10 @@ def run_ours(args, cfg):
         "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8" if cfg["bpp"] == 8
         else "u16", "data": "synthetic",
-        "config": {"workload": cfg["name"], "canvas": [W, H],
-                   "levels": info["levels"], "sharding": "panorama group per "
-                   "GPU, no data-path collective" if world > 1 else "1 GPU",
-                   "l2": "inputs and intermediates (>2 GB per step) exceed "
-                   "the 126 MB L2"},
+        "config": config_of(cfg, wl), "canvas": [W, H],
+        "levels": info["levels"], "resolution_capped":
+        info["resolution_capped"], "sharding": "panorama group per GPU, no "
+        "data-path collective" if world > 1 else "1 GPU",
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / e2e_steps,
                 "steps": e2e_steps, "wall_ms_per_step": 1e3 * wall / e2e_steps,
@@ -518,13 +674,34 @@ def run_ours(args, cfg):
                      "s_t": info["s_t"] / 1e6, "c": info["c"] / 1e6},
     }
     if rank == 0 and world == 1 and not args.no_cpu:
+        # CPU leg beside it, on the box's host cores: one warm-up pass and the
+        # mean of two timed ones over the bounded sample (default: all images)
         cores = host_cores()
-        si, sK, sR, sample = sample_of(cfg, ims, Ks, Rs, args.ref_images)
-        mp, s, kind = reference_step(si, sK, sR, cfg, cores)
-        line["cpu_baseline"] = {"value": mp / s, "unit": UNIT,
+        swl, sample = sample_of(cfg, wl, args.ref_images)
+        reference_step(swl, cfg, cores)
+        tot_mp = tot_s = 0.0
+        ref = None
+        for k in range(2):
+            mp, sec, kind, r = reference_step(
+                swl, cfg, cores, keep=(k == 1 and swl is wl and args.check))
+            tot_mp += mp
+            tot_s += sec
+            ref = r or ref
+        line["cpu_baseline"] = {"value": tot_mp / tot_s, "unit": UNIT,
                                 "cores": cores if kind == "reference" else 1,
                                 "kind": kind, "sample": sample,
-                                "seconds": round(s, 2)}
+                                "seconds": round(tot_s, 2), "passes": 2}
+        if ref is not None:
+            # full-size parity of the GPU panorama against the reference arm
+            pano, mask = comp.fetch()
+            line["parity"] = parity_check(
+                pano, mask, (info["min_x"], info["min_y"]), ref, cfg["bpp"])
+            line["parity"]["capped"] = [bool(info["resolution_capped"]),
+                                        bool(ref["capped"])]
+            if not line["parity"]["ok"]:
+                print(json.dumps(line))
+                raise SystemExit("bench.py: full-size parity check failed: "
+                                 + json.dumps(line["parity"]))
     if rank == 0:
         print(json.dumps(line))
     if world > 1:
@@ -538,9 +715,14 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="cfg2", choices=sorted(CONFIGS))
-    ap.add_argument("--ref-images", type=int, default=3,
-                    help="images in the bounded CPU sample")
+    ap.add_argument("--ref-images", type=int, default=0,
+                    help="images in the bounded CPU sample (0 = all)")
+    ap.add_argument("--masks", default="graphcut",
+                    choices=["graphcut", "full", "none"],
+                    help="seam masks fed to the path (SURVEY.md 8d)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-check", dest="check", action="store_false",
+                    help="skip the full-size parity check against the CPU arm")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     cfg = CONFIGS[args.config]
