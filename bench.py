@@ -432,6 +432,100 @@ def ncu_traffic(workload):
         return None
 
 
+def operator_surface_leg(xb, wl, cfg, steps):
+    """The path as xpano would drive it through the shim
+    (include/xpano_b200_shim.hpp), one image at a time with HOST buffers:
+    ComputeRoi, then per image warp(image) + warp(mask) on the GPU,
+    ExposureCompensator::apply and dilate / resize / bitwise_and by OpenCV on
+    the CPU exactly where stitcher.cc:389-401 has them, feed(), and finally
+    blend() + download. Returns wall ms per panorama and the split between
+    library calls and the CPU steps in between."""
+    try:
+        import cv2
+    except Exception:
+        return None
+    ims, Ks, Rs = wl["ims"], wl["Ks"], wl["Rs"]
+    gains, seams = wl["gains"], wl["seams"]
+    if cfg["max_pano_mpx"] > 0:
+        pass  # the cap changes the warp scale below, as in the composer
+    creator = xb.PickWarper(cfg["projection"])
+    comp = None
+    if gains is not None:
+        comp = cv2.detail_BlocksGainCompensator()
+        comp.setMatGains(gains)
+    ones = [np.full(im.shape[:2], 255, np.uint8) for im in ims[:1]]
+    lib = xb._lib.load()
+    import ctypes
+
+    def one():
+        t_lib = t_cv = 0.0
+        t0 = time.perf_counter()
+        warper = creator.create(cfg["focal"])
+        rois = [warper.warpRoi((im.shape[1], im.shape[0]), K, R)
+                for im, K, R in zip(ims, Ks, Rs)]
+        x0 = min(r[0] for r in rois)
+        y0 = min(r[1] for r in rois)
+        x1 = max(r[0] + r[2] for r in rois)
+        y1 = max(r[1] + r[3] for r in rois)
+        sc = ctypes.c_float()
+        if lib.xp_compose_capped_scale(float(np.float32(cfg["focal"])), 1.0,
+                                       x1 - x0, y1 - y0, cfg["max_pano_mpx"],
+                                       ctypes.byref(sc)):
+            warper = creator.create(sc.value)
+            rois = [warper.warpRoi((im.shape[1], im.shape[0]), K, R)
+                    for im, K, R in zip(ims, Ks, Rs)]
+            x0 = min(r[0] for r in rois)
+            y0 = min(r[1] for r in rois)
+            x1 = max(r[0] + r[2] for r in rois)
+            y1 = max(r[1] + r[3] for r in rois)
+        blender = xb.Multiblend(output_bpp=0,
+                                fixed_levels=cfg["fixed_levels"])
+        blender.prepare((x0, y0, x1 - x0, y1 - y0))
+        t_lib += time.perf_counter() - t0
+        for i, (im, K, R) in enumerate(zip(ims, Ks, Rs)):
+            if seams is not None and not seams[i].any():
+                continue
+            t0 = time.perf_counter()
+            corner, warped = warper.warp(im, K, R, xb.INTER_LINEAR,
+                                         xb.BORDER_REFLECT)
+            _, mw = warper.warp(ones[0], K, R, xb.INTER_NEAREST,
+                                xb.BORDER_CONSTANT)
+            t1 = time.perf_counter()
+            if comp is not None:
+                warped = comp.apply(i, corner, warped, mw)
+            if seams is not None:
+                dil = cv2.dilate(seams[i], None)
+                sm = cv2.resize(dil, (mw.shape[1], mw.shape[0]), 0, 0,
+                                cv2.INTER_LINEAR_EXACT)
+                mw = cv2.bitwise_and(sm, mw)
+            t2 = time.perf_counter()
+            blender.feed(warped, mw, corner)
+            t3 = time.perf_counter()
+            t_lib += (t1 - t0) + (t3 - t2)
+            t_cv += t2 - t1
+        t0 = time.perf_counter()
+        pano, mask = blender.blend()
+        t_lib += time.perf_counter() - t0
+        return pano, mask, t_lib, t_cv
+
+    one()  # warm-up
+    lib_s = cv_s = 0.0
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        pano, mask, a, b = one()
+        lib_s += a
+        cv_s += b
+    wall = time.perf_counter() - t0
+    return {"ms_per_step": 1e3 * wall / steps,
+            "ms_in_library_calls": 1e3 * lib_s / steps,
+            "ms_in_opencv_cpu_steps_between": 1e3 * cv_s / steps,
+            "steps": steps, "pano": pano, "mask": mask,
+            "what": "warp x2 + feed per image and blend through host "
+            "buffers (shim call sequence, stitcher.cc:358-419); gain apply "
+            "and seam-mask dilate/resize/and on the CPU by cv2 as in the "
+            "reference"}
+
+
 def sharding_group(world, rank):
     from xpano_b200 import sharding
     return sharding.assign_groups(world, world, rank)[0]
@@ -600,6 +694,20 @@ def run_ours(args, cfg):
     e2e_ms = max_over_ranks(max(ev0.elapsed_time(ev1), 0.0))
     e2e_value = total_mp * e2e_steps / (e2e_ms / 1e3)
 
+    # ---- e2e through the drop-in operator surface -------------------------
+    op_surface = None
+    if world == 1 and not args.no_surface:
+        op_surface = operator_surface_leg(xb, wl, cfg, min(args.steps, 3))
+        if op_surface is not None:
+            op_surface["value"] = mp_rank / (op_surface["ms_per_step"] / 1e3)
+            op_surface["unit"] = UNIT
+            po, mo = op_surface.pop("pano"), op_surface.pop("mask")
+            same = po.shape == outs[0][0].shape
+            op_surface["vs_composer"] = {
+                "mask_equal": bool(same and np.array_equal(mo, outs[0][1])),
+                "max_diff": int(np.abs(po.astype(np.int32) -
+                                       outs[0][0]).max()) if same else None}
+
     # ---- roofline of the dominant HBM-bound stage --------------------------
     peak, peak_src = measured_peaks()
     sbytes = dict(info["stage_bytes"])
@@ -668,6 +776,7 @@ def run_ours(args, cfg):
                 "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / e2e_steps,
                 "steps": e2e_steps, "wall_ms_per_step": 1e3 * wall / e2e_steps,
                 "panoramas_in_flight": in_flight},
+        "e2e_operator_surface": op_surface,
         "gpu_launches": int(launches), "clocks": clk, "roofline": roof,
         "stages": per_stage, "latency_bound_stages_ms": serial,
         "sizes_mp": {"s_src": info["s_src"] / 1e6, "s_w": info["s_w"] / 1e6,
@@ -721,6 +830,8 @@ def main():
                     choices=["graphcut", "full", "none"],
                     help="seam masks fed to the path (SURVEY.md 8d)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-surface", action="store_true",
+                    help="skip the operator-surface e2e leg")
     ap.add_argument("--no-check", dest="check", action="store_false",
                     help="skip the full-size parity check against the CPU arm")
     args = ap.parse_args()

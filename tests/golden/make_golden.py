@@ -137,8 +137,55 @@ def warp_goldens():
     np.savez_compressed(os.path.join(HERE, "warp_cv2_goldens.npz"), **g)
 
 
+# The three portrait warpers xpano defines itself (xpano/algorithm/warpers.h:
+# 9-31: PlanePortraitWarper, CylindricalPortraitWarper, SphericalPortraitWarper
+# creators) exist only in OpenCV's C++ detail namespace; cv2.PyRotationWarper
+# cannot construct them. OpenCV's portrait projectors (warpers_inl.hpp) swap
+# the first two rows of r_kinv, evaluate the landscape formula and negate u.
+# Swapping those rows is R' = P R with P = [[0,1,0],[1,0,0],[0,0,1]] (then
+# k_rinv' = K R'^T has its first two columns swapped, which is exactly the
+# portrait mapBackward, and rinv' has the pole column the portrait ROI test
+# uses), so cv2's LANDSCAPE warper called with R' yields the portrait result
+# mirrored in u: roi.x = -(x' + w' - 1), maps / warped images flipped
+# left-right, point.u = -u'.
+PORTRAIT_OF = {"planePortrait": "plane", "cylindricalPortrait": "cylindrical",
+               "sphericalPortrait": "spherical"}
+PORTRAIT_ROTS = [(0.4, -0.1, 0.05), (-0.2, 0.9, 0.1)]  # 2nd: pole in view
+P_SWAP = np.array([[0, 1, 0], [1, 0, 0], [0, 0, 1]], np.float32)
+
+
+def portrait_goldens():
+    w, h = WARP_SIZE
+    K = np.array([[150, 0, w / 2], [0, 150, h / 2], [0, 0, 1]], np.float32)
+    g = {"K": K, "cv2_version": np.array(cv2.__version__)}
+    src8 = synth.texture(h, w, 77, 3, 8)  # = warp_cv2_goldens.npz "src8"
+    for k, ypr in enumerate(PORTRAIT_ROTS):
+        R = rot(*ypr)
+        g[f"R_{k}"] = R
+        Rp = (P_SWAP @ R).astype(np.float32)
+        for name, land in PORTRAIT_OF.items():
+            cw = cv2.PyRotationWarper(land, WARP_SCALE)
+            x, y, rw, rh = cw.warpRoi((w, h), K, Rp)
+            if rw * rh > 4e6:
+                continue
+            key = f"{name}_{k}"
+            g[f"roi_{key}"] = np.array([-(x + rw - 1), y, rw, rh])
+            _, xm, ym = cw.buildMaps((w, h), K, Rp)
+            g[f"xmap_{key}"] = xm[:, ::-1][::WARP_STEP, ::WARP_STEP].copy()
+            g[f"ymap_{key}"] = ym[:, ::-1][::WARP_STEP, ::WARP_STEP].copy()
+            u, v = cw.warpPoint((123.5, 77.25), K, Rp)
+            g[f"pt_{key}"] = np.array([-u, v], np.float32)
+            c, d8 = cw.warp(src8, K, Rp, cv2.INTER_LINEAR, cv2.BORDER_REFLECT)
+            _, m = cw.warp(np.full((h, w), 255, np.uint8), K, Rp,
+                           cv2.INTER_NEAREST, cv2.BORDER_CONSTANT)
+            g[f"warp8_{key}"] = np.ascontiguousarray(d8[:, ::-1])
+            g[f"warpmask_{key}"] = np.ascontiguousarray(m[:, ::-1])
+    np.savez_compressed(os.path.join(HERE, "warp_portrait_goldens.npz"), **g)
+
+
 def main():
     warp_goldens()
+    portrait_goldens()
     g = {}
     pos_png = [(-91, 204), (-167, 202), (-41, 193)]
     pos_tif = [(76, 11), (0, 9), (126, 0)]
@@ -171,7 +218,7 @@ def main():
         r[f"meta_{seed}"] = np.array([res.min_x, res.min_y, int(res.no_mask)])
     np.savez_compressed(os.path.join(HERE, "blend_ref_outputs.npz"), **r)
     for f in ("blend_reference_goldens.npz", "blend_ref_outputs.npz",
-              "warp_cv2_goldens.npz"):
+              "warp_cv2_goldens.npz", "warp_portrait_goldens.npz"):
         print(f, os.path.getsize(os.path.join(HERE, f)) // 1024, "KiB")
 
 

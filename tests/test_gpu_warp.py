@@ -98,6 +98,48 @@ def test_warp_vs_cv2_goldens(g, name):
         assert (d <= tol).all() and (d > 0).mean() < 1e-3
 
 
+PORTRAIT_PROJ = {"planePortrait": wo.PLANE, "cylindricalPortrait":
+                 wo.CYLINDRICAL, "sphericalPortrait": wo.SPHERICAL}
+
+
+def _portrait_keys():
+    gp = np.load(os.path.join(GOLD, "warp_portrait_goldens.npz"))
+    return sorted(k[4:] for k in gp.files if k.startswith("roi_"))
+
+
+@pytest.mark.parametrize("key", _portrait_keys())
+def test_portrait_warpers_vs_goldens(g, key):
+    """The three warper classes xpano itself defines (warpers.h:9-31):
+    ROI, maps, point map, image warp and mask warp against goldens derived
+    from cv2 (tests/golden/make_golden.py portrait_goldens)."""
+    import xpano_b200 as xb
+    gp = np.load(os.path.join(GOLD, "warp_portrait_goldens.npz"))
+    name, k = key.rsplit("_", 1)
+    K, R = gp["K"], gp[f"R_{k}"]
+    w = xb.PickWarperPortrait(PORTRAIT_PROJ[name]).create(WARP_SCALE)
+    roi = w.warpRoi(WARP_SIZE, K, R)
+    assert roi == tuple(gp[f"roi_{key}"])
+    _, xm, ym = w.buildMaps(WARP_SIZE, K, R)
+    gx, gy = gp[f"xmap_{key}"], gp[f"ymap_{key}"]
+    ok = np.isfinite(gx) & np.isfinite(gy)
+    dx = np.abs(xm[::WARP_STEP, ::WARP_STEP] - gx)
+    dy = np.abs(ym[::WARP_STEP, ::WARP_STEP] - gy)
+    mag = np.maximum(1.0, np.maximum(np.abs(gx), np.abs(gy)))
+    assert (np.maximum(dx, dy)[ok] / mag[ok]).max() < 2e-5
+    pt = np.array(w.warpPoint((123.5, 77.25), K, R), np.float32)
+    assert np.array_equal(pt, gp[f"pt_{key}"])
+    corner, d8 = w.warp(g["src8"], K, R)
+    assert corner == roi[:2]
+    d = np.abs(d8.astype(int) - gp[f"warp8_{key}"].astype(int))
+    _, m = w.warp(np.full(WARP_SIZE[::-1], 255, np.uint8), K, R,
+                  xb.INTER_NEAREST, xb.BORDER_CONSTANT)
+    mdiff = float((m != gp[f"warpmask_{key}"]).mean())
+    _note(f"portrait_{key}", max_diff=int(d.max()),
+          frac=float((d > 0).mean()), mask_diff_fraction=mdiff)
+    assert d.max() <= 1 and (d > 0).mean() < 1e-3
+    assert mdiff < 1e-4
+
+
 @pytest.mark.parametrize("name", sorted(wo.CV2_NAMES))
 def test_all_projections_vs_oracle(name):
     """Every projection (and portrait variant) with a rotated camera

@@ -116,3 +116,59 @@ def test_live_cv2_gain_apply():
     mine = wo.apply_gain_u8(img, wo.resize_linear_f32(gsmall, (w, h)))
     d = np.abs(mine.astype(int) - ref.astype(int))
     assert d.max() <= 1 and (d > 0).mean() < 1e-3
+
+
+PORTRAIT_PROJ = {"planePortrait": wo.PLANE, "cylindricalPortrait":
+                 wo.CYLINDRICAL, "sphericalPortrait": wo.SPHERICAL}
+
+
+def _portrait_keys():
+    gp = np.load(os.path.join(GOLD, "warp_portrait_goldens.npz"))
+    return sorted(k[4:] for k in gp.files if k.startswith("roi_"))
+
+
+@pytest.mark.parametrize("key", _portrait_keys())
+def test_portrait_warpers_golden(key):
+    """The plain portrait warpers of xpano/algorithm/warpers.h:9-31 are not
+    constructible through cv2; their goldens come from cv2's landscape
+    warpers through the row-swap symmetry of OpenCV's portrait projectors
+    (tests/golden/make_golden.py portrait_goldens). Bit-exact."""
+    gp = np.load(os.path.join(GOLD, "warp_portrait_goldens.npz"))
+    g8 = np.load(os.path.join(GOLD, "warp_cv2_goldens.npz"))["src8"]
+    name, k = key.rsplit("_", 1)
+    K, R = gp["K"], gp[f"R_{k}"]
+    w = wo.Warper(PORTRAIT_PROJ[name], WARP_SCALE, True)
+    assert w.warp_roi(WARP_SIZE, K, R) == tuple(gp[f"roi_{key}"])
+    _, xm, ym = w.build_maps(WARP_SIZE, K, R)
+    assert np.array_equal(xm[::WARP_STEP, ::WARP_STEP], gp[f"xmap_{key}"],
+                          equal_nan=True)
+    assert np.array_equal(ym[::WARP_STEP, ::WARP_STEP], gp[f"ymap_{key}"],
+                          equal_nan=True)
+    pt = np.array(w.warp_point((123.5, 77.25), K, R), np.float32)
+    assert np.array_equal(pt, gp[f"pt_{key}"])
+    corner, d8 = w.warp(g8, K, R)
+    assert corner == tuple(gp[f"roi_{key}"][:2])
+    assert np.array_equal(d8, gp[f"warp8_{key}"])
+    _, m = w.warp_mask(WARP_SIZE, K, R)
+    assert np.array_equal(m, gp[f"warpmask_{key}"])
+
+
+@pytest.mark.skipif(cv2 is None, reason="cv2 not importable")
+@pytest.mark.parametrize("name", sorted(PORTRAIT_PROJ))
+def test_live_cv2_portrait_symmetry(name):
+    from golden.make_golden import P_SWAP, PORTRAIT_OF
+    w, h = 333, 211
+    K = np.array([[290, 0, w / 2 + 3], [0, 285, h / 2 - 2], [0, 0, 1]],
+                 np.float32)
+    for ypr in [(0, 0, 0), (-0.7, 0.3, -0.2), (0.3, 1.1, 0.2)]:
+        R = rot(*ypr)
+        cw = cv2.PyRotationWarper(PORTRAIT_OF[name], 240.0)
+        ow = wo.Warper(PORTRAIT_PROJ[name], 240.0, True)
+        x, y, rw, rh = cw.warpRoi((w, h), K, (P_SWAP @ R).astype(np.float32))
+        assert ow.warp_roi((w, h), K, R) == (-(x + rw - 1), y, rw, rh)
+        if rw * rh > 2e7:
+            continue
+        _, xm, ym = cw.buildMaps((w, h), K, (P_SWAP @ R).astype(np.float32))
+        _, xo, yo = ow.build_maps((w, h), K, R)
+        assert np.array_equal(xm[:, ::-1], xo, equal_nan=True)
+        assert np.array_equal(ym[:, ::-1], yo, equal_nan=True)

@@ -314,7 +314,8 @@ struct Composer {
                               roi_incl, s.gain.as<float>(), s.gw, s.gh,
                               s.seam.as<uint8_t>(), s.mw, s.mh, f->data.p,
                               (size_t)r[2] * 4 * bs);
-      warp_launches += 1 + (s.seam.p ? 1 : 0) + (is_separable(p.type) ? 1 : 0);
+      warp_launches += 1 + (s.seam.p ? 1 : 0) + (is_separable(p.type) ? 1 : 0) +
+                       (s.seam.p || s.gain.p ? 1 : 0);
       s_src += (double)s.w * s.h;
       s_w += (double)r[2] * r[3];
     }

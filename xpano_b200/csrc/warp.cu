@@ -516,14 +516,74 @@ __device__ __forceinline__ float resize_linear_f32(
   return __fadd_rn(__fmul_rn(h0, b0), __fmul_rn(h1, b1));
 }
 
+// Per-column / per-row coefficients of the two resizes of the fused kernel:
+// the double-precision coefficient arithmetic of exact_coeff /
+// linear_coeff_f32 depends on one coordinate only, so it is evaluated once
+// per column and row (W + H times) instead of four times per pixel.
+struct alignas(16) AuxCoef {
+  int g_ofs;   // gain map: first tap
+  float g_a1;  // gain map: weight of the second tap
+  int s_ofs;   // seam mask: first tap
+  int s_c1;    // seam mask: 8.8 weight of the second tap (c0 = 256 - c1)
+};
+
+__global__ void aux_tables_kernel(int W, int H, int gw, int gh, int mw, int mh,
+                                  AuxCoef* __restrict__ col,
+                                  AuxCoef* __restrict__ row) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= W + H) return;
+  const bool is_col = i < W;
+  const int d = is_col ? i : i - W;
+  const int dsize = is_col ? W : H;
+  AuxCoef c = {0, 0.f, 0, 0};
+  if (gw > 0) linear_coeff_f32(is_col ? gw : gh, dsize, d, c.g_ofs, c.g_a1);
+  if (mw > 0) {
+    int c0;
+    exact_coeff(is_col ? mw : mh, dsize, d, c.s_ofs, c0, c.s_c1);
+  }
+  (is_col ? col : row)[d] = c;
+}
+
+__device__ __forceinline__ int resize_exact_u8_tab(
+    const uint8_t* __restrict__ src, int sw, int sh, const AuxCoef& cx,
+    const AuxCoef& cy) {
+  const int ox = cx.s_ofs, oy = cy.s_ofs;
+  const int cx1 = cx.s_c1, cx0 = 256 - cx1, cy1 = cy.s_c1, cy0 = 256 - cy1;
+  const uint8_t* r0 = src + (size_t)oy * sw;
+  const uint8_t* r1 = src + (size_t)(oy + 1 < sh ? oy + 1 : oy) * sw;
+  const int ox1 = ox + 1 < sw ? ox + 1 : ox;
+  const unsigned h0 = (unsigned)(cx0 * r0[ox] + cx1 * r0[ox1]);
+  const unsigned h1 = (unsigned)(cx0 * r1[ox] + cx1 * r1[ox1]);
+  unsigned v = (unsigned)cy0 * h0 + (unsigned)cy1 * h1;
+  v = (v + (1u << 15)) >> 16;
+  return v > 255 ? 255 : (int)v;
+}
+
+__device__ __forceinline__ float resize_linear_f32_tab(
+    const float* __restrict__ src, int sw, int sh, const AuxCoef& cx,
+    const AuxCoef& cy) {
+  const int ox = cx.g_ofs, oy = cy.g_ofs;
+  const float al1 = cx.g_a1, b1 = cy.g_a1;
+  const float al0 = __fsub_rn(1.f, al1), b0 = __fsub_rn(1.f, b1);
+  const int ox1 = ox + 1 < sw ? ox + 1 : ox;
+  const int oy1 = oy + 1 < sh ? oy + 1 : oy;
+  const float* r0 = src + (size_t)oy * sw;
+  const float* r1 = src + (size_t)oy1 * sw;
+  const float h0 = __fadd_rn(__fmul_rn(r0[ox], al0), __fmul_rn(r0[ox1], al1));
+  const float h1 = __fadd_rn(__fmul_rn(r1[ox], al0), __fmul_rn(r1[ox1], al1));
+  return __fadd_rn(__fmul_rn(h0, b0), __fmul_rn(h1, b1));
+}
+
 // Fused stitcher.cc:377-405 + blenders.cc:99-112 for one image.
 template <typename T>
 __global__ void warp_bgra_kernel(MapSrc m, const T* __restrict__ src,
                                  size_t src_pitch, int sw, int sh, int W, int H,
                                  const float* __restrict__ gain, int gw, int gh,
                                  const uint8_t* __restrict__ seam_dilated,
-                                 int mw, int mh, T* __restrict__ dst,
-                                 size_t dst_pitch) {
+                                 int mw, int mh,
+                                 const AuxCoef* __restrict__ aux_col,
+                                 const AuxCoef* __restrict__ aux_row,
+                                 T* __restrict__ dst, size_t dst_pitch) {
   int dx = blockIdx.x * blockDim.x + threadIdx.x;
   int dy = blockIdx.y * blockDim.y + threadIdx.y;
   if (dx >= W || dy >= H) return;
@@ -533,9 +593,14 @@ __global__ void warp_bgra_kernel(MapSrc m, const T* __restrict__ src,
   sample_linear_reflect<T, 3>(src, src_pitch, sw, sh, x, y, px);
   int ix, iy;
   bool opaque = nearest_inside(sw, sh, x, y, ix, iy);
+  AuxCoef acx = {0, 0.f, 0, 0}, acy = {0, 0.f, 0, 0};
+  if (gain || seam_dilated) {
+    acx = aux_col[dx];
+    acy = aux_row[dy];
+  }
   if (gain) {
     // multiply(CV_8UC3|CV_16UC3, CV_32F gain): saturate_cast(rint(a * g))
-    const float g = resize_linear_f32(gain, gw, gh, W, H, dx, dy);
+    const float g = resize_linear_f32_tab(gain, gw, gh, acx, acy);
     const int maxv = sizeof(T) == 1 ? 255 : 65535;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
@@ -544,7 +609,7 @@ __global__ void warp_bgra_kernel(MapSrc m, const T* __restrict__ src,
     }
   }
   if (seam_dilated && opaque)
-    opaque = resize_exact_u8(seam_dilated, mw, mh, W, H, dx, dy) != 0;
+    opaque = resize_exact_u8_tab(seam_dilated, mw, mh, acx, acy) != 0;
   const T amax = (T)(sizeof(T) == 1 ? 255 : 65535);
   T* d = dst + (size_t)dy * dst_pitch + (size_t)dx * 4;
   if (sizeof(T) == 1) {
@@ -581,6 +646,15 @@ Warper::~Warper() {
   if (own_stream) cudaStreamDestroy(own_stream);
 }
 
+// Scratch that queued kernels may still be reading is only replaced after the
+// stream drained (the old block returns to the pool, which other objects
+// allocate from); growth is rare -- the ROIs of a panorama are alike.
+static void grow_scratch(DevBuf& b, size_t n, cudaStream_t s) {
+  if (n <= b.bytes) return;
+  if (b.p) XP_CUDA(cudaStreamSynchronize(s));
+  b.reserve(n);
+}
+
 MapSrc Warper::prepare_map(const Projector& p, const int roi[4]) {
   MapSrc m;
   m.p = p;
@@ -590,7 +664,7 @@ MapSrc Warper::prepare_map(const Projector& p, const int roi[4]) {
   m.separable = is_separable(p.type) ? 1 : 0;
   const int W = roi[2] - roi[0] + 1, H = roi[3] - roi[1] + 1;
   if (m.separable) {
-    tables.reserve(sizeof(float2) * (size_t)(W + H));
+    grow_scratch(tables, sizeof(float2) * (size_t)(W + H), stream);
     float2* col = tables.as<float2>();
     float2* row = col + W;
     sep_tables_kernel<<<div_up(W + H, 256), 256, 0, stream>>>(p, roi[0],
@@ -749,12 +823,23 @@ void Warper::warp_bgra_device(const void* dsrc, int sw, int sh, size_t spitch,
   const int W = roi[2] - roi[0] + 1, H = roi[3] - roi[1] + 1;
   const uint8_t* d_dil = nullptr;
   if (d_seam) {
-    dilated.reserve((size_t)mw * mh);
+    grow_scratch(dilated, (size_t)mw * mh, stream);
     dim3 b(32, 8);
     dilate3x3_kernel<<<grid2d(mw, mh, b), b, 0, stream>>>(d_seam, mw, mh,
                                                           dilated.as<uint8_t>());
     XP_LAUNCHED();
     d_dil = dilated.as<uint8_t>();
+  }
+  const AuxCoef *aux_col = nullptr, *aux_row = nullptr;
+  if (d_gain || d_dil) {
+    grow_scratch(aux_tables, sizeof(AuxCoef) * (size_t)(W + H), stream);
+    AuxCoef* t = aux_tables.as<AuxCoef>();
+    aux_tables_kernel<<<div_up(W + H, 256), 256, 0, stream>>>(
+        W, H, d_gain ? gw : 0, d_gain ? gh : 0, d_dil ? mw : 0,
+        d_dil ? mh : 0, t, t + W);
+    XP_LAUNCHED();
+    aux_col = t;
+    aux_row = t + W;
   }
   MapSrc m = prepare_map(p, roi);
   dim3 b(32, 8);
@@ -762,11 +847,11 @@ void Warper::warp_bgra_device(const void* dsrc, int sw, int sh, size_t spitch,
   if (depth == 8)
     warp_bgra_kernel<uint8_t><<<g, b, 0, stream>>>(
         m, (const uint8_t*)dsrc, spitch, sw, sh, W, H, d_gain, gw, gh, d_dil,
-        mw, mh, (uint8_t*)ddst, dpitch);
+        mw, mh, aux_col, aux_row, (uint8_t*)ddst, dpitch);
   else
     warp_bgra_kernel<uint16_t><<<g, b, 0, stream>>>(
         m, (const uint16_t*)dsrc, spitch / 2, sw, sh, W, H, d_gain, gw, gh,
-        d_dil, mw, mh, (uint16_t*)ddst, dpitch / 2);
+        d_dil, mw, mh, aux_col, aux_row, (uint16_t*)ddst, dpitch / 2);
   XP_LAUNCHED();
 }
 

@@ -15,7 +15,8 @@ struct Warper {
   bool external_stream = false;
   bool device_ready = false;  // ensure_device() ran: the stream may hold work
   bool detached = false;      // the owner (composer) synchronised already
-  DevBuf scratch, tables, staging_src, staging_dst, dilated, aux_gain,
+  DevBuf scratch, tables, aux_tables, staging_src, staging_dst, dilated,
+      aux_gain,
       aux_seam;
 
   ~Warper();

@@ -373,6 +373,15 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const Item* items,
         }
         return v;
       };
+      auto in_row = [&](int pos) -> bool { return pos >= 0 && pos < W; };
+      // one load of the previous band's last row, final or not
+      auto peek = [&](int pos) -> Val {
+        const bool valid = in_row(pos);
+        const Val* p = prob.val_ptr(B, B.rho0 - 1, valid ? pos : 0);
+        return valid ? ctx.ld_poll(p) : Val(0);
+      };
+      Val pv_ahead = 0;
+      bool have_ahead = false;
       // `older` is `last` one step back: with a skew of 3 the lane below needs
       // it a full step after it was formed, so the shuffle is off the chain
       Val last = 0, older = 0, w0 = 0, w1 = 0, w2 = 0;
@@ -416,12 +425,25 @@ XP_HD void run(Ctx& ctx, const P& prob, int* counter, const Item* items,
             kind_word = c + lane < item.c1 ? band_flags[c + lane] : 0u;
           uncovered = ctx.shfl_idx(kind_word, k & 31) == kTileUncovered;
         }
-        // previous band's last row, positions s0+1 .. s0+32 (one per lane)
+        // previous band's last row, positions s0+1 .. s0+32 (one per lane).
+        // The load was issued before the steps of the previous chunk (its
+        // trip to L2 is as long as half a chunk of steps); only a value that
+        // was not final yet is polled for.
         Val pv = 0;
-        if (B.dep >= 0) pv = poll(true, s0 + 1 + lane);
+        if (B.dep >= 0) {
+          pv = pv_ahead;
+          if (!have_ahead ||
+              !ctx.all(!in_row(s0 + 1 + lane) || pv != kSentinel))
+            pv = poll(true, s0 + 1 + lane);
+        }
         XP_WF_CLOCK(1);
         pv_row[lane] = pv;
         ctx.sync();
+        have_ahead = false;
+        if (B.dep >= 0 && c + 1 < item.c1) {
+          pv_ahead = peek(s0 + kChunk + 1 + lane);
+          have_ahead = true;
+        }
         ctx.wait(kInFull + (k % kInBufs));
         if (k >= 2) ctx.wait(kOutFree + (k & 1));
         XP_WF_CLOCK(2);
