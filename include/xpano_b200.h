@@ -284,6 +284,10 @@ typedef struct {
   int stage_launches[9];
   double warp_bytes;
   int warp_launches;
+  /* canvas tiling: the whole canvas, the first column this rank owns
+   * (width / min_x above then describe the owned strip) and the window
+   * (strip + halo) it computed */
+  int canvas_width, canvas_height, tile_x0, window_x0, window_width;
 } xp_compose_info;
 
 void xp_compose_opts_default(xp_compose_opts* o);
@@ -302,6 +306,29 @@ xp_status xp_composer_set_images(xp_composer* c, int n,
                                  const xp_compose_image* images, int mem);
 /* Run warp -> feed -> blend on the device; result stays resident. */
 xp_status xp_composer_run(xp_composer* c, xp_compose_info* info);
+/* Canvas tiling of ONE panorama over `count` GPUs (SURVEY.md section 8e;
+ * no counterpart in the reference, whose ComposePanorama runs on one thread,
+ * stitcher_pipeline.cc:340-344): every rank creates the same composer, calls
+ * xp_composer_set_tile(index = rank, count = ranks) BEFORE set_images, and
+ * then, instead of xp_composer_run,
+ *   xp_composer_run_tile_begin(c, partial)   warp, seams (whole canvas, every
+ *        rank) and the pyramids / composite / collapse of this rank's strip;
+ *   all-reduce (sum) the 8 doubles of `partial` over the ranks -- the only
+ *        exchange: 3 channel sums of the collapsed level, 3 input channel
+ *        totals and the pixel count of the offset correction
+ *        (multiblend.cpp:1232-1267), and a flag;
+ *   xp_composer_run_tile_end(c, reduced, info)   offset + output pass.
+ * The strips partition the canvas into vertical slices; xp_composer_fetch
+ * returns this rank's slice (info.width x info.height at canvas column
+ * info.tile_x0), bit-identical to the same columns of the single-GPU result.
+ * xp_composer_tile_needs tells which sources the rank uploads (the others
+ * only contribute their opacity). xp_tile_halo(levels): halo in pixels. */
+xp_status xp_composer_set_tile(xp_composer* c, int index, int count);
+xp_status xp_composer_tile_needs(xp_composer* c, int n, int* needed);
+xp_status xp_composer_run_tile_begin(xp_composer* c, double partial[8]);
+xp_status xp_composer_run_tile_end(xp_composer* c, const double reduced[8],
+                                   xp_compose_info* info);
+int xp_tile_halo(int levels);
 /* Copy the panorama (interleaved BGR, zero outside mask) and mask out. */
 xp_status xp_composer_fetch(xp_composer* c, void* dst_bgr, size_t dst_stride,
                             uint8_t* dst_mask, size_t mask_stride, int mem);

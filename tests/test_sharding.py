@@ -65,3 +65,51 @@ def test_two_ranks_gloo_reduce():
     assert groups == [[0, 2, 4], [1, 3]]
     assert r["megapixels"] == 50.0 and r["ms"] == 200.0
     assert abs(r["mp_per_s"] - 250.0) < 1e-9
+
+
+def test_strip_bounds_partition_the_roi():
+    for x, w in ((-505, 1009), (0, 7), (-9303, 18606), (12, 100001)):
+        for world in (1, 2, 3, 4, 8):
+            edges = [sharding.strip_bounds(x, w, world, r)
+                     for r in range(world)]
+            assert edges[0][0] == x and edges[-1][1] == x + w
+            for a, b in zip(edges, edges[1:]):
+                assert a[1] == b[0] and a[0] <= a[1]
+    with pytest.raises(ValueError):
+        sharding.strip_bounds(0, 10, 2, 2)
+    assert sharding.tile_halo(5) == 6 * 32 and sharding.tile_halo(7) == 768
+
+
+def _tile_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import numpy as np
+        # the exchange of a canvas-tiled run: 8 partial sums per rank
+        part = [float(rank + 1) * (k + 1) for k in range(8)]
+        red = sharding.all_reduce_sum(part)
+        x0, x1 = sharding.strip_bounds(-100, 333, world, rank)
+        strip = np.full((4, x1 - x0, 3), rank + 1, np.uint8)
+        mask = np.full((4, x1 - x0), 255, np.uint8)
+        pano, full = sharding.gather_strips(strip, mask, x0 + 100, 333)
+        if rank == 0:
+            out.put((red, pano[0, :, 0].tolist(), int(full.sum())))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_gloo_tile_exchange():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_tile_worker, args=(r, 2, port, q))
+             for r in range(2)]
+    for p in procs:
+        p.start()
+    red, row, msum = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert red == [3.0 * (k + 1) for k in range(8)]
+    assert row == [1] * 166 + [2] * 167 and msum == 255 * 4 * 333

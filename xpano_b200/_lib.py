@@ -70,7 +70,10 @@ class ComposeInfo(ctypes.Structure):
                 ("s_t", ctypes.c_double), ("c", ctypes.c_double),
                 ("stage_bytes", ctypes.c_double * 9),
                 ("stage_launches", c_int * 9),
-                ("warp_bytes", ctypes.c_double), ("warp_launches", c_int)]
+                ("warp_bytes", ctypes.c_double), ("warp_launches", c_int),
+                ("canvas_width", c_int), ("canvas_height", c_int),
+                ("tile_x0", c_int), ("window_x0", c_int),
+                ("window_width", c_int)]
 
 
 # every symbol include/xpano_b200.h declares: (restype, argtypes)
@@ -135,6 +138,12 @@ SYMBOLS = {
     "xp_composer_set_images": (c_int, [c_void_p, c_int, P(ComposeImage),
                                        c_int]),
     "xp_composer_run": (c_int, [c_void_p, P(ComposeInfo)]),
+    "xp_composer_set_tile": (c_int, [c_void_p, c_int, c_int]),
+    "xp_composer_tile_needs": (c_int, [c_void_p, c_int, c_void_p]),
+    "xp_composer_run_tile_begin": (c_int, [c_void_p, c_void_p]),
+    "xp_composer_run_tile_end": (c_int, [c_void_p, c_void_p,
+                                         P(ComposeInfo)]),
+    "xp_tile_halo": (c_int, [c_int]),
     "xp_composer_fetch": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p,
                                   c_size_t, c_int]),
     "xp_composer_blender": (c_void_p, [c_void_p]),

@@ -217,4 +217,5 @@ static void next_mask_rect(const MaskLevel& in, MaskLevel& out) {
 }  // namespace xp
 
 #include "blend_run.inc"
+#include "blend_tile.inc"
 #include "blend_api.inc"

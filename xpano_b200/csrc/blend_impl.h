@@ -77,7 +77,16 @@ void launch_canvas_stats(const void* cover, int cover_bytes,
                          const uint8_t* labels, int W, int H,
                          const ImgDev* d_imgs, int n, int bpp,
                          uint8_t* full_mask, uint8_t* xor_mask,
-                         CanvasStats* d_stats, int mode, cudaStream_t s);
+                         CanvasStats* d_stats, int mode, cudaStream_t s,
+                         int sum_x0 = 0, int sum_x1 = 0x7fffffff);
+// canvas-tiled runs: the window [wx0, wx0 + ww) of the label map with labels
+// renumbered through `relabel` (64 entries), of the xor mask (zero outside the
+// owned columns [ox0, ox1)) and of the full mask, as compact ww x H arrays
+void launch_window_copy(const uint8_t* labels, const uint8_t* xor_mask,
+                        const uint8_t* full_mask, int W, int H, int wx0,
+                        int ww, int ox0, int ox1, const uint8_t* d_relabel,
+                        uint8_t* wlabels, uint8_t* wxor, uint8_t* wfull,
+                        cudaStream_t s);
 void launch_stats_init(CanvasStats* d_stats, cudaStream_t s);
 
 // pyramid.cu

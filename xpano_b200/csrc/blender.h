@@ -77,6 +77,19 @@ struct Blender {
   std::vector<std::vector<MaskLevel>> dbg_mask_lv;
   DevBuf dbg_out, dbg_collapsed;
 
+  // ---- canvas tiling (blend_tile.inc): this blender computes one strip ----
+  struct Tile {
+    int index = 0, count = 1;
+    int abs_x0 = 0, abs_x1 = 0;  // owned columns in feed (ROI) coordinates
+  } tile;
+  std::vector<char> fed_local;   // per fed image: its colours are present
+  bool tile_pending = false;     // between blend_tile_begin and _end
+  int own_x0 = 0, own_x1 = 0;    // owned canvas columns
+  int win_x0 = 0, win_w = 0;     // window (strip + halo) on the canvas
+  int out_w = 0;                 // row length of planes / bgr (W, or win_w)
+  std::vector<int> win_img;      // window image -> fed index
+  DevBuf wlabels, wxor, wfull, d_relabel;
+
   explicit Blender(const xp_blend_opts& o) : opts(o) {}
   ~Blender();
   void ensure_device();
@@ -85,6 +98,8 @@ struct Blender {
             size_t mask_stride, int w, int h, int depth, int spp, int tl_x,
             int tl_y, int mem);
   void blend(xp_timing* timing);
+  void blend_tile_begin(double partial[8]);
+  void blend_tile_end(const double reduced[8], xp_timing* timing);
   void fetch(void* dst_bgr, size_t dst_stride, uint8_t* dst_mask,
              size_t mask_stride, int mem);
   void fetch_planes(void* planes_out, int mem);
@@ -98,5 +113,7 @@ struct Blender {
 
 int blend_levels(int n, const int* widths, const int* heights,
                  int fixed_levels, int add_levels);
+// halo of a canvas-tiled run, in canvas pixels, on either side of a strip
+int tile_halo(int levels);
 
 }  // namespace xp

@@ -157,10 +157,13 @@ struct Composer {
   void set_images(int n, const xp_compose_image* images, int mem) {
     XP_REQUIRE(n >= 1 && images, "set_images: no images");
     XP_REQUIRE(opts.depth == 8 || opts.depth == 16, "depth must be 8 or 16");
+    XP_REQUIRE(!tile_pending, "set_images between run_tile_begin and _end");
     ensure_device();
     src.clear();
+    plan.valid = false;
     const size_t bs = opts.depth / 8;
     XP_CUDA(cudaEventRecord(ev[0], stream));
+    // cameras, gain maps and low-resolution seam masks of every image
     for (int i = 0; i < n; ++i) {
       const xp_compose_image& in = images[i];
       XP_REQUIRE(in.data && in.w > 0 && in.h > 0, "image %d is empty", i);
@@ -169,17 +172,6 @@ struct Composer {
       s->h = in.h;
       memcpy(s->K, in.K, sizeof(s->K));
       memcpy(s->R, in.R, sizeof(s->R));
-      const size_t row = (size_t)in.w * 3 * bs;
-      const size_t stride = in.stride ? in.stride : row;
-      if (mem == XP_MEM_DEVICE) {
-        s->dev = in.data;
-        s->pitch = stride;
-      } else {
-        s->buf.reserve(row * (size_t)in.h);
-        copy_in_2d(s->buf.p, row, in.data, stride, row, in.h, mem, stream);
-        s->dev = s->buf.p;
-        s->pitch = row;
-      }
       if (in.aux.gain) {
         s->gw = in.aux.gain_w;
         s->gh = in.aux.gain_h;
@@ -202,6 +194,24 @@ struct Composer {
                                 cudaMemcpyHostToDevice, stream));
       }
       src.push_back(std::move(s));
+    }
+    // a canvas tile uploads only the sources whose colours reach its strip
+    if (tile_count > 1) make_plan();
+    for (int i = 0; i < n; ++i) {
+      const xp_compose_image& in = images[i];
+      SrcImage* s = src[i].get();
+      if (tile_count > 1 && !plan.local[i]) continue;
+      const size_t row = (size_t)in.w * 3 * bs;
+      const size_t stride = in.stride ? in.stride : row;
+      if (mem == XP_MEM_DEVICE) {
+        s->dev = in.data;
+        s->pitch = stride;
+      } else {
+        s->buf.reserve(row * (size_t)in.h);
+        copy_in_2d(s->buf.p, row, in.data, stride, row, in.h, mem, stream);
+        s->dev = s->buf.p;
+        s->pitch = row;
+      }
     }
     XP_CUDA(cudaEventRecord(ev[1], stream));
     sync_blocking(stream);
@@ -266,8 +276,151 @@ struct Composer {
     rect[3] = (int)(y1 - y0);
   }
 
+  // ---- plan: ROIs, size cap, and (tiled) the strip of this rank ----------
+  struct Plan {
+    bool valid = false;
+    float scale = 0;
+    bool capped = false;
+    std::vector<int> rois;
+    int rect[4] = {0, 0, 0, 0};
+    int abs_x0 = 0, abs_x1 = 0;   // owned columns (feed coordinates)
+    std::vector<char> local;      // per source image: colours needed
+  } plan;
+  int tile_index = 0, tile_count = 1;
+  bool tile_pending = false;
+  double t_s_src = 0, t_s_w = 0;
+  int t_warp_launches = 0;
+
+  void make_plan() {
+    // stitcher.cc:306-313: warp_scale = float(warped_image_scale_ *
+    // compose_work_aspect), both doubles there
+    double wis = opts.warped_image_scale, cwa = opts.compose_work_aspect;
+    if (!(wis > 0)) {
+      wis = (double)opts.warp_scale;
+      cwa = 1.0;
+    }
+    plan.scale = (float)(wis * cwa);
+    compute_roi(plan.scale, plan.rois, plan.rect);
+    plan.capped = xp_compose_capped_scale(wis, cwa, plan.rect[2], plan.rect[3],
+                                          opts.max_pano_mpx, &plan.scale) != 0;
+    if (plan.capped) compute_roi(plan.scale, plan.rois, plan.rect);
+    const int n = (int)src.size();
+    plan.local.assign(n, 1);
+    plan.abs_x0 = plan.rect[0];
+    plan.abs_x1 = plan.rect[0] + plan.rect[2];
+    if (tile_count > 1) {
+      // Strips partition the ROI rectangle (known before any pixel is
+      // warped; the trimmed canvas lies inside it). An image's colours are
+      // needed when its ROI reaches into the strip widened by the halo, one
+      // alignment unit and the slack of the level count (levels are fixed
+      // after trim; from the ROI sizes they can only come out larger).
+      plan.abs_x0 = plan.rect[0] + (int)((long)plan.rect[2] * tile_index / tile_count);
+      plan.abs_x1 = plan.rect[0] + (int)((long)plan.rect[2] * (tile_index + 1) / tile_count);
+      std::vector<int> ws, hs;
+      for (int i = 0; i < n; ++i)
+        if (!src[i]->skip) {
+          ws.push_back(plan.rois[4 * i + 2]);
+          hs.push_back(plan.rois[4 * i + 3]);
+        }
+      XP_REQUIRE(ws.size() >= 2, "canvas tiling needs at least two images");
+      const int lv = blend_levels((int)ws.size(), ws.data(), hs.data(),
+                                  opts.blend.fixed_levels,
+                                  opts.blend.add_levels);
+      XP_REQUIRE(lv >= 2 && lv <= kMaxLevels,
+                 "canvas tiling needs 2..%d pyramid levels", kMaxLevels);
+      const long margin = (long)tile_halo(lv) + (1L << lv);
+      for (int i = 0; i < n; ++i) {
+        const long x0 = plan.rois[4 * i], x1 = x0 + plan.rois[4 * i + 2];
+        plan.local[i] =
+            x1 > plan.abs_x0 - margin && x0 < plan.abs_x1 + margin ? 1 : 0;
+      }
+    }
+    plan.valid = true;
+  }
+
+  // warp every image into a new blender (tiled: alpha only for the images
+  // whose colours cannot reach this rank's strip)
+  void warp_all() {
+    xp_blend_opts bo = opts.blend;
+    blender.reset(new Blender(bo));
+    blender->stream = stream;
+    blender->external_stream = true;
+    for (int k = 0; k < 4; ++k) blender->roi[k] = plan.rect[k];
+    warper.scale = plan.scale;
+    t_s_src = t_s_w = 0;
+    t_warp_launches = 0;
+    const size_t bs = opts.depth / 8;
+    std::vector<char> fed_local;
+    for (size_t i = 0; i < src.size(); ++i) {
+      SrcImage& s = *src[i];
+      if (s.skip) continue;
+      const int* r = &plan.rois[4 * i];
+      const int roi_incl[4] = {r[0], r[1], r[0] + r[2] - 1, r[1] + r[3] - 1};
+      Fed* f = blender->new_fed(r[2], r[3], opts.depth, r[0], r[1]);
+      const Projector p = warper.projector(s.K, s.R);
+      const bool colours = plan.local[i] != 0;
+      XP_REQUIRE(!colours || s.dev, "image %zu was not uploaded", i);
+      warper.warp_bgra_device(colours ? s.dev : nullptr, s.w, s.h, s.pitch,
+                              opts.depth, p, roi_incl, s.gain.as<float>(),
+                              s.gw, s.gh, s.seam.as<uint8_t>(), s.mw, s.mh,
+                              f->data.p, (size_t)r[2] * 4 * bs);
+      fed_local.push_back(colours ? 1 : 0);
+      t_warp_launches += 1 + (s.seam.p ? 1 : 0) +
+                         (is_separable(p.type) ? 1 : 0) +
+                         (s.seam.p || (colours && s.gain.p) ? 1 : 0);
+      if (colours) t_s_src += (double)s.w * s.h;
+      t_s_w += (double)r[2] * r[3];
+    }
+    if (tile_count > 1) {
+      blender->tile.index = tile_index;
+      blender->tile.count = tile_count;
+      blender->tile.abs_x0 = plan.abs_x0;
+      blender->tile.abs_x1 = plan.abs_x1;
+      blender->fed_local = fed_local;
+    }
+  }
+
+  void fill_info(xp_compose_info* info, const xp_timing& tm, float warp_ms,
+                 float blend_ms) {
+    if (!info) return;
+    memset(info, 0, sizeof(*info));
+    const bool tiled = tile_count > 1;
+    info->width = tiled ? blender->own_x1 - blender->own_x0 : blender->W;
+    info->height = blender->H;
+    info->min_x = blender->min_x + (tiled ? blender->own_x0 : 0);
+    info->min_y = blender->min_y;
+    info->bpp = blender->out_bpp;
+    info->levels = blender->levels;
+    info->resolution_capped = plan.capped ? 1 : 0;
+    memcpy(info->roi, plan.rect, sizeof(plan.rect));
+    info->warp_scale = plan.scale;
+    info->warp_ms = warp_ms;
+    info->blend_ms = blend_ms;
+    info->h2d_ms = h2d_ms;
+    info->timing = tm;
+    info->s_src = t_s_src;
+    info->s_w = t_s_w;
+    info->s_t = blender->s_t;
+    info->c = tiled ? (double)info->width * info->height : blender->c_px;
+    for (int k = 0; k < 9; ++k) {
+      info->stage_bytes[k] = blender->stage_bytes[k];
+      info->stage_launches[k] = blender->stage_launches[k];
+    }
+    const size_t bs = opts.depth / 8;
+    info->warp_bytes = (3.0 * t_s_src + 4.0 * t_s_w) * bs;
+    info->warp_launches = t_warp_launches;
+    info->canvas_width = blender->W;
+    info->canvas_height = blender->H;
+    info->tile_x0 = tiled ? blender->own_x0 : 0;
+    info->window_x0 = tiled ? blender->win_x0 : 0;
+    info->window_width = tiled ? blender->win_w : blender->W;
+  }
+
   void run(xp_compose_info* info) {
     XP_REQUIRE(!src.empty(), "run: set_images first");
+    XP_REQUIRE(tile_count == 1,
+               "run: this composer holds a canvas tile, use run_tile_begin / "
+               "run_tile_end");
     const bool trace = getenv("XP_TRACE") != nullptr;
     auto now = [] {
       return std::chrono::duration<double, std::milli>(
@@ -276,49 +429,10 @@ struct Composer {
     };
     const double h0 = now();
     ensure_device();
-    // stitcher.cc:306-313: warp_scale = float(warped_image_scale_ *
-    // compose_work_aspect), both doubles there
-    double wis = opts.warped_image_scale, cwa = opts.compose_work_aspect;
-    if (!(wis > 0)) {
-      wis = (double)opts.warp_scale;
-      cwa = 1.0;
-    }
-    float scale = (float)(wis * cwa);
-    std::vector<int> rois;
-    int rect[4];
-    compute_roi(scale, rois, rect);
-    const bool capped = xp_compose_capped_scale(wis, cwa, rect[2], rect[3],
-                                                opts.max_pano_mpx, &scale) != 0;
-    if (capped) compute_roi(scale, rois, rect);
+    make_plan();
     const double h1 = now();
-    xp_blend_opts bo = opts.blend;
-    blender.reset(new Blender(bo));
-    blender->stream = stream;
-    blender->external_stream = true;
-    blender->roi[0] = rect[0];
-    blender->roi[1] = rect[1];
-    blender->roi[2] = rect[2];
-    blender->roi[3] = rect[3];
-    double s_src = 0, s_w = 0;
-    int warp_launches = 0;
     XP_CUDA(cudaEventRecord(ev[0], stream));
-    const size_t bs = opts.depth / 8;
-    for (size_t i = 0; i < src.size(); ++i) {
-      SrcImage& s = *src[i];
-      if (s.skip) continue;
-      const int* r = &rois[4 * i];
-      const int roi_incl[4] = {r[0], r[1], r[0] + r[2] - 1, r[1] + r[3] - 1};
-      Fed* f = blender->new_fed(r[2], r[3], opts.depth, r[0], r[1]);
-      const Projector p = warper.projector(s.K, s.R);
-      warper.warp_bgra_device(s.dev, s.w, s.h, s.pitch, opts.depth, p,
-                              roi_incl, s.gain.as<float>(), s.gw, s.gh,
-                              s.seam.as<uint8_t>(), s.mw, s.mh, f->data.p,
-                              (size_t)r[2] * 4 * bs);
-      warp_launches += 1 + (s.seam.p ? 1 : 0) + (is_separable(p.type) ? 1 : 0) +
-                       (s.seam.p || s.gain.p ? 1 : 0);
-      s_src += (double)s.w * s.h;
-      s_w += (double)r[2] * r[3];
-    }
+    warp_all();
     XP_CUDA(cudaEventRecord(ev[1], stream));
     const double h2 = now();
     xp_timing tm;
@@ -331,35 +445,35 @@ struct Composer {
               "trace host: roi %.3f ms, new blender + warp launches %.3f ms, "
               "blend %.3f ms\n",
               h1 - h0, h2 - h1, now() - h2);
-    if (info) {
-      memset(info, 0, sizeof(*info));
-      float a = 0, b = 0;
-      cudaEventElapsedTime(&a, ev[0], ev[1]);
-      cudaEventElapsedTime(&b, ev[1], ev[2]);
-      info->width = blender->W;
-      info->height = blender->H;
-      info->min_x = blender->min_x;
-      info->min_y = blender->min_y;
-      info->bpp = blender->out_bpp;
-      info->levels = blender->levels;
-      info->resolution_capped = capped ? 1 : 0;
-      memcpy(info->roi, rect, sizeof(rect));
-      info->warp_scale = scale;
-      info->warp_ms = a;
-      info->blend_ms = b;
-      info->h2d_ms = h2d_ms;
-      info->timing = tm;
-      info->s_src = s_src;
-      info->s_w = s_w;
-      info->s_t = blender->s_t;
-      info->c = blender->c_px;
-      for (int k = 0; k < 9; ++k) {
-        info->stage_bytes[k] = blender->stage_bytes[k];
-        info->stage_launches[k] = blender->stage_launches[k];
-      }
-      info->warp_bytes = (3.0 * s_src + 4.0 * s_w) * bs;
-      info->warp_launches = warp_launches;
-    }
+    float a = 0, b = 0;
+    cudaEventElapsedTime(&a, ev[0], ev[1]);
+    cudaEventElapsedTime(&b, ev[1], ev[2]);
+    fill_info(info, tm, a, b);
+  }
+
+  // Canvas-tiled run: everything up to the collapsed strip;
+  // `partial` = this rank's share of the sums the offset correction needs.
+  void run_tile_begin(double partial[8]) {
+    XP_REQUIRE(!src.empty(), "run_tile_begin: set_images first");
+    XP_REQUIRE(tile_count > 1, "run_tile_begin: set_tile first");
+    ensure_device();
+    if (!plan.valid) make_plan();
+    XP_CUDA(cudaEventRecord(ev[0], stream));
+    warp_all();
+    XP_CUDA(cudaEventRecord(ev[1], stream));
+    blender->blend_tile_begin(partial);
+    tile_pending = true;
+  }
+
+  void run_tile_end(const double reduced[8], xp_compose_info* info) {
+    XP_REQUIRE(tile_pending && blender, "run_tile_end before run_tile_begin");
+    xp_timing tm;
+    memset(&tm, 0, sizeof(tm));
+    blender->blend_tile_end(reduced, &tm);
+    tile_pending = false;
+    float a = 0;
+    cudaEventElapsedTime(&a, ev[0], ev[1]);
+    fill_info(info, tm, a, (float)tm.total);
   }
 };
 
@@ -436,6 +550,46 @@ xp_status xp_composer_run(xp_composer* c, xp_compose_info* info) {
     XP_REQUIRE(c, "null composer");
     c->run(info);
   });
+}
+
+xp_status xp_composer_set_tile(xp_composer* c, int index, int count) {
+  return xp::guard([&] {
+    XP_REQUIRE(c, "null composer");
+    XP_REQUIRE(count >= 1 && index >= 0 && index < count,
+               "set_tile: index %d of %d", index, count);
+    XP_REQUIRE(!c->tile_pending, "set_tile between run_tile_begin and _end");
+    c->tile_index = index;
+    c->tile_count = count;
+    c->plan.valid = false;
+  });
+}
+
+xp_status xp_composer_tile_needs(xp_composer* c, int n, int* needed) {
+  return xp::guard([&] {
+    XP_REQUIRE(c && needed, "tile_needs: null argument");
+    XP_REQUIRE(c->plan.valid && (int)c->plan.local.size() == n,
+               "tile_needs: set_images first");
+    for (int i = 0; i < n; ++i) needed[i] = c->plan.local[i];
+  });
+}
+
+xp_status xp_composer_run_tile_begin(xp_composer* c, double partial[8]) {
+  return xp::guard([&] {
+    XP_REQUIRE(c && partial, "run_tile_begin: null argument");
+    c->run_tile_begin(partial);
+  });
+}
+
+xp_status xp_composer_run_tile_end(xp_composer* c, const double reduced[8],
+                                   xp_compose_info* info) {
+  return xp::guard([&] {
+    XP_REQUIRE(c && reduced, "run_tile_end: null argument");
+    c->run_tile_end(reduced, info);
+  });
+}
+
+int xp_tile_halo(int levels) {
+  return levels >= 0 && levels <= xp::kMaxLevels ? xp::tile_halo(levels) : -1;
 }
 
 xp_status xp_composer_fetch(xp_composer* c, void* dst_bgr, size_t dst_stride,

@@ -723,7 +723,10 @@ __global__ void __launch_bounds__(256)
     canvas_masks_kernel(const C* __restrict__ cover, int W, size_t n_px,
                         const ImgDev* __restrict__ imgs, int n,
                         uint8_t* __restrict__ full_mask,
-                        uint8_t* __restrict__ xor_mask, CanvasStats* stats) {
+                        uint8_t* __restrict__ xor_mask, CanvasStats* stats,
+                        int sum_x0, int sum_x1) {
+  // sums are taken over the columns [sum_x0, sum_x1) only: the whole canvas,
+  // or the strip a rank of a canvas-tiled run owns
   typedef Cov<C, F> Cv;
   __shared__ ImgDev s_img[64];
   __shared__ unsigned long long s_sum[4];
@@ -761,7 +764,7 @@ __global__ void __launch_bounds__(256)
       fm |= any ? 255u << (8 * k) : 0u;
       xm |= one ? 1u << (8 * k) : 0u;
       uncovered = uncovered || (in && !any);
-      if (in && one) {
+      if (in && one && x >= sum_x0 && x < sum_x1) {
         const ImgDev& im = s_img[Cv::low(cv[k])];
         const size_t q =
             (size_t)(im.top + y - im.ypos) * im.tiff_w + im.left + x - im.xpos;
@@ -869,6 +872,43 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+__global__ void window_copy_kernel(const uint8_t* __restrict__ labels,
+                                   const uint8_t* __restrict__ xor_mask,
+                                   const uint8_t* __restrict__ full_mask,
+                                   int W, int H, int wx0, int ww, int ox0,
+                                   int ox1,
+                                   const uint8_t* __restrict__ relabel,
+                                   uint8_t* __restrict__ wlabels,
+                                   uint8_t* __restrict__ wxor,
+                                   uint8_t* __restrict__ wfull) {
+  __shared__ uint8_t map[64];
+  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+  if (tid < 64) map[tid] = relabel[tid];
+  __syncthreads();
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= ww || y >= H) return;
+  const size_t src = (size_t)y * W + wx0 + x, dst = (size_t)y * ww + x;
+  const uint8_t l = labels[src];
+  wlabels[dst] = l < 64 ? map[l] : (uint8_t)255;
+  const int gx = wx0 + x;
+  wxor[dst] = gx >= ox0 && gx < ox1 ? xor_mask[src] : (uint8_t)0;
+  wfull[dst] = full_mask[src];
+}
+
+void launch_window_copy(const uint8_t* labels, const uint8_t* xor_mask,
+                        const uint8_t* full_mask, int W, int H, int wx0,
+                        int ww, int ox0, int ox1, const uint8_t* d_relabel,
+                        uint8_t* wlabels, uint8_t* wxor, uint8_t* wfull,
+                        cudaStream_t s) {
+  dim3 b(64, 4);
+  dim3 g(div_up(ww, 64), div_up(H, 4));
+  window_copy_kernel<<<g, b, 0, s>>>(labels, xor_mask, full_mask, W, H, wx0,
+                                     ww, ox0, ox1, d_relabel, wlabels, wxor,
+                                     wfull);
+  XP_LAUNCHED();
+}
+
 __global__ void stats_init_kernel(CanvasStats* st) {
   const int i = threadIdx.x;
   if (i < 4) st->totals[i] = 0;
@@ -886,7 +926,8 @@ void launch_canvas_stats(const void* cover, int cover_bytes,
                          const uint8_t* labels, int W, int H,
                          const ImgDev* d_imgs, int n, int bpp,
                          uint8_t* full_mask, uint8_t* xor_mask,
-                         CanvasStats* d_stats, int mode, cudaStream_t s) {
+                         CanvasStats* d_stats, int mode, cudaStream_t s,
+                         int sum_x0, int sum_x1) {
   if (mode == 2) {  // needs the labels only
     if (n > 1) {
       label_boxes_kernel<<<sm_count() * 8, 256, 0, s>>>(labels, W, (size_t)W * H, n,
@@ -906,7 +947,7 @@ void launch_canvas_stats(const void* cover, int cover_bytes,
   if (mode == 1)                                                            \
     canvas_masks_kernel<C, F, BPP><<<sm_count() * 8, 256, 0, s>>>(                 \
         (const C*)cover, W, (size_t)W * H, d_imgs, n, full_mask, xor_mask, \
-        d_stats);                                                           \
+        d_stats, sum_x0, sum_x1);                                           \
   else if (mode == 2)          \
     XP_STATS3(C, F, BPP, 2);   \
   else                         \

@@ -621,6 +621,36 @@ __global__ void warp_bgra_kernel(MapSrc m, const T* __restrict__ src,
   }
 }
 
+// The alpha channel of warp_bgra_kernel alone (colour samples zero): what a
+// rank of a canvas-tiled run needs of the images outside its strip -- their
+// opacity enters the cover map and the seams, their colours never reach its
+// pixels. No source read, no gain.
+template <typename T>
+__global__ void warp_alpha_kernel(MapSrc m, int sw, int sh, int W, int H,
+                                  const uint8_t* __restrict__ seam_dilated,
+                                  int mw, int mh,
+                                  const AuxCoef* __restrict__ aux_col,
+                                  const AuxCoef* __restrict__ aux_row,
+                                  T* __restrict__ dst, size_t dst_pitch) {
+  int dx = blockIdx.x * blockDim.x + threadIdx.x;
+  int dy = blockIdx.y * blockDim.y + threadIdx.y;
+  if (dx >= W || dy >= H) return;
+  float x, y;
+  eval_map(m, dx, dy, x, y);
+  int ix, iy;
+  bool opaque = nearest_inside(sw, sh, x, y, ix, iy);
+  if (seam_dilated && opaque)
+    opaque = resize_exact_u8_tab(seam_dilated, mw, mh, aux_col[dx],
+                                 aux_row[dy]) != 0;
+  const T amax = (T)(sizeof(T) == 1 ? 255 : 65535);
+  T* d = dst + (size_t)dy * dst_pitch + (size_t)dx * 4;
+  if (sizeof(T) == 1) {
+    *reinterpret_cast<uchar4*>(d) = make_uchar4(0, 0, 0, opaque ? 255 : 0);
+  } else {
+    *reinterpret_cast<ushort4*>(d) = make_ushort4(0, 0, 0, opaque ? amax : 0);
+  }
+}
+
 // ---------------------------------------------------------------------------
 // Warper methods
 // ---------------------------------------------------------------------------
@@ -830,6 +860,7 @@ void Warper::warp_bgra_device(const void* dsrc, int sw, int sh, size_t spitch,
     XP_LAUNCHED();
     d_dil = dilated.as<uint8_t>();
   }
+  if (!dsrc) d_gain = nullptr;  // alpha only: colours are not produced
   const AuxCoef *aux_col = nullptr, *aux_row = nullptr;
   if (d_gain || d_dil) {
     grow_scratch(aux_tables, sizeof(AuxCoef) * (size_t)(W + H), stream);
@@ -844,6 +875,18 @@ void Warper::warp_bgra_device(const void* dsrc, int sw, int sh, size_t spitch,
   MapSrc m = prepare_map(p, roi);
   dim3 b(32, 8);
   dim3 g = grid2d(W, H, b);
+  if (!dsrc) {
+    if (depth == 8)
+      warp_alpha_kernel<uint8_t><<<g, b, 0, stream>>>(
+          m, sw, sh, W, H, d_dil, mw, mh, aux_col, aux_row, (uint8_t*)ddst,
+          dpitch);
+    else
+      warp_alpha_kernel<uint16_t><<<g, b, 0, stream>>>(
+          m, sw, sh, W, H, d_dil, mw, mh, aux_col, aux_row, (uint16_t*)ddst,
+          dpitch / 2);
+    XP_LAUNCHED();
+    return;
+  }
   if (depth == 8)
     warp_bgra_kernel<uint8_t><<<g, b, 0, stream>>>(
         m, (const uint8_t*)dsrc, spitch, sw, sh, W, H, d_gain, gw, gh, d_dil,

@@ -44,7 +44,8 @@ struct Warper {
                  const float* K, const float* R, const xp_compose_aux* aux,
                  int aux_mem, void* dst, size_t dst_stride, int mem,
                  int out_xywh[4]);
-  // all-device form used by the composer; no synchronisation
+  // all-device form used by the composer; no synchronisation. dsrc == null:
+  // only the alpha channel is produced (colours zero), see warp_alpha_kernel
   void warp_bgra_device(const void* dsrc, int sw, int sh, size_t spitch,
                         int depth, const Projector& p, const int roi[4],
                         const float* d_gain, int gw, int gh,

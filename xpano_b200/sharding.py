@@ -1,4 +1,5 @@
-"""Multi-GPU sharding of the export path: by panorama group.
+"""Multi-GPU sharding of the export path: by panorama group, and by canvas
+strips of one panorama.
 
 Panoramas are independent jobs in the reference (`StitcherData.panos`,
 xpano/pipeline/stitcher_pipeline.h:48-52; one `Stitch()` per panorama), so
@@ -7,6 +8,13 @@ only communication is the reduction of the per-rank counters that `bench.py`
 reports (pixels produced, max elapsed time). One process per GPU, rendezvous
 through `torch.distributed` (NCCL on the GPU box, gloo in the CPU tests).
 """
+# Canvas strips (SURVEY.md 8e, BASELINE.json configs[2]): rank r of N owns the
+# columns [x + w*r/N, x + w*(r+1)/N) of the ROI rectangle (x, w) that
+# ComputeRoi (stitcher.cc:144-169) gives; seams are computed for the whole
+# canvas on every rank, the pyramids / composite / collapse for the strip plus
+# a halo of tile_halo(levels) pixels that is recomputed locally, and the only
+# exchange is an all-reduce of the 8 partial sums of the offset correction
+# (`all_reduce_sum`; xp_composer_run_tile_begin / _end).
 from __future__ import annotations
 
 from typing import List, Sequence
@@ -62,3 +70,48 @@ def job_throughput(local_megapixels: float, local_ms: float) -> dict:
     ms = reduce_max(local_ms)
     return {"megapixels": total_mp, "ms": ms,
             "mp_per_s": total_mp / (ms / 1e3) if ms > 0 else 0.0}
+
+
+def strip_bounds(roi_x: int, roi_w: int, world: int, rank: int):
+    """Columns of the ROI rectangle that rank `rank` of `world` owns (same
+    integer arithmetic as the library, csrc/compose.cu make_plan)."""
+    if world < 1 or not (0 <= rank < world):
+        raise ValueError(f"bad rank {rank} of {world}")
+    return (roi_x + roi_w * rank // world, roi_x + roi_w * (rank + 1) // world)
+
+
+def tile_halo(levels: int) -> int:
+    """Halo (canvas pixels, each side) a strip recomputes: 6 * 2^levels."""
+    from . import _lib
+    return int(_lib.load().xp_tile_halo(int(levels)))
+
+
+def all_reduce_sum(values: Sequence[float]) -> List[float]:
+    """Sum of a short vector of doubles over the ranks (NCCL on the GPU box,
+    gloo in the CPU tests); identity without a process group."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return [float(v) for v in values]
+    t = _tensor(values, _device())
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return [float(v) for v in t.tolist()]
+
+
+def gather_strips(strip, mask, x0: int, canvas_w: int):
+    """Assemble the panorama on rank 0 from the strips of all ranks (host
+    arrays): -> (pano, mask) on rank 0, (None, None) elsewhere."""
+    import numpy as np
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return strip, mask
+    parts = [None] * dist.get_world_size()
+    dist.all_gather_object(parts, (int(x0), strip, mask))
+    if dist.get_rank() != 0:
+        return None, None
+    h = strip.shape[0]
+    pano = np.zeros((h, canvas_w, 3), strip.dtype)
+    full = np.zeros((h, canvas_w), np.uint8)
+    for px0, ps, pm in parts:
+        pano[:, px0:px0 + ps.shape[1]] = ps
+        full[:, px0:px0 + pm.shape[1]] = pm
+    return pano, full

@@ -93,9 +93,46 @@ class Composer:
                                                _lib.MEM_HOST))
         self._keep = keep
 
+    # ---- canvas tiling of one panorama over several GPUs -------
+    def set_tile(self, index, count):
+        """This composer computes strip `index` of `count` vertical strips of
+        the canvas; call before set_images (a tile uploads only the sources
+        whose colours reach its strip)."""
+        check(self._lib.xp_composer_set_tile(self._h, int(index), int(count)))
+        self._tile = (int(index), int(count))
+
+    def tile_needs(self, n):
+        need = (ctypes.c_int * n)()
+        check(self._lib.xp_composer_tile_needs(self._h, n, need))
+        return [bool(v) for v in need]
+
+    def run_tile_begin(self):
+        """-> the 8 partial sums every rank contributes (all-reduce SUM)."""
+        part = (ctypes.c_double * 8)()
+        check(self._lib.xp_composer_run_tile_begin(self._h, part))
+        return [float(v) for v in part]
+
+    def run_tile_end(self, reduced):
+        red = (ctypes.c_double * 8)(*[float(v) for v in reduced])
+        info = _lib.ComposeInfo()
+        check(self._lib.xp_composer_run_tile_end(self._h, red,
+                                                 ctypes.byref(info)))
+        return self._set_info(info)
+
+    def run_tile(self, reduce=None):
+        """One canvas-tiled run; `reduce` sums a list of 8 floats over the
+        ranks (default: xpano_b200.sharding.all_reduce_sum)."""
+        if reduce is None:
+            from . import sharding
+            reduce = sharding.all_reduce_sum
+        return self.run_tile_end(reduce(self.run_tile_begin()))
+
     def run(self):
         info = _lib.ComposeInfo()
         check(self._lib.xp_composer_run(self._h, ctypes.byref(info)))
+        return self._set_info(info)
+
+    def _set_info(self, info):
         self.info = {
             "width": info.width, "height": info.height, "min_x": info.min_x,
             "min_y": info.min_y, "bpp": info.bpp, "levels": info.levels,
@@ -108,7 +145,10 @@ class Composer:
             "stage_bytes": dict(zip(_STAGES, info.stage_bytes)),
             "stage_launches": dict(zip(_STAGES, info.stage_launches)),
             "warp_bytes": info.warp_bytes,
-            "warp_launches": info.warp_launches}
+            "warp_launches": info.warp_launches,
+            "canvas": (info.canvas_width, info.canvas_height),
+            "tile_x0": info.tile_x0,
+            "window": (info.window_x0, info.window_width)}
         return self.info
 
     def fetch(self, pano=None, mask=None):
