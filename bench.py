@@ -531,11 +531,10 @@ def sharding_group(world, rank):
     return sharding.assign_groups(world, world, rank)[0]
 
 
-def run_ours(args, cfg):
+def init_ranks():
+    """-> (torch, dist, rank, world, local): one process per GPU, NCCL."""
     import torch
     import torch.distributed as dist
-    import xpano_b200 as xb
-
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -559,18 +558,170 @@ def run_ours(args, cfg):
             sys.stdout.flush()
             os.dup2(saved, 1)
             os.close(saved)
-    lib = xb._lib.load()
+    return torch, dist, rank, world, local
 
-    group = sharding_group(world, rank)
-    wl = make_workload(cfg, group, args.masks)
-    ims, Ks, Rs = wl["ims"], wl["Ks"], wl["Rs"]
-    # host sources in pinned memory (e2e leg copies from here every step)
+
+def pin_images(torch, ims):
     pinned = []
     for im in ims:
         t = torch.empty(im.shape, dtype=torch.uint8 if im.dtype == np.uint8
                         else torch.uint16, pin_memory=True)
         t.numpy()[...] = im
         pinned.append(t)
+    return pinned
+
+
+def run_tiled(args, cfg):
+    """ONE panorama over all ranks: canvas strips with recomputed halos
+    (BASELINE.json configs[2]); strong scaling. Every rank
+    computes the seams of the whole canvas, the pyramids / composite /
+    collapse of its strip; the exchange is one all-reduce of 8 doubles."""
+    torch, dist, rank, world, local = init_ranks()
+    import xpano_b200 as xb
+    from xpano_b200 import sharding
+    lib = xb._lib.load()
+    wl = make_workload(cfg, 0, args.masks)     # the same panorama everywhere
+    ims, Ks, Rs = wl["ims"], wl["Ks"], wl["Rs"]
+    pinned = pin_images(torch, ims)
+    host = [t.numpy() for t in pinned]
+    stream = torch.cuda.current_stream().cuda_stream
+    kw = dict(projection=cfg["projection"], warp_scale=cfg["focal"],
+              max_pano_mpx=cfg["max_pano_mpx"], depth=cfg["bpp"],
+              fixed_levels=cfg["fixed_levels"], device=local)
+    comp = xb.Composer(**kw)
+    comp.set_stream(stream)
+    if world > 1:
+        comp.set_tile(rank, world)
+
+    def step():
+        return comp.run_tile() if world > 1 else comp.run()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    comp.set_images(host, Ks, Rs, wl["gains"], wl["seams"])
+    needs = comp.tile_needs(len(ims)) if world > 1 else [True] * len(ims)
+    info = None
+    for _ in range(args.warmup):
+        info = step()
+    barrier()
+    clocks = ClockSampler(local if rank == 0 else None,
+                          20 if world == 1 else 250)
+    launches0 = lib.xp_kernel_launch_count()
+    ev0, ev1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    stage_ms = {}
+    ev0.record()
+    for _ in range(args.steps):
+        info = step()
+        for k, v in info["timing"].items():
+            stage_ms[k] = stage_ms.get(k, 0.0) + v
+        stage_ms["warp"] = stage_ms.get("warp", 0.0) + info["warp_ms"]
+    ev1.record()
+    barrier()
+    launches = lib.xp_kernel_launch_count() - launches0
+    clk = clocks.stop()
+    ms_rank = ev0.elapsed_time(ev1)
+    print(f"[rank {rank}] {ms_rank / args.steps:.3f} ms/step, strip "
+          f"{info['width']}x{info['height']} at x={info['tile_x0']}, window "
+          f"{info['window']}, uploads {sum(needs)}/{len(ims)} sources",
+          file=sys.stderr)
+    ms = sharding.reduce_max(ms_rank)
+    CW, CH = info["canvas"]
+    canvas_mp = CW * CH / 1e6
+    value = canvas_mp * args.steps / (ms / 1e3)
+
+    # e2e: upload of this rank's sources, tiled run, download of its strip
+    dt = torch.uint8 if info["bpp"] == 8 else torch.uint16
+    pano = torch.empty((info["height"], max(info["width"], 1), 3), dtype=dt,
+                       pin_memory=True)
+    mask = torch.empty((info["height"], max(info["width"], 1)),
+                       dtype=torch.uint8, pin_memory=True)
+    h2d = sum(im.nbytes for im, nd in zip(host, needs) if nd)
+    d2h = pano.numpy().nbytes + mask.numpy().nbytes
+    e2e_steps = min(max(args.steps, 3), 8)
+
+    def e2e_step():
+        comp.set_images(host, Ks, Rs, wl["gains"], wl["seams"])
+        step()
+        if info["width"] > 0:
+            comp.fetch(pano.numpy(), mask.numpy())
+
+    e2e_step()
+    barrier()
+    ev0.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    ev1.record()
+    barrier()
+    e2e_ms = sharding.reduce_max(ev0.elapsed_time(ev1))
+    h2d_all = sharding.reduce_sum(h2d)
+    d2h_all = sharding.reduce_sum(d2h)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None,
+        "dtype": "u8" if cfg["bpp"] == 8 else "u16", "data": "synthetic",
+        "config": config_of(cfg, wl), "canvas": [CW, CH],
+        "levels": info["levels"],
+        "resolution_capped": info["resolution_capped"],
+        "sharding": (f"one panorama, {world} canvas strips + recomputed halo "
+                     f"of {sharding.tile_halo(info['levels'])} px, seams "
+                     "replicated, all-reduce of 8 doubles per step")
+        if world > 1 else "1 GPU",
+        "e2e": {"value": canvas_mp * e2e_steps / (e2e_ms / 1e3), "unit": UNIT,
+                "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all,
+                "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps},
+        "gpu_launches": int(launches), "clocks": clk,
+        "rank0": {"ms_per_step": ms_rank / args.steps,
+                  "strip": [info["width"], info["height"]],
+                  "window": list(info["window"]),
+                  "sources_uploaded": int(sum(needs)),
+                  "stages_ms": {k: round(v / args.steps, 3)
+                                for k, v in stage_ms.items()}},
+    }
+    if args.check and world > 1:
+        # the strips of all ranks against the single-GPU panorama (rank 0)
+        sp, sm = comp.fetch() if info["width"] > 0 else (
+            np.zeros((CH, 0, 3), pano.numpy().dtype),
+            np.zeros((CH, 0), np.uint8))
+        gp, gm = sharding.gather_strips(sp, sm, info["tile_x0"], CW)
+        if rank == 0:
+            one = xb.Composer(**kw)
+            one.set_images(host, Ks, Rs, wl["gains"], wl["seams"])
+            one.run()
+            p1, m1 = one.fetch()
+            same = bool(np.array_equal(gp, p1) and np.array_equal(gm, m1))
+            line["tiled_equals_single_gpu"] = same
+            if not same:
+                d = np.abs(gp.astype(np.int32) - p1)
+                line["tiled_diff"] = {
+                    "max": int(d.max()),
+                    "columns": [int(v) for v in
+                                np.nonzero(d.max(axis=(0, 2)))[0][[0, -1]]]}
+    if rank == 0:
+        print(json.dumps(line))
+        if line.get("tiled_equals_single_gpu") is False:
+            raise SystemExit("bench.py: tiled panorama differs from the "
+                             "single-GPU one")
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_ours(args, cfg):
+    torch, dist, rank, world, local = init_ranks()
+    import xpano_b200 as xb
+    lib = xb._lib.load()
+
+    group = sharding_group(world, rank)
+    wl = make_workload(cfg, group, args.masks)
+    ims, Ks, Rs = wl["ims"], wl["Ks"], wl["Rs"]
+    # host sources in pinned memory (e2e leg copies from here every step)
+    pinned = pin_images(torch, ims)
     host = [t.numpy() for t in pinned]
 
     stream = torch.cuda.current_stream().cuda_stream
@@ -833,6 +984,10 @@ def main():
                     choices=["graphcut", "full", "none"],
                     help="seam masks fed to the path (SURVEY.md 8d)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--tiled", action="store_true",
+                    help="N > 1: ONE panorama over all GPUs as canvas strips "
+                    "(strong scaling; use with --config cfg3) instead of one "
+                    "panorama group per GPU")
     ap.add_argument("--cpu-passes", type=int, default=2,
                     help="timed passes of the inline CPU leg (one warm-up "
                     "pass before them when > 1)")
@@ -845,6 +1000,8 @@ def main():
     cfg = CONFIGS[args.config]
     if args.impl == "reference":
         run_reference(args, cfg)
+    elif args.tiled:
+        run_tiled(args, cfg)
     else:
         run_ours(args, cfg)
 

@@ -79,7 +79,7 @@ def test_strips_equal_single_gpu(case):
     pano1, mask1 = one.fetch()
     W, H = info1["width"], info1["height"]
     halo = xb.sharding.tile_halo(levels)
-    assert halo == 6 << levels
+    assert halo == 8 << levels
     for count in ranks:
         strips = _tiled(xb, kw, wl, count)
         x = 0

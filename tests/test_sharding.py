@@ -77,7 +77,7 @@ def test_strip_bounds_partition_the_roi():
                 assert a[1] == b[0] and a[0] <= a[1]
     with pytest.raises(ValueError):
         sharding.strip_bounds(0, 10, 2, 2)
-    assert sharding.tile_halo(5) == 6 * 32 and sharding.tile_halo(7) == 768
+    assert sharding.tile_halo(5) == 8 * 32 and sharding.tile_halo(7) == 1024
 
 
 def _tile_worker(rank, world, port, out):

@@ -328,7 +328,7 @@ struct Composer {
                                   opts.blend.add_levels);
       XP_REQUIRE(lv >= 2 && lv <= kMaxLevels,
                  "canvas tiling needs 2..%d pyramid levels", kMaxLevels);
-      const long margin = (long)tile_halo(lv) + (1L << lv);
+      const long margin = (long)tile_halo(lv) + (2L << lv);
       for (int i = 0; i < n; ++i) {
         const long x0 = plan.rois[4 * i], x1 = x0 + plan.rois[4 * i + 2];
         plan.local[i] =

@@ -81,7 +81,7 @@ def strip_bounds(roi_x: int, roi_w: int, world: int, rank: int):
 
 
 def tile_halo(levels: int) -> int:
-    """Halo (canvas pixels, each side) a strip recomputes: 6 * 2^levels."""
+    """Halo (canvas pixels, each side) a strip recomputes: 8 * 2^levels."""
     from . import _lib
     return int(_lib.load().xp_tile_halo(int(levels)))
 
