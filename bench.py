@@ -151,6 +151,29 @@ def estimate_seams(ims, Ks, Rs, cfg, masks):
 
 
 def make_workload(cfg, group, masks="graphcut"):
+    """Synthetic registered image set + the EstimateSeams
+    inputs. With XP_BENCH_CACHE=<dir> the arrays are kept on disk, so that
+    successive bench runs on one box (N = 1, 2, 4, 8) do not regenerate them;
+    nothing computed by the path itself is cached."""
+    cache = os.environ.get("XP_BENCH_CACHE")
+    if cache:
+        import pickle
+        os.makedirs(cache, exist_ok=True)
+        key = "".join(c if c.isalnum() else "_" for c in cfg["name"])
+        path = os.path.join(cache, f"{key}_g{group}_{masks}.pkl")
+        if os.path.exists(path):
+            with open(path, "rb") as f:
+                return pickle.load(f)
+        wl = _make_workload(cfg, group, masks)
+        tmp = f"{path}.{os.getpid()}.tmp"
+        with open(tmp, "wb") as f:
+            pickle.dump(wl, f, protocol=4)
+        os.replace(tmp, path)
+        return wl
+    return _make_workload(cfg, group, masks)
+
+
+def _make_workload(cfg, group, masks="graphcut"):
     from xpano_b200 import synthetic as co
     hfov = 2 * math.atan(cfg["w"] / 2 / cfg["focal"])
     extra = None

@@ -281,6 +281,43 @@ struct RectSrc {
 // is the squished first source line verbatim (functions.cpp:195-214).
 constexpr int kMaskTileRows = 2 * 8 + 4, kMaskTileCols = 2 * 32 + 4;
 
+// Uniformity of a label window, tested on the aligned 32-bit words that cover
+// its rows (up to three bytes more on either side of a row: a conservative
+// test -- a window that is uniform together with those bytes is uniform).
+// -> 1: every label is `image`, 0: none is, -1: mixed (or undecided).
+// Nearly every tile is uniform; this test replaces the byte-wise staging of
+// 19 x 67 labels for them.
+template <class Src>
+__device__ __forceinline__ int mask_window_uniform(const Src&, int, int, int,
+                                                   int, int) {
+  return -1;
+}
+template <>
+__device__ __forceinline__ int mask_window_uniform<LabelSrc>(
+    const LabelSrc& src, int rmin, int nrows, int cmin, int ncols, int tid) {
+  constexpr int kWords = (kMaskTileCols + 3) / 4 + 1;  // words per row
+  const unsigned pat = (unsigned)src.image * 0x01010101u;
+  const size_t total = (size_t)src.W * src.H;
+  bool all_one = true, all_zero = true;
+  for (int i = tid; i < nrows * kWords; i += 256) {
+    const int r = i / kWords, k = i - r * kWords;
+    const size_t first = (size_t)(rmin + r) * src.W + cmin;
+    const size_t w0 = first >> 2, w1 = (first + ncols - 1) >> 2;
+    const size_t w = w0 + k;
+    if (w <= w1 && 4 * w + 3 < total) {
+      const unsigned v =
+          __ldg(reinterpret_cast<const unsigned*>(src.labels) + w);
+      all_one = all_one && v == pat;
+      all_zero = all_zero && __vcmpeq4(v, pat) == 0u;
+    } else if (w <= w1) {
+      all_one = all_zero = false;  // last bytes of the map: slow path
+    }
+  }
+  all_one = __syncthreads_and(all_one);
+  all_zero = __syncthreads_and(all_zero);
+  return all_one ? 1 : (all_zero ? 0 : -1);
+}
+
 template <class Src>
 __device__ __forceinline__ void mask_shrink_tile(const Src& src,
                                                  const MaskLevel& out,
@@ -295,6 +332,16 @@ __device__ __forceinline__ void mask_shrink_tile(const Src& src,
   const int cmin = pm::clampi(2 * X0 - 4, 0, wmax);
   const int cmax = pm::clampi(2 * (X0 + 31), 0, wmax);
   const int nrows = rmax - rmin + 1, ncols = cmax - cmin + 1;
+  {
+    const int u = mask_window_uniform(src, rmin, nrows, cmin, ncols, tid);
+    if (u >= 0) {
+      const int x = blockIdx.x * 32 + threadIdx.x;
+      const int y = blockIdx.y * 8 + threadIdx.y;
+      if (x < out.w && y < out.h)
+        dst[(size_t)y * out.w + x] = u ? 1.0f : 0.0f;
+      return;
+    }
+  }
   bool all_one = true, all_zero = true;
   for (int i = tid; i < nrows * kMaskTileCols; i += 256) {
     const int r = i / kMaskTileCols, c = i - r * kMaskTileCols;

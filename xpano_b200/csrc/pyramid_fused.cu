@@ -59,6 +59,8 @@ template <int BPP>
 struct PixelSrc : Level0<BPP> {
   typedef typename Level0<BPP>::Px Raw;
   static constexpr int kChannels = 3;
+  // 8-bit pixels: B, G, R in the low three bytes of a 32-bit word
+  static constexpr bool kPackedBytes = BPP == 8;
   __device__ __forceinline__ Raw raw(int, int row, int col) const {
     return row < this->h ? this->px(row, col) : (Raw)0;  // zeroed rows
   }

@@ -70,6 +70,65 @@ __device__ __forceinline__ void shrink_tile(const Src& hi, int hh, int hp,
                        j0 + kShrinkTileW <= lo_pitch;
   const bool fast = __syncthreads_and(mine_ok && cols_ok && ny == kShrinkTileH);
   const int rmin = s_rmin, nrows = s_rmax - rmin + 1;
+  if constexpr (Src::kPackedBytes) {
+    // 8-bit source pixels, no bit-depth conversion: every intermediate of the
+    // five-tap forms is an integer below 2^16 (255 * 16 * 16 = 65280), so the
+    // sums are formed on two channels at a time in 16-bit halves of a word
+    // and converted once; the float arithmetic of the general path has
+    // nothing to round on these values, the results are the same bits.
+    if (fast && hi.mul == 1.0f) {
+      unsigned(*R)[kFastPitch] = reinterpret_cast<unsigned(*)[kFastPitch]>(stage);
+      unsigned(*VE)[kShrinkMaxCols] =
+          reinterpret_cast<unsigned(*)[kShrinkMaxCols]>(&vert[0][0][0]);
+      unsigned(*VO)[kShrinkMaxCols] =
+          reinterpret_cast<unsigned(*)[kShrinkMaxCols]>(&vert[1][0][0]);
+      const int c0 = 2 * j0 - 4 - xs;
+      constexpr int kPer = (kFastRows * kFastCols + 255) / 256;
+      unsigned v[kPer];
+#pragma unroll
+      for (int k = 0; k < kPer; ++k) {
+        const int i = tid + 256 * k;
+        const int r = i / kFastCols, c = i - r * kFastCols;
+        if (i < kFastRows * kFastCols) v[k] = (unsigned)hi.raw(z, rmin + r, c0 + c);
+      }
+#pragma unroll
+      for (int k = 0; k < kPer; ++k) {
+        const int i = tid + 256 * k;
+        const int r = i / kFastCols, c = i - r * kFastCols;
+        if (i < kFastRows * kFastCols) R[r][c] = v[k];
+      }
+      __syncthreads();
+      for (int i = tid; i < kShrinkTileH * kFastCols; i += 256) {
+        const int yy = i / kFastCols, c = i - yy * kFastCols;
+        const unsigned r0 = R[2 * yy][c], r1 = R[2 * yy + 1][c],
+                       r2 = R[2 * yy + 2][c], r3 = R[2 * yy + 3][c],
+                       r4 = R[2 * yy + 4][c];
+        constexpr unsigned kE = 0x00ff00ffu;  // channels 0 and 2
+        const unsigned e = ((r0 & kE) + (r4 & kE)) +
+                           (((r1 & kE) + (r3 & kE)) << 2) + (r2 & kE) * 6u;
+        const unsigned o = (((r0 >> 8) & 0xffu) + ((r4 >> 8) & 0xffu)) +
+                           ((((r1 >> 8) & 0xffu) + ((r3 >> 8) & 0xffu)) << 2) +
+                           ((r2 >> 8) & 0xffu) * 6u;
+        VE[yy][c] = e;
+        VO[yy][c] = o;
+      }
+      __syncthreads();
+      const int jj = tid & (kShrinkTileW - 1);
+#pragma unroll
+      for (int it = 0; it < kShrinkTileH * kShrinkTileW / 256; ++it) {
+        const int yy = (tid / kShrinkTileW) + it * (256 / kShrinkTileW);
+        const unsigned* pe = &VE[yy][2 * jj];
+        const unsigned* po = &VO[yy][2 * jj];
+        const unsigned he = (pe[0] + pe[4]) + (((pe[1] + pe[3]) << 2) + pe[2] * 6u);
+        const unsigned ho = (po[0] + po[4]) + (((po[1] + po[3]) << 2) + po[2] * 6u);
+        const size_t o = (size_t)(y0 + yy) * lo_pitch + j0 + jj;
+        lo[o] = (float)(he & 0xffffu) * (1.0f / 256);
+        lo[chan_stride + o] = (float)ho * (1.0f / 256);
+        lo[2 * chan_stride + o] = (float)(he >> 16) * (1.0f / 256);
+      }
+      return;
+    }
+  }
   if (fast) {
     float(*S)[kFastRows][kFastPitch] =
         reinterpret_cast<float(*)[kFastRows][kFastPitch]>(stage);
@@ -209,6 +268,7 @@ __global__ void __launch_bounds__(256)
 struct PlaneSrc {
   typedef float Raw;
   static constexpr int kChannels = 1;
+  static constexpr bool kPackedBytes = false;
   const float* p;  // channel 0
   int pitch;
   size_t cs;
