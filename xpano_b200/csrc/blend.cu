@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <climits>
 #include <cmath>
+#include <mutex>
 
 #include "blender.h"
 #include "common.h"
@@ -44,13 +45,40 @@ int blend_levels(int n, const int* widths, const int* heights,
 // ---------------------------------------------------------------------------
 // stage timing with CUDA events on the blender's stream
 // ---------------------------------------------------------------------------
+// timing events are kept across blenders (a blender is single-use and
+// records ~40 of them; cudaEventCreate is host time on every panorama)
+namespace {
+struct EventCache {
+  std::mutex mu;
+  std::vector<cudaEvent_t> free_events[16];
+};
+EventCache& event_cache() {
+  static EventCache* c = new EventCache();
+  return *c;
+}
+}  // namespace
+
 StageTimer::~StageTimer() {
-  for (cudaEvent_t e : pool) cudaEventDestroy(e);
+  if (pool.empty()) return;
+  EventCache& c = event_cache();
+  std::lock_guard<std::mutex> lk(c.mu);
+  auto& f = c.free_events[device & 15];
+  f.insert(f.end(), pool.begin(), pool.end());
 }
 cudaEvent_t StageTimer::get() {
   if (used == pool.size()) {
-    cudaEvent_t e;
-    XP_CUDA(cudaEventCreate(&e));
+    if (device < 0) XP_CUDA(cudaGetDevice(&device));
+    cudaEvent_t e = nullptr;
+    {
+      EventCache& c = event_cache();
+      std::lock_guard<std::mutex> lk(c.mu);
+      auto& f = c.free_events[device & 15];
+      if (!f.empty()) {
+        e = f.back();
+        f.pop_back();
+      }
+    }
+    if (!e) XP_CUDA(cudaEventCreate(&e));
     pool.push_back(e);
   }
   return pool[used++];
@@ -107,16 +135,24 @@ Blender::~Blender() {
     if (cur != opts.device) cudaSetDevice(opts.device);
     if (side_stream) cudaStreamSynchronize(side_stream);
     if (aux_stream) cudaStreamSynchronize(aux_stream);
+    if (seam_stream) cudaStreamSynchronize(seam_stream);
+    if (part_side) cudaStreamSynchronize(part_side);
+    if (part_aux) cudaStreamSynchronize(part_aux);
     cudaStreamSynchronize(stream);
     if (cur != opts.device) cudaSetDevice(cur);
   }
-  if (ev_fork) cudaEventDestroy(ev_fork);
-  if (ev_join) cudaEventDestroy(ev_join);
-  if (ev_cover) cudaEventDestroy(ev_cover);
-  if (ev_aux) cudaEventDestroy(ev_aux);
-  if (ev_cls) cudaEventDestroy(ev_cls);
-  if (side_stream) cudaStreamDestroy(side_stream);
-  if (aux_stream) cudaStreamDestroy(aux_stream);
+  // the side streams and events are idle now: back to the per-device cache
+  if (side_stream) {
+    StreamSet set;
+    set.device = opts.device;
+    set.side = side_stream;
+    set.aux = aux_stream;
+    set.ev[0] = ev_fork, set.ev[1] = ev_join, set.ev[2] = ev_cover;
+    set.ev[3] = ev_aux, set.ev[4] = ev_cls, set.ev[5] = ev_seam;
+    set.seam = seam_stream, set.part_side = part_side, set.part_aux = part_aux;
+    set.seam_sms = seam_sms, set.side_sms = side_sms;
+    release_stream_set(set);
+  }
   if (own_stream) cudaStreamDestroy(own_stream);
 }
 
@@ -128,20 +164,20 @@ void Blender::ensure_device() {
     stream = own_stream;
   }
   if (!side_stream) {
-    side_stream = create_stream(false);
-    XP_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
-    XP_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
-    XP_CUDA(cudaEventCreateWithFlags(&ev_cover, cudaEventDisableTiming));
-    aux_stream = create_stream(false);
-    XP_CUDA(cudaEventCreateWithFlags(&ev_aux, cudaEventDisableTiming));
-    XP_CUDA(cudaEventCreateWithFlags(&ev_cls, cudaEventDisableTiming));
+    const StreamSet set = acquire_stream_set(opts.device);
+    side_stream = set.side;
+    aux_stream = set.aux;
+    ev_fork = set.ev[0], ev_join = set.ev[1], ev_cover = set.ev[2];
+    ev_aux = set.ev[3], ev_cls = set.ev[4], ev_seam = set.ev[5];
+    seam_stream = set.seam, part_side = set.part_side, part_aux = set.part_aux;
+    seam_sms = set.seam_sms, side_sms = set.side_sms;
   }
 }
 
 Fed* Blender::new_fed(int w, int h, int depth, int tl_x, int tl_y) {
   XP_REQUIRE(w > 0 && h > 0, "feed: empty image");
   XP_REQUIRE(depth == 8 || depth == 16, "feed: depth must be 8 or 16");
-  XP_REQUIRE((size_t)w * h < (1ull << 32), "feed: image too large");
+  XP_REQUIRE(((size_t)w + 3) * h < (1ull << 32), "feed: image too large");
   XP_REQUIRE(!blended, "blender instances are single-use (blenders.cc)");
   if (!fed.empty())
     XP_REQUIRE(fed[0]->depth == depth,
@@ -150,11 +186,12 @@ Fed* Blender::new_fed(int w, int h, int depth, int tl_x, int tl_y) {
   ensure_device();
   std::unique_ptr<Fed> f(new Fed());
   f->w = w;
+  f->pitch = (w + 3) & ~3;
   f->h = h;
   f->depth = depth;
   f->xpos = tl_x;
   f->ypos = tl_y;
-  f->data.reserve((size_t)w * h * 4 * (depth / 8));
+  f->data.reserve((size_t)f->pitch * h * 4 * (depth / 8));
   fed.push_back(std::move(f));
   return fed.back().get();
 }
@@ -186,7 +223,7 @@ void Blender::feed(const void* data, size_t stride, const uint8_t* mask,
     }
   }
   launch_pack_bgra(dsrc, dpitch, dmask, mpitch, w, h, depth, spp, f->data.p,
-                   stream);
+                   f->pitch, stream);
   XP_CUDA(cudaStreamSynchronize(stream));
 }
 

@@ -54,9 +54,10 @@ struct MaskLevel {
 // box = (INT_MAX, INT_MAX, -1, -1), count = 0 for n images
 void launch_trim_init(int* d_bbox, unsigned long long* d_opaque, int n,
                       cudaStream_t s);
-void launch_trim(const void* const* data, const int* w, const int* h, int n,
-                 int bpp, int* d_bbox, unsigned long long* d_opaque_count,
-                 cudaStream_t s);
+// pitch: pixels per row of each image
+void launch_trim(const void* const* data, const int* w, const int* h,
+                 const int* pitch, int n, int bpp, int* d_bbox,
+                 unsigned long long* d_opaque_count, cudaStream_t s);
 // cover word of every canvas pixel in one pass (format chosen by n, see
 // scan_problems.h Cov<>)
 void launch_cover(void* cover, int cover_bytes, int W, int H,
@@ -66,6 +67,8 @@ void launch_seams(const void* cover, int cover_bytes, int n_images, int W,
                   int H, int reverse, uint32_t* bwd, uint32_t* fwd, uint8_t* labels,
                   int* counter, uint8_t* flags, cudaStream_t s,
                   cudaStream_t beside = nullptr, cudaEvent_t ev = nullptr);
+// blocks (= SMs) the wavefront launches of the calling thread may use; 0: all
+void set_wavefront_blocks(int n);
 // bytes of tile flags launch_seams / launch_inpaint need
 size_t wavefront_flag_bytes(int n_bands, int max_w);
 void launch_seam_unpack(const uint32_t* in, size_t n, uint64_t* out,
@@ -141,9 +144,11 @@ void launch_inpaint_gather_tiles(const InpaintJob* d_jobs,
                                  const InpaintBandRef* d_bands, int n_bands,
                                  int max_w, int bpp, const uint8_t* scratch,
                                  cudaStream_t s);
+// d_tmaps: 128 bytes of device scratch per image for the TMA tensor maps of
+// the sources (written through `mbox`); null: plain loads only
 void launch_shrink0_batch(const ImgDev* im, int bpp, float mul,
                           const PyrGeom* g, float* const* pyr, int n,
-                          cudaStream_t s);
+                          void* d_tmaps, Mailbox* mbox, cudaStream_t s);
 void launch_shrink_batch(const PyrGeom* g, float* const* pyr, int n, int level,
                          int channels, cudaStream_t s);
 void launch_shrink0(const ImgDev& im, int bpp, float mul, const PyrGeom& g,
@@ -166,6 +171,6 @@ void launch_labels_to_i32(const uint8_t* labels, size_t n, int32_t* out,
 // BGR (+mask) -> 4-sample interleaved (blenders.cc:99-112)
 void launch_pack_bgra(const void* bgr, size_t bgr_pitch, const uint8_t* mask,
                       size_t mask_pitch, int w, int h, int depth, int spp_in,
-                      void* out, cudaStream_t s);
+                      void* out, int out_pitch, cudaStream_t s);
 
 }  // namespace xp

@@ -11,7 +11,10 @@ namespace xp {
 
 struct Fed {
   int w = 0, h = 0, depth = 8, xpos = 0, ypos = 0;
-  DevBuf data;  // w*h pixels of 4 samples (B, G, R, alpha)
+  // Row pitch in pixels: w rounded up to a multiple of 4, so that rows start
+  // on 16-byte boundaries (what a TMA tensor map over the pixels needs).
+  int pitch = 0;
+  DevBuf data;  // pitch*h pixels of 4 samples (B, G, R, alpha)
 };
 
 struct StageTimer {
@@ -23,6 +26,7 @@ struct StageTimer {
   std::vector<Span> spans;
   std::vector<cudaEvent_t> pool;
   size_t used = 0;
+  int device = -1;  // the device the events belong to
   cudaStream_t s = nullptr;
   ~StageTimer();
   cudaEvent_t get();
@@ -38,7 +42,11 @@ struct Blender {
   cudaStream_t side_stream = nullptr;  // inpaint runs beside the seam passes
   cudaStream_t aux_stream = nullptr;   // cover-only statistics
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_cover = nullptr,
-              ev_aux = nullptr, ev_cls = nullptr;
+              ev_aux = nullptr, ev_cls = nullptr, ev_seam = nullptr;
+  // SM partition (common.h StreamSet): the seam chain on its own SMs, the work
+  // beside it on the rest; null when the device is not partitioned
+  cudaStream_t seam_stream = nullptr, part_side = nullptr, part_aux = nullptr;
+  int seam_sms = 0, side_sms = 0;
   bool external_stream = false;
   bool device_ready = false;  // ensure_device() ran: streams may hold work
   int roi[4] = {0, 0, 0, 0};
@@ -54,7 +62,7 @@ struct Blender {
   std::vector<unsigned long long> transparent;
   PyrGeom out_g;
   DevBuf d_bbox, d_transparent, d_imgs, d_stats, d_jobs, d_bands, d_counter,
-      d_progress, d_flags_inp, d_partials, d_sums, d_mask_jobs;
+      d_progress, d_flags_inp, d_partials, d_sums, d_mask_jobs, d_tmaps;
   DevBuf cover, seam_bwd, seam_fwd, labels, full_mask, xor_mask;
   std::vector<DevBuf> inp_fwd, inp_bwd;  // per image (empty if no holes)
   DevBuf img_pyr, mask_buf, out_pyr, planes, bgr;

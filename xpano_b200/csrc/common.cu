@@ -1,5 +1,7 @@
 #include "common.h"
 
+#include <cuda.h>
+
 #include <map>
 #include <mutex>
 #include <thread>
@@ -203,6 +205,44 @@ void select_device(int device) {
   XP_CUDA(cudaSetDevice(device));
 }
 
+bool make_tensor_map_2d(void* out, int elem_bytes, const void* base,
+                        unsigned long long dim0, unsigned long long dim1,
+                        unsigned long long stride_bytes, unsigned box0,
+                        unsigned box1) {
+  typedef CUresult (*EncodeFn)(
+      CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+      const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+      CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+      CUtensorMapFloatOOBfill);
+  static EncodeFn encode = [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault,
+                                &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      fn = nullptr;
+    }
+    return reinterpret_cast<EncodeFn>(fn);
+  }();
+  if (!encode) return false;
+  if (((uintptr_t)base & 15) || (stride_bytes & 15) ||
+      ((size_t)box0 * elem_bytes & 15) || box0 > 256 || box1 > 256)
+    return false;
+  const cuuint64_t dims[2] = {dim0, dim1};
+  const cuuint64_t strides[1] = {stride_bytes};
+  const cuuint32_t box[2] = {box0, box1};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUtensorMapDataType type = elem_bytes == 8
+                                       ? CU_TENSOR_MAP_DATA_TYPE_UINT64
+                                       : CU_TENSOR_MAP_DATA_TYPE_UINT32;
+  return encode(static_cast<CUtensorMap*>(out), type, 2,
+                const_cast<void*>(base), dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 int sm_count() {
   static std::atomic<int> cached[16];
   int dev = 0;
@@ -245,6 +285,144 @@ cudaStream_t create_stream(bool high_priority) {
   XP_CUDA(cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking,
                                        high_priority ? greatest : least));
   return s;
+}
+
+namespace {
+struct StreamSetCache {
+  std::mutex mu;
+  std::vector<StreamSet> free_sets;
+};
+StreamSetCache& stream_set_cache() {
+  static StreamSetCache* c = new StreamSetCache();  // outlives static dtors
+  return *c;
+}
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// SM partition. The seam recurrences are latency chains (one compute warp per
+// SM, every step waits for the previous one); a streaming kernel that shares
+// their SMs takes issue slots from that warp and stretches every step, while
+// the streaming kernels themselves do not need all 148 SMs to saturate HBM.
+// Two green contexts (CUDA 12.4 driver API: cuDevSmResourceSplitByCount /
+// cuGreenCtxCreate) split the device once: `seam_sms` SMs for the seam chain,
+// the rest for what runs beside it. Streams created in a green context accept
+// ordinary runtime launches and share the primary context's memory.
+// XP_SEAM_SMS=<n> sets the split (0 = no partition).
+// ---------------------------------------------------------------------------
+namespace {
+struct SmPartition {
+  bool tried = false, ok = false;
+  CUgreenCtx ctx_a = nullptr, ctx_b = nullptr;
+  int sms_a = 0, sms_b = 0;
+  CUresult (*stream_create)(CUstream*, CUgreenCtx, unsigned, int) = nullptr;
+};
+SmPartition g_part[16];
+std::mutex g_part_mu;
+
+template <class F>
+bool driver_fn(const char* name, F& fn) {
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess || !p) {
+    cudaGetLastError();
+    return false;
+  }
+  fn = reinterpret_cast<F>(p);
+  return true;
+}
+
+SmPartition& sm_partition(int device) {
+  std::lock_guard<std::mutex> lk(g_part_mu);
+  SmPartition& P = g_part[device & 15];
+  if (P.tried) return P;
+  P.tried = true;
+  int want = 96;
+  if (const char* e = getenv("XP_SEAM_SMS")) want = atoi(e);
+  if (want <= 0) return P;
+  CUresult (*get_res)(CUdevice, CUdevResource*, CUdevResourceType) = nullptr;
+  CUresult (*split)(CUdevResource*, unsigned*, const CUdevResource*,
+                    CUdevResource*, unsigned, unsigned) = nullptr;
+  CUresult (*gen_desc)(CUdevResourceDesc*, CUdevResource*, unsigned) = nullptr;
+  CUresult (*ctx_create)(CUgreenCtx*, CUdevResourceDesc, CUdevice, unsigned) =
+      nullptr;
+  CUresult (*dev_get)(CUdevice*, int) = nullptr;
+  if (!driver_fn("cuDeviceGetDevResource", get_res) ||
+      !driver_fn("cuDevSmResourceSplitByCount", split) ||
+      !driver_fn("cuDevResourceGenerateDesc", gen_desc) ||
+      !driver_fn("cuGreenCtxCreate", ctx_create) ||
+      !driver_fn("cuGreenCtxStreamCreate", P.stream_create) ||
+      !driver_fn("cuDeviceGet", dev_get))
+    return P;
+  CUdevice dev;
+  if (dev_get(&dev, device) != CUDA_SUCCESS) return P;
+  CUdevResource all, part_a, part_b;
+  if (get_res(dev, &all, CU_DEV_RESOURCE_TYPE_SM) != CUDA_SUCCESS) return P;
+  if ((int)all.sm.smCount < want + 16) return P;
+  unsigned groups = 1;
+  if (split(&part_a, &groups, &all, &part_b, 0, (unsigned)want) !=
+          CUDA_SUCCESS ||
+      groups != 1 || part_b.sm.smCount < 8)
+    return P;
+  CUdevResourceDesc da, db;
+  if (gen_desc(&da, &part_a, 1) != CUDA_SUCCESS ||
+      gen_desc(&db, &part_b, 1) != CUDA_SUCCESS)
+    return P;
+  if (ctx_create(&P.ctx_a, da, dev, CU_GREEN_CTX_DEFAULT_STREAM) !=
+          CUDA_SUCCESS ||
+      ctx_create(&P.ctx_b, db, dev, CU_GREEN_CTX_DEFAULT_STREAM) !=
+          CUDA_SUCCESS)
+    return P;
+  P.sms_a = (int)part_a.sm.smCount;
+  P.sms_b = (int)part_b.sm.smCount;
+  P.ok = true;
+  return P;
+}
+}  // namespace
+
+StreamSet acquire_stream_set(int device) {
+  StreamSetCache& c = stream_set_cache();
+  {
+    std::lock_guard<std::mutex> lk(c.mu);
+    for (size_t i = 0; i < c.free_sets.size(); ++i)
+      if (c.free_sets[i].device == device) {
+        StreamSet s = c.free_sets[i];
+        c.free_sets.erase(c.free_sets.begin() + i);
+        return s;
+      }
+  }
+  StreamSet s;
+  s.device = device;
+  s.side = create_stream(false);
+  s.aux = create_stream(false);
+  for (cudaEvent_t& e : s.ev)
+    XP_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  SmPartition& P = sm_partition(device);
+  if (P.ok) {
+    int least = 0, greatest = 0;
+    XP_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    CUstream a = nullptr, b1 = nullptr, b2 = nullptr;
+    if (P.stream_create(&a, P.ctx_a, CU_STREAM_NON_BLOCKING, greatest) ==
+            CUDA_SUCCESS &&
+        P.stream_create(&b1, P.ctx_b, CU_STREAM_NON_BLOCKING, least) ==
+            CUDA_SUCCESS &&
+        P.stream_create(&b2, P.ctx_b, CU_STREAM_NON_BLOCKING, least) ==
+            CUDA_SUCCESS) {
+      s.seam = a;
+      s.part_side = b1;
+      s.part_aux = b2;
+      s.seam_sms = P.sms_a;
+      s.side_sms = P.sms_b;
+    }
+  }
+  return s;
+}
+
+void release_stream_set(const StreamSet& s) {
+  if (!s.side) return;
+  StreamSetCache& c = stream_set_cache();
+  std::lock_guard<std::mutex> lk(c.mu);
+  c.free_sets.push_back(s);
 }
 
 namespace {

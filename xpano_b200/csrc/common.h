@@ -142,6 +142,24 @@ struct DevBuf {
 // have blocks pending, the main chain's are placed first.
 cudaStream_t create_stream(bool high_priority);
 
+// The side streams and events of a blender: blenders are single-use (one per
+// panorama, like the reference's), and creating two streams and five events
+// costs more host time than a whole pyramid level; sets are kept per device
+// and handed out again. A set is returned only after its streams were
+// synchronised.
+struct StreamSet {
+  int device = -1;
+  cudaStream_t side = nullptr, aux = nullptr;
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  // SM partition (green contexts, see sm_partition): a stream that runs on
+  // the seam partition only, and two that run on the rest of the device.
+  // Null when the device is not partitioned.
+  cudaStream_t seam = nullptr, part_side = nullptr, part_aux = nullptr;
+  int seam_sms = 0, side_sms = 0;
+};
+StreamSet acquire_stream_set(int device);
+void release_stream_set(const StreamSet& s);
+
 // Wait for a stream with the calling thread blocked in the OS instead of
 // spinning in the driver: for the long waits on bulk copies (uploads,
 // downloads) that overlap another thread's kernel launches.
@@ -154,6 +172,18 @@ void sync_blocking(cudaStream_t s);
 // Overrides: XP_HOST_THREADS, XP_SYNC_BLOCK.
 int host_worker_threads(int wanted);
 void sync_stream(cudaStream_t s);
+
+// TMA tensor map (cuTensorMapEncodeTiled, reached through
+// cudaGetDriverEntryPoint: no link-time dependency on libcuda) over a
+// row-major 2-D array of 4- or 8-byte elements: dim0 elements per row, dim1
+// rows, `stride_bytes` between rows (a multiple of 16, base 16-byte aligned),
+// box0 x box1 elements per copy (box0 * elem_bytes a multiple of 16), no
+// swizzle, zero fill outside the array. `out` is 128 bytes (a CUtensorMap).
+// Returns false where the driver refuses (the callers keep a plain-load path).
+bool make_tensor_map_2d(void* out, int elem_bytes, const void* base,
+                        unsigned long long dim0, unsigned long long dim1,
+                        unsigned long long stride_bytes, unsigned box0,
+                        unsigned box1);
 
 inline int div_up(int a, int b) { return (a + b - 1) / b; }
 inline size_t div_up(size_t a, size_t b) { return (a + b - 1) / b; }

@@ -123,6 +123,8 @@ void launch_shrink_batch(const PyrGeom* g, float* const* pyr, int n, int level,
   for (int i0 = 0; i0 < n; i0 += kShrinkBatch) {
     const int m = std::min(kShrinkBatch, n - i0);
     ShrinkBatch<PlaneSrc> batch;
+    batch.tma = 0;
+    batch.tmaps = nullptr;
     int gx = 0, gy = 0;
     for (int k = 0; k < m; ++k) {
       const PyrGeom& G = g[i0 + k];
@@ -866,7 +868,7 @@ template <typename T>
 __global__ void pack_bgra_kernel(const T* __restrict__ src, size_t src_pitch,
                                  const uint8_t* __restrict__ mask,
                                  size_t mask_pitch, int w, int h, int spp_in,
-                                 T* __restrict__ out) {
+                                 T* __restrict__ out, int out_pitch) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y * blockDim.y + threadIdx.y;
   if (x >= w || y >= h) return;
@@ -875,7 +877,7 @@ __global__ void pack_bgra_kernel(const T* __restrict__ src, size_t src_pitch,
   T a = amax;
   if (spp_in == 4) a = s[3];
   if (mask) a = mask[(size_t)y * mask_pitch + x] != 0 ? amax : (T)0;
-  T* d = out + ((size_t)y * w + x) * 4;
+  T* d = out + ((size_t)y * out_pitch + x) * 4;
   d[0] = s[0];
   d[1] = s[1];
   d[2] = s[2];
@@ -884,17 +886,17 @@ __global__ void pack_bgra_kernel(const T* __restrict__ src, size_t src_pitch,
 
 void launch_pack_bgra(const void* bgr, size_t bgr_pitch, const uint8_t* mask,
                       size_t mask_pitch, int w, int h, int depth, int spp_in,
-                      void* out, cudaStream_t s) {
+                      void* out, int out_pitch, cudaStream_t s) {
   dim3 b(32, 8);
   dim3 g = grid3(w, h, 1, b);
   if (depth == 8)
     pack_bgra_kernel<uint8_t><<<g, b, 0, s>>>((const uint8_t*)bgr, bgr_pitch,
                                               mask, mask_pitch, w, h, spp_in,
-                                              (uint8_t*)out);
+                                              (uint8_t*)out, out_pitch);
   else
     pack_bgra_kernel<uint16_t><<<g, b, 0, s>>>(
         (const uint16_t*)bgr, bgr_pitch / 2, mask, mask_pitch, w, h, spp_in,
-        (uint16_t*)out);
+        (uint16_t*)out, out_pitch);
   XP_LAUNCHED();
 }
 

@@ -73,10 +73,15 @@ struct PixelSrc : Level0<BPP> {
 // up to kShrinkBatch images
 template <int BPP>
 static void shrink0_batch_t(const ImgDev* im, float mul, const PyrGeom* g,
-                            float* const* pyr, int n, cudaStream_t s) {
+                            float* const* pyr, int n, void* d_tmaps,
+                            Mailbox* mbox, cudaStream_t s) {
   for (int i0 = 0; i0 < n; i0 += kShrinkBatch) {
     const int m = std::min(kShrinkBatch, n - i0);
     ShrinkBatch<PixelSrc<BPP>> batch;
+    batch.tma = 0;
+    batch.tmaps = static_cast<const TensorMapBytes*>(d_tmaps) + i0;
+    TensorMapBytes host_maps[kShrinkBatch];
+    memset(host_maps, 0, sizeof(host_maps));
     int gx = 0, gy = 0;
     for (int k = 0; k < m; ++k) {
       const PyrGeom& G = g[i0 + k];
@@ -89,7 +94,22 @@ static void shrink0_batch_t(const ImgDev* im, float mul, const PyrGeom* g,
           G.channel_floats};
       gx = std::max(gx, div_up(L.pitch, kShrinkTileW));
       gy = std::max(gy, div_up(L.h, kShrinkTileH));
+      // 8-bit pixels: interior tiles are staged by TMA (one bulk tensor copy
+      // of 2*64+4 x 2*8+3 pixels per block) where the driver gives a map
+      if (BPP == 8 && mul == 1.0f && d_tmaps && mbox &&
+          getenv("XP_NO_TMA") == nullptr) {
+        const ImgDev& d = im[i0 + k];
+        if (make_tensor_map_2d(host_maps[k].b, 4, d.data,
+                               (unsigned long long)d.tiff_w,
+                               (unsigned long long)d.tiff_h,
+                               (unsigned long long)d.tiff_w * 4,
+                               2 * kShrinkTileW + 8, 2 * kShrinkTileH + 3))
+          batch.tma |= 1u << k;
+      }
     }
+    if (batch.tma)
+      mbox->to_device(const_cast<TensorMapBytes*>(batch.tmaps), host_maps,
+                      sizeof(TensorMapBytes) * m, s);
     for (int k = m; k < kShrinkBatch; ++k) batch.job[k] = batch.job[0];
     shrink_batch_kernel<<<dim3(gx, gy, m), 256, 0, s>>>(batch, 1);
     XP_LAUNCHED();
@@ -98,11 +118,11 @@ static void shrink0_batch_t(const ImgDev* im, float mul, const PyrGeom* g,
 
 void launch_shrink0_batch(const ImgDev* im, int bpp, float mul,
                           const PyrGeom* g, float* const* pyr, int n,
-                          cudaStream_t s) {
+                          void* d_tmaps, Mailbox* mbox, cudaStream_t s) {
   if (bpp == 8)
-    shrink0_batch_t<8>(im, mul, g, pyr, n, s);
+    shrink0_batch_t<8>(im, mul, g, pyr, n, d_tmaps, mbox, s);
   else
-    shrink0_batch_t<16>(im, mul, g, pyr, n, s);
+    shrink0_batch_t<16>(im, mul, g, pyr, n, d_tmaps, mbox, s);
 }
 
 void launch_shrink0(const ImgDev& im, int bpp, float mul, const PyrGeom& g,

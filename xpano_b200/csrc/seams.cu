@@ -235,6 +235,11 @@ static void launch_classify(const P& prob, uint8_t* scratch, int flag_pitch,
   XP_LAUNCHED();
 }
 
+// Upper bound of the blocks a wavefront launch uses: the SMs of the partition
+// its stream runs on (one block per SM, see below). 0: the whole device.
+static thread_local int t_wavefront_blocks = 0;
+void set_wavefront_blocks(int n) { t_wavefront_blocks = n; }
+
 template <class P>
 static void launch_wavefront(const P& prob, int* counter, uint8_t* scratch,
                              int flag_pitch, cudaStream_t s,
@@ -255,7 +260,8 @@ static void launch_wavefront(const P& prob, int* counter, uint8_t* scratch,
   // scheduler with the first block's compute warp and slow every step of it.
   // Items are short, so one per SM (148) in flight cover the active front.
   const int blocks = (int)std::min<size_t>(
-      wf::max_items(prob.n_bands, flag_pitch), (size_t)sm_count());
+      wf::max_items(prob.n_bands, flag_pitch),
+      (size_t)(t_wavefront_blocks > 0 ? t_wavefront_blocks : sm_count()));
   wavefront_kernel<P><<<blocks, 32 * wf::kWarpsPerBand, smem, s>>>(
       prob, counter, w.items, w.first + prob.n_bands, w.flags, flag_pitch);
   XP_LAUNCHED();
@@ -268,7 +274,7 @@ static void launch_wavefront(const P& prob, int* counter, uint8_t* scratch,
 // all images of a blend in one launch: blockIdx.y = image
 struct TrimBatch {
   const void* data[kMaxImages + 1];
-  int w[kMaxImages + 1], h[kMaxImages + 1];
+  int w[kMaxImages + 1], h[kMaxImages + 1], pitch[kMaxImages + 1];
 };
 
 template <int BPP>
@@ -277,6 +283,7 @@ __global__ void trim_kernel(const __grid_constant__ TrimBatch batch,
                             unsigned long long* opaque_count_all) {
   const void* data = batch.data[blockIdx.y];
   const int w = batch.w[blockIdx.y], h = batch.h[blockIdx.y];
+  const int pitch = batch.pitch[blockIdx.y];
   int* bbox = bbox_all + 4 * blockIdx.y;
   unsigned long long* opaque_count = opaque_count_all + blockIdx.y;
   int minx = INT_MAX, miny = INT_MAX, maxx = -1, maxy = -1, cnt = 0;
@@ -285,7 +292,7 @@ __global__ void trim_kernel(const __grid_constant__ TrimBatch batch,
   const int warps = (gridDim.x * blockDim.x) >> 5;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   for (int y = warp; y < h; y += warps) {
-    const size_t row = (size_t)y * w;
+    const size_t row = (size_t)y * pitch;
     bool any = false;
     // eight independent loads per lane in flight
     for (int x0 = lane; x0 < w; x0 += 32 * 8) {
@@ -342,15 +349,16 @@ void launch_trim_init(int* d_bbox, unsigned long long* d_opaque, int n,
 
 // trim boxes and opaque counts of n images (d_bbox: 4 ints, d_opaque_count:
 // one word per image; both initialised by launch_trim_init)
-void launch_trim(const void* const* data, const int* w, const int* h, int n,
-                 int bpp, int* d_bbox, unsigned long long* d_opaque_count,
-                 cudaStream_t s) {
+void launch_trim(const void* const* data, const int* w, const int* h,
+                 const int* pitch, int n, int bpp, int* d_bbox,
+                 unsigned long long* d_opaque_count, cudaStream_t s) {
   TrimBatch batch;
   int max_h = 0;
   for (int i = 0; i < n; ++i) {
     batch.data[i] = data[i];
     batch.w[i] = w[i];
     batch.h[i] = h[i];
+    batch.pitch[i] = pitch[i];
     max_h = std::max(max_h, h[i]);
   }
   // rows are strided over gridDim.x blocks of eight warps

@@ -21,20 +21,69 @@ constexpr int kShrinkTileW = 64, kShrinkTileH = 8;
 constexpr int kShrinkMaxCols = 2 * kShrinkTileW + 6;  // 2*(W-1) + 4 + 1 (+xs)
 constexpr int kShrinkMaxRows = 2 * kShrinkTileH + 4;
 
+// ---- TMA / mbarrier primitives (sm_90+: cp.async.bulk.tensor) -------------
+// One elected thread arms an mbarrier with the byte count of the box and
+// issues the bulk tensor copy; the copy engine walks the rows of the box,
+// writes them densely into shared memory and completes the transaction on
+// the barrier, which every thread of the block then waits on. No per-element
+// address arithmetic, no per-thread loads.
+__device__ __forceinline__ unsigned smem_addr(const void* p) {
+  return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)),
+               "r"(count)
+               : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar,
+                                               unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(
+                   smem_addr(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tmap,
+                                            int x, int y,
+                                            unsigned long long* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::"
+      "bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(smem_addr(smem_dst)),
+      "l"(tmap), "r"(x), "r"(y), "r"(smem_addr(bar))
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar,
+                                          unsigned parity) {
+  unsigned done;
+  do {
+    asm volatile(
+        "{\n.reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n}"
+        : "=r"(done)
+        : "r"(smem_addr(bar)), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+
+// `tmap`: a CUtensorMap over the source pixels (2-D, 32-bit elements, box
+// kFastPitch x kFastRows) in global memory, or null.
 template <class Src>
 __device__ __forceinline__ void shrink_tile(const Src& hi, int hh, int hp,
                                             int xs, int ys,
                                             float* __restrict__ lo, int lo_h,
                                             int lo_pitch, size_t chan_stride,
-                                            int bx, int by, int z) {
+                                            int bx, int by, int z,
+                                            const void* tmap = nullptr) {
   typedef typename Src::Raw Raw;
   constexpr int NC = Src::kChannels;
   constexpr int kFastRows = 2 * kShrinkTileH + 3, kFastCols = 2 * kShrinkTileW + 3;
   constexpr int kFastPitch = kFastCols + 1;
   constexpr size_t kRawBytes = sizeof(Raw) * kShrinkMaxRows * kShrinkMaxCols;
   constexpr size_t kFastBytes = sizeof(float) * NC * kFastRows * kFastPitch;
-  __shared__ __align__(16) unsigned char
+  __shared__ __align__(128) unsigned char
       stage[kRawBytes > kFastBytes ? kRawBytes : kFastBytes];
+  __shared__ __align__(8) unsigned long long tma_bar;
   Raw* tile = reinterpret_cast<Raw*>(stage);
   __shared__ float vert[NC][kShrinkTileH][kShrinkMaxCols];
   __shared__ pm::VForm forms[kShrinkTileH];
@@ -77,32 +126,58 @@ __device__ __forceinline__ void shrink_tile(const Src& hi, int hh, int hp,
     // and converted once; the float arithmetic of the general path has
     // nothing to round on these values, the results are the same bits.
     if (fast && hi.mul == 1.0f) {
-      unsigned(*R)[kFastPitch] = reinterpret_cast<unsigned(*)[kFastPitch]>(stage);
+      // staged source pixels: kFastRows rows of kTmaPitch words; the window
+      // starts `off` words into a row (TMA boxes start on 16-byte boundaries
+      // of global memory: the innermost coordinate is rounded down to a
+      // multiple of four pixels and the box is four pixels wider)
+      constexpr int kTmaPitch = (kFastCols + 3 + 3) & ~3;  // 136
+      unsigned* R = reinterpret_cast<unsigned*>(stage);
       unsigned(*VE)[kShrinkMaxCols] =
           reinterpret_cast<unsigned(*)[kShrinkMaxCols]>(&vert[0][0][0]);
       unsigned(*VO)[kShrinkMaxCols] =
           reinterpret_cast<unsigned(*)[kShrinkMaxCols]>(&vert[1][0][0]);
       const int c0 = 2 * j0 - 4 - xs;
-      constexpr int kPer = (kFastRows * kFastCols + 255) / 256;
-      unsigned v[kPer];
+      static_assert(kTmaPitch * 4 % 16 == 0, "TMA box rows are 16-byte units");
+      static_assert(kTmaPitch == 2 * kShrinkTileW + 8, "box of the tensor map");
+      static_assert(sizeof(stage) >= sizeof(unsigned) * kFastRows * kTmaPitch,
+                    "the box fits the staging tile");
+      int off = 0;
+      // the box must not reach the columns right of the image, which the
+      // plain path replicates (pyramid.cpp:268-330)
+      if (tmap != nullptr && c0 + kFastCols - 1 <= hi.w - 1) {
+        const int gx = hi.left + c0;
+        off = gx & 3;
+        if (tid == 0) mbar_init(&tma_bar, 1);
+        __syncthreads();
+        if (tid == 0) {
+          mbar_expect_tx(&tma_bar, sizeof(unsigned) * kFastRows * kTmaPitch);
+          tma_load_2d(stage, tmap, gx - off, hi.top + rmin, &tma_bar);
+        }
+        mbar_wait(&tma_bar, 0);
+      } else {
+        constexpr int kPer = (kFastRows * kFastCols + 255) / 256;
+        unsigned v[kPer];
 #pragma unroll
-      for (int k = 0; k < kPer; ++k) {
-        const int i = tid + 256 * k;
-        const int r = i / kFastCols, c = i - r * kFastCols;
-        if (i < kFastRows * kFastCols) v[k] = (unsigned)hi.raw(z, rmin + r, c0 + c);
-      }
+        for (int k = 0; k < kPer; ++k) {
+          const int i = tid + 256 * k;
+          const int r = i / kFastCols, c = i - r * kFastCols;
+          if (i < kFastRows * kFastCols)
+            v[k] = (unsigned)hi.raw(z, rmin + r, c0 + c);
+        }
 #pragma unroll
-      for (int k = 0; k < kPer; ++k) {
-        const int i = tid + 256 * k;
-        const int r = i / kFastCols, c = i - r * kFastCols;
-        if (i < kFastRows * kFastCols) R[r][c] = v[k];
+        for (int k = 0; k < kPer; ++k) {
+          const int i = tid + 256 * k;
+          const int r = i / kFastCols, c = i - r * kFastCols;
+          if (i < kFastRows * kFastCols) R[r * kTmaPitch + c] = v[k];
+        }
+        __syncthreads();
       }
-      __syncthreads();
       for (int i = tid; i < kShrinkTileH * kFastCols; i += 256) {
         const int yy = i / kFastCols, c = i - yy * kFastCols;
-        const unsigned r0 = R[2 * yy][c], r1 = R[2 * yy + 1][c],
-                       r2 = R[2 * yy + 2][c], r3 = R[2 * yy + 3][c],
-                       r4 = R[2 * yy + 4][c];
+        const unsigned* col = R + (2 * yy) * kTmaPitch + c + off;
+        const unsigned r0 = col[0], r1 = col[kTmaPitch],
+                       r2 = col[2 * kTmaPitch], r3 = col[3 * kTmaPitch],
+                       r4 = col[4 * kTmaPitch];
         constexpr unsigned kE = 0x00ff00ffu;  // channels 0 and 2
         const unsigned e = ((r0 & kE) + (r4 & kE)) +
                            (((r1 & kE) + (r3 & kE)) << 2) + (r2 & kE) * 6u;
@@ -246,9 +321,16 @@ struct ShrinkJob {
   size_t chan_stride;
 };
 constexpr int kShrinkBatch = 16;
+struct alignas(64) TensorMapBytes {
+  unsigned char b[128];  // a CUtensorMap
+};
 template <class Src>
 struct ShrinkBatch {
   ShrinkJob<Src> job[kShrinkBatch];
+  // TMA tensor maps of the jobs' sources, in global memory (tmaps[k] belongs
+  // to job k; bit k of `tma`: job k has one)
+  const TensorMapBytes* tmaps;
+  unsigned tma;
 };
 
 template <class Src>
@@ -259,9 +341,11 @@ __global__ void __launch_bounds__(256)
   if ((int)blockIdx.x * kShrinkTileW >= j.lo_pitch ||
       (int)blockIdx.y * kShrinkTileH >= j.lo_h)
     return;
+  const int k = blockIdx.z / planes;
   shrink_tile(j.hi, j.hh, j.hp, j.xs, j.ys, j.lo, j.lo_h, j.lo_pitch,
               j.chan_stride, (int)blockIdx.x, (int)blockIdx.y,
-              (int)(blockIdx.z % planes));
+              (int)(blockIdx.z % planes),
+              (batch.tma >> k) & 1u ? (const void*)(batch.tmaps + k) : nullptr);
 }
 
 // float plane(s) as the hi level
