@@ -334,6 +334,25 @@ xp_status xp_composer_fetch(xp_composer* c, void* dst_bgr, size_t dst_stride,
                             uint8_t* dst_mask, size_t mask_stride, int mem);
 /* the blender a composer drives (for debug_fetch) */
 xp_blender* xp_composer_blender(xp_composer* c);
+/* ------------------------------------------------------------------------
+ * Auto-crop of the panorama mask: crop::FindLargestCrop
+ * (xpano/algorithm/auto_crop.cc:118-143), which consumes Blender::blend's
+ * dst_mask (stitcher_pipeline.cc:374-403). out_rect = {start.x, start.y,
+ * end.x, end.y} (utils::RectPPi); *found = 0 where the reference returns an
+ * empty optional (empty matrix, no column with a set pixel at the seeds).
+ * The per-column longest runs are found on the device; the seeded rectangle
+ * growth (auto_crop.cc:65-113) is host arithmetic, exposed on its own as
+ * xp_largest_crop_from_lines (lines = n_columns x {start, end}, {rows, 0}
+ * for a column without a set pixel).
+ * ---------------------------------------------------------------------- */
+xp_status xp_find_largest_crop(const uint8_t* mask, int w, int h,
+                               size_t stride, int mem, int device,
+                               int out_rect[4], int* found);
+/* the same on the mask of a blended blender, without a download */
+xp_status xp_blender_auto_crop(xp_blender* b, int out_rect[4], int* found);
+xp_status xp_largest_crop_from_lines(const int* lines_start_end, int n_columns,
+                                     int rows, int out_rect[4], int* found);
+
 /* Device buffers are cached across objects (a blender is single-use, like the
  * reference's); this returns the cached blocks to the driver. */
 void xp_trim_memory(void);

@@ -183,9 +183,21 @@ def portrait_goldens():
     np.savez_compressed(os.path.join(HERE, "warp_portrait_goldens.npz"), **g)
 
 
+def crop_goldens():
+    """The reference's "Real life example" of tests/auto_crop_test.cc:154-160
+    (tests/data/mask.png, expected crop (67, 659)-(5985, 2950)) as a packed
+    bit array."""
+    m = cv2.imread("/root/reference/tests/data/mask.png",
+                   cv2.IMREAD_UNCHANGED)
+    np.savez_compressed(os.path.join(HERE, "crop_real_life_mask.npz"),
+                        shape=np.array(m.shape), bits=np.packbits(m == 255),
+                        expected=np.array([67, 659, 5985, 2950]))
+
+
 def main():
     warp_goldens()
     portrait_goldens()
+    crop_goldens()
     g = {}
     pos_png = [(-91, 204), (-167, 202), (-41, 193)]
     pos_tif = [(76, 11), (0, 9), (126, 0)]
@@ -224,3 +236,5 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+

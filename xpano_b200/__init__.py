@@ -5,6 +5,7 @@ behind a C ABI, include/xpano_b200.h); these modules are thin ctypes mirrors
 of the reference interfaces. No CPU fallback."""
 from . import _lib  # noqa: F401
 from . import sharding  # noqa: F401
+from .auto_crop import FindLargestCrop  # noqa: F401
 from .blenders import Multiblend  # noqa: F401
 from .stitcher import Composer, compose_panorama  # noqa: F401
 from .warpers import (BORDER_CONSTANT, BORDER_REFLECT, INTER_LINEAR,  # noqa

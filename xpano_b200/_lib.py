@@ -147,6 +147,11 @@ SYMBOLS = {
     "xp_composer_fetch": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p,
                                   c_size_t, c_int]),
     "xp_composer_blender": (c_void_p, [c_void_p]),
+    "xp_find_largest_crop": (c_int, [c_void_p, c_int, c_int, c_size_t, c_int,
+                                     c_int, c_void_p, c_void_p]),
+    "xp_blender_auto_crop": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "xp_largest_crop_from_lines": (c_int, [c_void_p, c_int, c_int, c_void_p,
+                                           c_void_p]),
 }
 
 

@@ -251,6 +251,15 @@ static void next_mask_rect(const MaskLevel& in, MaskLevel& out) {
   out.h = k1 - k0 + 1;
 }
 
+// SM partition policy (blend_run.inc): XP_PARTITION_HOLES overrides the ratio
+static double partition_max_hole_ratio() {
+  static const double v = [] {
+    const char* e = getenv("XP_PARTITION_HOLES");
+    return e ? atof(e) : 0.5;
+  }();
+  return v;
+}
+
 }  // namespace xp
 
 #include "blend_run.inc"

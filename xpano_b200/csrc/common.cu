@@ -337,7 +337,7 @@ SmPartition& sm_partition(int device) {
   SmPartition& P = g_part[device & 15];
   if (P.tried) return P;
   P.tried = true;
-  int want = 96;
+  int want = 80;
   if (const char* e = getenv("XP_SEAM_SMS")) want = atoi(e);
   if (want <= 0) return P;
   CUresult (*get_res)(CUdevice, CUdevResource*, CUdevResourceType) = nullptr;

@@ -363,7 +363,7 @@ struct Composer {
       warper.warp_bgra_device(colours ? s.dev : nullptr, s.w, s.h, s.pitch,
                               opts.depth, p, roi_incl, s.gain.as<float>(),
                               s.gw, s.gh, s.seam.as<uint8_t>(), s.mw, s.mh,
-                              f->data.p, (size_t)f->pitch * 4 * bs);
+                              f->data.p, (size_t)f->pitch * 4 * bs, true);
       fed_local.push_back(colours ? 1 : 0);
       t_warp_launches += 1 + (s.seam.p ? 1 : 0) +
                          (is_separable(p.type) ? 1 : 0) +

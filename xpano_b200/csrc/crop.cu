@@ -1,0 +1,203 @@
+// Auto-crop of the panorama mask: crop::FindLargestCrop
+// (xpano/algorithm/auto_crop.cc:118-143), the consumer of result_mask_
+// (SURVEY.md 8f3).
+//
+// The reference walks every column of the mask for its longest run of 255
+// (FindLongestLineInColumn, :32-63: H*W byte reads, one column at a time, with
+// a 60-MB stride) and then grows rectangles from 1 + W/512 seed columns over
+// the per-column lines (:65-113, O(W) each). The first part is the data-
+// parallel one and runs on the device -- one thread per column, a warp reads
+// 32 adjacent bytes of a row, so the mask is streamed once, coalesced; the
+// second part works on W (start, end) pairs and stays host arithmetic.
+#include <climits>
+#include <vector>
+
+#include "blender.h"
+#include "common.h"
+
+namespace xp {
+
+constexpr int kAutoCropSamplingDistance = 512;  // xpano/constants.h:89
+constexpr int kMaskValueOn = 255;               // xpano/constants.h
+
+// lines[x] = {start, end} of the longest run of kMaskValueOn in column x (the
+// first one among equally long runs: auto_crop.cc:51-53 replaces only on a
+// strictly longer run), {rows, 0} when the column has none.
+__global__ void __launch_bounds__(128)
+    column_runs_kernel(const uint8_t* __restrict__ mask, int w, int h,
+                       size_t stride, int2* __restrict__ lines) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= w) return;
+  int best = 0, best_start = h, best_end = 0, run = 0, start = 0;
+  const uint8_t* p = mask + x;
+  int y = 0;
+  // eight rows in flight per thread
+  for (; y + 8 <= h; y += 8) {
+    uint8_t v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = __ldg(p + (size_t)(y + k) * stride);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (v[k] == kMaskValueOn) {
+        if (run == 0) start = y + k;
+        ++run;
+        if (run > best) best = run, best_start = start, best_end = y + k + 1;
+      } else {
+        run = 0;
+      }
+    }
+  }
+  for (; y < h; ++y) {
+    if (__ldg(p + (size_t)y * stride) == kMaskValueOn) {
+      if (run == 0) start = y;
+      ++run;
+      if (run > best) best = run, best_start = start, best_end = y + 1;
+    } else {
+      run = 0;
+    }
+  }
+  lines[x] = make_int2(best_start, best_end);
+}
+
+namespace {
+struct Rect {
+  int x0, y0, x1, y1;
+};
+inline long area(const Rect& r) {
+  return (long)(r.x1 - r.x0) * (long)(r.y1 - r.y0);
+}
+inline bool valid(const int2& l) { return l.x < l.y; }
+
+// auto_crop.cc:65-113
+bool expand(const std::vector<int2>& lines, int2 invalid, int seed,
+            Rect* out) {
+  const int n = (int)lines.size();
+  if (!valid(lines[seed])) return false;
+  Rect cur{seed, lines[seed].x, seed + 1, lines[seed].y};
+  Rect largest = cur;
+  if (n == 1) {
+    *out = largest;
+    return true;
+  }
+  int left = seed - 1;
+  int right = seed + n % 2;
+  int2 ll = lines[left], rl = lines[right];
+  while (valid(ll) || valid(rl)) {
+    const Rect lr{left, std::max(ll.x, cur.y0), cur.x1, std::min(ll.y, cur.y1)};
+    const Rect rr{cur.x0, std::max(rl.x, cur.y0), right + 1,
+                  std::min(rl.y, cur.y1)};
+    if (area(lr) > area(rr)) {
+      cur = lr;
+      ll = left == 0 ? invalid : lines[--left];
+    } else {
+      cur = rr;
+      rl = right == n - 1 ? invalid : lines[++right];
+    }
+    if (area(cur) >= area(largest)) largest = cur;
+  }
+  *out = largest;
+  return true;
+}
+}  // namespace
+
+// auto_crop.cc:118-143 on the per-column lines
+bool largest_crop_from_lines(const std::vector<int2>& lines, int rows,
+                             int out_rect[4]) {
+  const int n = (int)lines.size();
+  if (n == 0 || rows == 0) return false;
+  const int2 invalid = make_int2(rows, 0);
+  bool have = false;
+  Rect best{0, 0, 0, 0};
+  const int num_samples = 1 + n / kAutoCropSamplingDistance;
+  for (int i = 0; i < num_samples; ++i) {
+    const int start = (int)((long)(i + 1) * n / (num_samples + 1));
+    Rect r;
+    if (expand(lines, invalid, start, &r) &&
+        (!have || area(r) >= area(best))) {
+      best = r;
+      have = true;
+    }
+  }
+  if (have) {
+    out_rect[0] = best.x0;
+    out_rect[1] = best.y0;
+    out_rect[2] = best.x1;
+    out_rect[3] = best.y1;
+  }
+  return have;
+}
+
+// device mask -> rect; `s` is synchronised
+bool find_largest_crop_device(const uint8_t* d_mask, int w, int h,
+                              size_t stride, cudaStream_t s, int out_rect[4]) {
+  if (w <= 0 || h <= 0) return false;
+  DevBuf d_lines;
+  d_lines.reserve(sizeof(int2) * (size_t)w);
+  column_runs_kernel<<<div_up(w, 128), 128, 0, s>>>(d_mask, w, h, stride,
+                                                    d_lines.as<int2>());
+  XP_LAUNCHED();
+  std::vector<int2> lines(w);
+  XP_CUDA(cudaMemcpyAsync(lines.data(), d_lines.p, sizeof(int2) * (size_t)w,
+                          cudaMemcpyDeviceToHost, s));
+  XP_CUDA(cudaStreamSynchronize(s));
+  return largest_crop_from_lines(lines, h, out_rect);
+}
+
+}  // namespace xp
+
+extern "C" {
+
+xp_status xp_largest_crop_from_lines(const int* lines_start_end, int n_columns,
+                                     int rows, int out_rect[4], int* found) {
+  return xp::guard([&] {
+    XP_REQUIRE(out_rect && found && (lines_start_end || n_columns == 0),
+               "largest_crop_from_lines: null argument");
+    std::vector<int2> lines(n_columns > 0 ? n_columns : 0);
+    for (int i = 0; i < n_columns; ++i)
+      lines[i] = make_int2(lines_start_end[2 * i], lines_start_end[2 * i + 1]);
+    *found = xp::largest_crop_from_lines(lines, rows, out_rect) ? 1 : 0;
+  });
+}
+
+xp_status xp_find_largest_crop(const uint8_t* mask, int w, int h,
+                               size_t stride, int mem, int device,
+                               int out_rect[4], int* found) {
+  return xp::guard([&] {
+    XP_REQUIRE(out_rect && found, "find_largest_crop: null argument");
+    *found = 0;
+    if (!mask || w <= 0 || h <= 0) return;  // empty matrix: no crop
+    if (stride == 0) stride = (size_t)w;
+    xp::select_device(device);
+    const uint8_t* d = mask;
+    xp::DevBuf staging;
+    size_t dstride = stride;
+    if (mem == XP_MEM_HOST) {
+      staging.reserve((size_t)w * h);
+      xp::copy_in_2d(staging.p, (size_t)w, mask, stride, (size_t)w, (size_t)h,
+                     mem, nullptr);
+      d = staging.as<uint8_t>();
+      dstride = (size_t)w;
+    }
+    *found = xp::find_largest_crop_device(d, w, h, dstride, nullptr, out_rect)
+                 ? 1
+                 : 0;
+    XP_CUDA(cudaStreamSynchronize(nullptr));
+  });
+}
+
+xp_status xp_blender_auto_crop(xp_blender* b, int out_rect[4], int* found) {
+  return xp::guard([&] {
+    XP_REQUIRE(b && out_rect && found, "auto_crop: null argument");
+    xp::Blender* bl = reinterpret_cast<xp::Blender*>(b);
+    XP_REQUIRE(bl->blended, "auto_crop before blend()");
+    XP_REQUIRE(bl->tile.count == 1, "auto_crop: not available for a tile");
+    xp::select_device(bl->opts.device);
+    *found = xp::find_largest_crop_device(bl->full_mask.as<uint8_t>(), bl->W,
+                                          bl->H, (size_t)bl->W, bl->stream,
+                                          out_rect)
+                 ? 1
+                 : 0;
+  });
+}
+
+}  // extern "C"

@@ -50,7 +50,7 @@ struct Warper {
                         int depth, const Projector& p, const int roi[4],
                         const float* d_gain, int gw, int gh,
                         const uint8_t* d_seam, int mw, int mh, void* ddst,
-                        size_t dpitch);
+                        size_t dpitch, bool skip_transparent = false);
 };
 
 }  // namespace xp

@@ -162,6 +162,12 @@ class Composer:
                                           mask.ctypes.data, 0, _lib.MEM_HOST))
         return pano, mask
 
+    def auto_crop(self):
+        """crop::FindLargestCrop on the panorama mask, on the device
+        (auto_crop.cc:118-143) -> (x0, y0, x1, y1) or None."""
+        from .auto_crop import blender_auto_crop
+        return blender_auto_crop(self._lib.xp_composer_blender(self._h))
+
     def debug(self, what, image=0, channel=0, level=0, dtype=None):
         h = self._lib.xp_composer_blender(self._h)
         return debug_fetch(self._lib, c_void_p(h), what, image, channel, level,
