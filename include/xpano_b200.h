@@ -34,7 +34,8 @@ enum {
   XP_ERR_CUDA = 2,        /* CUDA runtime failure / no device               */
   XP_ERR_UNSUPPORTED = 3, /* combination the reference path never uses      */
   XP_ERR_EMPTY = 4,       /* image without an opaque pixel / nothing fed    */
-  XP_ERR_NOMEM = 5
+  XP_ERR_NOMEM = 5,
+  XP_CANCELLED = 6        /* Status::kCancelled (stitcher.cc:408-412)       */
 };
 
 enum { XP_MEM_HOST = 0, XP_MEM_DEVICE = 1 };
@@ -208,6 +209,16 @@ xp_status xp_blender_blend(xp_blender* b, int out_wh[2], int out_min_xy[2],
  * Strides in bytes (0 = packed). */
 xp_status xp_blender_fetch(xp_blender* b, void* dst_bgr, size_t dst_stride,
                            uint8_t* dst_mask, size_t mask_stride, int mem);
+/* Result.full_mask in the reference's own wire format (utils::Flex,
+ * mb/include/mb/flex.h:22-75; decoded by xpano's ToMat, blenders.cc:38-62):
+ * per row the maximal runs as 32-bit words (white << 31) | length, rows back
+ * to back; row_offsets (H ints, may be NULL, host memory) = Flex::rows_, the
+ * byte offset of every row. runs == NULL: size query (*n_words). The dense
+ * dst_mask of xp_blender_fetch stays available; this form is ~100x smaller
+ * on the way to the host. */
+xp_status xp_blender_fetch_mask_rle(xp_blender* b, uint32_t* runs,
+                                    size_t cap_words, size_t* n_words,
+                                    int32_t* row_offsets, int mem);
 /* Result.output_channels as the library returns them: 3 planes, not zeroed
  * outside the mask. */
 xp_status xp_blender_fetch_planes(xp_blender* b, void* planes, int mem);
@@ -304,6 +315,12 @@ xp_status xp_composer_set_stream(xp_composer* c, void* cuda_stream);
 /* Upload (or adopt, mem == XP_MEM_DEVICE) the source images. */
 xp_status xp_composer_set_images(xp_composer* c, int n,
                                  const xp_compose_image* images, int mem);
+/* Cooperative cancellation, as Stitcher::Cancelled() is polled between images
+ * (stitcher.cc:408-412, :345-347): `flag` is read before every image's warp
+ * and once more before the blend; a non-zero value makes xp_composer_run (or
+ * run_tile_begin) return XP_CANCELLED with nothing left queued. The blend
+ * itself is not cancellable, as in the reference. NULL removes the flag. */
+xp_status xp_composer_set_cancel_flag(xp_composer* c, const volatile int* flag);
 /* Run warp -> feed -> blend on the device; result stays resident. */
 xp_status xp_composer_run(xp_composer* c, xp_compose_info* info);
 /* Canvas tiling of ONE panorama over `count` GPUs (SURVEY.md section 8e;

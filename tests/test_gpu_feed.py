@@ -223,3 +223,51 @@ def test_operator_surface_equals_compose_driver(bpp):
     # 1 LSB for 8-bit samples, 1e-3 relative for 16-bit ones
     tol = 1 if bpp == 8 else np.maximum(1, 1e-3 * want["pano"].astype(int)[m])
     assert (d <= tol).mean() >= 0.999, (d.max(), (d <= tol).mean())
+
+
+def test_compose_cancellation_between_images():
+    """Stitcher::Cancelled() is polled between images (stitcher.cc:408-412):
+    the composer polls a caller-owned flag at the same points."""
+    import ctypes
+    import xpano_b200 as xb
+    n_cols, w_, h_, f = 3, 240, 180, 200.0
+    hfov = 2 * math.atan(w_ / 2 / f)
+    Ks, Rs = co.make_cameras(n_cols, 1, w_, h_, f, 0.6 * hfov, [0.0], 9, None)
+    ims = [synth.texture(h_, w_, 60 + i, 3, 8) for i in range(n_cols)]
+    c = xb.Composer(projection=wo.SPHERICAL, warp_scale=f, fixed_levels=3)
+    c.set_images(ims, Ks, Rs)
+    flag = ctypes.c_int(1)
+    c.set_cancel_flag(flag)
+    with pytest.raises(xb._lib.XpError) as e:
+        c.run()
+    assert e.value.code == 6
+    flag.value = 0            # the same composer runs once the flag is clear
+    info = c.run()
+    pano, mask = c.fetch()
+    assert pano.shape[:2] == (info["height"], info["width"]) and mask.any()
+
+
+def test_mask_in_the_reference_rle_format():
+    """Result.full_mask as utils::Flex words (mb/flex.h, flex.cpp:78-98),
+    decoded the way xpano's ToMat does (blenders.cc:38-62)."""
+    import xpano_b200 as xb
+    from xpano_b200.blenders import decode_mask_rle
+    for seed, ckw in ((51, dict(n=3, mode="ellipse")),
+                      (52, dict(n=4, mode="blobs", w=330, h=210))):
+        ims, pos = synth.blend_case(seed, **ckw)
+        b = xb.Multiblend(fixed_levels=3)
+        for im, p in zip(ims, pos):
+            b.feed_interleaved(im, p)
+        dst, mask = b.blend()
+        runs, rows = b.mask_rle()
+        H, W = mask.shape
+        assert np.array_equal(decode_mask_rle(runs, W, H), mask)
+        # maximal runs: colours alternate inside a row; Flex::rows_ offsets
+        assert rows[0] == 0 and (np.diff(rows) > 0).all()
+        for y in (0, H // 2, H - 1):
+            a = rows[y] // 4
+            e = rows[y + 1] // 4 if y + 1 < H else len(runs)
+            r = runs[a:e]
+            assert int((r & 0x7FFFFFFF).sum()) == W
+            assert ((r[1:] >> 31) != (r[:-1] >> 31)).all()
+        assert runs.nbytes < mask.nbytes / 10

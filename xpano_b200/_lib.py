@@ -121,6 +121,8 @@ SYMBOLS = {
                                  c_void_p, P(Timing)]),
     "xp_blender_fetch": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p,
                                  c_size_t, c_int]),
+    "xp_blender_fetch_mask_rle": (c_int, [c_void_p, c_void_p, c_size_t,
+                                          P(c_size_t), c_void_p, c_int]),
     "xp_blender_fetch_planes": (c_int, [c_void_p, c_void_p, c_int]),
     "xp_blender_stage_bytes": (c_int, [c_void_p, c_void_p, c_void_p]),
     "xp_blender_debug_fetch": (c_int, [c_void_p, ctypes.c_char_p, c_int, c_int,
@@ -138,6 +140,7 @@ SYMBOLS = {
     "xp_composer_set_images": (c_int, [c_void_p, c_int, P(ComposeImage),
                                        c_int]),
     "xp_composer_run": (c_int, [c_void_p, P(ComposeInfo)]),
+    "xp_composer_set_cancel_flag": (c_int, [c_void_p, c_void_p]),
     "xp_composer_set_tile": (c_int, [c_void_p, c_int, c_int]),
     "xp_composer_tile_needs": (c_int, [c_void_p, c_int, c_void_p]),
     "xp_composer_run_tile_begin": (c_int, [c_void_p, c_void_p]),

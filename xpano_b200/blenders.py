@@ -122,6 +122,12 @@ class Multiblend:
             c_void_p(mask_ptr or None), int(mask_stride), _lib.MEM_DEVICE))
         return size
 
+    def mask_rle(self):
+        """Result.full_mask as the reference returns it (utils::Flex): ->
+        (runs uint32 array of (white << 31) | length words, row byte offsets).
+        `decode_mask_rle` is xpano's ToMat (blenders.cc:38-62)."""
+        return fetch_mask_rle(self._lib, self._h, self.run()[1])
+
     def planes(self):
         """Result.output_channels: (3, H, W), not zeroed outside the mask."""
         W, H = self.run()
@@ -161,3 +167,37 @@ def debug_fetch(lib, handle, what, image=0, channel=0, level=0, dtype=None):
     if rows * pitch == arr.size and rows > 1:
         arr = arr.reshape(rows, pitch)[:, :cols]
     return arr
+
+
+def fetch_mask_rle(lib, handle, height):
+    n = ctypes.c_size_t()
+    check(lib.xp_blender_fetch_mask_rle(handle, None, 0, ctypes.byref(n),
+                                        None, _lib.MEM_HOST))
+    runs = np.empty(max(n.value, 1), np.uint32)
+    rows = np.empty(height, np.int32)
+    check(lib.xp_blender_fetch_mask_rle(handle, runs.ctypes.data, runs.size,
+                                        ctypes.byref(n), rows.ctypes.data,
+                                        _lib.MEM_HOST))
+    return runs[:n.value], rows
+
+
+def decode_mask_rle(runs, width, height):
+    """blenders.cc:38-62 ToMat: walk the words row by row; a word with the
+    top bit set is a run of 255, otherwise a run of 0; zero-length runs and
+    runs past the end of a row are errors ("invalid mask format" / "mask out
+    of bounds")."""
+    mask = np.empty((height, width), np.uint8)
+    k = 0
+    for y in range(height):
+        x = 0
+        while x < width:
+            w = int(runs[k])
+            k += 1
+            n = w & 0x7FFFFFFF
+            if n == 0:
+                raise RuntimeError("Multiblend: invalid mask format")
+            if x + n > width:
+                raise RuntimeError("Multiblend: mask out of bounds")
+            mask[y, x:x + n] = 255 if w & 0x80000000 else 0
+            x += n
+    return mask

@@ -98,6 +98,11 @@ struct Blender {
   std::vector<int> win_img;      // window image -> fed index
   DevBuf wlabels, wxor, wfull, d_relabel;
 
+  // run-length form of the mask (crop.cu), built on first request
+  bool rle_ready = false;
+  size_t rle_words = 0;
+  DevBuf rle_runs, rle_offs;
+
   explicit Blender(const xp_blend_opts& o) : opts(o) {}
   ~Blender();
   void ensure_device();

@@ -288,6 +288,17 @@ struct Composer {
   } plan;
   int tile_index = 0, tile_count = 1;
   bool tile_pending = false;
+  const volatile int* cancel_flag = nullptr;
+  void check_cancelled() {
+    if (cancel_flag && *cancel_flag) {
+      // nothing of this run may stay queued behind the caller's back
+      if (blender) {
+        cudaStreamSynchronize(stream);
+        blender.reset();
+      }
+      fail(XP_CANCELLED, "cancelled (stitcher.cc:408-412)");
+    }
+  }
   double t_s_src = 0, t_s_w = 0;
   int t_warp_launches = 0;
 
@@ -354,6 +365,7 @@ struct Composer {
     for (size_t i = 0; i < src.size(); ++i) {
       SrcImage& s = *src[i];
       if (s.skip) continue;
+      check_cancelled();
       const int* r = &plan.rois[4 * i];
       const int roi_incl[4] = {r[0], r[1], r[0] + r[2] - 1, r[1] + r[3] - 1};
       Fed* f = blender->new_fed(r[2], r[3], opts.depth, r[0], r[1]);
@@ -371,6 +383,7 @@ struct Composer {
       if (colours) t_s_src += (double)s.w * s.h;
       t_s_w += (double)r[2] * r[3];
     }
+    check_cancelled();
     if (tile_count > 1) {
       blender->tile.index = tile_index;
       blender->tile.count = tile_count;
@@ -549,6 +562,14 @@ xp_status xp_composer_run(xp_composer* c, xp_compose_info* info) {
   return xp::guard([&] {
     XP_REQUIRE(c, "null composer");
     c->run(info);
+  });
+}
+
+xp_status xp_composer_set_cancel_flag(xp_composer* c,
+                                      const volatile int* flag) {
+  return xp::guard([&] {
+    XP_REQUIRE(c, "null composer");
+    c->cancel_flag = flag;
   });
 }
 

@@ -201,3 +201,184 @@ xp_status xp_blender_auto_crop(xp_blender* b, int out_rect[4], int* found) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Run-length form of the panorama mask: multiblend's Result.full_mask
+// (utils::Flex, mb/include/mb/flex.h:22-75, written by Flex::MaskWrite /
+// MaskFinalise, src/flex.cpp:78-98, and decoded by xpano's ToMat,
+// blenders.cc:38-62): per row a sequence of 32-bit words
+// (white << 31) | run_length over maximal runs, rows back to back, plus the
+// byte offset of every row (Flex::rows_). 60 MB of dense mask become a few
+// hundred kilobytes on the way to the host.
+// ---------------------------------------------------------------------------
+namespace xp {
+
+// one block per row: number of runs of the row
+__global__ void __launch_bounds__(256)
+    rle_count_kernel(const uint8_t* __restrict__ mask, int w, size_t stride,
+                     int* __restrict__ counts) {
+  const uint8_t* row = mask + (size_t)blockIdx.x * stride;
+  int n = 0;
+  for (int x = threadIdx.x; x < w; x += blockDim.x)
+    n += x == 0 || (row[x] != 0) != (row[x - 1] != 0);
+  __shared__ int sh[8];
+  for (int o = 16; o > 0; o >>= 1) n += __shfl_down_sync(~0u, n, o);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = n;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int k = 0; k < 8; ++k) t += sh[k];
+    counts[blockIdx.x] = t;
+  }
+}
+
+// exclusive scan of the row counts (one block); offs[h] = total
+__global__ void __launch_bounds__(1024)
+    rle_scan_kernel(const int* __restrict__ counts, int h,
+                    int* __restrict__ offs) {
+  __shared__ int sh[1024];
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < h; base += 1024) {
+    const int i = base + threadIdx.x;
+    const int v = i < h ? counts[i] : 0;
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+      const int t = threadIdx.x >= d ? sh[threadIdx.x - d] : 0;
+      __syncthreads();
+      sh[threadIdx.x] += t;
+      __syncthreads();
+    }
+    if (i < h) offs[i] = carry + sh[threadIdx.x] - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry += sh[1023];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) offs[h] = carry;
+}
+
+// one block per row: the run starts, in order, as (white << 31) | x
+__global__ void __launch_bounds__(256)
+    rle_emit_kernel(const uint8_t* __restrict__ mask, int w, size_t stride,
+                    const int* __restrict__ offs, uint32_t* __restrict__ runs) {
+  const uint8_t* row = mask + (size_t)blockIdx.x * stride;
+  uint32_t* out = runs + offs[blockIdx.x];
+  __shared__ int warp_sum[8];
+  __shared__ int base;
+  if (threadIdx.x == 0) base = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int x0 = 0; x0 < w; x0 += blockDim.x) {
+    const int x = x0 + threadIdx.x;
+    const bool start =
+        x < w && (x == 0 || (row[x] != 0) != (row[x - 1] != 0));
+    const unsigned b = __ballot_sync(~0u, start);
+    if (lane == 0) warp_sum[wid] = __popc(b);
+    __syncthreads();
+    int before = base;
+    for (int k = 0; k < wid; ++k) before += warp_sum[k];
+    if (start)
+      out[before + __popc(b & ((1u << lane) - 1u))] =
+          (row[x] != 0 ? 0x80000000u : 0u) | (uint32_t)x;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int t = 0;
+      for (int k = 0; k < 8; ++k) t += warp_sum[k];
+      base += t;
+    }
+    __syncthreads();
+  }
+}
+
+// start positions -> run lengths (in place, every word reads its successor
+// first: one thread per word, two phases through a register)
+__global__ void rle_lengths_kernel(uint32_t* __restrict__ runs,
+                                   const int* __restrict__ offs, int h, int w,
+                                   const uint32_t* __restrict__ starts) {
+  const int y = blockIdx.y;
+  const int n = offs[y + 1] - offs[y];
+  const uint32_t* in = starts + offs[y];
+  uint32_t* out = runs + offs[y];
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n;
+       k += gridDim.x * blockDim.x) {
+    const uint32_t s = in[k];
+    const uint32_t next = k + 1 < n ? (in[k + 1] & 0x7fffffffu) : (uint32_t)w;
+    out[k] = (s & 0x80000000u) | (next - (s & 0x7fffffffu));
+  }
+  (void)h;
+}
+
+}  // namespace xp
+
+extern "C" {
+
+xp_status xp_blender_fetch_mask_rle(xp_blender* b, uint32_t* runs,
+                                    size_t cap_words, size_t* n_words,
+                                    int32_t* row_offsets, int mem) {
+  return xp::guard([&] {
+    XP_REQUIRE(b && n_words, "fetch_mask_rle: null argument");
+    xp::Blender* bl = reinterpret_cast<xp::Blender*>(b);
+    XP_REQUIRE(bl->blended, "fetch_mask_rle before blend()");
+    XP_REQUIRE(bl->tile.count == 1,
+               "fetch_mask_rle: not available for a canvas tile");
+    xp::select_device(bl->opts.device);
+    cudaStream_t s = bl->stream;
+    const int W = bl->W, H = bl->H;
+    if (!bl->rle_ready) {
+      bl->rle_offs.reserve(sizeof(int) * ((size_t)H + 1));
+      xp::DevBuf counts;
+      counts.reserve(sizeof(int) * (size_t)H);
+      xp::rle_count_kernel<<<H, 256, 0, s>>>(bl->full_mask.as<uint8_t>(), W,
+                                             (size_t)W, counts.as<int>());
+      XP_LAUNCHED();
+      xp::rle_scan_kernel<<<1, 1024, 0, s>>>(counts.as<int>(), H,
+                                             bl->rle_offs.as<int>());
+      XP_LAUNCHED();
+      int total = 0;
+      XP_CUDA(cudaMemcpyAsync(&total, bl->rle_offs.as<int>() + H, sizeof(int),
+                              cudaMemcpyDeviceToHost, s));
+      XP_CUDA(cudaStreamSynchronize(s));
+      bl->rle_words = (size_t)total;
+      xp::DevBuf starts;
+      starts.reserve(sizeof(uint32_t) * std::max<size_t>(bl->rle_words, 1));
+      bl->rle_runs.reserve(sizeof(uint32_t) *
+                           std::max<size_t>(bl->rle_words, 1));
+      xp::rle_emit_kernel<<<H, 256, 0, s>>>(bl->full_mask.as<uint8_t>(), W,
+                                            (size_t)W, bl->rle_offs.as<int>(),
+                                            starts.as<uint32_t>());
+      XP_LAUNCHED();
+      xp::rle_lengths_kernel<<<dim3(4, H), 128, 0, s>>>(
+          bl->rle_runs.as<uint32_t>(), bl->rle_offs.as<int>(), H, W,
+          starts.as<uint32_t>());
+      XP_LAUNCHED();
+      XP_CUDA(cudaStreamSynchronize(s));  // `starts`, `counts` are released
+      bl->rle_ready = true;
+    }
+    *n_words = bl->rle_words;
+    if (!runs) return;  // size query
+    XP_REQUIRE(cap_words >= bl->rle_words,
+               "fetch_mask_rle: buffer too small (%zu < %zu words)", cap_words,
+               bl->rle_words);
+    const cudaMemcpyKind kind = mem == XP_MEM_DEVICE
+                                    ? cudaMemcpyDeviceToDevice
+                                    : cudaMemcpyDeviceToHost;
+    if (bl->rle_words)
+      XP_CUDA(cudaMemcpyAsync(runs, bl->rle_runs.p,
+                              sizeof(uint32_t) * bl->rle_words, kind, s));
+    if (row_offsets) {
+      // Flex::rows_: byte offset of every row's first word
+      std::vector<int> offs((size_t)H + 1);
+      XP_CUDA(cudaMemcpyAsync(offs.data(), bl->rle_offs.p,
+                              sizeof(int) * ((size_t)H + 1),
+                              cudaMemcpyDeviceToHost, s));
+      XP_CUDA(cudaStreamSynchronize(s));
+      XP_REQUIRE(mem == XP_MEM_HOST, "row_offsets are returned to the host");
+      for (int y = 0; y < H; ++y) row_offsets[y] = offs[y] * 4;
+    }
+    XP_CUDA(cudaStreamSynchronize(s));
+  });
+}
+
+}  // extern "C"

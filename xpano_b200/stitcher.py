@@ -93,6 +93,14 @@ class Composer:
                                                _lib.MEM_HOST))
         self._keep = keep
 
+    def set_cancel_flag(self, flag):
+        """flag: a ctypes.c_int the caller sets non-zero to cancel; polled
+        between images like Stitcher::Cancelled() (stitcher.cc:408-412). A
+        cancelled run raises XpError with code 6 (XP_CANCELLED)."""
+        self._cancel = flag
+        check(self._lib.xp_composer_set_cancel_flag(
+            self._h, ctypes.byref(flag) if flag is not None else None))
+
     # ---- canvas tiling of one panorama over several GPUs (SURVEY 8e) -------
     def set_tile(self, index, count):
         """This composer computes strip `index` of `count` vertical strips of
@@ -161,6 +169,14 @@ class Composer:
         check(self._lib.xp_composer_fetch(self._h, pano.ctypes.data, 0,
                                           mask.ctypes.data, 0, _lib.MEM_HOST))
         return pano, mask
+
+    def fetch_mask_rle(self):
+        """The panorama mask as run-length words (utils::Flex layout) instead
+        of the dense array: -> (runs, row byte offsets)."""
+        from .blenders import fetch_mask_rle
+        return fetch_mask_rle(self._lib,
+                              c_void_p(self._lib.xp_composer_blender(self._h)),
+                              self.info["height"])
 
     def auto_crop(self):
         """crop::FindLargestCrop on the panorama mask, on the device
