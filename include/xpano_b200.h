@@ -370,6 +370,66 @@ xp_status xp_blender_auto_crop(xp_blender* b, int out_rect[4], int* found);
 xp_status xp_largest_crop_from_lines(const int* lines_start_end, int n_columns,
                                      int rows, int out_rect[4], int* found);
 
+/* ------------------------------------------------------------------------
+ * Exposure step of Stitcher::EstimateSeams (xpano/algorithm/stitcher.cc:
+ * 273-278): cv::detail::BlocksGainCompensator as xpano constructs it
+ * (stitcher.cc:200-201; OpenCV defaults: 32x32 blocks, one feed, two gain
+ * filtering iterations, similarity threshold 1). SURVEY.md 8(f1).
+ *
+ *   feed   : BlocksCompensator::feed(corners, images_warped, masks_warped)
+ *            -- seam-scale warped images (8-bit BGR interleaved) and masks
+ *            (255 = inside), as xp_warper_warp produces them. Block-pair
+ *            statistics on the device, the per-block system in double on
+ *            the host; one float gain map per image.
+ *   get_map: ExposureCompensator::getMatGains (the arrays
+ *            xp_composer_set_images / xp_warp_aux.gain take).
+ *   set_map: ExposureCompensator::setMatGains.
+ *   apply  : BlocksCompensator::apply(index, corner, image, mask) in place
+ *            on an interleaved BGR image (8 or 16 bit): gain map resized to
+ *            the image (INTER_LINEAR), multiply, saturate.
+ * The graph-cut seam finder that follows (stitcher.cc:290) is sequential
+ * max-flow and stays with the caller's CPU code.
+ * ---------------------------------------------------------------------- */
+typedef struct xp_gain_compensator xp_gain_compensator;
+xp_status xp_gain_compensator_create(int block_w, int block_h,
+                                     int filter_iterations, int device,
+                                     xp_gain_compensator** out);
+void xp_gain_compensator_destroy(xp_gain_compensator* g);
+/* corners_xy: n x {x, y}; strides in bytes (NULL or 0 = packed) */
+xp_status xp_gain_compensator_feed(xp_gain_compensator* g, int n,
+                                   const int* corners_xy,
+                                   const void* const* bgr, const int* widths,
+                                   const int* heights, const size_t* strides,
+                                   const uint8_t* const* masks,
+                                   const size_t* mask_strides, int mem);
+/* feed in three steps, the middle one being the device kernel; host-only,
+ * for callers that hold the block-pair statistics already and for the CPU
+ * tests of the host arithmetic: plan (block grids, overlapping block pairs),
+ * pairs (n_pairs x {block i, block j, x, y, w, h}), solve (gains and maps
+ * from per-pair {count, sum |a|, sum |b|}). */
+xp_status xp_gain_compensator_plan(xp_gain_compensator* g, int n,
+                                   const int* corners_xy, const int* widths,
+                                   const int* heights, int* n_pairs);
+xp_status xp_gain_compensator_pairs(const xp_gain_compensator* g,
+                                    int* pairs6);
+xp_status xp_gain_compensator_solve(xp_gain_compensator* g, int n_pairs,
+                                    const long long* counts,
+                                    const double* sums_first,
+                                    const double* sums_second);
+xp_status xp_gain_compensator_map_size(const xp_gain_compensator* g,
+                                       int index, int wh[2]);
+/* dst: host, wh[1] x wh[0] float32 */
+xp_status xp_gain_compensator_get_map(const xp_gain_compensator* g, int index,
+                                      float* dst);
+xp_status xp_gain_compensator_set_map(xp_gain_compensator* g, int index,
+                                      const float* src, int w, int h);
+xp_status xp_gain_compensator_apply(const xp_gain_compensator* g, int index,
+                                    void* bgr, int w, int h, size_t stride,
+                                    int depth, int mem);
+/* out = {block pairs, unknowns of the system, solver iterations} of the
+ * last feed */
+xp_status xp_gain_compensator_stats(const xp_gain_compensator* g, int out[3]);
+
 /* Device buffers are cached across objects (a blender is single-use, like the
  * reference's); this returns the cached blocks to the driver. */
 void xp_trim_memory(void);

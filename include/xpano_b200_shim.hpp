@@ -1,5 +1,5 @@
 // xpano_b200_shim.hpp -- the reference-side binding of libxpano_b200.so: the
-// three classes a maintainer adds to xpano (e.g. as xpano/algorithm/b200.h) so
+// classes a maintainer adds to xpano (e.g. as xpano/algorithm/b200.h) so
 // that the library drops in behind the two interfaces the stitcher already
 // drives through cv::Ptr,
 //   cv::WarperCreator / cv::detail::RotationWarper
@@ -9,7 +9,11 @@
 //   cv::detail::Blender
 //       (Stitcher::SetBlender, stitcher.h:205-207, installed from algorithm.cc:269-270;
 //        calls at stitcher.cc:357, 405, 419; replaces blenders::Multiblend,
-//        xpano/algorithm/blenders.h:25-39).
+//        xpano/algorithm/blenders.h:25-39)
+//   cv::detail::ExposureCompensator
+//       (Stitcher::SetExposureCompensator, stitcher.h:188-191, installed from
+//        stitcher.cc:200-201; calls at stitcher.cc:274, 276, 389; replaces
+//        cv::detail::BlocksGainCompensator).
 // Header-only; needs OpenCV's stitching headers and include/xpano_b200.h; link
 // with -lxpano_b200. Errors follow the reference convention: a non-zero
 // xp_status becomes std::runtime_error (blenders.cc:28-31, 137, 156).
@@ -20,8 +24,11 @@
 #pragma once
 
 #include <stdexcept>
+#include <utility>
+#include <vector>
 
 #include <opencv2/stitching/detail/blenders.hpp>
+#include <opencv2/stitching/detail/exposure_compensate.hpp>
 #include <opencv2/stitching/detail/warpers.hpp>
 #include <opencv2/stitching/warpers.hpp>
 
@@ -166,6 +173,83 @@ class B200Blender : public cv::detail::Blender {
 
  private:
   xp_blender* b_ = nullptr;
+};
+
+class B200GainCompensator : public cv::detail::ExposureCompensator {
+ public:
+  // cv::detail::BlocksGainCompensator's defaults (32x32 blocks, two gain
+  // filtering iterations), as stitcher.cc:200-201 constructs it
+  explicit B200GainCompensator(int bl_width = 32, int bl_height = 32,
+                               int nr_gain_filtering_iterations = 2, int device = 0) {
+    Check(xp_gain_compensator_create(bl_width, bl_height, nr_gain_filtering_iterations,
+                                     device, &g_));
+  }
+  ~B200GainCompensator() override { xp_gain_compensator_destroy(g_); }
+  B200GainCompensator(const B200GainCompensator&) = delete;
+  B200GainCompensator& operator=(const B200GainCompensator&) = delete;
+  using cv::detail::ExposureCompensator::feed;  // the all-255 overload, stitcher.cc:274
+
+  void feed(const std::vector<cv::Point>& corners, const std::vector<cv::UMat>& images,
+            const std::vector<std::pair<cv::UMat, uchar>>& masks) override {
+    CV_Assert(corners.size() == images.size() && images.size() == masks.size());
+    if (!getUpdateGain() && n_ == static_cast<int>(images.size())) return;
+    const int n = static_cast<int>(images.size());
+    std::vector<cv::Mat> im(n), mk(n);
+    std::vector<int> xy(2 * n), w(n), h(n);
+    std::vector<const void*> ip(n);
+    std::vector<const uint8_t*> mp(n);
+    std::vector<size_t> is(n), ms(n);
+    for (int i = 0; i < n; ++i) {
+      im[i] = images[i].getMat(cv::ACCESS_READ);
+      mk[i] = masks[i].first.getMat(cv::ACCESS_READ);
+      CV_Assert(im[i].type() == CV_8UC3 && mk[i].type() == CV_8U);
+      CV_Assert(mk[i].rows == im[i].rows && mk[i].cols == im[i].cols);
+      CV_Assert(masks[i].second == 255);  // kMaskValueOn, stitcher.cc:254
+      xy[2 * i] = corners[i].x;
+      xy[2 * i + 1] = corners[i].y;
+      w[i] = im[i].cols;
+      h[i] = im[i].rows;
+      ip[i] = im[i].data;
+      mp[i] = mk[i].data;
+      is[i] = im[i].step;
+      ms[i] = mk[i].step;
+    }
+    Check(xp_gain_compensator_feed(g_, n, xy.data(), ip.data(), w.data(), h.data(),
+                                   is.data(), mp.data(), ms.data(), XP_MEM_HOST));
+    n_ = n;
+  }
+
+  void apply(int index, cv::Point /*corner*/, cv::InputOutputArray image,
+             cv::InputArray /*mask*/) override {
+    cv::Mat m = image.getMat();
+    CV_Assert(m.type() == CV_8UC3 || m.type() == CV_16UC3);
+    Check(xp_gain_compensator_apply(g_, index, m.data, m.cols, m.rows, m.step,
+                                    8 * static_cast<int>(m.elemSize1()), XP_MEM_HOST));
+  }
+
+  void getMatGains(std::vector<cv::Mat>& gains) override {
+    gains.clear();
+    for (int i = 0; i < n_; ++i) {
+      int wh[2];
+      Check(xp_gain_compensator_map_size(g_, i, wh));
+      cv::Mat g(wh[1], wh[0], CV_32F);
+      Check(xp_gain_compensator_get_map(g_, i, g.ptr<float>()));
+      gains.push_back(g);
+    }
+  }
+
+  void setMatGains(std::vector<cv::Mat>& gains) override {
+    for (size_t i = 0; i < gains.size(); ++i) {
+      CV_Assert(gains[i].type() == CV_32F && gains[i].isContinuous());
+      Check(xp_gain_compensator_set_map(g_, static_cast<int>(i), gains[i].ptr<float>(),
+                                        gains[i].cols, gains[i].rows));
+    }
+    n_ = static_cast<int>(gains.size());
+  }
+
+ private:
+  xp_gain_compensator* g_ = nullptr;
+  int n_ = 0;
 };
 
 }  // namespace xpano::algorithm::b200

@@ -27,6 +27,8 @@
     if (!(expr)) throw cv::Exception("CV_Assert failed: " #expr);    \
   } while (0)
 
+typedef unsigned char uchar;  // global, as in opencv2/core/hal/interface.h
+
 namespace cv {
 
 struct Exception : std::runtime_error {
@@ -97,6 +99,16 @@ class Mat {
  private:
   int type_ = 0;
   std::shared_ptr<unsigned char> buf_;
+};
+
+enum AccessFlag { ACCESS_READ = 1 << 24, ACCESS_WRITE = 1 << 25 };
+// cv::UMat: for the shim's purposes a Mat whose host view is asked for
+// explicitly (UMat::getMat(AccessFlag)).
+class UMat : public Mat {
+ public:
+  UMat() = default;
+  UMat(const Mat& m) : Mat(m) {}
+  Mat getMat(AccessFlag) const { return *this; }
 };
 
 // InputArray / OutputArray / InputOutputArray: proxies of a Mat, passed by

@@ -194,10 +194,123 @@ def crop_goldens():
                         expected=np.array([67, 659, 5985, 2950]))
 
 
+def gain_scenes():
+    """Two small exposure-compensation scenes (corners, images, masks):
+    A: four overlapping exposures of one smooth texture with warped-looking
+       masks (cut corners, empty margins) plus one isolated image;
+    B: block-grid edge cases (33x20, 31x65, 100x31; one half-empty mask)."""
+    rng = np.random.default_rng(11)
+    noise = rng.integers(0, 256, (260, 520, 3)).astype(np.float32)
+    base = noise.copy()
+    for _ in range(6):  # smooth without cv2: repeated 5-point averaging
+        base = (base + np.roll(base, 1, 0) + np.roll(base, -1, 0)
+                + np.roll(base, 1, 1) + np.roll(base, -1, 1)) / 5
+    base = (base - base.min()) / (base.max() - base.min()) * 255
+    cs, ims, ms = [], [], []
+    for k, (x, y, w, h) in enumerate([(0, 10, 170, 120), (120, 0, 180, 131),
+                                      (250, 30, 160, 110),
+                                      (60, 90, 130, 70)]):
+        im = np.clip(base[y:y + h, x:x + w] * (0.75 + 0.17 * k)
+                     + rng.normal(0, 2, (h, w, 3)), 0, 255).astype(np.uint8)
+        m = np.full((h, w), 255, np.uint8)
+        m[:5] = 0
+        m[:, :4] = 0
+        yy, xx = np.mgrid[0:h, 0:w]
+        m[(xx + yy) < 40] = 0
+        m[(w - xx) + (h - yy) < 25] = 0
+        cs.append((x - 50, y + 3))
+        ims.append(im)
+        ms.append(m)
+    ims.append(np.full((70, 80, 3), 99, np.uint8))
+    ms.append(np.full((70, 80), 255, np.uint8))
+    cs.append((2000, 2000))
+    a = (cs, ims, ms)
+    ims = [rng.integers(0, 256, (h, w, 3)).astype(np.uint8)
+           for (w, h) in [(33, 20), (31, 65), (100, 31)]]
+    ms = [np.full(i.shape[:2], 255, np.uint8) for i in ims]
+    ms[1][:30] = 0
+    b = ([(0, 0), (20, -5), (10, 10)], ims, ms)
+    return {"A": a, "B": b}
+
+
+def gain_goldens():
+    """cv::detail::BlocksGainCompensator (cv2 4.13.0) on gain_scenes():
+    getMatGains with 0 and 2 filtering iterations, and apply on every image
+    (8-bit: BlocksCompensator::apply asserts CV_8UC3)."""
+    g = {}
+    for name, (cs, ims, ms) in gain_scenes().items():
+        g[f"{name}_corners"] = np.array(cs, np.int32)
+        for i, (im, m) in enumerate(zip(ims, ms)):
+            g[f"{name}_img_{i}"] = im
+            g[f"{name}_mask_{i}"] = m
+        for it in (0, 2):
+            comp = cv2.detail_BlocksGainCompensator()
+            comp.setNrGainsFilteringIterations(it)
+            comp.feed(cs, ims, ms)
+            for i, gm in enumerate(comp.getMatGains()):
+                g[f"{name}_gain{it}_{i}"] = np.ascontiguousarray(gm)
+        for i, (im, m) in enumerate(zip(ims, ms)):
+            g[f"{name}_applied_{i}"] = comp.apply(i, cs[i], im.copy(), m)
+    np.savez_compressed(os.path.join(HERE, "gain_cv2_goldens.npz"), **g)
+
+
+SEAM_SCENE = dict(n_cols=4, n_rows=1, w=400, h=300, f=300.0, step=0.62,
+                  pitches=[0.0], seed=23)
+
+
+def seam_scene():
+    """A registered 4-image row at the seam scale (the images double as
+    seam_est_imgs_, seam_work_aspect = 1) with per-image exposure errors."""
+    import math
+    import compose_oracle as co
+    import synth
+    c = SEAM_SCENE
+    hfov = 2 * math.atan(c["w"] / 2 / c["f"])
+    Ks, Rs = co.make_cameras(c["n_cols"], c["n_rows"], c["w"], c["h"], c["f"],
+                             c["step"] * hfov, c["pitches"], c["seed"], None)
+    ims = []
+    for i in range(len(Ks)):
+        t = synth.texture(c["h"], c["w"], 300 + i, 3, 8).astype(np.float32)
+        ims.append(np.clip(t * (0.8 + 0.12 * i), 0, 255).astype(np.uint8))
+    return ims, Ks, Rs
+
+
+def seam_goldens():
+    """Stitcher::EstimateSeams (stitcher.cc:241-296) with cv2 4.13.0 on
+    seam_scene(): corners, gain maps, the compensated warped images and the
+    GraphCutSeamFinder(COST_COLOR) masks."""
+    ims, Ks, Rs = seam_scene()
+    warper = cv2.PyRotationWarper("spherical", SEAM_SCENE["f"])
+    corners, warped, masks = [], [], []
+    for im, K, R in zip(ims, Ks, Rs):
+        k = np.asarray(K, np.float32)
+        c, iw = warper.warp(im, k, R, cv2.INTER_LINEAR, cv2.BORDER_REFLECT)
+        _, mw = warper.warp(np.full(im.shape[:2], 255, np.uint8), k, R,
+                            cv2.INTER_NEAREST, cv2.BORDER_CONSTANT)
+        corners.append(c)
+        warped.append(iw)
+        masks.append(mw)
+    comp = cv2.detail_BlocksGainCompensator()
+    comp.feed(corners, warped, masks)
+    warped = [comp.apply(i, corners[i], warped[i], masks[i])
+              for i in range(len(ims))]
+    g = {"corners": np.array(corners, np.int32)}
+    for i, gm in enumerate(comp.getMatGains()):
+        g[f"gain_{i}"] = np.ascontiguousarray(gm)
+        g[f"warped_{i}"] = warped[i]
+    finder = cv2.detail_GraphCutSeamFinder("COST_COLOR")
+    out = finder.find([w.astype(np.float32) for w in warped], corners, masks)
+    for i, m in enumerate(out):
+        g[f"seam_{i}"] = m.get() if hasattr(m, "get") else np.asarray(m)
+    np.savez_compressed(os.path.join(HERE, "seam_cv2_goldens.npz"), **g)
+
+
 def main():
     warp_goldens()
     portrait_goldens()
     crop_goldens()
+    gain_goldens()
+    seam_goldens()
     g = {}
     pos_png = [(-91, 204), (-167, 202), (-41, 193)]
     pos_tif = [(76, 11), (0, 9), (126, 0)]

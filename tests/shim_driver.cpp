@@ -6,7 +6,8 @@
 //   shim_driver <in.bin> <out.bin>
 // in : int32 n, w, h, projection; float32 scale; n x (K[9], R[9]) float32;
 //      n x (h*w*3) u8, rows padded to a step of w*3+12 bytes
-// out: int32 W, H, corner_x, corner_y of image 0; pano (H*W*3 u8); mask (H*W)
+// out: int32 W, H, corner_x, corner_y of image 0; pano (H*W*3 u8); mask (H*W);
+//      int32 gw, gh; gain map of image 0 (gh*gw float32)
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -51,6 +52,9 @@ int main(int argc, char** argv) {
     cv::Ptr<cv::WarperCreator> creator =
         cv::makePtr<b200::B200WarperCreator>(projection, false, 2.0f, 1.0f);
     cv::Ptr<cv::detail::Blender> blender = cv::makePtr<b200::B200Blender>();
+    // what stitcher.cc:200-201 would install
+    cv::Ptr<cv::detail::ExposureCompensator> exposure_comp =
+        cv::makePtr<b200::B200GainCompensator>();
     cv::Ptr<cv::detail::RotationWarper> warper = creator->create(scale);
     // ComputeRoi (stitcher.cc:144-169)
     long x0 = 1L << 40, y0 = 1L << 40, x1 = -(1L << 40), y1 = -(1L << 40);
@@ -62,18 +66,27 @@ int main(int argc, char** argv) {
       if (r.y + r.height > y1) y1 = r.y + r.height;
     }
     blender->prepare(cv::Rect((int)x0, (int)y0, (int)(x1 - x0), (int)(y1 - y0)));
-    cv::Point corner0;
-    for (int i = 0; i < n; ++i) {  // stitcher.cc:358-408
-      cv::Mat img_warped, mask, mask_warped;
-      cv::Point corner = warper->warp(imgs[i], Ks[i], Rs[i], cv::INTER_LINEAR,
-                                      cv::BORDER_REFLECT, img_warped);
+    // the exposure step of EstimateSeams (stitcher.cc:257-278), here at the
+    // compose scale: warp images and masks, feed the compensator
+    std::vector<cv::UMat> images_warped(n), masks_warped(n);
+    std::vector<cv::Point> corners(n);
+    for (int i = 0; i < n; ++i) {
+      cv::Mat mask;
+      corners[i] = warper->warp(imgs[i], Ks[i], Rs[i], cv::INTER_LINEAR,
+                                cv::BORDER_REFLECT, images_warped[i]);
       mask.create(h, w, CV_8U);
       for (int y = 0; y < h; ++y)
         for (int x = 0; x < w; ++x) mask.ptr<unsigned char>(y)[x] = 255;
       warper->warp(mask, Ks[i], Rs[i], cv::INTER_NEAREST, cv::BORDER_CONSTANT,
-                   mask_warped);
-      blender->feed(img_warped, mask_warped, corner);
-      if (i == 0) corner0 = corner;
+                   masks_warped[i]);
+    }
+    exposure_comp->feed(corners, images_warped, masks_warped);
+    std::vector<cv::Mat> gains;
+    exposure_comp->getMatGains(gains);
+    cv::Point corner0 = corners[0];
+    for (int i = 0; i < n; ++i) {  // stitcher.cc:358-408
+      exposure_comp->apply(i, corners[i], images_warped[i], masks_warped[i]);
+      blender->feed(images_warped[i], masks_warped[i], corners[i]);
     }
     cv::Mat result, result_mask;
     blender->blend(result, result_mask);  // stitcher.cc:419
@@ -92,6 +105,9 @@ int main(int argc, char** argv) {
       fwrite(result.ptr<unsigned char>(y), 1, (size_t)result.cols * 3, o);
     for (int y = 0; y < result_mask.rows; ++y)
       fwrite(result_mask.ptr<unsigned char>(y), 1, (size_t)result_mask.cols, o);
+    int gwh[2] = {gains[0].cols, gains[0].rows};
+    fwrite(gwh, sizeof(gwh), 1, o);
+    fwrite(gains[0].ptr<float>(), 4, gains[0].total(), o);
     fclose(o);
     // error convention: a second blend on a single-use blender, or feeding
     // after blend, throws std::runtime_error with the library's message

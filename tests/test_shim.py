@@ -1,5 +1,6 @@
 """The reference-side binding compiles and runs: include/xpano_b200_shim.hpp
-(B200Warper / B200WarperCreator / B200Blender, the classes INTEGRATION.md
+(B200Warper / B200WarperCreator / B200Blender / B200GainCompensator, the
+classes INTEGRATION.md
 tells a maintainer to add) is compiled against a stand-in for OpenCV's
 declarations (tests/cv_stub/, OpenCV's C++ headers are not in this image) and
 driven polymorphically like stitcher.cc:144-169, 357-419 drives the originals;
@@ -32,7 +33,8 @@ def build_native():
                          "-I", os.path.join(ROOT, "include"),
                          os.path.join(HERE, "shim_driver.cpp")],
          ["shim_driver.cpp", "../include/xpano_b200_shim.hpp",
-          "../include/xpano_b200.h", "cv_stub/opencv2/core.hpp"]),
+          "../include/xpano_b200.h", "cv_stub/opencv2/core.hpp",
+          "cv_stub/opencv2/stitching/detail/exposure_compensate.hpp"]),
         ("c_abi_smoke", ["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror",
                          "-O1", "-I", os.path.join(ROOT, "include"),
                          os.path.join(HERE, "c_abi_smoke.c")],
@@ -73,7 +75,9 @@ def test_shim_driver_equals_python_surface(tmp_path):
     n, w, h, scale = 4, 420, 300, 310.0
     K = np.array([[320, 0, w / 2], [0, 320, h / 2], [0, 0, 1]], np.float32)
     Rs = [_rot_y(0.5 * (i - 1.5)) for i in range(n)]
-    ims = [synth.texture(h, w, 500 + i, 3, 8) for i in range(n)]
+    ims = [np.clip(synth.texture(h, w, 500 + i, 3, 8).astype(np.float32)
+                   * (0.8 + 0.1 * i), 0, 255).astype(np.uint8)
+           for i in range(n)]  # exposures differ: the compensator has work
     fin, fout = tmp_path / "in.bin", tmp_path / "out.bin"
     with open(fin, "wb") as f:
         f.write(struct.pack("<4if", n, w, h, int(xb.ProjectionType.kSpherical),
@@ -88,18 +92,29 @@ def test_shim_driver_equals_python_surface(tmp_path):
     raw = np.fromfile(fout, np.uint8)
     W, H, cx, cy = (int(v) for v in raw[:16].view(np.int32))
     pano = raw[16:16 + W * H * 3].reshape(H, W, 3)
-    mask = raw[16 + W * H * 3:].reshape(H, W)
+    mask = raw[16 + W * H * 3:16 + W * H * 4].reshape(H, W)
+    tail = raw[16 + W * H * 4:]
+    gw, gh = (int(v) for v in tail[:8].view(np.int32))
+    gain0 = tail[8:8 + 4 * gw * gh].view(np.float32).reshape(gh, gw)
 
     warper = xb.PickWarper(xb.ProjectionType.kSpherical).create(scale)
     blender = xb.Multiblend(output_bpp=8)
     blender.prepare((0, 0, 1, 1))
-    corners = []
+    corners, warped, masks = [], [], []
     for im, R in zip(ims, Rs):
-        corner, warped = warper.warp(im, K, R)
+        corner, wi = warper.warp(im, K, R)
         _, mw = warper.warp(np.full((h, w), 255, np.uint8), K, R,
                             xb.INTER_NEAREST, xb.BORDER_CONSTANT)
-        blender.feed(warped, mw, corner)
         corners.append(corner)
+        warped.append(wi)
+        masks.append(mw)
+    comp = xb.BlocksGainCompensator()
+    comp.feed(corners, warped, masks)
+    assert np.array_equal(comp.getMatGains()[0], gain0)
+    assert gain0.min() < 0.99 or gain0.max() > 1.01
+    for i in range(n):
+        blender.feed(comp.apply(i, corners[i], warped[i], masks[i]), masks[i],
+                     corners[i])
     dst, dst_mask = blender.blend()
     assert (W, H) == dst.shape[1::-1] and (cx, cy) == corners[0]
     assert np.array_equal(mask, dst_mask)

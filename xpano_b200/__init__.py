@@ -7,6 +7,8 @@ from . import _lib  # noqa: F401
 from . import sharding  # noqa: F401
 from .auto_crop import FindLargestCrop  # noqa: F401
 from .blenders import Multiblend  # noqa: F401
+from .exposure import (BlocksGainCompensator, ComputeSeamScale,  # noqa
+                       EstimateSeams)
 from .stitcher import Composer, compose_panorama  # noqa: F401
 from .warpers import (BORDER_CONSTANT, BORDER_REFLECT, INTER_LINEAR,  # noqa
                       INTER_NEAREST, PickWarper, PickWarperPortrait,

@@ -155,6 +155,24 @@ SYMBOLS = {
     "xp_blender_auto_crop": (c_int, [c_void_p, c_void_p, c_void_p]),
     "xp_largest_crop_from_lines": (c_int, [c_void_p, c_int, c_int, c_void_p,
                                            c_void_p]),
+    "xp_gain_compensator_create": (c_int, [c_int, c_int, c_int, c_int,
+                                           c_void_p]),
+    "xp_gain_compensator_destroy": (None, [c_void_p]),
+    "xp_gain_compensator_feed": (c_int, [c_void_p, c_int, c_void_p, c_void_p,
+                                         c_void_p, c_void_p, c_void_p,
+                                         c_void_p, c_void_p, c_int]),
+    "xp_gain_compensator_plan": (c_int, [c_void_p, c_int, c_void_p, c_void_p,
+                                         c_void_p, c_void_p]),
+    "xp_gain_compensator_pairs": (c_int, [c_void_p, c_void_p]),
+    "xp_gain_compensator_solve": (c_int, [c_void_p, c_int, c_void_p, c_void_p,
+                                          c_void_p]),
+    "xp_gain_compensator_map_size": (c_int, [c_void_p, c_int, c_void_p]),
+    "xp_gain_compensator_get_map": (c_int, [c_void_p, c_int, c_void_p]),
+    "xp_gain_compensator_set_map": (c_int, [c_void_p, c_int, c_void_p, c_int,
+                                            c_int]),
+    "xp_gain_compensator_apply": (c_int, [c_void_p, c_int, c_void_p, c_int,
+                                          c_int, c_size_t, c_int, c_int]),
+    "xp_gain_compensator_stats": (c_int, [c_void_p, c_void_p]),
 }
 
 
