@@ -1,37 +1,108 @@
-"""Development probe: per-phase wall times of pipelined end-to-end steps."""
-import sys, os, time, threading
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np, torch
-import bench, xpano_b200 as xb
+"""Development probe: (1) pinned-memory copy rates of the box, each direction
+alone and both at once; (2) per-phase wall times of the pipelined end-to-end
+steps of bench.py (upload / wait for the compute turn / run / fetch)."""
+import os
+import sys
+import threading
+import time
 
-cfg = bench.CONFIGS["cfg2"]
-ims, Ks, Rs = bench.make_workload(cfg, 0)
-pinned = []
-for im in ims:
-    t = torch.empty(im.shape, dtype=torch.uint8, pin_memory=True); t.numpy()[...] = im; pinned.append(t)
-host = [t.numpy() for t in pinned]
-NF = int(sys.argv[1]) if len(sys.argv) > 1 else 2
-comps = [xb.Composer(projection=cfg["projection"], warp_scale=cfg["focal"], max_pano_mpx=cfg["max_pano_mpx"],
-                     depth=cfg["bpp"], fixed_levels=cfg["fixed_levels"], device=0) for _ in range(NF)]
-comps[0].set_images(host, Ks, Rs); info = comps[0].run()
-W, H = info["width"], info["height"]
-outs = [(torch.empty((H, W, 3), dtype=torch.uint8, pin_memory=True), torch.empty((H, W), dtype=torch.uint8, pin_memory=True)) for _ in range(NF)]
-log = []
-turn = threading.Lock()
-def worker(j, n):
-    for k in range(n):
-        a = time.perf_counter(); comps[j].set_images(host, Ks, Rs)
-        b = time.perf_counter()
-        with turn:
-            b2 = time.perf_counter(); comps[j].run()
-        c = time.perf_counter(); comps[j].fetch(outs[j][0].numpy(), outs[j][1].numpy())
-        d = time.perf_counter(); log.append((j, k, a, b, c, d, b2))
-for rep in range(2):
-    log.clear()
-    torch.cuda.synchronize(); t0 = time.perf_counter()
-    ts = [threading.Thread(target=worker, args=(j, 4)) for j in range(NF)]
-    [t.start() for t in ts]; [t.join() for t in ts]
-    torch.cuda.synchronize(); t1 = time.perf_counter()
-print("in flight", NF, "ms per pano", 1e3 * (t1 - t0) / (4 * NF))
-for j, k, a, b, c, d, b2 in sorted(log, key=lambda r: r[2]):
-    print(f"thr {j} step {k}: start {1e3*(a-t0):7.2f} upload {1e3*(b-a):6.2f} wait {1e3*(b2-b):6.2f} run {1e3*(c-b2):6.2f} fetch {1e3*(d-c):6.2f}")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+import bench  # noqa: E402
+import xpano_b200 as xb  # noqa: E402
+
+
+def copy_rates():
+    n = 256 << 20
+    hin = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    hout = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    din = torch.empty(n, dtype=torch.uint8, device="cuda")
+    dout = torch.empty(n, dtype=torch.uint8, device="cuda")
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def run(up, down, reps=8):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            if up:
+                with torch.cuda.stream(s1):
+                    din.copy_(hin, non_blocking=True)
+            if down:
+                with torch.cuda.stream(s2):
+                    hout.copy_(dout, non_blocking=True)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        return reps * n / dt / 1e9
+    run(True, True, 2)
+    print(f"pinned copies: H2D alone {run(True, False):.1f} GB/s, "
+          f"D2H alone {run(False, True):.1f} GB/s, both at once "
+          f"{run(True, True):.1f} GB/s each")
+
+
+def main():
+    NF = int(sys.argv[1]) if len(sys.argv) > 1 else 3
+    copy_rates()
+    cfg = bench.CONFIGS["cfg2"]
+    wl = bench.make_workload(cfg, 0, "graphcut")
+    keep = bench.pin_images(torch, wl["ims"])
+    host = [t.numpy() for t in keep]
+    Ks, Rs = wl["Ks"], wl["Rs"]
+    mk = lambda: xb.Composer(projection=cfg["projection"],  # noqa: E731
+                             warp_scale=cfg["focal"],
+                             max_pano_mpx=cfg["max_pano_mpx"],
+                             depth=cfg["bpp"],
+                             fixed_levels=cfg["fixed_levels"], device=0)
+    comps = [mk() for _ in range(NF)]
+    comps[0].set_images(host, Ks, Rs, wl["gains"], wl["seams"])
+    info = comps[0].run()
+    W, H = info["width"], info["height"]
+    outs = [(torch.empty((H, W, 3), dtype=torch.uint8, pin_memory=True),
+             torch.empty((H, W), dtype=torch.uint8, pin_memory=True))
+            for _ in range(NF)]
+    log = []
+    turn = threading.Lock()
+    STEPS = 4
+
+    def worker(j):
+        for k in range(STEPS):
+            a = time.perf_counter()
+            comps[j].set_images(host, Ks, Rs, wl["gains"], wl["seams"])
+            b = time.perf_counter()
+            with turn:
+                b2 = time.perf_counter()
+                comps[j].run()
+                c = time.perf_counter()
+            comps[j].fetch(outs[j][0].numpy(), outs[j][1].numpy())
+            d = time.perf_counter()
+            log.append((j, k, a, b, c, d, b2))
+    for rep in range(2):
+        log.clear()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ts = [threading.Thread(target=worker, args=(j,)) for j in range(NF)]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+    print("in flight", NF, "ms per pano", 1e3 * (t1 - t0) / (STEPS * NF))
+    for j, k, a, b, c, d, b2 in sorted(log, key=lambda r: r[2]):
+        print(f"thr {j} step {k}: start {1e3 * (a - t0):7.2f} upload "
+              f"{1e3 * (b - a):6.2f} wait {1e3 * (b2 - b):6.2f} run "
+              f"{1e3 * (c - b2):6.2f} fetch {1e3 * (d - c):6.2f}")
+    # each phase alone
+    for name, fn in (("upload", lambda: comps[0].set_images(
+            host, Ks, Rs, wl["gains"], wl["seams"])),
+                     ("run", comps[0].run),
+                     ("fetch", lambda: comps[0].fetch(outs[0][0].numpy(),
+                                                      outs[0][1].numpy()))):
+        fn()
+        t0 = time.perf_counter()
+        for _ in range(5):
+            fn()
+        print(f"{name} alone: {1e3 * (time.perf_counter() - t0) / 5:.2f} ms")
+
+
+if __name__ == "__main__":
+    main()
