@@ -797,15 +797,15 @@ def run_ours(args, cfg):
     value = total_mp * args.steps / (ms / 1e3)
 
     # ---- e2e leg: host buffers in, host panorama out, every step -----------
-    # Batch export keeps two panoramas in flight (one composer, stream and
-    # pinned output buffer each, driven by two host threads through the
-    # synchronous public API), so the upload of one overlaps the kernels and
-    # the download of the other. Every step still uploads its own inputs and
+    # Batch export keeps several panoramas in flight (one composer, stream and
+    # pinned output buffer each, driven by one host thread each through the
+    # public API), so the upload of one overlaps the kernels of another and
+    # the download of a third. Every step still uploads its own inputs and
     # downloads its own result inside the timed region.
     import threading
     W, H = info["width"], info["height"]
     dt = torch.uint8 if info["bpp"] == 8 else torch.uint16
-    in_flight = 3
+    in_flight = max(1, args.in_flight)
     comps = [comp]
     for _ in range(in_flight - 1):
         c2 = xb.Composer(projection=cfg["projection"],
@@ -822,12 +822,14 @@ def run_ours(args, cfg):
         a.nbytes for k in ("gains", "seams") if wl[k] is not None
         for a in wl[k])
     d2h = outs[0][0].nbytes + outs[0][1].nbytes
-    e2e_steps = min(max(args.steps, 2 * in_flight), 12)
+    e2e_steps = max(args.steps, 2 * in_flight)
 
-    # one panorama computes while the others upload / download. Letting two
-    # compute at once is slower (measured: 11.3 -> 13.0 ms per panorama): the
-    # seam wavefronts are latency chains and every co-resident warp on their
-    # SMs stretches each step.
+    # one panorama at a time runs its warps and seam passes, while the others
+    # upload / download. Letting two do that at once is slower (measured:
+    # 11.3 -> 13.0 ms per panorama): the seam wavefronts are latency chains
+    # and every co-resident warp on their SMs stretches each step. The turn is
+    # handed over at run_begin's return, when only the bandwidth-bound pyramid
+    # tail of the panorama is still queued: it overlaps the next one's warps.
     compute_turn = threading.Lock()
 
     def e2e_worker(j, n_steps, errs):
@@ -836,7 +838,8 @@ def run_ours(args, cfg):
             for _ in range(j, n_steps, in_flight):
                 comps[j].set_images(host, Ks, Rs, wl["gains"], wl["seams"])
                 with compute_turn:
-                    comps[j].run()
+                    comps[j].run_begin()
+                comps[j].run_end()
                 comps[j].fetch(outs[j][0], outs[j][1])
         except Exception as e:  # surfaced after join
             errs.append(e)
@@ -1007,6 +1010,9 @@ def main():
                     choices=["graphcut", "full", "none"],
                     help="seam masks fed to the path (SURVEY.md 8d)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--in-flight", type=int, default=4,
+                    help="panoramas in flight in the end-to-end leg (one "
+                    "composer, host thread and pinned output buffer each)")
     ap.add_argument("--tiled", action="store_true",
                     help="N > 1: ONE panorama over all GPUs as canvas strips "
                     "(strong scaling; use with --config cfg3) instead of one "

@@ -323,6 +323,16 @@ xp_status xp_composer_set_images(xp_composer* c, int n,
 xp_status xp_composer_set_cancel_flag(xp_composer* c, const volatile int* flag);
 /* Run warp -> feed -> blend on the device; result stays resident. */
 xp_status xp_composer_run(xp_composer* c, xp_compose_info* info);
+/* The same in two halves, for a batch export that keeps several panoramas
+ * in flight on one GPU (stitcher_pipeline.h:48-52 hands the pipeline one
+ * group after another): run_begin returns once the last kernel is queued --
+ * after the blend's last host round trip, while its pyramid tail is still
+ * running -- and run_end (or xp_composer_fetch) waits for it. Between the
+ * two, another composer's run_begin may start on the same GPU: its warps and
+ * seam passes overlap this panorama's bandwidth-bound tail. info may be
+ * NULL. */
+xp_status xp_composer_run_begin(xp_composer* c);
+xp_status xp_composer_run_end(xp_composer* c, xp_compose_info* info);
 /* Canvas tiling of ONE panorama over `count` GPUs (SURVEY.md section 8e;
  * no counterpart in the reference, whose ComposePanorama runs on one thread,
  * stitcher_pipeline.cc:340-344): every rank creates the same composer, calls

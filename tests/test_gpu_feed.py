@@ -247,6 +247,73 @@ def test_compose_cancellation_between_images():
     assert pano.shape[:2] == (info["height"], info["width"]) and mask.any()
 
 
+def test_run_in_two_halves_and_panoramas_in_flight():
+    """run_begin / run_end (the batch-export form of xp_composer_run): the
+    same panorama bit for bit; fetch completes a pending run; three composers
+    driven by three host threads with the compute turn handed over at
+    run_begin's return (bench.py's end-to-end leg) each give the panorama of a
+    lone run; misuse is rejected."""
+    import threading
+    import xpano_b200 as xb
+    n_cols, w_, h_, f = 4, 400, 300, 300.0
+    hfov = 2 * math.atan(w_ / 2 / f)
+    Ks, Rs = co.make_cameras(n_cols, 1, w_, h_, f, 0.6 * hfov, [0.0], 9, None)
+    sets = [[synth.texture(h_, w_, 700 + 10 * k + i, 3, 8)
+             for i in range(n_cols)] for k in range(3)]
+    mk = lambda: xb.Composer(projection=wo.SPHERICAL, warp_scale=f,  # noqa
+                             fixed_levels=5)
+    want = []
+    for ims in sets:
+        c = mk()
+        c.set_images(ims, Ks, Rs)
+        c.run()
+        want.append(c.fetch())
+    c = mk()
+    with pytest.raises(xb._lib.XpError):
+        c.run_end()                        # nothing begun
+    c.set_images(sets[0], Ks, Rs)
+    c.run_begin()
+    with pytest.raises(xb._lib.XpError):
+        c.run_begin()                      # not ended yet
+    with pytest.raises(xb._lib.XpError):
+        c.set_images(sets[1], Ks, Rs)
+    info = c.run_end()
+    pano, mask = c.fetch()
+    assert (info["width"], info["height"]) == pano.shape[1::-1]
+    assert np.array_equal(pano, want[0][0]) and np.array_equal(mask, want[0][1])
+    c.set_images(sets[1], Ks, Rs)
+    c.run_begin()
+    pano, mask = c.fetch()                 # completes the run
+    assert np.array_equal(pano, want[1][0]) and np.array_equal(mask, want[1][1])
+
+    comps = [mk() for _ in range(3)]
+    turn = threading.Lock()
+    got = [[None] * 4 for _ in range(3)]
+    errs = []
+
+    def worker(j):
+        try:
+            for rep in range(4):
+                k = (j + rep) % 3
+                comps[j].set_images(sets[k], Ks, Rs)
+                with turn:
+                    comps[j].run_begin()
+                comps[j].run_end()
+                got[j][rep] = (k,) + comps[j].fetch()
+        except Exception as e:  # pragma: no cover
+            errs.append(e)
+    ts = [threading.Thread(target=worker, args=(j,)) for j in range(3)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errs, errs
+    for j in range(3):
+        for k, pano, mask in got[j]:
+            assert np.array_equal(pano, want[k][0])
+            assert np.array_equal(mask, want[k][1])
+
+
 def test_mask_in_the_reference_rle_format():
     """Result.full_mask as utils::Flex words (mb/flex.h, flex.cpp:78-98),
     decoded the way xpano's ToMat does (blenders.cc:38-62)."""

@@ -14,6 +14,9 @@ import bench  # noqa: E402
 import xpano_b200 as xb  # noqa: E402
 
 
+SPLIT = False
+
+
 def copy_rates():
     n = 256 << 20
     hin = torch.empty(n, dtype=torch.uint8, pin_memory=True)
@@ -43,6 +46,8 @@ def copy_rates():
 
 def main():
     NF = int(sys.argv[1]) if len(sys.argv) > 1 else 3
+    global SPLIT
+    SPLIT = len(sys.argv) > 2 and sys.argv[2] == "split"
     copy_rates()
     cfg = bench.CONFIGS["cfg2"]
     wl = bench.make_workload(cfg, 0, "graphcut")
@@ -72,11 +77,18 @@ def main():
             b = time.perf_counter()
             with turn:
                 b2 = time.perf_counter()
-                comps[j].run()
+                if SPLIT:
+                    comps[j].run_begin()
+                else:
+                    inf = comps[j].run()
                 c = time.perf_counter()
+            if SPLIT:
+                inf = comps[j].run_end()
             comps[j].fetch(outs[j][0].numpy(), outs[j][1].numpy())
             d = time.perf_counter()
-            log.append((j, k, a, b, c, d, b2))
+            tm = inf["timing"]
+            log.append((j, k, a, b, c, d, b2, inf["warp_ms"], tm["total"],
+                        tm["seam"], tm["pyramid_tail"]))
     for rep in range(2):
         log.clear()
         torch.cuda.synchronize()
@@ -87,10 +99,13 @@ def main():
         torch.cuda.synchronize()
         t1 = time.perf_counter()
     print("in flight", NF, "ms per pano", 1e3 * (t1 - t0) / (STEPS * NF))
-    for j, k, a, b, c, d, b2 in sorted(log, key=lambda r: r[2]):
+    for j, k, a, b, c, d, b2, wm, tot, seam, tail in sorted(
+            log, key=lambda r: r[2]):
         print(f"thr {j} step {k}: start {1e3 * (a - t0):7.2f} upload "
               f"{1e3 * (b - a):6.2f} wait {1e3 * (b2 - b):6.2f} run "
-              f"{1e3 * (c - b2):6.2f} fetch {1e3 * (d - c):6.2f}")
+              f"{1e3 * (c - b2):6.2f} (device: warp {wm:.2f} + blend "
+              f"{tot:.2f}, seam {seam:.2f}, tail {tail:.2f}) fetch "
+              f"{1e3 * (d - c):6.2f}")
     # each phase alone
     for name, fn in (("upload", lambda: comps[0].set_images(
             host, Ks, Rs, wl["gains"], wl["seams"])),

@@ -150,6 +150,8 @@ SYMBOLS = {
     "xp_composer_fetch": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p,
                                   c_size_t, c_int]),
     "xp_composer_blender": (c_void_p, [c_void_p]),
+    "xp_composer_run_begin": (c_int, [c_void_p]),
+    "xp_composer_run_end": (c_int, [c_void_p, c_void_p]),
     "xp_find_largest_crop": (c_int, [c_void_p, c_int, c_int, c_size_t, c_int,
                                      c_int, c_void_p, c_void_p]),
     "xp_blender_auto_crop": (c_int, [c_void_p, c_void_p, c_void_p]),

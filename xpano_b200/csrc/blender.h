@@ -110,7 +110,10 @@ struct Blender {
   void feed(const void* data, size_t stride, const uint8_t* mask,
             size_t mask_stride, int w, int h, int depth, int spp, int tl_x,
             int tl_y, int mem);
-  void blend(xp_timing* timing);
+  void blend(xp_timing* timing);        // blend_launch + blend_finish
+  void blend_launch();
+  void blend_finish(xp_timing* timing);
+  bool launch_pending = false;
   void blend_tile_begin(double partial[8]);
   void blend_tile_end(const double reduced[8], xp_timing* timing);
   void fetch(void* dst_bgr, size_t dst_stride, uint8_t* dst_mask,

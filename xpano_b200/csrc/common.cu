@@ -262,20 +262,30 @@ void copy_in_2d(void* dev, size_t dev_pitch, const void* user,
                 size_t user_pitch, size_t row_bytes, size_t rows, int mem,
                 cudaStream_t s) {
   if (rows == 0 || row_bytes == 0) return;
-  XP_CUDA(cudaMemcpy2DAsync(
-      dev, dev_pitch, user, user_pitch, row_bytes, rows,
-      mem == XP_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
-      s));
+  const cudaMemcpyKind kind =
+      mem == XP_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  // packed on both sides: one linear copy (the 2-D form is submitted row
+  // group by row group and holds the driver's lock for longer)
+  if (dev_pitch == row_bytes && user_pitch == row_bytes) {
+    XP_CUDA(cudaMemcpyAsync(dev, user, row_bytes * rows, kind, s));
+    return;
+  }
+  XP_CUDA(cudaMemcpy2DAsync(dev, dev_pitch, user, user_pitch, row_bytes, rows,
+                            kind, s));
 }
 
 void copy_out_2d(void* user, size_t user_pitch, const void* dev,
                  size_t dev_pitch, size_t row_bytes, size_t rows, int mem,
                  cudaStream_t s) {
   if (rows == 0 || row_bytes == 0) return;
-  XP_CUDA(cudaMemcpy2DAsync(
-      user, user_pitch, dev, dev_pitch, row_bytes, rows,
-      mem == XP_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost,
-      s));
+  const cudaMemcpyKind kind =
+      mem == XP_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+  if (dev_pitch == row_bytes && user_pitch == row_bytes) {
+    XP_CUDA(cudaMemcpyAsync(user, dev, row_bytes * rows, kind, s));
+    return;
+  }
+  XP_CUDA(cudaMemcpy2DAsync(user, user_pitch, dev, dev_pitch, row_bytes, rows,
+                            kind, s));
 }
 
 cudaStream_t create_stream(bool high_priority) {

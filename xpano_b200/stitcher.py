@@ -140,6 +140,17 @@ class Composer:
         check(self._lib.xp_composer_run(self._h, ctypes.byref(info)))
         return self._set_info(info)
 
+    def run_begin(self):
+        """First half of run(): returns when the panorama's last kernel is
+        queued; another composer may start its own run on the same GPU."""
+        check(self._lib.xp_composer_run_begin(self._h))
+
+    def run_end(self):
+        """Second half of run(): waits for the panorama; -> info."""
+        info = _lib.ComposeInfo()
+        check(self._lib.xp_composer_run_end(self._h, ctypes.byref(info)))
+        return self._set_info(info)
+
     def _set_info(self, info):
         self.info = {
             "width": info.width, "height": info.height, "min_x": info.min_x,
