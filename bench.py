@@ -831,16 +831,22 @@ def run_ours(args, cfg):
     # handed over at run_begin's return, when only the bandwidth-bound pyramid
     # tail of the panorama is still queued: it overlaps the next one's warps.
     compute_turn = threading.Lock()
+    # each direction of the bus is one resource: two uploads at once only
+    # finish later, both of them, so transfers take turns as well
+    upload_turn, fetch_turn = threading.Lock(), threading.Lock()
 
     def e2e_worker(j, n_steps, errs):
         try:
             torch.cuda.set_device(local)
             for _ in range(j, n_steps, in_flight):
-                comps[j].set_images(host, Ks, Rs, wl["gains"], wl["seams"])
+                with upload_turn:
+                    comps[j].set_images(host, Ks, Rs, wl["gains"],
+                                        wl["seams"])
                 with compute_turn:
                     comps[j].run_begin()
                 comps[j].run_end()
-                comps[j].fetch(outs[j][0], outs[j][1])
+                with fetch_turn:
+                    comps[j].fetch(outs[j][0], outs[j][1])
         except Exception as e:  # surfaced after join
             errs.append(e)
 
