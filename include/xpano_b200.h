@@ -120,7 +120,14 @@ xp_status xp_warper_warp(xp_warper* w, const void* src, int src_w, int src_h,
  *    scratch of the warp, the per-column and per-row trig table of a separable
  *    projection, lives in a static device array of
  *    XP_NOALLOC_MAX_ROI_PERIMETER float2 entries (512 KiB, held by every GPU
- *    that loads the library until exit);
+ *    that loads the library until exit). Its values -- width + height sines
+ *    and cosines -- are formed on the host with the host's libm, as in
+ *    xp_warper_warp (the maps are OpenCV's bit for bit that way), in a static
+ *    host array, and reach the device array as one pageable
+ *    cudaMemcpyAsync of at most 512 KiB on `cuda_stream` (no allocation; not
+ *    capturable in a CUDA graph -- XP_HOST_TABLES=0 in the environment makes
+ *    the device evaluate the table instead, last-bit differences in ~7 % of
+ *    the map values);
  *  - limits: spherical and cylindrical projections only (their ROI is host
  *    arithmetic); result ROI width + height <= XP_NOALLOC_MAX_ROI_PERIMETER,
  *    larger ones fail with XP_ERR_INVALID and a message naming the limit;

@@ -2,9 +2,12 @@
 ABI, against the warp oracle (oracle/warp_oracle.c, pinned bit-exact against
 cv2 4.13.0 vectors in tests/test_oracle_warp.py) and the cv2 goldens.
 
-Bars (BASELINE.json north_star), written as the thresholds below: ROIs and
-warped masks bit-exact except where a map value differs in the last bit
-exactly at a rounding boundary (< 1e-4 of pixels); maps within 5e-5 relative;
+Bars (BASELINE.json north_star), written as the thresholds below. The
+separable projections (spherical, cylindrical, Mercator -- the sines and
+cosines of their maps come from the host's libm, like OpenCV's): maps, warped
+masks and warped pixels bit-exact. The other projections (device libm): ROIs
+and warped masks bit-exact except where a map value differs in the last bit
+exactly at a rounding boundary (< 1e-4 of pixels); maps within 2e-5 relative;
 warped pixels within 1 LSB (8-bit) / 1e-3 relative (16-bit) at every pixel;
 composed panorama within 1 LSB (8-bit) / 1e-3 relative (16-bit) at >= 99.9 %
 of pixels and PSNR >= 50 dB.
@@ -70,6 +73,8 @@ def test_roi_maps_points_vs_cv2_goldens(g, name):
     # relative to the magnitude of the coordinate (float32 ulps grow with it)
     mag = np.maximum(1.0, np.maximum(np.abs(gx), np.abs(gy)))
     assert (np.maximum(dx, dy)[ok] / mag[ok]).max() < 2e-5
+    if name in ("spherical", "cylindrical", "mercator", "plane"):
+        assert exact == 1.0  # trig from the host's libm, the rest is IEEE
     pt = np.array(w.warpPoint((123.5, 77.25), K, R), np.float32)
     assert np.array_equal(pt, g[f"pt_{name}"])  # host libm: bit-exact
 
@@ -87,15 +92,13 @@ def test_warp_vs_cv2_goldens(g, name):
     mdiff = float((m != g[f"warpmask_{name}"]).mean())
     _note(f"warp8_{name}", max_diff=int(d.max()), frac=float((d > 0).mean()),
           mask_diff_fraction=mdiff)
-    assert d.max() <= 1 and (d > 0).mean() < 1e-3
-    assert mdiff < 1e-4
+    assert d.max() == 0 and mdiff == 0.0   # bit-exact against cv2
     if name == "spherical":
         _, d16 = w.warp(g["src16"], K, R)
         d = np.abs(d16.astype(int) - g["warp16_spherical"].astype(int))
-        tol = np.maximum(1, 1e-3 * g["warp16_spherical"].astype(int))
         _note("warp16_spherical", max_diff=int(d.max()),
               frac=float((d > 0).mean()))
-        assert (d <= tol).all() and (d > 0).mean() < 1e-3
+        assert d.max() == 0
 
 
 PORTRAIT_PROJ = {"planePortrait": wo.PLANE, "cylindricalPortrait":
@@ -126,6 +129,8 @@ def test_portrait_warpers_vs_goldens(g, key):
     dy = np.abs(ym[::WARP_STEP, ::WARP_STEP] - gy)
     mag = np.maximum(1.0, np.maximum(np.abs(gx), np.abs(gy)))
     assert (np.maximum(dx, dy)[ok] / mag[ok]).max() < 2e-5
+    if name in ("spherical", "cylindrical", "mercator", "plane"):
+        assert exact == 1.0  # trig from the host's libm, the rest is IEEE
     pt = np.array(w.warpPoint((123.5, 77.25), K, R), np.float32)
     assert np.array_equal(pt, gp[f"pt_{key}"])
     corner, d8 = w.warp(g["src8"], K, R)

@@ -361,6 +361,14 @@ struct Composer {
   // whose colours cannot reach this rank's strip)
   void warp_all() {
     xp_blend_opts bo = opts.blend;
+    {  // the stream is idle here (the previous run ended, set_images waited):
+       // the warper's host-side table slots of the previous run are free
+      size_t tab = 0;
+      for (size_t i = 0; i < src.size(); ++i)
+        tab += 16 + sizeof(float2) * ((size_t)plan.rois[4 * i + 2] +
+                                      (size_t)plan.rois[4 * i + 3]);
+      warper.tab_reset(tab);
+    }
     blender.reset(new Blender(bo));
     blender->stream = stream;
     blender->external_stream = true;

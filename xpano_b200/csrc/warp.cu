@@ -365,6 +365,14 @@ __global__ void sep_tables_kernel(Projector p, int tlx, int tly, int W, int H,
   }
 }
 
+// tables evaluated on the host (see Warper::prepare_map): pinned, mapped
+// memory -> device, without a copy engine
+__global__ void tables_from_host_kernel(const float2* __restrict__ src,
+                                        float2* __restrict__ dst, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = src[i];
+}
+
 __device__ __forceinline__ void eval_map(const MapSrc& m, int dx, int dy,
                                          float& x, float& y) {
   if (m.separable) {
@@ -700,6 +708,18 @@ static void grow_scratch(DevBuf& b, size_t n, cudaStream_t s) {
   b.reserve(n);
 }
 
+static bool host_trig_tables() {
+  static const bool on = [] {
+    const char* e = getenv("XP_HOST_TABLES");
+    return e ? atoi(e) != 0 : true;
+  }();
+  return on;
+}
+
+void Warper::tab_reset(size_t bytes) {
+  tab_box.reset(std::max(tab_box.cap, std::max(bytes, (size_t)1 << 20)));
+}
+
 MapSrc Warper::prepare_map(const Projector& p, const int roi[4]) {
   MapSrc m;
   m.p = p;
@@ -712,9 +732,38 @@ MapSrc Warper::prepare_map(const Projector& p, const int roi[4]) {
     grow_scratch(tables, sizeof(float2) * (size_t)(W + H), stream);
     float2* col = tables.as<float2>();
     float2* row = col + W;
-    sep_tables_kernel<<<div_up(W + H, 256), 256, 0, stream>>>(p, roi[0],
-                                                               roi[1], W, H,
-                                                               col, row);
+    if (host_trig_tables()) {
+      // The W + H sines and cosines of a separable projection come from the
+      // host's libm -- the one OpenCV's projectors call (warpers_inl.hpp:
+      // sinf / cosf) -- so the inverse map is the reference's bit for bit;
+      // CUDA's sinf / cosf differ from glibc's in the last bit for ~7 % of
+      // the arguments, which moves a handful of mask pixels per panorama.
+      // Everything per pixel (sep_combine: products, the K R^-1 transform,
+      // one division) is IEEE arithmetic on both sides.
+      const size_t bytes = sizeof(float2) * (size_t)(W + H);
+      if (tab_box.cap - tab_box.used < ((bytes + 15) & ~(size_t)15)) {
+        XP_CUDA(cudaStreamSynchronize(stream));
+        tab_box.reset(std::max(bytes * 4, (size_t)1 << 20));
+      }
+      float2* h = static_cast<float2*>(tab_box.take(bytes));
+      for (int i = 0; i < W; ++i) {
+        float S, C;
+        sep_col(p, (float)(i + roi[0]), S, C);
+        h[i] = make_float2(S, C);
+      }
+      for (int j = 0; j < H; ++j) {
+        float A, B;
+        sep_row(p, (float)(j + roi[1]), A, B);
+        h[W + j] = make_float2(A, B);
+      }
+      void* dh = nullptr;
+      XP_CUDA(cudaHostGetDevicePointer(&dh, h, 0));
+      tables_from_host_kernel<<<div_up(W + H, 256), 256, 0, stream>>>(
+          static_cast<const float2*>(dh), col, W + H);
+    } else {
+      sep_tables_kernel<<<div_up(W + H, 256), 256, 0, stream>>>(
+          p, roi[0], roi[1], W, H, col, row);
+    }
     XP_LAUNCHED();
     m.col = col;
     m.row = row;
@@ -1065,9 +1114,31 @@ void warp_noalloc(const Warper& wr, const void* d_src, int sw, int sh,
   float2* row = col + W;
   // every entry that is read (W + H of them) is written here first: nothing
   // carried over from the previous call is used
-  sep_tables_kernel<<<div_up(W + H, 256), 256, 0, stream>>>(p, roi[0], roi[1],
-                                                             W, H, col, row);
-  XP_LAUNCHED();
+  if (host_trig_tables()) {
+    // as in Warper::prepare_map, the sines and cosines come from the host's
+    // libm; they are formed in a static host array (plain memory, no
+    // allocation) and handed to the driver as a pageable copy, which has
+    // taken the bytes when the call returns
+    static std::mutex mu;
+    static float2 h_tab[kNoAllocTableEntries];
+    std::lock_guard<std::mutex> lk(mu);
+    for (int i = 0; i < W; ++i) {
+      float S, C;
+      sep_col(p, (float)(i + roi[0]), S, C);
+      h_tab[i] = make_float2(S, C);
+    }
+    for (int j = 0; j < H; ++j) {
+      float A, B;
+      sep_row(p, (float)(j + roi[1]), A, B);
+      h_tab[W + j] = make_float2(A, B);
+    }
+    XP_CUDA(cudaMemcpyAsync(col, h_tab, sizeof(float2) * (size_t)(W + H),
+                            cudaMemcpyHostToDevice, stream));
+  } else {
+    sep_tables_kernel<<<div_up(W + H, 256), 256, 0, stream>>>(
+        p, roi[0], roi[1], W, H, col, row);
+    XP_LAUNCHED();
+  }
   m.col = col;
   m.row = row;
   dim3 b(32, 8);

@@ -18,6 +18,12 @@ struct Warper {
   DevBuf scratch, tables, aux_tables, staging_src, staging_dst, dilated,
       aux_gain,
       aux_seam;
+  // Host-side trig tables of the separable projections (prepare_map): pinned,
+  // mapped memory the table kernel reads; a slot per call until tab_reset().
+  Mailbox tab_box;
+  // the stream is idle: every slot of tab_box may be reused (with room for
+  // `bytes` more)
+  void tab_reset(size_t bytes);
 
   ~Warper();
   void ensure_device();
