@@ -447,6 +447,34 @@ xp_status xp_gain_compensator_apply(const xp_gain_compensator* g, int index,
  * last feed */
 xp_status xp_gain_compensator_stats(const xp_gain_compensator* g, int out[3]);
 
+/* ------------------------------------------------------------------------
+ * xpano's second blender, blenders::MultiBandOpenCV (xpano/algorithm/
+ * blenders.h:41-50, blenders.cc:160-175; BlendingMethod::kOpenCV,
+ * algorithm.cc:135-136): cv::detail::MultiBandBlender(false, num_bands = 5,
+ * CV_32F) fed with CV_16SC3 images, result converted to CV_8U.
+ * SURVEY.md 8(f4).
+ *   prepare: MultiBandBlender::prepare(dst_roi)      (stitcher.cc:357)
+ *   feed   : MultiBandOpenCV::feed(img CV_8UC3, mask CV_8U, tl) -- the
+ *            conversion to CV_16S of blenders.cc:164 included; mask / 255 is
+ *            the weight                                (stitcher.cc:405)
+ *   blend  : MultiBandOpenCV::blend                  (stitcher.cc:419)
+ *   fetch  : dst (h x w x 3 u8, zero outside the mask) and dst_mask
+ *            (255 where the accumulated weight exceeds 1e-5)
+ * Integer pyramids as OpenCV's, see csrc/mbcv.cu. strides in bytes, 0 =
+ * packed.
+ * ---------------------------------------------------------------------- */
+typedef struct xp_multiband xp_multiband;
+xp_status xp_multiband_create(int num_bands, int device, xp_multiband** out);
+void xp_multiband_destroy(xp_multiband* b);
+xp_status xp_multiband_prepare(xp_multiband* b, int x, int y, int w, int h);
+xp_status xp_multiband_feed(xp_multiband* b, const void* bgr, size_t stride,
+                            const uint8_t* mask, size_t mask_stride, int w,
+                            int h, int tl_x, int tl_y, int mem);
+/* num_bands: the band count prepare() settled on (may be NULL) */
+xp_status xp_multiband_blend(xp_multiband* b, int out_wh[2], int* num_bands);
+xp_status xp_multiband_fetch(xp_multiband* b, void* dst_bgr, size_t dst_stride,
+                             uint8_t* dst_mask, size_t mask_stride, int mem);
+
 /* Device buffers are cached across objects (a blender is single-use, like the
  * reference's); this returns the cached blocks to the driver. */
 void xp_trim_memory(void);

@@ -8,8 +8,10 @@
 //        stitcher.cc:160, 265, 269, 377, 384; gui/widgets/rotate.cc:94-372)
 //   cv::detail::Blender
 //       (Stitcher::SetBlender, stitcher.h:205-207, installed from algorithm.cc:269-270;
-//        calls at stitcher.cc:357, 405, 419; replaces blenders::Multiblend,
-//        xpano/algorithm/blenders.h:25-39)
+//        calls at stitcher.cc:357, 405, 419; B200Blender replaces
+//        blenders::Multiblend, xpano/algorithm/blenders.h:25-39, and
+//        B200MultiBandBlender replaces blenders::MultiBandOpenCV,
+//        blenders.h:41-50, the BlendingMethod::kOpenCV choice)
 //   cv::detail::ExposureCompensator
 //       (Stitcher::SetExposureCompensator, stitcher.h:188-191, installed from
 //        stitcher.cc:200-201; calls at stitcher.cc:274, 276, 389; replaces
@@ -173,6 +175,43 @@ class B200Blender : public cv::detail::Blender {
 
  private:
   xp_blender* b_ = nullptr;
+};
+
+// BlendingMethod::kOpenCV (algorithm.cc:135-136): OpenCV's MultiBandBlender
+// with xpano's CV_16S feed and CV_8U result (blenders.cc:160-175)
+class B200MultiBandBlender : public cv::detail::Blender {
+ public:
+  explicit B200MultiBandBlender(int num_bands = 5, int device = 0) {
+    Check(xp_multiband_create(num_bands, device, &b_));
+  }
+  ~B200MultiBandBlender() override { xp_multiband_destroy(b_); }
+  B200MultiBandBlender(const B200MultiBandBlender&) = delete;
+  B200MultiBandBlender& operator=(const B200MultiBandBlender&) = delete;
+
+  void prepare(cv::Rect dst_roi) override {
+    Check(xp_multiband_prepare(b_, dst_roi.x, dst_roi.y, dst_roi.width, dst_roi.height));
+  }
+
+  void feed(cv::InputArray img, cv::InputArray mask, cv::Point tl) override {
+    cv::Mat i = img.getMat(), m = mask.getMat();
+    CV_Assert(i.type() == CV_8UC3);
+    CV_Assert(m.type() == CV_8U);
+    CV_Assert(m.rows == i.rows && m.cols == i.cols);
+    Check(xp_multiband_feed(b_, i.data, i.step, m.data, m.step, i.cols, i.rows, tl.x,
+                            tl.y, XP_MEM_HOST));
+  }
+
+  void blend(cv::InputOutputArray dst, cv::InputOutputArray dst_mask) override {
+    int wh[2];
+    Check(xp_multiband_blend(b_, wh, nullptr));
+    dst.create(wh[1], wh[0], CV_8UC3);
+    dst_mask.create(wh[1], wh[0], CV_8U);
+    cv::Mat d = dst.getMat(), m = dst_mask.getMat();
+    Check(xp_multiband_fetch(b_, d.data, d.step, m.data, m.step, XP_MEM_HOST));
+  }
+
+ private:
+  xp_multiband* b_ = nullptr;
 };
 
 class B200GainCompensator : public cv::detail::ExposureCompensator {

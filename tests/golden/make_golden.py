@@ -305,12 +305,55 @@ def seam_goldens():
     np.savez_compressed(os.path.join(HERE, "seam_cv2_goldens.npz"), **g)
 
 
+def mbcv_scene(seed, n=3, w=200, h=150, step=130):
+    """Images, masks (with fractional values on one image) and corners for
+    the MultiBandOpenCV tests; regenerated from the seed by the tests."""
+    feeds = []
+    for i in range(n):
+        img = synth.texture(h, w, seed * 10 + i, 3, 8)
+        m = np.full((h, w), 255, np.uint8)
+        yy, xx = np.mgrid[0:h, 0:w]
+        m[(xx + yy) < 30] = 0
+        m[:, : 3 + i] = 0
+        if i == 1:
+            m[h // 2:, w // 2:] = 128        # a half-weight region
+        feeds.append((img, m, (i * step - 40, 7 * i - 5)))
+    x0 = min(f[2][0] for f in feeds)
+    y0 = min(f[2][1] for f in feeds)
+    x1 = max(f[2][0] + f[0].shape[1] for f in feeds)
+    y1 = max(f[2][1] + f[0].shape[0] for f in feeds)
+    return (x0, y0, x1 - x0, y1 - y0), feeds
+
+
+MBCV_CASES = [(1, dict()), (2, dict(n=4, w=331, h=207, step=250)),
+              (3, dict(n=2, w=64, h=40, step=30)),
+              (4, dict(n=1, w=20, h=9, step=0))]
+
+
+def mbcv_goldens():
+    """blenders::MultiBandOpenCV as xpano runs it (blenders.cc:160-175) with
+    cv2 4.13.0: MultiBandBlender(0, 5, CV_32F), feed(int16 image),
+    blend, convert to 8 bits."""
+    g = {}
+    for seed, kw in MBCV_CASES:
+        roi, feeds = mbcv_scene(seed, **kw)
+        b = cv2.detail_MultiBandBlender(0, 5, cv2.CV_32F)
+        b.prepare(roi)
+        for img, mask, tl in feeds:
+            b.feed(img.astype(np.int16), mask, tl)
+        dst, m = b.blend(None, None)
+        g[f"dst_{seed}"] = np.clip(dst, 0, 255).astype(np.uint8)
+        g[f"mask_{seed}"] = m
+    np.savez_compressed(os.path.join(HERE, "mbcv_cv2_goldens.npz"), **g)
+
+
 def main():
     warp_goldens()
     portrait_goldens()
     crop_goldens()
     gain_goldens()
     seam_goldens()
+    mbcv_goldens()
     g = {}
     pos_png = [(-91, 204), (-167, 202), (-41, 193)]
     pos_tif = [(76, 11), (0, 9), (126, 0)]

@@ -3,7 +3,9 @@
 // compose loop drives its warper and blender, polymorphically through cv::Ptr
 // (xpano/algorithm/stitcher.cc:144-169 ComputeRoi, :357-419 the loop).
 //
-//   shim_driver <in.bin> <out.bin>
+//   shim_driver <in.bin> <out.bin> [opencv]
+//     opencv: install B200MultiBandBlender (BlendingMethod::kOpenCV) instead
+//     of B200Blender
 // in : int32 n, w, h, projection; float32 scale; n x (K[9], R[9]) float32;
 //      n x (h*w*3) u8, rows padded to a step of w*3+12 bytes
 // out: int32 W, H, corner_x, corner_y of image 0; pano (H*W*3 u8); mask (H*W);
@@ -24,7 +26,8 @@ static void rd(void* p, size_t n, FILE* f) {
 }
 
 int main(int argc, char** argv) {
-  if (argc != 3) return 2;
+  if (argc != 3 && argc != 4) return 2;
+  const bool opencv_blender = argc == 4;
   FILE* f = fopen(argv[1], "rb");
   if (!f) return 2;
   int hdr[4];
@@ -51,7 +54,11 @@ int main(int argc, char** argv) {
     // what algorithm.cc:257-258, 269-270 would install
     cv::Ptr<cv::WarperCreator> creator =
         cv::makePtr<b200::B200WarperCreator>(projection, false, 2.0f, 1.0f);
-    cv::Ptr<cv::detail::Blender> blender = cv::makePtr<b200::B200Blender>();
+    cv::Ptr<cv::detail::Blender> blender;
+    if (opencv_blender)  // PickBlender, algorithm.cc:132-148
+      blender = cv::makePtr<b200::B200MultiBandBlender>();
+    else
+      blender = cv::makePtr<b200::B200Blender>();
     // what stitcher.cc:200-201 would install
     cv::Ptr<cv::detail::ExposureCompensator> exposure_comp =
         cv::makePtr<b200::B200GainCompensator>();

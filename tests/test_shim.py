@@ -120,6 +120,27 @@ def test_shim_driver_equals_python_surface(tmp_path):
     assert np.array_equal(mask, dst_mask)
     assert np.array_equal(pano, dst)
 
+    # the same loop with the BlendingMethod::kOpenCV blender installed
+    r = subprocess.run([shim, str(fin), str(fout), "opencv"],
+                       capture_output=True, text=True)
+    assert r.returncode == 0 and "shim ok" in r.stdout, r.stderr
+    raw = np.fromfile(fout, np.uint8)
+    W2, H2 = (int(v) for v in raw[:8].view(np.int32))
+    pano2 = raw[16:16 + W2 * H2 * 3].reshape(H2, W2, 3)
+    mask2 = raw[16 + W2 * H2 * 3:16 + W2 * H2 * 4].reshape(H2, W2)
+    x0 = min(c[0] for c in corners)
+    y0 = min(c[1] for c in corners)
+    x1 = max(c[0] + w_.shape[1] for c, w_ in zip(corners, warped))
+    y1 = max(c[1] + w_.shape[0] for c, w_ in zip(corners, warped))
+    mb = xb.MultiBandOpenCV()
+    mb.prepare((x0, y0, x1 - x0, y1 - y0))
+    for i in range(n):
+        mb.feed(comp.apply(i, corners[i], warped[i], masks[i]), masks[i],
+                corners[i])
+    dst2, dst_mask2 = mb.blend()
+    assert (W2, H2) == dst2.shape[1::-1]
+    assert np.array_equal(mask2, dst_mask2) and np.array_equal(pano2, dst2)
+
 
 @pytest.mark.gpu
 def test_plain_c_program_runs_the_path():

@@ -175,6 +175,15 @@ SYMBOLS = {
     "xp_gain_compensator_apply": (c_int, [c_void_p, c_int, c_void_p, c_int,
                                           c_int, c_size_t, c_int, c_int]),
     "xp_gain_compensator_stats": (c_int, [c_void_p, c_void_p]),
+    "xp_multiband_create": (c_int, [c_int, c_int, c_void_p]),
+    "xp_multiband_destroy": (None, [c_void_p]),
+    "xp_multiband_prepare": (c_int, [c_void_p, c_int, c_int, c_int, c_int]),
+    "xp_multiband_feed": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p,
+                                  c_size_t, c_int, c_int, c_int, c_int,
+                                  c_int]),
+    "xp_multiband_blend": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "xp_multiband_fetch": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p,
+                                   c_size_t, c_int]),
 }
 
 

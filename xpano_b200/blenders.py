@@ -201,3 +201,58 @@ def decode_mask_rle(runs, width, height):
             mask[y, x:x + n] = 255 if w & 0x80000000 else 0
             x += n
     return mask
+
+
+class MultiBandOpenCV:
+    """xpano::algorithm::blenders::MultiBandOpenCV look-alike
+    (xpano/algorithm/blenders.h:41-50, blenders.cc:160-175): OpenCV's
+    MultiBandBlender(false, num_bands = 5, CV_32F) fed with 16-bit signed
+    copies of the 8-bit images, result converted back to 8 bits --
+    BlendingMethod::kOpenCV (algorithm.cc:135-136)."""
+
+    def __init__(self, num_bands=5, device=0):
+        self._lib = _lib.load()
+        self._h = c_void_p()
+        check(self._lib.xp_multiband_create(int(num_bands), int(device),
+                                            ctypes.byref(self._h)))
+        self.num_bands = None
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.xp_multiband_destroy(self._h)
+            self._h = c_void_p()
+
+    def prepare(self, dst_roi):
+        x, y, w, h = dst_roi
+        check(self._lib.xp_multiband_prepare(self._h, int(x), int(y), int(w),
+                                             int(h)))
+
+    def feed(self, img, mask, tl):
+        """img: (h, w, 3) uint8, mask: (h, w) uint8 (mask / 255 is the blend
+        weight), tl: (x, y); rows may be strided."""
+        img, mask = np.asarray(img), np.asarray(mask)
+        if img.ndim != 3 or img.shape[2] != 3 or img.dtype != np.uint8:
+            raise ValueError("feed: CV_8UC3 image expected")
+        if mask.dtype != np.uint8 or mask.shape != img.shape[:2]:
+            raise ValueError("feed: CV_8U mask of the image size expected")
+        if img.strides[2] != 1 or img.strides[1] != 3 or img.strides[0] < 0:
+            img = np.ascontiguousarray(img)
+        if mask.strides[1] != 1 or mask.strides[0] < 0:
+            mask = np.ascontiguousarray(mask)
+        check(self._lib.xp_multiband_feed(
+            self._h, img.ctypes.data, img.strides[0], mask.ctypes.data,
+            mask.strides[0], img.shape[1], img.shape[0], int(tl[0]),
+            int(tl[1]), _lib.MEM_HOST))
+
+    def blend(self):
+        """-> (dst (h, w, 3) uint8, dst_mask (h, w) uint8)."""
+        wh = (ctypes.c_int * 2)()
+        nb = ctypes.c_int()
+        check(self._lib.xp_multiband_blend(self._h, wh, ctypes.byref(nb)))
+        self.num_bands = nb.value
+        dst = np.empty((wh[1], wh[0], 3), np.uint8)
+        mask = np.empty((wh[1], wh[0]), np.uint8)
+        check(self._lib.xp_multiband_fetch(self._h, dst.ctypes.data, 0,
+                                           mask.ctypes.data, 0,
+                                           _lib.MEM_HOST))
+        return dst, mask
