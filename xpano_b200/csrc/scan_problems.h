@@ -31,6 +31,27 @@ namespace xp {
 typedef uint64_t u64;
 typedef uint32_t u32;
 
+// A value another block polls for (wavefront.h: the band below reads the last
+// row of this band with ld.relaxed.gpu) is published with a store of the same
+// strength: a weak store paired with a strong load is a data race under the
+// PTX memory model, even though whole-word stores reach L2 intact today.
+XP_HD void publish(u32* p, u32 v) {
+#if defined(__CUDA_ARCH__)
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v)
+               : "memory");
+#else
+  *p = v;
+#endif
+}
+XP_HD void publish(u64* p, u64 v) {
+#if defined(__CUDA_ARCH__)
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v)
+               : "memory");
+#else
+  *p = v;
+#endif
+}
+
 constexpr u64 kTopBit = 0x8000000000000000ull;
 constexpr u64 kLow63 = 0x7fffffffffffffffull;
 constexpr u64 kDtMax = 0x9000000000000000ull;
@@ -245,7 +266,7 @@ struct SeamBwd {
   }
   XP_HD u32 sentinel() const { return kInf32; }
   XP_HD void store(const wf::Band&, int rho, int q, u32 v) const {
-    out[at(rho, q)] = v;
+    publish(out + at(rho, q), v);
   }
   // chunks made of seeds only skip the recurrence; not on the bottom band,
   // whose first row carries the first_run state
@@ -350,7 +371,7 @@ struct SeamFwd {
   XP_HD u32 sentinel() const { return kInf32; }
   XP_HD void store(const wf::Band&, int rho, int q, u32 v) const {
     const size_t p = (size_t)rho * W + q;
-    out[p] = v;
+    publish(out + p, v);
     labels[p] = (uint8_t)(v & 0xffu);
   }
   XP_HD bool allow_trivial(const wf::Band&) const { return true; }
@@ -492,7 +513,7 @@ struct InpaintFwd {
   }
   XP_HD u64 sentinel() const { return ~0ull; }
   XP_HD void store(const wf::Band& B, int y, int x, u64 v) const {
-    jobs[B.job].fwd[(size_t)y * B.W + x] = v;
+    publish(jobs[B.job].fwd + ((size_t)y * B.W + x), v);
   }
   // no uncovered-tile variant (wavefront.h); never called
   static constexpr bool kHasUncovered = false;
@@ -570,7 +591,7 @@ struct InpaintBwd {
   }
   XP_HD u64 sentinel() const { return ~0ull; }
   XP_HD void store(const wf::Band& B, int rho, int q, u64 v) const {
-    jobs[B.job].bwd[at(B, rho, q)] = v;
+    publish(jobs[B.job].bwd + at(B, rho, q), v);
   }
   // no uncovered-tile variant (wavefront.h); never called
   static constexpr bool kHasUncovered = false;
