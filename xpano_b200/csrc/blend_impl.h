@@ -18,6 +18,11 @@ struct ImgDev {
   int tiff_w, tiff_h;
   int left, top, w, h;  // trim bbox
   int xpos, ypos;       // canvas position of the bbox after tighten
+  // opacity bit plane of the untrimmed image (bit x & 31 of word x >> 5 of a
+  // row of abits_pitch words), or null: what the composer's warps leave
+  // beside the pixels, so that trim and the cover map need not read them
+  const uint32_t* abits;
+  int abits_pitch;
 };
 
 struct CanvasStats {
@@ -55,6 +60,9 @@ struct MaskLevel {
 void launch_trim_init(int* d_bbox, unsigned long long* d_opaque, int n,
                       cudaStream_t s);
 // pitch: pixels per row of each image
+void launch_trim_bits(const uint32_t* const* bits, const int* pitch,
+                      const int* h, int n, int* d_bbox,
+                      unsigned long long* d_opaque_count, cudaStream_t s);
 void launch_trim(const void* const* data, const int* w, const int* h,
                  const int* pitch, int n, int bpp, int* d_bbox,
                  unsigned long long* d_opaque_count, cudaStream_t s);

@@ -15,6 +15,11 @@ struct Fed {
   // on 16-byte boundaries (what a TMA tensor map over the pixels needs).
   int pitch = 0;
   DevBuf data;  // pitch*h pixels of 4 samples (B, G, R, alpha)
+  // by-product of the composer's warp (warp.cu AlphaOut): the opacity bit
+  // plane, h rows of abits_pitch words; empty for images that came through
+  // feed()
+  DevBuf abits;
+  int abits_pitch = 0;
 };
 
 struct StageTimer {

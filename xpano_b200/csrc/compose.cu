@@ -388,10 +388,13 @@ struct Composer {
       const Projector p = warper.projector(s.K, s.R);
       const bool colours = plan.local[i] != 0;
       XP_REQUIRE(!colours || s.dev, "image %zu was not uploaded", i);
+      f->abits_pitch = Warper::alpha_bits_pitch(r[2]);
+      f->abits.reserve(sizeof(uint32_t) * (size_t)f->abits_pitch * r[3]);
       warper.warp_bgra_device(colours ? s.dev : nullptr, s.w, s.h, s.pitch,
                               opts.depth, p, roi_incl, s.gain.as<float>(),
                               s.gw, s.gh, s.seam.as<uint8_t>(), s.mw, s.mh,
-                              f->data.p, (size_t)f->pitch * 4 * bs, true);
+                              f->data.p, (size_t)f->pitch * 4 * bs, true,
+                              f->abits.as<uint32_t>(), f->abits_pitch);
       fed_local.push_back(colours ? 1 : 0);
       t_warp_launches += 1 + (s.seam.p ? 1 : 0) +
                          (is_separable(p.type) ? 1 : 0) +

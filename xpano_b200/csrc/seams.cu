@@ -347,6 +347,66 @@ void launch_trim_init(int* d_bbox, unsigned long long* d_opaque, int n,
   XP_LAUNCHED();
 }
 
+// Trim from the opacity bit planes the composer's warps left (warp.cu
+// AlphaOut): one bit per pixel. blockIdx.y = image.
+struct TrimBits {
+  const uint32_t* bits[kMaxImages + 1];
+  int pitch[kMaxImages + 1], h[kMaxImages + 1];
+};
+
+__global__ void __launch_bounds__(256)
+    trim_bits_kernel(const __grid_constant__ TrimBits tb, int* bbox_all,
+                     unsigned long long* opaque_count_all) {
+  const uint32_t* bits = tb.bits[blockIdx.y];
+  const int pitch = tb.pitch[blockIdx.y];
+  const int nw = pitch * tb.h[blockIdx.y];
+  int minx = INT_MAX, miny = INT_MAX, maxx = -1, maxy = -1;
+  unsigned long long cnt = 0;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < nw;
+       k += gridDim.x * blockDim.x) {
+    const uint32_t v = __ldg(bits + k);
+    if (v) {
+      const int y = k / pitch, x0 = (k - y * pitch) * 32;
+      minx = min(minx, x0 + __ffs((int)v) - 1);
+      maxx = max(maxx, x0 + 31 - __clz((int)v));
+      miny = min(miny, y);
+      maxy = max(maxy, y);
+      cnt += (unsigned long long)__popc(v);
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    cnt += __shfl_xor_sync(~0u, cnt, o);
+    minx = min(minx, __shfl_xor_sync(~0u, minx, o));
+    miny = min(miny, __shfl_xor_sync(~0u, miny, o));
+    maxx = max(maxx, __shfl_xor_sync(~0u, maxx, o));
+    maxy = max(maxy, __shfl_xor_sync(~0u, maxy, o));
+  }
+  if ((threadIdx.x & 31) == 0 && maxx >= 0) {
+    int* bbox = bbox_all + 4 * blockIdx.y;
+    atomicMin(bbox + 0, minx);
+    atomicMin(bbox + 1, miny);
+    atomicMax(bbox + 2, maxx);
+    atomicMax(bbox + 3, maxy);
+    atomicAdd(opaque_count_all + blockIdx.y, cnt);
+  }
+}
+
+// d_bbox / d_opaque_count initialised by launch_trim_init
+void launch_trim_bits(const uint32_t* const* bits, const int* pitch,
+                      const int* h, int n, int* d_bbox,
+                      unsigned long long* d_opaque_count, cudaStream_t s) {
+  XP_REQUIRE(n <= kMaxImages, "too many images");
+  TrimBits tb;
+  int most = 0;
+  for (int i = 0; i < n; ++i) {
+    tb.bits[i] = bits[i], tb.pitch[i] = pitch[i], tb.h[i] = h[i];
+    most = std::max(most, pitch[i] * h[i]);
+  }
+  dim3 g(std::max(1, std::min(div_up(most, 256 * 8), 64)), n);
+  trim_bits_kernel<<<g, 256, 0, s>>>(tb, d_bbox, d_opaque_count);
+  XP_LAUNCHED();
+}
+
 // trim boxes and opaque counts of n images (d_bbox: 4 ints, d_opaque_count:
 // one word per image; both initialised by launch_trim_init)
 void launch_trim(const void* const* data, const int* w, const int* h,
@@ -424,16 +484,27 @@ __global__ void __launch_bounds__(256)
     const bool row_in = y < H && (unsigned)ly < (unsigned)im.h;
     const size_t row = (size_t)(im.top + (row_in ? ly : 0)) * im.tiff_w + im.left;
     const int lx0 = x0 - im.xpos;
+    // with a bit plane (composer warps) one word holds 32 pixels' opacity
+    const uint32_t* brow =
+        im.abits ? im.abits + (size_t)(im.top + (row_in ? ly : 0)) *
+                                  im.abits_pitch
+                 : nullptr;
+    auto opaque_at = [&](int lx) {
+      if (brow) {
+        const int X = im.left + lx;
+        return ((__ldg(brow + (X >> 5)) >> (X & 31)) & 1u) != 0;
+      }
+      return px_opaque<BPP>(im.data, row + lx);
+    };
     bool op[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int lx = lx0 + 32 * j;
-      op[j] = row_in && (unsigned)lx < (unsigned)im.w &&
-              px_opaque<BPP>(im.data, row + lx);
+      op[j] = row_in && (unsigned)lx < (unsigned)im.w && opaque_at(lx);
     }
     // opacity of the pixel left of the tile's first column
     bool carry = row_in && lane == 0 && lx0 >= 1 && lx0 - 1 < im.w &&
-                 px_opaque<BPP>(im.data, row + lx0 - 1);
+                 opaque_at(lx0 - 1);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int lx = lx0 + 32 * j;

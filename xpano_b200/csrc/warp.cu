@@ -586,6 +586,25 @@ __device__ __forceinline__ float resize_linear_f32_tab(
 // kSkipTransparent: pixels that come out with alpha 0 get colour 0 instead of
 // their (unused) reflected sample -- the compose driver's form; the public
 // xp_warper_warp_bgra keeps the reference's colours everywhere.
+// Optional by-product of the composer's warps (null = off): the opacity of
+// every pixel as a bit plane, one 32-bit word per 32 consecutive x (bit =
+// x & 31). The blender's trim (image.cpp:396-512) then reads one bit per pixel
+// instead of a 4- or 8-byte pixel, and so does its cover map.
+struct AlphaOut {
+  uint32_t* bits;   // H rows of bits_pitch words
+  int bits_pitch;
+};
+
+// every thread of a warp calls this once, from one place, inactive ones with
+// opaque = false; threadIdx.x is the lane (blocks are 32 wide)
+__device__ __forceinline__ void alpha_out(const AlphaOut& ao, bool opaque,
+                                          int dx, int dy, int W, int H) {
+  if (!ao.bits) return;
+  const unsigned bal = __ballot_sync(0xffffffffu, opaque);
+  if (threadIdx.x == 0 && dy < H && dx < W)
+    ao.bits[(size_t)dy * ao.bits_pitch + (dx >> 5)] = bal;
+}
+
 template <typename T, bool kSkipTransparent>
 __global__ void warp_bgra_kernel(MapSrc m, const T* __restrict__ src,
                                  size_t src_pitch, int sw, int sh, int W, int H,
@@ -594,21 +613,28 @@ __global__ void warp_bgra_kernel(MapSrc m, const T* __restrict__ src,
                                  int mw, int mh,
                                  const AuxCoef* __restrict__ aux_col,
                                  const AuxCoef* __restrict__ aux_row,
-                                 T* __restrict__ dst, size_t dst_pitch) {
-  int dx = blockIdx.x * blockDim.x + threadIdx.x;
-  int dy = blockIdx.y * blockDim.y + threadIdx.y;
-  if (dx >= W || dy >= H) return;
-  float x, y;
-  eval_map(m, dx, dy, x, y);
-  int ix, iy;
-  bool opaque = nearest_inside(sw, sh, x, y, ix, iy);
+                                 T* __restrict__ dst, size_t dst_pitch,
+                                 AlphaOut ao) {
+  const int dx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int dy = blockIdx.y * blockDim.y + threadIdx.y;
+  const bool in = dx < W && dy < H;
+  float x = 0.f, y = 0.f;
+  bool opaque = false;
   AuxCoef acx = {0, 0.f, 0, 0}, acy = {0, 0.f, 0, 0};
-  if (gain || seam_dilated) {
-    acx = aux_col[dx];
-    acy = aux_row[dy];
+  if (in) {
+    eval_map(m, dx, dy, x, y);
+    int ix, iy;
+    opaque = nearest_inside(sw, sh, x, y, ix, iy);
+    if (gain || seam_dilated) {
+      acx = aux_col[dx];
+      acy = aux_row[dy];
+    }
+    if (seam_dilated && opaque)
+      opaque = resize_exact_u8_tab(seam_dilated, mw, mh, acx, acy) != 0;
   }
-  if (seam_dilated && opaque)
-    opaque = resize_exact_u8_tab(seam_dilated, mw, mh, acx, acy) != 0;
+  // one call site for the whole block (ballot + barrier inside)
+  alpha_out(ao, opaque, dx, dy, W, H);
+  if (!in) return;
   T* d = dst + (size_t)dy * dst_pitch + (size_t)dx * 4;
   if (kSkipTransparent && !opaque) {
     // The colour of a pixel that is fed with alpha 0 never reaches the
@@ -654,17 +680,23 @@ __global__ void warp_alpha_kernel(MapSrc m, int sw, int sh, int W, int H,
                                   int mw, int mh,
                                   const AuxCoef* __restrict__ aux_col,
                                   const AuxCoef* __restrict__ aux_row,
-                                  T* __restrict__ dst, size_t dst_pitch) {
-  int dx = blockIdx.x * blockDim.x + threadIdx.x;
-  int dy = blockIdx.y * blockDim.y + threadIdx.y;
-  if (dx >= W || dy >= H) return;
-  float x, y;
-  eval_map(m, dx, dy, x, y);
-  int ix, iy;
-  bool opaque = nearest_inside(sw, sh, x, y, ix, iy);
-  if (seam_dilated && opaque)
-    opaque = resize_exact_u8_tab(seam_dilated, mw, mh, aux_col[dx],
-                                 aux_row[dy]) != 0;
+                                  T* __restrict__ dst, size_t dst_pitch,
+                                  AlphaOut ao) {
+  const int dx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int dy = blockIdx.y * blockDim.y + threadIdx.y;
+  const bool in = dx < W && dy < H;
+  bool opaque = false;
+  if (in) {
+    float x, y;
+    eval_map(m, dx, dy, x, y);
+    int ix, iy;
+    opaque = nearest_inside(sw, sh, x, y, ix, iy);
+    if (seam_dilated && opaque)
+      opaque = resize_exact_u8_tab(seam_dilated, mw, mh, aux_col[dx],
+                                   aux_row[dy]) != 0;
+  }
+  alpha_out(ao, opaque, dx, dy, W, H);
+  if (!in) return;
   const T amax = (T)(sizeof(T) == 1 ? 255 : 65535);
   T* d = dst + (size_t)dy * dst_pitch + (size_t)dx * 4;
   if (sizeof(T) == 1) {
@@ -914,8 +946,10 @@ void Warper::warp_bgra_device(const void* dsrc, int sw, int sh, size_t spitch,
                               const float* d_gain, int gw, int gh,
                               const uint8_t* d_seam, int mw, int mh,
                               void* ddst, size_t dpitch,
-                              bool skip_transparent) {
+                              bool skip_transparent, uint32_t* abits,
+                              int abits_pitch) {
   const int W = roi[2] - roi[0] + 1, H = roi[3] - roi[1] + 1;
+  const AlphaOut ao = {abits, abits_pitch};
   const uint8_t* d_dil = nullptr;
   if (d_seam) {
     grow_scratch(dilated, (size_t)mw * mh, stream);
@@ -944,18 +978,18 @@ void Warper::warp_bgra_device(const void* dsrc, int sw, int sh, size_t spitch,
     if (depth == 8)
       warp_alpha_kernel<uint8_t><<<g, b, 0, stream>>>(
           m, sw, sh, W, H, d_dil, mw, mh, aux_col, aux_row, (uint8_t*)ddst,
-          dpitch);
+          dpitch, ao);
     else
       warp_alpha_kernel<uint16_t><<<g, b, 0, stream>>>(
           m, sw, sh, W, H, d_dil, mw, mh, aux_col, aux_row, (uint16_t*)ddst,
-          dpitch / 2);
+          dpitch / 2, ao);
     XP_LAUNCHED();
     return;
   }
 #define XP_WARP_BGRA(T, SKIP, DIV)                                          \
   warp_bgra_kernel<T, SKIP><<<g, b, 0, stream>>>(                           \
       m, (const T*)dsrc, spitch / DIV, sw, sh, W, H, d_gain, gw, gh, d_dil, \
-      mw, mh, aux_col, aux_row, (T*)ddst, dpitch / DIV)
+      mw, mh, aux_col, aux_row, (T*)ddst, dpitch / DIV, ao)
   if (depth == 8) {
     if (skip_transparent)
       XP_WARP_BGRA(uint8_t, true, 1);

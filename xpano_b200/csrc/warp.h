@@ -56,7 +56,11 @@ struct Warper {
                         int depth, const Projector& p, const int roi[4],
                         const float* d_gain, int gw, int gh,
                         const uint8_t* d_seam, int mw, int mh, void* ddst,
-                        size_t dpitch, bool skip_transparent = false);
+                        size_t dpitch, bool skip_transparent = false,
+                        uint32_t* abits = nullptr, int abits_pitch = 0);
+  // by-product for the blender (see AlphaOut in warp.cu): words per row of
+  // the opacity bit plane
+  static int alpha_bits_pitch(int W) { return (W + 31) / 32; }
 };
 
 }  // namespace xp
