@@ -97,3 +97,35 @@ def test_sixteen_bit_levels_left_to_the_library():
     ims = [synth.texture(h, w, 90 + i, 3, 16) for i in range(3)]
     pano, _, info = run_both(ims, Ks, Rs, f, bpp=16)
     assert pano.dtype == np.uint16 and info["levels"] >= 5
+
+
+@pytest.mark.parametrize("n_cols,reverse", [(3, False), (5, True)])
+def test_cover_map_from_opacity_bits_equals_the_pixel_path(n_cols, reverse,
+                                                           monkeypatch):
+    """The composer's warps leave an opacity bit plane; the cover map built
+    from it (cover_bits_kernel) is the one built from the pixels
+    (cover_kernel), word for word, and so is everything after it."""
+    import xpano_b200 as xb
+    w, h, f = 333, 190, 210.0
+    Ks, Rs = cams(n_cols, w, h, f, 0.55, seed=8)
+    ims = [synth.texture(h, w, 120 + i, 3, 8) for i in range(n_cols)]
+    rng = np.random.default_rng(2)
+    seams = []
+    for i in range(n_cols):   # ragged seam masks: holes and run starts
+        m = (rng.random((24, 40)) > 0.25).astype(np.uint8) * 255
+        m[:, 10:30] = 255
+        seams.append(m)
+    got = {}
+    for mode in ("bits", "pixels"):
+        if mode == "pixels":
+            monkeypatch.setenv("XP_NO_COVER_BITS", "1")
+        c = xb.Composer(projection=wo.SPHERICAL, warp_scale=f, depth=8,
+                        fixed_levels=3, reverse=reverse, keep_debug=True)
+        c.set_images(ims, Ks, Rs, None, seams)
+        c.run()
+        pano, mask = c.fetch()
+        got[mode] = (c.debug("cover", dtype=np.uint32),
+                     c.debug("labels", dtype=np.int32), pano, mask)
+    for a, b in zip(got["bits"], got["pixels"]):
+        assert a.shape == b.shape and np.array_equal(a, b)
+    assert got["bits"][0].any()

@@ -70,7 +70,7 @@ void launch_trim(const void* const* data, const int* w, const int* h,
 // scan_problems.h Cov<>)
 void launch_cover(void* cover, int cover_bytes, int W, int H,
                   const ImgDev* d_imgs, int n, int bpp, int reverse,
-                  cudaStream_t s);
+                  cudaStream_t s, bool with_bits = false);
 void launch_seams(const void* cover, int cover_bytes, int n_images, int W,
                   int H, int reverse, uint32_t* bwd, uint32_t* fwd, uint8_t* labels,
                   int* counter, uint8_t* flags, cudaStream_t s,
