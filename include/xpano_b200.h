@@ -386,6 +386,15 @@ xp_status xp_find_largest_crop(const uint8_t* mask, int w, int h,
 xp_status xp_blender_auto_crop(xp_blender* b, int out_rect[4], int* found);
 xp_status xp_largest_crop_from_lines(const int* lines_start_end, int n_columns,
                                      int rows, int out_rect[4], int* found);
+/* The inputs of the auto-fill step (StitcherPipeline::RunInpainting,
+ * stitcher_pipeline.cc:374-403): inpaint_mask = bitwise_not(pano_mask) and
+ * pixels_filled = countNonZero(inpaint_mask), from the mask on the device.
+ * dst_mask may be NULL (count only). The fill itself, cv::inpaint (Telea's
+ * fast marching / Navier-Stokes, algorithm.cc:344-353), advances a
+ * heap-ordered front pixel by pixel and stays the caller's CPU code. */
+xp_status xp_blender_inpaint_mask(xp_blender* b, uint8_t* dst_mask,
+                                  size_t mask_stride, int mem,
+                                  long long* pixels_to_fill);
 
 /* ------------------------------------------------------------------------
  * Exposure step of Stitcher::EstimateSeams (xpano/algorithm/stitcher.cc:

@@ -129,3 +129,20 @@ def test_cover_map_from_opacity_bits_equals_the_pixel_path(n_cols, reverse,
     for a, b in zip(got["bits"], got["pixels"]):
         assert a.shape == b.shape and np.array_equal(a, b)
     assert got["bits"][0].any()
+
+
+def test_auto_fill_inputs_from_the_device_mask():
+    """RunInpainting's inpaint_mask and pixels_filled
+    (stitcher_pipeline.cc:384-389) from the mask on the device."""
+    import xpano_b200 as xb
+    w, h, f = 160, 120, 200.0
+    Ks, Rs = cams(2, w, h, f, 1.6)
+    ims = [synth.texture(h, w, 60 + i, 3, 8) for i in range(2)]
+    c = xb.Composer(projection=wo.SPHERICAL, warp_scale=f, depth=8,
+                    fixed_levels=4)
+    c.set_images(ims, Ks, Rs)
+    c.run()
+    _, mask = c.fetch()
+    inv, n = c.inpaint_mask()
+    assert np.array_equal(inv, np.bitwise_not(mask))
+    assert n == int(np.count_nonzero(inv)) and n > 0

@@ -155,6 +155,8 @@ SYMBOLS = {
     "xp_find_largest_crop": (c_int, [c_void_p, c_int, c_int, c_size_t, c_int,
                                      c_int, c_void_p, c_void_p]),
     "xp_blender_auto_crop": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "xp_blender_inpaint_mask": (c_int, [c_void_p, c_void_p, c_size_t, c_int,
+                                        c_void_p]),
     "xp_largest_crop_from_lines": (c_int, [c_void_p, c_int, c_int, c_void_p,
                                            c_void_p]),
     "xp_gain_compensator_create": (c_int, [c_int, c_int, c_int, c_int,

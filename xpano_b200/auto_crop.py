@@ -55,3 +55,17 @@ def blender_auto_crop(blender_handle):
     check(lib.xp_blender_auto_crop(c_void_p(blender_handle), out,
                                    ctypes.byref(found)))
     return _rect(out, found)
+
+
+def blender_inpaint_mask(blender_handle, size):
+    """The inputs of the auto-fill step (stitcher_pipeline.cc:384-389) from
+    the mask a blended blender holds on the device: -> (inpaint_mask (h, w)
+    uint8 = ~pano_mask, pixels_filled). size = (w, h) of the panorama."""
+    lib = _lib.load()
+    w, h = size
+    inv = np.empty((h, w), np.uint8)
+    n = ctypes.c_longlong()
+    check(lib.xp_blender_inpaint_mask(c_void_p(blender_handle),
+                                      inv.ctypes.data, 0, _lib.MEM_HOST,
+                                      ctypes.byref(n)))
+    return inv, int(n.value)

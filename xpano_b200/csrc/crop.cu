@@ -143,6 +143,23 @@ bool find_largest_crop_device(const uint8_t* d_mask, int w, int h,
   return largest_crop_from_lines(lines, h, out_rect);
 }
 
+// inpaint_mask = ~pano_mask and its countNonZero (the inputs of the auto-fill
+// step, stitcher_pipeline.cc:384-389)
+__global__ void __launch_bounds__(256)
+    invert_count_kernel(const uint8_t* __restrict__ mask, size_t n,
+                        uint8_t* __restrict__ inv,
+                        unsigned long long* __restrict__ count) {
+  unsigned long long c = 0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const uint8_t v = (uint8_t)~mask[i];
+    inv[i] = v;
+    c += v != 0;
+  }
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_down_sync(~0u, c, o);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(count, c);
+}
+
 }  // namespace xp
 
 extern "C" {
@@ -182,6 +199,37 @@ xp_status xp_find_largest_crop(const uint8_t* mask, int w, int h,
                  ? 1
                  : 0;
     XP_CUDA(cudaStreamSynchronize(nullptr));
+  });
+}
+
+xp_status xp_blender_inpaint_mask(xp_blender* b, uint8_t* dst_mask,
+                                  size_t mask_stride, int mem,
+                                  long long* pixels_to_fill) {
+  return xp::guard([&] {
+    XP_REQUIRE(b && pixels_to_fill, "inpaint_mask: null argument");
+    xp::Blender* bl = reinterpret_cast<xp::Blender*>(b);
+    XP_REQUIRE(bl->blended, "inpaint_mask before blend()");
+    XP_REQUIRE(bl->tile.count == 1, "inpaint_mask: not available for a tile");
+    xp::select_device(bl->opts.device);
+    cudaStream_t s = bl->stream;
+    const size_t n = (size_t)bl->W * bl->H;
+    xp::DevBuf inv, cnt;
+    inv.reserve(n);
+    cnt.reserve(sizeof(unsigned long long));
+    XP_CUDA(cudaMemsetAsync(cnt.p, 0, sizeof(unsigned long long), s));
+    xp::invert_count_kernel<<<xp::sm_count() * 8, 256, 0, s>>>(
+        bl->full_mask.as<uint8_t>(), n, inv.as<uint8_t>(),
+        cnt.as<unsigned long long>());
+    XP_LAUNCHED();
+    unsigned long long h = 0;
+    XP_CUDA(cudaMemcpyAsync(&h, cnt.p, sizeof(h), cudaMemcpyDeviceToHost, s));
+    if (dst_mask) {
+      if (mask_stride == 0) mask_stride = (size_t)bl->W;
+      xp::copy_out_2d(dst_mask, mask_stride, inv.p, (size_t)bl->W,
+                      (size_t)bl->W, (size_t)bl->H, mem, s);
+    }
+    XP_CUDA(cudaStreamSynchronize(s));
+    *pixels_to_fill = (long long)h;
   });
 }
 

@@ -195,6 +195,13 @@ class Composer:
         from .auto_crop import blender_auto_crop
         return blender_auto_crop(self._lib.xp_composer_blender(self._h))
 
+    def inpaint_mask(self):
+        """~pano_mask and its non-zero count: what RunInpainting hands to
+        cv::inpaint (stitcher_pipeline.cc:384-389)."""
+        from .auto_crop import blender_inpaint_mask
+        return blender_inpaint_mask(self._lib.xp_composer_blender(self._h),
+                                    (self.info["width"], self.info["height"]))
+
     def debug(self, what, image=0, channel=0, level=0, dtype=None):
         h = self._lib.xp_composer_blender(self._h)
         return debug_fetch(self._lib, c_void_p(h), what, image, channel, level,
