@@ -1,3 +1,4 @@
+#include <time.h>
 #include "common.h"
 
 #include <cuda.h>
@@ -475,6 +476,27 @@ void sync_stream(cudaStream_t s) {
 }
 
 void sync_blocking(cudaStream_t s) {
+  // Waits that last milliseconds (bulk uploads and downloads) neither spin
+  // on a core nor sleep on an interrupt: the first costs a core per waiting
+  // thread -- with several panoramas in flight per rank and several ranks
+  // per box that is all of them --, the second was measured at several
+  // milliseconds per wake-up with eight ranks on one box. The stream is
+  // polled with short sleeps in between instead: no core held, wake-up
+  // within tens of microseconds. XP_SYNC_EVENT=1 restores the blocking-sync
+  // event.
+  static const bool use_event = [] {
+    const char* e = getenv("XP_SYNC_EVENT");
+    return e && atoi(e) != 0;
+  }();
+  if (!use_event) {
+    for (;;) {
+      const cudaError_t q = cudaStreamQuery(s);
+      if (q == cudaSuccess) return;
+      if (q != cudaErrorNotReady) XP_CUDA(q);
+      struct timespec ts = {0, 30000};  // 30 us
+      nanosleep(&ts, nullptr);
+    }
+  }
   // one event per thread and device; blocking-sync events make
   // cudaEventSynchronize yield the core
   struct Ev {

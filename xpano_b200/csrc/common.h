@@ -160,9 +160,9 @@ struct StreamSet {
 StreamSet acquire_stream_set(int device);
 void release_stream_set(const StreamSet& s);
 
-// Wait for a stream with the calling thread blocked in the OS instead of
-// spinning in the driver: for the long waits on bulk copies (uploads,
-// downloads) that overlap another thread's kernel launches.
+// Wait for a stream without holding a core: for the long waits on bulk
+// copies (uploads, downloads) that overlap another thread's kernel launches.
+// Polls the stream with 30-us sleeps in between (see common.cu).
 void sync_blocking(cudaStream_t s);
 
 // Host threads this process should use for short parallel host work, and
