@@ -145,3 +145,35 @@ def test_host_errors():
         comp.solve([1, 2], [0.0, 0.0], [0.0, 0.0])  # one pair planned
     with pytest.raises(_lib.XpError):
         BlocksGainCompensator(0, 32)
+
+
+def test_host_solver_at_scale():
+    """The sparse conjugate-gradient solve against a dense solve of the same
+    system (GainCompensator::singleFeed's A, b) for a 24-image panorama's
+    worth of blocks with made-up but plausible statistics."""
+    from xpano_b200.exposure import BlocksGainCompensator
+    rng = np.random.default_rng(7)
+    n_img, w, h = 24, 420, 330
+    corners = [(int(i % 8) * 300 + int(rng.integers(-20, 20)),
+                int(i // 8) * 240 + int(rng.integers(-20, 20)))
+               for i in range(n_img)]
+    comp = BlocksGainCompensator(32, 32, 0)
+    pairs = comp.plan(corners, [(w, h)] * n_img)
+    n_pairs = len(pairs)
+    area = pairs[:, 4].astype(np.int64) * pairs[:, 5]
+    counts = (area * rng.uniform(0.0, 1.0, n_pairs)).astype(np.int64)
+    counts[rng.random(n_pairs) < 0.1] = 0          # empty intersections
+    exposure = rng.uniform(0.7, 1.4, n_img)
+    blocks, per = go.make_blocks(corners, [(w, h)] * n_img)
+    img_of = np.array([b[0] for b in blocks])
+    mean = rng.uniform(60, 200, n_pairs)
+    s1 = counts * mean * exposure[img_of[pairs[:, 0]]]
+    s2 = counts * mean * exposure[img_of[pairs[:, 1]]]
+    comp.solve(counts, s1, s2)
+    _, unknowns, iterations = comp.stats()
+    assert unknowns > 2500 and iterations < 400
+    got = np.concatenate([m.ravel() for m in comp.getMatGains()])
+    stats = [(int(p[0]), int(p[1]), int(c), float(a), float(b))
+             for p, c, a, b in zip(pairs, counts, s1, s2)]
+    want = go.solve_gains(len(blocks), stats).astype(np.float32)
+    np.testing.assert_allclose(got, want, rtol=2e-6)

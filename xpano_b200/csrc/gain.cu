@@ -276,11 +276,21 @@ void GainCompensator::solve(const std::vector<GainStat>& stats) {
     d[k] = z[k];
     rz += r[k] * z[k];
   }
+  // stop at a relative residual of 1e-15, or when rounding has taken over
+  // (the residual has not halved in 25 iterations)
   const double tol2 = 1e-30 * bnorm;
+  double best = 1e300;
+  int since_best = 0;
   for (int it = 0; it < 20 * ne + 100; ++it) {
     double rr = 0;
     for (int k = 0; k < ne; ++k) rr += r[k] * r[k];
     if (rr <= tol2) break;
+    if (rr < 0.25 * best) {
+      best = rr;
+      since_best = 0;
+    } else if (++since_best > 25) {
+      break;
+    }
     mul(d, q);
     double dq = 0;
     for (int k = 0; k < ne; ++k) dq += d[k] * q[k];
