@@ -178,6 +178,9 @@ typedef struct {
   int reverse;
   int device;       /* CUDA device ordinal                                  */
   int keep_debug;   /* keep intermediates for xp_blender_debug_fetch        */
+  int wideblend;    /* multiblend::Options::wideblend (mb/multiblend.h:33):
+                       levels from the canvas size, plus one
+                       (multiblend.cpp:164-193); xpano leaves it off          */
 } xp_blend_opts;
 
 /* multiblend::TimingResult (mb/multiblend.h:16-27), milliseconds on device.

@@ -1076,8 +1076,14 @@ int mbo_blend(int n, const mbo_image* images, const mbo_options* opts,
     hs[i] = T[i].height;
     ops[i] = T[i].opaque;
   }
-  const int blend_levels =
+  int blend_levels =
       mbo_blend_levels(n, ws, hs, opts->fixed_levels, opts->add_levels);
+  if (opts->wideblend && opts->fixed_levels == 0 && n > 1) {
+    /* multiblend.cpp:189-193: blend_wh = max(width, height); one more */
+    const int blend_wh = width > height ? width : height;
+    blend_levels = (int)floorf(log2f((float)blend_wh + 4.0f) - 1) + 1 +
+                   opts->add_levels;
+  }
   const size_t C = (size_t)width * height;
   out->width = width;
   out->height = height;

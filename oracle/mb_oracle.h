@@ -40,6 +40,8 @@ typedef struct {
   int add_levels;
   int dither;       /* default 1         (mb/multiblend.h:38)           */
   int reverse;
+  int wideblend;    /* levels from the canvas size, plus one
+                       (multiblend.cpp:164-193)                           */
 } mbo_options;
 
 /* Per-image state after trim + inpaint (image.cpp:396-868). */

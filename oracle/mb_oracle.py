@@ -30,7 +30,7 @@ class _Image(ctypes.Structure):
 class _Options(ctypes.Structure):
     _fields_ = [("output_bpp", ctypes.c_int), ("fixed_levels", ctypes.c_int),
                 ("add_levels", ctypes.c_int), ("dither", ctypes.c_int),
-                ("reverse", ctypes.c_int)]
+                ("reverse", ctypes.c_int), ("wideblend", ctypes.c_int)]
 
 
 class _Trimmed(ctypes.Structure):
@@ -153,7 +153,8 @@ class OracleResult:
 
 
 def blend(images, positions, output_bpp=0, fixed_levels=0, add_levels=0,
-          dither=True, reverse=False, debug=False) -> OracleResult:
+          dither=True, reverse=False, debug=False,
+          wideblend=False) -> OracleResult:
     lib = _load()
     n = len(images)
     arrs = [np.ascontiguousarray(im) for im in images]
@@ -165,7 +166,7 @@ def blend(images, positions, output_bpp=0, fixed_levels=0, add_levels=0,
                         a.shape[2], int(positions[i][0]),
                         int(positions[i][1]), a.ctypes.data)
     opts = _Options(output_bpp, fixed_levels, add_levels, int(dither),
-                    int(reverse))
+                    int(reverse), int(wideblend))
     res = _Result()
     rc = lib.mbo_blend(n, ims, ctypes.byref(opts), int(debug),
                        ctypes.byref(res))

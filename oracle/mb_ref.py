@@ -73,7 +73,8 @@ class BlendResult:
 
 
 def blend(images, positions, output_bpp=0, fixed_levels=0, add_levels=0,
-          dither=True, reverse=False, n_threads=None) -> BlendResult:
+          dither=True, reverse=False, n_threads=None,
+          wideblend=False) -> BlendResult:
     """images: list of (H, W, 3|4) u8/u16 arrays; positions: list of (x, y)."""
     lib = _load()
     n = len(images)
@@ -91,6 +92,7 @@ def blend(images, positions, output_bpp=0, fixed_levels=0, add_levels=0,
     xs = iarr(p[0] for p in positions)
     ys = iarr(p[1] for p in positions)
     ptrs = (ctypes.c_void_p * n)(*[a.ctypes.data for a in arrs])
+    lib.mb_ref_set_wideblend(int(bool(wideblend)))
     hnd = lib.mb_ref_blend(n, w, h, bpp, spp, xs, ys, ptrs, output_bpp,
                            fixed_levels, add_levels, int(dither),
                            int(reverse), n_threads)

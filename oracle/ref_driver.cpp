@@ -36,7 +36,13 @@ thread_local std::string g_err;
 
 }  // namespace
 
+// multiblend::Options::wideblend for the next mb_ref_blend call
+static int g_wideblend = 0;
+
 extern "C" {
+
+void mb_ref_set_wideblend(int on) { g_wideblend = on; }
+
 
 const char* mb_ref_last_error() { return g_err.c_str(); }
 
@@ -77,6 +83,7 @@ void* mb_ref_blend(int n, const int* w, const int* h, const int* bpp,
     opts.add_levels = add_levels;
     opts.dither = dither != 0;
     opts.reverse = reverse != 0;
+    opts.wideblend = g_wideblend != 0;
     auto result = multiblend::Multiblend(images, opts,
                                          multiblend::mt::ThreadpoolPtr{&pool});
 

@@ -49,6 +49,7 @@ REF_CASES = [
     (8, dict(n=4, mode="ellipse", bpp=8), dict(reverse=True, fixed_levels=2)),
     (9, dict(n=1, mode="ellipse", bpp=8), dict()),
     (10, dict(n=3, mode="ellipse", bpp=8), dict(fixed_levels=1)),
+    (11, dict(n=3, mode="ellipse", bpp=8), dict(wideblend=True)),
 ]
 
 

@@ -32,7 +32,8 @@ class ComposeAux(ctypes.Structure):
 class BlendOpts(ctypes.Structure):
     _fields_ = [("output_bpp", c_int), ("fixed_levels", c_int),
                 ("add_levels", c_int), ("dither", c_int), ("reverse", c_int),
-                ("device", c_int), ("keep_debug", c_int)]
+                ("device", c_int), ("keep_debug", c_int),
+                ("wideblend", c_int)]
 
 
 class Timing(ctypes.Structure):

@@ -19,13 +19,14 @@ class Multiblend:
     only sets output_bpp = 8 (blenders.cc:145-149)."""
 
     def __init__(self, output_bpp=0, fixed_levels=0, add_levels=0,
-                 dither=True, reverse=False, device=0, keep_debug=False):
+                 dither=True, reverse=False, device=0, keep_debug=False,
+                 wideblend=False):
         self._lib = _lib.load()
         self._h = c_void_p()
         o = _lib.BlendOpts(int(output_bpp), int(fixed_levels),
                            int(add_levels), int(bool(dither)),
                            int(bool(reverse)), int(device),
-                           int(bool(keep_debug)))
+                           int(bool(keep_debug)), int(bool(wideblend)))
         check(self._lib.xp_blender_create(ctypes.byref(o),
                                           ctypes.byref(self._h)))
         self.timing = None
