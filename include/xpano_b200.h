@@ -487,6 +487,42 @@ xp_status xp_multiband_blend(xp_multiband* b, int out_wh[2], int* num_bands);
 xp_status xp_multiband_fetch(xp_multiband* b, void* dst_bgr, size_t dst_stride,
                              uint8_t* dst_mask, size_t mask_stride, int mem);
 
+/* ------------------------------------------------------------------------
+ * JPEG either side of the path: cv::imread of the sources
+ * (xpano/algorithm/image.cc:83) and cv::imwrite of the panorama
+ * (xpano/pipeline/stitcher_pipeline.cc:94-116; parameters as
+ * CompressionParameters, :40-65: quality 95, baseline, 4:2:2 by default).
+ * Done by nvJPEG (library code, linked statically), on the device, so that
+ * only compressed bytes cross PCIe. Pixels are interleaved 8-bit BGR as
+ * cv::imread returns them; a decoder's inverse DCT and chroma upsampling are
+ * its own, so they are close to libjpeg-turbo's, not identical.
+ *   info   : width, height, channel count of a JPEG stream (host bytes)
+ *   decode : -> dst_bgr (mem = XP_MEM_DEVICE: e.g. straight into the buffer
+ *            xp_composer_set_images adopts; XP_MEM_HOST: downloaded)
+ *   encode : bgr (host or device) -> JPEG bytes on the host. out == NULL
+ *            encodes, keeps the stream and returns its size in *len; the next
+ *            call with a buffer retrieves it. subsampling: 444, 422 or 420
+ *   xp_blender_encode_jpeg: the same from the blended panorama on the device,
+ *            optionally cropped (utils::GetCvRect, stitcher_pipeline.cc:
+ *            99-102); crop_xywh may be NULL
+ * ---------------------------------------------------------------------- */
+typedef struct xp_codec xp_codec;
+xp_status xp_codec_create(int device, xp_codec** out);
+void xp_codec_destroy(xp_codec* c);
+xp_status xp_codec_jpeg_info(xp_codec* c, const uint8_t* data, size_t len,
+                             int wh[2], int* channels);
+xp_status xp_codec_jpeg_decode(xp_codec* c, const uint8_t* data, size_t len,
+                               void* dst_bgr, size_t stride, int mem);
+xp_status xp_codec_jpeg_encode(xp_codec* c, const void* bgr, int w, int h,
+                               size_t stride, int mem, int quality,
+                               int subsampling, int progressive, int optimize,
+                               uint8_t* out, size_t cap, size_t* len);
+xp_status xp_blender_encode_jpeg(xp_blender* b, xp_codec* c,
+                                 const int crop_xywh[4], int quality,
+                                 int subsampling, int progressive,
+                                 int optimize, uint8_t* out, size_t cap,
+                                 size_t* len);
+
 /* Device buffers are cached across objects (a blender is single-use, like the
  * reference's); this returns the cached blocks to the driver. */
 void xp_trim_memory(void);

@@ -7,6 +7,7 @@ from . import _lib  # noqa: F401
 from . import sharding  # noqa: F401
 from .auto_crop import FindLargestCrop  # noqa: F401
 from .blenders import Multiblend, MultiBandOpenCV  # noqa: F401
+from .codec import JpegCodec  # noqa: F401
 from .exposure import (BlocksGainCompensator, ComputeSeamScale,  # noqa
                        EstimateSeams)
 from .stitcher import Composer, compose_panorama  # noqa: F401

@@ -178,6 +178,18 @@ SYMBOLS = {
     "xp_gain_compensator_apply": (c_int, [c_void_p, c_int, c_void_p, c_int,
                                           c_int, c_size_t, c_int, c_int]),
     "xp_gain_compensator_stats": (c_int, [c_void_p, c_void_p]),
+    "xp_codec_create": (c_int, [c_int, c_void_p]),
+    "xp_codec_destroy": (None, [c_void_p]),
+    "xp_codec_jpeg_info": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p,
+                                   c_void_p]),
+    "xp_codec_jpeg_decode": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p,
+                                     c_size_t, c_int]),
+    "xp_codec_jpeg_encode": (c_int, [c_void_p, c_void_p, c_int, c_int,
+                                     c_size_t, c_int, c_int, c_int, c_int,
+                                     c_int, c_void_p, c_size_t, c_void_p]),
+    "xp_blender_encode_jpeg": (c_int, [c_void_p, c_void_p, c_void_p, c_int,
+                                       c_int, c_int, c_int, c_void_p,
+                                       c_size_t, c_void_p]),
     "xp_multiband_create": (c_int, [c_int, c_int, c_void_p]),
     "xp_multiband_destroy": (None, [c_void_p]),
     "xp_multiband_prepare": (c_int, [c_void_p, c_int, c_int, c_int, c_int]),

@@ -93,6 +93,38 @@ class Composer:
                                                _lib.MEM_HOST))
         self._keep = keep
 
+    def set_images_device(self, ptrs, sizes, Ks, Rs, gains=None,
+                          seam_masks=None, strides=None):
+        """The same with the source pixels already on the device (e.g.
+        decoded there by JpegCodec.decode_device): ptrs = device addresses of
+        interleaved BGR images, sizes = [(w, h)], strides in bytes (None =
+        packed). The buffers are adopted, not copied: they must stay valid
+        until the run has ended. gains / seam_masks are small host arrays."""
+        n = len(ptrs)
+        arr = (_lib.ComposeImage * n)()
+        keep = []
+        for i in range(n):
+            arr[i].data = int(ptrs[i])
+            arr[i].w, arr[i].h = int(sizes[i][0]), int(sizes[i][1])
+            arr[i].stride = int(strides[i]) if strides is not None else 0
+            arr[i].K = (ctypes.c_float * 9)(
+                *np.asarray(Ks[i], np.float32).reshape(9))
+            arr[i].R = (ctypes.c_float * 9)(
+                *np.asarray(Rs[i], np.float32).reshape(9))
+            if gains is not None and gains[i] is not None:
+                g = np.ascontiguousarray(gains[i], np.float32)
+                keep.append(g)
+                arr[i].aux.gain = g.ctypes.data
+                arr[i].aux.gain_h, arr[i].aux.gain_w = g.shape
+            if seam_masks is not None and seam_masks[i] is not None:
+                m = np.ascontiguousarray(seam_masks[i], np.uint8)
+                keep.append(m)
+                arr[i].aux.seam_mask = m.ctypes.data
+                arr[i].aux.seam_h, arr[i].aux.seam_w = m.shape
+        check(self._lib.xp_composer_set_images(self._h, n, arr,
+                                               _lib.MEM_DEVICE))
+        self._keep = keep
+
     def set_cancel_flag(self, flag):
         """flag: a ctypes.c_int the caller sets non-zero to cancel; polled
         between images like Stitcher::Cancelled() (stitcher.cc:408-412). A
@@ -194,6 +226,13 @@ class Composer:
         (auto_crop.cc:118-143) -> (x0, y0, x1, y1) or None."""
         from .auto_crop import blender_auto_crop
         return blender_auto_crop(self._lib.xp_composer_blender(self._h))
+
+    def encode_jpeg(self, codec, crop=None, **kw):
+        """The panorama as JPEG bytes, encoded on the device by `codec`
+        (xpano_b200.JpegCodec): RunExportPipeline's cv::imwrite
+        (stitcher_pipeline.cc:94-116) without the raw download."""
+        return codec.encode_panorama(self._lib.xp_composer_blender(self._h),
+                                     crop, **kw)
 
     def inpaint_mask(self):
         """~pano_mask and its non-zero count: what RunInpainting hands to
