@@ -513,6 +513,14 @@ xp_status xp_codec_jpeg_info(xp_codec* c, const uint8_t* data, size_t len,
                              int wh[2], int* channels);
 xp_status xp_codec_jpeg_decode(xp_codec* c, const uint8_t* data, size_t len,
                                void* dst_bgr, size_t stride, int mem);
+/* n streams into n device buffers at once, several host threads each with
+ * its own decoder state (nvJPEG decodes the Huffman stage on the calling
+ * host thread): the sources of a panorama */
+xp_status xp_codec_jpeg_decode_batch(xp_codec* c, int n,
+                                     const uint8_t* const* data,
+                                     const size_t* lens,
+                                     void* const* dst_bgr_device,
+                                     const size_t* strides);
 xp_status xp_codec_jpeg_encode(xp_codec* c, const void* bgr, int w, int h,
                                size_t stride, int mem, int quality,
                                int subsampling, int progressive, int optimize,

@@ -111,9 +111,13 @@ def test_compressed_in_compressed_out(photos):
     Rs = [g["R"][i] for i in range(3)]
     dev = [torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
            for _ in range(3)]
-    for j, t in zip(jpegs, dev):
-        codec.decode_device(j, t.data_ptr())
+    codec.decode_batch_device(jpegs, [t.data_ptr() for t in dev])
     torch.cuda.synchronize()
+    one = torch.empty_like(dev[1])        # the batch equals one-by-one decodes
+    codec.decode_device(jpegs[1], one.data_ptr())
+    assert torch.equal(one, dev[1])
+    assert psnr(dev[1].cpu().numpy(),
+                cv2.imdecode(jpegs[1], cv2.IMREAD_COLOR)) >= 40.0
     c = xb.Composer(projection=wo.SPHERICAL, warp_scale=f * s, depth=8)
     c.set_images_device([t.data_ptr() for t in dev], [(w, h)] * 3, Ks, Rs)
     info = c.run()

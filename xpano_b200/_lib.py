@@ -184,6 +184,8 @@ SYMBOLS = {
                                    c_void_p]),
     "xp_codec_jpeg_decode": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p,
                                      c_size_t, c_int]),
+    "xp_codec_jpeg_decode_batch": (c_int, [c_void_p, c_int, c_void_p,
+                                           c_void_p, c_void_p, c_void_p]),
     "xp_codec_jpeg_encode": (c_int, [c_void_p, c_void_p, c_int, c_int,
                                      c_size_t, c_int, c_int, c_int, c_int,
                                      c_int, c_void_p, c_size_t, c_void_p]),

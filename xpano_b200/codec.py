@@ -64,6 +64,18 @@ class JpegCodec:
                                              buf.size, c_void_p(dst_ptr),
                                              int(stride), _lib.MEM_DEVICE))
 
+    def decode_batch_device(self, datas, dst_ptrs, strides=None):
+        """All sources of a panorama in one batch, into device memory."""
+        bufs = [self._bytes(d) for d in datas]
+        n = len(bufs)
+        dp = (ctypes.c_void_p * n)(*[b.ctypes.data for b in bufs])
+        ln = (ctypes.c_size_t * n)(*[b.size for b in bufs])
+        op = (ctypes.c_void_p * n)(*[int(p) for p in dst_ptrs])
+        st = (ctypes.c_size_t * n)(*[int(s) for s in strides]) \
+            if strides is not None else None
+        check(self._lib.xp_codec_jpeg_decode_batch(self._h, n, dp, ln, op,
+                                                   st))
+
     def encode(self, image, quality=95, subsampling=K422, progressive=False,
                optimize=False):
         """image: (h, w, 3) uint8 BGR host array -> JPEG bytes."""
