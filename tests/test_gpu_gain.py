@@ -173,3 +173,30 @@ def test_estimate_seams_matches_cv2():
         diff = float((res["masks_warped"][i] != g[f"seam_{i}"]).mean())
         # a rounding moved by the gain resize can move a cut by a pixel
         assert diff < (1e-3 if changed > 0 else 1e-12), (i, diff, changed)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_feed_random_cases(seed):
+    """Seeded random layouts, sizes, block sizes and ragged masks against the
+    exposure oracle (pinned bit for bit against cv2)."""
+    from xpano_b200.exposure import BlocksGainCompensator
+    rng = np.random.default_rng(900 + seed)
+    n = int(rng.integers(2, 7))
+    bw, bh = int(rng.integers(8, 48)), int(rng.integers(8, 48))
+    iters = int(rng.integers(0, 4))
+    cs, ims, ms = [], [], []
+    for _ in range(n):
+        w, h = int(rng.integers(20, 180)), int(rng.integers(20, 140))
+        ims.append(rng.integers(0, 256, (h, w, 3)).astype(np.uint8))
+        m = np.full((h, w), 255, np.uint8)
+        m[rng.random((h, w)) < 0.15] = 0
+        if rng.random() < 0.3:
+            m[:, : w // 2] = 0
+        ms.append(m)
+        cs.append((int(rng.integers(-90, 90)), int(rng.integers(-60, 60))))
+    comp = BlocksGainCompensator(bw, bh, iters)
+    comp.feed(cs, ims, ms)
+    want, _ = go.blocks_gain_feed(cs, ims, ms, bw, bh, iters)
+    for a, b in zip(comp.getMatGains(), want):
+        assert a.shape == b.shape
+        np.testing.assert_allclose(a, b, rtol=2e-6)

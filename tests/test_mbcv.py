@@ -166,3 +166,35 @@ def test_device_on_a_composed_panorama():
     dst, mask = b.blend()
     assert np.array_equal(mask, wmask) and np.array_equal(dst, want)
     assert mask.mean() > 0.5 * 255
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", range(12))
+def test_device_random_cases(seed):
+    """Seeded random layouts, band counts and fractional masks: the device
+    result is the oracle's bit for bit."""
+    import xpano_b200 as xb
+    rng = np.random.default_rng(400 + seed)
+    n = int(rng.integers(1, 6))
+    nb = int(rng.integers(0, 8))
+    feeds = []
+    for i in range(n):
+        w, h = int(rng.integers(17, 260)), int(rng.integers(9, 200))
+        img = rng.integers(0, 256, (h, w, 3)).astype(np.uint8)
+        m = rng.choice(np.array([0, 64, 128, 255], np.uint8), (h, w),
+                       p=[0.1, 0.1, 0.1, 0.7])
+        feeds.append((img, m, (int(rng.integers(-150, 300)),
+                               int(rng.integers(-80, 120)))))
+    x0 = min(f[2][0] for f in feeds)
+    y0 = min(f[2][1] for f in feeds)
+    x1 = max(f[2][0] + f[0].shape[1] for f in feeds)
+    y1 = max(f[2][1] + f[0].shape[0] for f in feeds)
+    roi = (x0, y0, x1 - x0, y1 - y0)
+    want, wmask, got_nb = oracle_blend(roi, feeds, nb)
+    b = xb.MultiBandOpenCV(num_bands=nb)
+    b.prepare(roi)
+    for f in feeds:
+        b.feed(*f)
+    dst, mask = b.blend()
+    assert b.num_bands == got_nb
+    assert np.array_equal(mask, wmask) and np.array_equal(dst, want)
