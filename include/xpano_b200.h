@@ -12,7 +12,9 @@
  *
  * Plain pointers and sizes only; every call returns an xp_status, never
  * throws; xp_last_error() gives the message of the last failure on the
- * calling thread. All calls are synchronous at return (the reference API is).
+ * calling thread. All calls are synchronous at return (the reference API is),
+ * except the explicitly split ones (xp_composer_run_begin / run_tile_begin,
+ * completed by run_end / run_tile_end).
  * Pointers are host pointers unless the `mem` argument says XP_MEM_DEVICE.
  * There is no CPU fallback: without a CUDA device every compute entry point
  * fails with XP_ERR_CUDA.
