@@ -494,10 +494,17 @@ xp_status xp_multiband_fetch(xp_multiband* b, void* dst_bgr, size_t dst_stride,
  * (xpano/algorithm/image.cc:83) and cv::imwrite of the panorama
  * (xpano/pipeline/stitcher_pipeline.cc:94-116; parameters as
  * CompressionParameters, :40-65: quality 95, baseline, 4:2:2 by default).
- * Done by nvJPEG (library code, linked statically), on the device, so that
- * only compressed bytes cross PCIe. Pixels are interleaved 8-bit BGR as
- * cv::imread returns them; a decoder's inverse DCT and chroma upsampling are
- * its own, so they are close to libjpeg-turbo's, not identical.
+ * Done on the device, so that only compressed bytes cross PCIe. Decoding:
+ * baseline / sequential Huffman streams (8-bit, one interleaved scan, grey or
+ * YCbCr 4:4:4 / 4:2:2 / 4:2:0, with or without restart intervals -- what
+ * cameras write) are decoded by this library's own kernels (csrc/jpeg_sm.cu:
+ * parallel Huffman decoding, libjpeg-turbo's inverse DCT, fancy upsampling
+ * and colour conversion restated), and the pixels equal cv::imread's bit for
+ * bit; everything else (progressive, ...) and all encoding go to nvJPEG
+ * (library code, linked statically), whose decoded pixels are close to
+ * libjpeg-turbo's, not identical. XP_JPEG_SM=0 in the environment sends every
+ * stream to nvJPEG, =2 makes a stream the kernels do not cover an error.
+ * Pixels are interleaved 8-bit BGR, oriented by EXIF, as cv::imread returns.
  *   info   : width, height, channel count of a JPEG stream (host bytes)
  *   decode : -> dst_bgr (mem = XP_MEM_DEVICE: e.g. straight into the buffer
  *            xp_composer_set_images adopts; XP_MEM_HOST: downloaded)
@@ -513,11 +520,14 @@ xp_status xp_codec_create(int device, xp_codec** out);
 void xp_codec_destroy(xp_codec* c);
 xp_status xp_codec_jpeg_info(xp_codec* c, const uint8_t* data, size_t len,
                              int wh[2], int* channels);
+/* out = {images decoded by the library's own kernels, images decoded by
+ * nvJPEG} since the codec was created */
+xp_status xp_codec_stats(xp_codec* c, int out[2]);
 xp_status xp_codec_jpeg_decode(xp_codec* c, const uint8_t* data, size_t len,
                                void* dst_bgr, size_t stride, int mem);
 /* n streams into n device buffers at once, several host threads each with
- * its own decoder state (nvJPEG decodes the Huffman stage on the calling
- * host thread): the sources of a panorama */
+ * its own stream and decoder state (nvJPEG, where it is used, decodes the
+ * Huffman stage on the calling host thread): the sources of a panorama */
 xp_status xp_codec_jpeg_decode_batch(xp_codec* c, int n,
                                      const uint8_t* const* data,
                                      const size_t* lens,

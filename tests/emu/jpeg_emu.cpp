@@ -1,0 +1,135 @@
+// TEST INFRASTRUCTURE: host emulation of the SM JPEG decoder. It compiles the
+// SAME headers the CUDA kernels use (xpano_b200/csrc/jpeg_sm.h, jpeg_parse.h)
+// and runs the kernels' steps as plain loops -- guess pass, synchronisation
+// sweeps, block-index scan, write pass, DC scan, inverse DCT, upsampling and
+// colour conversion -- so the CPU suite checks the decoder's arithmetic and
+// its synchronisation rule against cv2.imdecode without a GPU.
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../../xpano_b200/csrc/jpeg_parse.h"
+
+using namespace xp::jpg;
+
+static char g_why[256];
+
+extern "C" const char* emu_jpeg_why() { return g_why; }
+
+// -> 0 ok, 1 unsupported, 2 did not converge. info: {width, height, sweeps,
+// subsequences}
+extern "C" int emu_jpeg_decode(const uint8_t* d, size_t n, int sub_bytes,
+                               uint8_t* bgr, size_t stride, int info[4],
+                               int order) {
+  Parsed P;
+  if (!parse(d, n, sub_bytes, &P)) {
+    strncpy(g_why, P.why.c_str(), sizeof(g_why) - 1);
+    return 1;
+  }
+  const Frame& f = P.f;
+  info[0] = f.width;
+  info[1] = f.height;
+  info[3] = (int)P.subs.size();
+  if (!bgr) return 0;
+  const int ns = (int)P.subs.size();
+  const uint32_t scan_end = (uint32_t)P.scan_end;
+  std::vector<uint64_t> exit_state(ns);
+  std::vector<int> done(ns);
+  auto start_of = [&](int i, bool guess) {
+    State s;
+    const SubRec& r = P.subs[i];
+    if (r.is_first || guess) {
+      s.cb = r.start;
+      if (!r.is_first && d[r.start] == 0x00 && d[r.start - 1] == 0xFF)
+        s.cb = r.start + 1;
+      s.k = 0, s.b = 0, s.z = 0;
+    } else {
+      s = unpack(exit_state[i - 1]);
+    }
+    return s;
+  };
+  // guess pass
+  for (int i = 0; i < ns; ++i) {
+    State s = start_of(i, true);
+    done[i] = decode_subsequence<false>(d, P.subs[i].end, scan_end, f, P.huff,
+                                        kNatural, &s, nullptr, 0, 0);
+    exit_state[i] = pack(s);
+  }
+  // sweeps until nothing changes; order 0: every subsequence reads the
+  // previous sweep's states, 1: ascending in place, 2: descending in place
+  int sweeps = 0;
+  for (;; ++sweeps) {
+    if (sweeps > ns + 2) return 2;
+    bool changed = false;
+    std::vector<uint64_t> prev;
+    if (order == 0) prev = exit_state;
+    for (int j = 0; j < ns; ++j) {
+      const int i = order == 2 ? ns - 1 - j : j;
+      State s;
+      if (P.subs[i].is_first || order != 0)
+        s = start_of(i, false);
+      else
+        s = unpack(prev[i - 1]);
+      done[i] = decode_subsequence<false>(d, P.subs[i].end, scan_end, f, P.huff,
+                                          kNatural, &s, nullptr, 0, 0);
+      if (pack(s) != exit_state[i]) changed = true;
+      exit_state[i] = pack(s);
+    }
+    if (!changed) break;
+  }
+  info[2] = sweeps;
+  // block index of every subsequence's first symbol
+  std::vector<int> base(ns);
+  int run = 0;
+  for (int i = 0; i < ns; ++i) {
+    if (P.subs[i].is_first) run = (int)P.subs[i].first_mcu * f.bpm;
+    base[i] = run;
+    run += done[i];
+  }
+  std::vector<int16_t> coef((size_t)f.total_blocks * 64, 0);
+  const long long per = f.restart ? f.restart : (long long)f.mcus_x * f.mcus_y;
+  for (int i = 0; i < ns; ++i) {
+    State s = start_of(i, false);
+    long long limit = ((long long)P.subs[i].first_mcu + per) * f.bpm;
+    if (limit > f.total_blocks) limit = f.total_blocks;
+    decode_subsequence<true>(d, P.subs[i].end, scan_end, f, P.huff, kNatural,
+                             &s, coef.data(), base[i], (int)limit);
+  }
+  // DC prediction
+  int pred[3] = {0, 0, 0};
+  const int mcus = f.mcus_x * f.mcus_y;
+  for (int m = 0; m < mcus; ++m) {
+    if (f.restart && m % f.restart == 0) pred[0] = pred[1] = pred[2] = 0;
+    for (int b = 0; b < f.bpm; ++b) {
+      int16_t& dc = coef[((size_t)m * f.bpm + b) * 64];
+      pred[f.blk_comp[b]] += dc;
+      dc = (int16_t)pred[f.blk_comp[b]];
+    }
+  }
+  // inverse DCT into the component planes
+  std::vector<uint8_t> planes[3];
+  const uint8_t* pl[3] = {nullptr, nullptr, nullptr};
+  int pitch[3] = {0, 0, 0};
+  for (int c = 0; c < f.ncomp; ++c) {
+    planes[c].assign((size_t)f.plane_w[c] * f.plane_h[c], 0);
+    pitch[c] = f.plane_w[c];
+  }
+  for (int m = 0; m < mcus; ++m) {
+    const int mx = m % f.mcus_x, my = m / f.mcus_x;
+    for (int b = 0; b < f.bpm; ++b) {
+      const int c = f.blk_comp[b];
+      uint8_t px[64];
+      idct_islow(&coef[((size_t)m * f.bpm + b) * 64], P.quant[c], px);
+      const int bx = mx * f.hs[c] + f.blk_x[b], by = my * f.vs[c] + f.blk_y[b];
+      for (int r = 0; r < 8; ++r)
+        memcpy(&planes[c][(size_t)(by * 8 + r) * pitch[c] + bx * 8],
+               px + 8 * r, 8);
+    }
+  }
+  for (int c = 0; c < f.ncomp; ++c) pl[c] = planes[c].data();
+  for (int y = 0; y < f.height; ++y)
+    for (int x = 0; x < f.width; ++x)
+      pixel_bgr(f, pl, pitch, x, y, bgr + (size_t)y * stride + 3 * (size_t)x);
+  return 0;
+}

@@ -182,6 +182,7 @@ SYMBOLS = {
     "xp_codec_destroy": (None, [c_void_p]),
     "xp_codec_jpeg_info": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p,
                                    c_void_p]),
+    "xp_codec_stats": (c_int, [c_void_p, c_void_p]),
     "xp_codec_jpeg_decode": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p,
                                      c_size_t, c_int]),
     "xp_codec_jpeg_decode_batch": (c_int, [c_void_p, c_int, c_void_p,

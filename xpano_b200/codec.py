@@ -1,7 +1,9 @@
 """Host-side mirror of the JPEG steps either side of the path -- cv::imread of
 the sources (xpano/algorithm/image.cc:83) and cv::imwrite of the panorama
-(xpano/pipeline/stitcher_pipeline.cc:94-116) -- executed by nvJPEG inside
-libxpano_b200.so, so that only compressed bytes cross PCIe. SURVEY.md 8(f2)."""
+(xpano/pipeline/stitcher_pipeline.cc:94-116) -- executed on the device inside
+libxpano_b200.so, so that only compressed bytes cross PCIe: baseline streams
+are decoded by the library's own kernels (bit-identical to cv::imread), the
+rest and all encoding by nvJPEG. SURVEY.md 8(f2)."""
 from __future__ import annotations
 
 import ctypes
@@ -45,6 +47,13 @@ class JpegCodec:
         check(self._lib.xp_codec_jpeg_info(self._h, buf.ctypes.data, buf.size,
                                            wh, ctypes.byref(nc)))
         return wh[0], wh[1], nc.value
+
+    def stats(self):
+        """-> (images decoded by the library's kernels, images decoded by
+        nvJPEG) since this codec was created."""
+        out = (ctypes.c_int * 2)()
+        check(self._lib.xp_codec_stats(self._h, out))
+        return out[0], out[1]
 
     def decode(self, data):
         """-> (h, w, 3) uint8 BGR host array, like cv2.imdecode(IMREAD_COLOR)."""

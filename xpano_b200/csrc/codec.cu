@@ -16,8 +16,11 @@
 #include <nvjpeg.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstring>
+#include <exception>
 #include <mutex>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -25,6 +28,11 @@
 #include "common.h"
 
 namespace xp {
+
+// jpeg_sm.cu: baseline Huffman streams decoded by this repository's kernels
+bool sm_jpeg_decode(const uint8_t* data, size_t len, uint8_t* d_out,
+                    size_t out_pitch, cudaStream_t s, std::string* why,
+                    int stats[2]);
 
 static const char* nvjpeg_name(nvjpegStatus_t s) {
   switch (s) {
@@ -140,10 +148,31 @@ struct Codec {
   nvjpegEncoderState_t enc = nullptr;
   nvjpegEncoderParams_t par = nullptr;
   int backend = -1;
+  // XP_JPEG_SM: 1 (default) = baseline streams go to the SM decoder of
+  // jpeg_sm.cu and only what it does not cover to nvJPEG, 0 = nvJPEG for
+  // everything, 2 = a stream the SM decoder does not cover is an error
+  int sm_mode = 1;
+  std::atomic<int> n_sm{0}, n_lib{0};  // images decoded by either
+
+  // -> true when the SM decoder produced the image
+  bool decode_sm(const uint8_t* data, size_t len, uint8_t* d_out, size_t pitch,
+                 cudaStream_t s) {
+    if (!sm_mode) return false;
+    std::string why;
+    if (sm_jpeg_decode(data, len, d_out, pitch, s, &why, nullptr)) {
+      ++n_sm;
+      return true;
+    }
+    if (sm_mode == 2)
+      fail(XP_ERR_UNSUPPORTED, "jpeg: not covered by the SM decoder: %s",
+           why.c_str());
+    return false;
+  }
 
   void init() {
     select_device(device);
     if (handle) return;
+    if (const char* e = getenv("XP_JPEG_SM")) sm_mode = atoi(e);
     stream = create_stream(false);
     // Backend of the decoder: the hardware JPEG engine where the device has
     // one, else Huffman decoding on the SMs, else nvJPEG's default (Huffman
@@ -238,8 +267,11 @@ struct Codec {
       out.channel[0] = raw.as<unsigned char>();
       out.pitch[0] = (size_t)sw[0] * 3;
     }
-    XP_JPEG(nvjpegDecode(handle, state, data, len, NVJPEG_OUTPUT_BGRI, &out,
-                         stream));
+    if (!decode_sm(data, len, out.channel[0], out.pitch[0], stream)) {
+      XP_JPEG(nvjpegDecode(handle, state, data, len, NVJPEG_OUTPUT_BGRI, &out,
+                           stream));
+      ++n_lib;
+    }
     if (o != 1) {
       dim3 b(32, 8), g(div_up(W, 32), div_up(H, 8));
       orient_kernel<<<g, b, 0, stream>>>(raw.as<uint8_t>(), (size_t)sw[0] * 3,
@@ -251,9 +283,10 @@ struct Codec {
     XP_CUDA(cudaStreamSynchronize(stream));
   }
 
-  // n streams -> n device buffers (interleaved BGR, oriented). The Huffman
-  // stage of nvjpegDecode runs on the calling host thread (measured: 37 ms
-  // per 12-MP image with every backend this device accepts, the batched
+  // n streams -> n device buffers (interleaved BGR, oriented). Baseline
+  // streams are decoded by the kernels of jpeg_sm.cu. For the others the
+  // Huffman stage of nvjpegDecode runs on the calling host thread (measured:
+  // 37 ms per 12-MP image with every backend this device accepts, the batched
   // GPU-Huffman API included), so the images are decoded by several host
   // threads at once, each with its own decoder state and stream.
   struct Lane {
@@ -286,10 +319,12 @@ struct Codec {
         raw[i].reserve((size_t)sw[2 * i] * 3 * sw[2 * i + 1]);
     }
     std::vector<nvjpegStatus_t> status(n, NVJPEG_STATUS_SUCCESS);
+    std::vector<std::exception_ptr> thrown(T);
     std::vector<std::thread> threads;
     for (int t = 0; t < T; ++t)
       threads.emplace_back([&, t] {
         cudaSetDevice(device);
+        try {
         for (int i = t; i < n; i += T) {
           const int w = sw[2 * i], h = sw[2 * i + 1];
           const int W = orient[i] >= 5 ? h : w, H = orient[i] >= 5 ? w : h;
@@ -303,8 +338,12 @@ struct Codec {
             out.channel[0] = raw[i].as<unsigned char>();
             out.pitch[0] = (size_t)w * 3;
           }
-          status[i] = nvjpegDecode(handle, lanes[t].state, data[i], lens[i],
-                                   NVJPEG_OUTPUT_BGRI, &out, lanes[t].stream);
+          if (!decode_sm(data[i], lens[i], out.channel[0], out.pitch[0],
+                         lanes[t].stream)) {
+            status[i] = nvjpegDecode(handle, lanes[t].state, data[i], lens[i],
+                                     NVJPEG_OUTPUT_BGRI, &out, lanes[t].stream);
+            ++n_lib;
+          }
           if (status[i] == NVJPEG_STATUS_SUCCESS && orient[i] != 1) {
             dim3 b(32, 8), g(div_up(W, 32), div_up(H, 8));
             orient_kernel<<<g, b, 0, lanes[t].stream>>>(
@@ -312,9 +351,14 @@ struct Codec {
                 static_cast<uint8_t*>(dst[i]), stride, orient[i]);
           }
         }
+        } catch (...) {
+          thrown[t] = std::current_exception();
+        }
         cudaStreamSynchronize(lanes[t].stream);
       });
     for (std::thread& th : threads) th.join();
+    for (int t = 0; t < T; ++t)
+      if (thrown[t]) std::rethrow_exception(thrown[t]);
     for (int i = 0; i < n; ++i) XP_JPEG(status[i]);
     XP_CUDA(cudaGetLastError());
   }
@@ -401,6 +445,14 @@ xp_status xp_codec_jpeg_info(xp_codec* c, const uint8_t* data, size_t len,
   return xp::guard([&] {
     XP_REQUIRE(c && data && len && wh, "jpeg_info: null argument");
     c->info(data, len, wh, channels);
+  });
+}
+
+xp_status xp_codec_stats(xp_codec* c, int out[2]) {
+  return xp::guard([&] {
+    XP_REQUIRE(c && out, "codec_stats: null argument");
+    out[0] = c->n_sm.load();
+    out[1] = c->n_lib.load();
   });
 }
 
