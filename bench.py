@@ -549,6 +549,104 @@ def operator_surface_leg(xb, wl, cfg, steps):
             "reference"}
 
 
+def jpeg_leg(xb, torch, cfg, wl, local, steps, slots=3):
+    """Compressed in -> compressed out, pipelined: the sources
+    arrive as JPEG bytes in ordinary host memory (cv::imread's input,
+    image.cc:83) and are decoded on the device by the library's kernels, the
+    panorama is composed there and leaves as JPEG bytes (cv::imwrite's
+    output, stitcher_pipeline.cc:94-116): no raw pixel crosses PCIe. Three
+    host threads -- decode, compose, encode -- hand `slots` panoramas round.
+    Returns wall ms per panorama and the bytes moved, or None."""
+    import queue
+    import threading
+    if cfg["bpp"] != 8:
+        return None
+    ims, Ks, Rs = wl["ims"], wl["Ks"], wl["Rs"]
+    h, w = ims[0].shape[:2]
+    enc = xb.JpegCodec(device=local)
+    dec = xb.JpegCodec(device=local)
+    # camera-like sources: baseline, 4:2:2, quality 95
+    jpegs = [np.frombuffer(enc.encode(im, quality=95, subsampling=422),
+                           np.uint8) for im in ims]
+    kw = dict(projection=cfg["projection"], warp_scale=cfg["focal"],
+              max_pano_mpx=cfg["max_pano_mpx"], depth=8,
+              fixed_levels=cfg["fixed_levels"], device=local)
+    comps = [xb.Composer(**kw) for _ in range(slots)]
+    bufs = [[torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+             for _ in ims] for _ in range(slots)]
+    free, decoded, composed = queue.Queue(), queue.Queue(), queue.Queue()
+    errs, sizes = [], []
+
+    def guard(fn):
+        def run(n):
+            try:
+                torch.cuda.set_device(local)
+                fn(n)
+            except Exception as e:
+                errs.append(e)
+        return run
+
+    @guard
+    def decode(n):
+        for _ in range(n):
+            k = free.get(timeout=120)
+            dec.decode_batch_device(jpegs, [t.data_ptr() for t in bufs[k]])
+            decoded.put(k)
+
+    @guard
+    def compose(n):
+        for _ in range(n):
+            k = decoded.get(timeout=120)
+            comps[k].set_images_device([t.data_ptr() for t in bufs[k]],
+                                       [(w, h)] * len(ims), Ks, Rs,
+                                       wl["gains"], wl["seams"])
+            comps[k].run()
+            composed.put(k)
+
+    @guard
+    def encode(n):
+        for _ in range(n):
+            k = composed.get(timeout=120)
+            sizes.append(len(comps[k].encode_jpeg(enc)))
+            free.put(k)
+
+    def one_pass(n):
+        for k in range(slots):
+            free.put(k)
+        ts = [threading.Thread(target=f, args=(n,), daemon=True)
+              for f in (decode, compose, encode)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join(timeout=300)
+        while not free.empty():
+            free.get()
+        if errs:
+            raise errs[0]
+        if any(t.is_alive() for t in ts):
+            raise RuntimeError("jpeg leg: a stage did not finish")
+
+    one_pass(slots)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    one_pass(steps)
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    aux = sum(a.nbytes for k in ("gains", "seams") if wl[k] is not None
+              for a in wl[k])
+    own, lib = dec.stats()
+    return {"ms_per_step": 1e3 * wall / steps, "steps": steps,
+            "h2d_bytes_per_step": int(sum(j.size for j in jpegs) + aux),
+            "d2h_bytes_per_step": int(sizes[-1]),
+            "sources_decoded_by": {"own_kernels": own, "nvjpeg": lib},
+            "panoramas_in_flight": slots,
+            "what": "JPEG bytes in (baseline 4:2:2 q95, pageable host memory) "
+                    "-> decode on the device -> compose -> JPEG bytes out "
+                    "(4:2:2 q95); decode / compose / encode of successive "
+                    "panoramas overlap"}
+
+
+
 def sharding_group(world, rank):
     from xpano_b200 import sharding
     return sharding.assign_groups(world, world, rank)[0]
@@ -904,6 +1002,21 @@ def run_ours(args, cfg):
                      "what": "run_begin of panorama k+1 issued while the "
                              "pyramid tail of panorama k runs (two composers)"}
 
+    # ---- compressed in -> compressed out (informational) -------------------
+    e2e_jpeg = None
+    if not args.no_jpeg:
+        try:
+            e2e_jpeg = jpeg_leg(xb, torch, cfg, wl, local, e2e_steps)
+        except Exception as e:  # never costs the headline numbers
+            e2e_jpeg = {"error": str(e)[:200]}
+        if e2e_jpeg and "ms_per_step" in e2e_jpeg:
+            j_ms = max_over_ranks(e2e_jpeg["ms_per_step"])
+            e2e_jpeg["ms_per_step"] = j_ms
+            e2e_jpeg["value"] = total_mp / (j_ms / 1e3)
+            e2e_jpeg["unit"] = UNIT
+        elif world > 1:
+            max_over_ranks(0.0)  # keep the ranks' collectives in step
+
     # ---- e2e through the drop-in operator surface -------------------------
     op_surface = None
     if world == 1 and not args.no_surface:
@@ -987,7 +1100,7 @@ def run_ours(args, cfg):
                 "steps": e2e_steps, "wall_ms_per_step": 1e3 * wall / e2e_steps,
                 "panoramas_in_flight": in_flight},
         "e2e_operator_surface": op_surface,
-        "resident_pipelined": pipelined,
+        "resident_pipelined": pipelined, "e2e_jpeg": e2e_jpeg,
         "gpu_launches": int(launches), "clocks": clk, "roofline": roof,
         "stages": per_stage, "latency_bound_stages_ms": serial,
         "sizes_mp": {"s_src": info["s_src"] / 1e6, "s_w": info["s_w"] / 1e6,
@@ -1054,6 +1167,8 @@ def main():
     ap.add_argument("--cpu-passes", type=int, default=2,
                     help="timed passes of the inline CPU leg (one warm-up "
                     "pass before them when > 1)")
+    ap.add_argument("--no-jpeg", action="store_true",
+                    help="skip the compressed-in / compressed-out leg")
     ap.add_argument("--no-surface", action="store_true",
                     help="skip the operator-surface e2e leg")
     ap.add_argument("--no-check", dest="check", action="store_false",

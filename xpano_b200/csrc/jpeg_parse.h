@@ -223,6 +223,18 @@ inline bool parse(const uint8_t* d, size_t n, int sub_bytes, Parsed* out) {
   };
   std::vector<Seg> segs;
   size_t q = out->scan_begin, seg_begin = q, end = n;
+  if (!f.restart) {
+    // One interval: its end only has to be at or after the scan's last byte
+    // (decoding stops with the last block), so the last EOI of the stream
+    // serves -- found from the back -- and the scan is not searched at all.
+    q = n;
+    const size_t stop = n > 65536 + out->scan_begin ? n - 65536 : out->scan_begin;
+    for (size_t k = n; k >= stop + 2; --k)
+      if (d[k - 2] == 0xFF && d[k - 1] == 0xD9) {
+        end = k - 2;
+        break;
+      }
+  }
   while (q < n) {
     const uint8_t* hit =
         static_cast<const uint8_t*>(memchr(d + q, 0xFF, n - q));

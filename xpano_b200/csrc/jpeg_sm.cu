@@ -18,6 +18,7 @@
 // The arithmetic is in jpeg_sm.h / jpeg_parse.h, which tests/emu/jpeg_emu.cpp
 // also compiles for the host. (After Weissenberger & Schmidt, "Massively
 // parallel Huffman decoding on GPUs", ICPP 2018, and its JPEG follow-up.)
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -27,7 +28,15 @@
 namespace xp {
 namespace jpg {
 
-constexpr int kSubBytes = 128;
+constexpr int kSubBytes = 128;  // XP_JPEG_SUB overrides (experiments)
+static int sub_bytes() {
+  static const int v = [] {
+    const char* e = getenv("XP_JPEG_SUB");
+    const int n = e ? atoi(e) : kSubBytes;
+    return n >= 8 && n <= 4096 ? n : kSubBytes;
+  }();
+  return v;
+}
 constexpr int kThreads = 256;
 
 __constant__ uint8_t c_natural[64] = XP_JPG_NATURAL;
@@ -44,6 +53,9 @@ struct Job {
   uint64_t* in_state;     // start state its last decode used
   int* done;              // blocks it completed
   int* base;              // block index of its first symbol
+  int* dc_has;            // [3][dc_chunks] DC scan: chunk saw a restart,
+  int* dc_val;            //                its sum since the last one
+  int dc_chunks;
   int16_t* coef;
   uint8_t* plane[3];
 };
@@ -136,6 +148,30 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// Exclusive scan over the 1024 threads of a block of (has, val) pairs under
+// combine(a, b) = b.has ? b : {a.has, a.val + b.val}: "the value since the
+// last restart".
+__device__ __forceinline__ void block_scan_1024(int* has, int* val, int* s_has,
+                                                int* s_val) {
+  const int t = threadIdx.x;
+  int h = *has, v = *val;
+  s_has[t] = h;
+  s_val[t] = v;
+  __syncthreads();
+  for (int off = 1; off < 1024; off <<= 1) {
+    if (t >= off && !h) {
+      v += s_val[t - off];
+      h = s_has[t - off];
+    }
+    __syncthreads();
+    s_has[t] = h;
+    s_val[t] = v;
+    __syncthreads();
+  }
+  *has = t ? s_has[t - 1] : 0;
+  *val = t ? s_val[t - 1] : 0;
+}
+
 // base[i] = first block of subsequence i: its restart interval's first block
 // plus the blocks completed by the interval's earlier subsequences
 __global__ void __launch_bounds__(1024) huff_base_kernel(const Job j) {
@@ -149,23 +185,8 @@ __global__ void __launch_bounds__(1024) huff_base_kernel(const Job j) {
     if (r.is_first) has = 1, val = (int)r.first_mcu * j.f.bpm;
     val += j.done[i];
   }
-  s_has[t] = has;
-  s_val[t] = val;
-  __syncthreads();
-  if (t == 0) {  // exclusive combine, 1024 steps
-    int h = 0, v = 0;
-    for (int k = 0; k < 1024; ++k) {
-      const int kh = s_has[k], kv = s_val[k];
-      s_has[k] = h;
-      s_val[k] = v;
-      if (kh)
-        h = 1, v = kv;
-      else
-        v += kv;
-    }
-  }
-  __syncthreads();
-  int run = s_val[t];
+  block_scan_1024(&has, &val, s_has, s_val);
+  int run = val;
   for (int i = lo; i < hi; ++i) {
     const SubRec r = j.subs[i];
     if (r.is_first) run = (int)r.first_mcu * j.f.bpm;
@@ -191,37 +212,57 @@ __global__ void __launch_bounds__(kThreads) huff_write_kernel(const Job j) {
 }
 
 // DC differences -> DC values: per component a prefix sum over its blocks in
-// scan order, restarted with every restart interval. One CTA per component.
-__global__ void __launch_bounds__(1024) dc_scan_kernel(const Job j) {
-  __shared__ int s_has[1024], s_val[1024];
-  const int c = blockIdx.x, t = threadIdx.x;
+// scan order, restarted with every restart interval. Chunks of kDcChunk MCUs:
+// sums per chunk, a scan of the chunk sums (one CTA per component), then
+// every chunk is rewritten from its prefix.
+constexpr int kDcChunk = 16;
+
+__global__ void __launch_bounds__(256) dc_partial_kernel(const Job j) {
+  const int c = blockIdx.y, q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= j.dc_chunks) return;
   const int mcus = j.f.mcus_x * j.f.mcus_y;
   const int nb = j.f.hs[c] * j.f.vs[c], first = j.f.blk_first[c];
-  const int chunk = (mcus + 1023) / 1024;
-  const int lo = min(mcus, t * chunk), hi = min(mcus, lo + chunk);
+  const int lo = q * kDcChunk, hi = min(mcus, lo + kDcChunk);
   int has = 0, val = 0;
   for (int m = lo; m < hi; ++m) {
     if (j.f.restart && m % j.f.restart == 0) has = 1, val = 0;
     for (int b = 0; b < nb; ++b)
       val += j.coef[((size_t)m * j.f.bpm + first + b) * 64];
   }
-  s_has[t] = has;
-  s_val[t] = val;
-  __syncthreads();
-  if (t == 0) {
-    int h = 0, v = 0;
-    for (int k = 0; k < 1024; ++k) {
-      const int kh = s_has[k], kv = s_val[k];
-      s_has[k] = h;
-      s_val[k] = v;
-      if (kh)
-        h = 1, v = kv;
-      else
-        v += kv;
-    }
+  j.dc_has[c * j.dc_chunks + q] = has;
+  j.dc_val[c * j.dc_chunks + q] = val;
+}
+
+__global__ void __launch_bounds__(1024) dc_prefix_kernel(const Job j) {
+  __shared__ int s_has[1024], s_val[1024];
+  const int c = blockIdx.x, t = threadIdx.x;
+  int* hs = j.dc_has + c * j.dc_chunks;
+  int* vs = j.dc_val + c * j.dc_chunks;
+  const int per = (j.dc_chunks + 1023) / 1024;
+  const int lo = min(j.dc_chunks, t * per), hi = min(j.dc_chunks, lo + per);
+  int has = 0, val = 0;
+  for (int q = lo; q < hi; ++q) {
+    if (hs[q])
+      has = 1, val = vs[q];
+    else
+      val += vs[q];
   }
-  __syncthreads();
-  int run = s_val[t];
+  block_scan_1024(&has, &val, s_has, s_val);
+  int run = val;
+  for (int q = lo; q < hi; ++q) {  // chunk sums -> exclusive prefixes
+    const int h = hs[q], v = vs[q];
+    vs[q] = run;
+    run = h ? v : run + v;
+  }
+}
+
+__global__ void __launch_bounds__(256) dc_apply_kernel(const Job j) {
+  const int c = blockIdx.y, q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= j.dc_chunks) return;
+  const int mcus = j.f.mcus_x * j.f.mcus_y;
+  const int nb = j.f.hs[c] * j.f.vs[c], first = j.f.blk_first[c];
+  const int lo = q * kDcChunk, hi = min(mcus, lo + kDcChunk);
+  int run = j.dc_val[c * j.dc_chunks + q];
   for (int m = lo; m < hi; ++m) {
     if (j.f.restart && m % j.f.restart == 0) run = 0;
     for (int b = 0; b < nb; ++b) {
@@ -285,7 +326,7 @@ __global__ void __launch_bounds__(256)
 bool sm_jpeg_probe(const uint8_t* data, size_t len, int wh[2],
                    std::string* why) {
   jpg::Parsed P;
-  if (!jpg::parse(data, len, jpg::kSubBytes, &P)) {
+  if (!jpg::parse(data, len, jpg::sub_bytes(), &P)) {
     if (why) *why = P.why;
     return false;
   }
@@ -303,7 +344,7 @@ bool sm_jpeg_decode(const uint8_t* data, size_t len, uint8_t* d_out,
                     int stats[2]) {
   using namespace jpg;
   Parsed P;
-  if (!parse(data, len, kSubBytes, &P)) {
+  if (!parse(data, len, sub_bytes(), &P)) {
     if (why) *why = P.why;
     return false;
   }
@@ -327,7 +368,9 @@ bool sm_jpeg_decode(const uint8_t* data, size_t len, uint8_t* d_out,
   raw.reserve(raw_bytes + 16);
   subs.reserve((size_t)ns * sizeof(SubRec));
   tabs.reserve(sizeof(P.huff) + sizeof(P.quant));
-  state.reserve((size_t)ns * (2 * sizeof(uint64_t) + 2 * sizeof(int)));
+  j.dc_chunks = div_up(f.mcus_x * f.mcus_y, kDcChunk);
+  state.reserve((size_t)ns * (2 * sizeof(uint64_t) + 2 * sizeof(int)) +
+                (size_t)j.dc_chunks * 6 * sizeof(int));
   coef.reserve(coef_bytes);
   planes.reserve(planes_total);
   for (SubRec& r : P.subs) {
@@ -344,50 +387,74 @@ bool sm_jpeg_decode(const uint8_t* data, size_t len, uint8_t* d_out,
   j.in_state = j.exit_state + ns;
   j.done = reinterpret_cast<int*>(j.in_state + ns);
   j.base = j.done + ns;
+  j.dc_has = j.base + ns;
+  j.dc_val = j.dc_has + 3 * (size_t)j.dc_chunks;
   j.coef = coef.as<int16_t>();
   uint8_t* pp = planes.as<uint8_t>();
   for (int c = 0; c < 3; ++c) {
     j.plane[c] = c < f.ncomp ? pp : nullptr;
     pp += plane_bytes[c];
   }
+  // The stream's bytes and the subsequence table go through pinned staging
+  // memory of our own: a cudaMemcpyAsync from pageable memory is staged by
+  // the driver under a lock that the other decoding threads also wait for.
   Mailbox box;
-  box.reset(sizeof(P.huff) + sizeof(P.quant) + 64);
-  int* flag = static_cast<int*>(box.take(sizeof(int)));
+  const size_t subs_bytes = (size_t)ns * sizeof(SubRec);
+  // (sizes rounded up to a power of two, so that the cached pinned blocks of
+  // one panorama's sources serve the next one's)
+  size_t pinned = 65536;
+  while (pinned < raw_bytes + subs_bytes + sizeof(P.huff) + sizeof(P.quant) + 256)
+    pinned *= 2;
+  box.reset(pinned);
+  int* flag = static_cast<int*>(box.take(2 * sizeof(int)));
   void* d_flag = nullptr;
   XP_CUDA(cudaHostGetDevicePointer(&d_flag, flag, 0));
-  XP_CUDA(cudaMemcpyAsync(raw.p, data + skip, raw_bytes, cudaMemcpyHostToDevice,
+  void* h_raw = box.take(raw_bytes);
+  memcpy(h_raw, data + skip, raw_bytes);
+  XP_CUDA(cudaMemcpyAsync(raw.p, h_raw, raw_bytes, cudaMemcpyHostToDevice, s));
+  void* h_subs = box.take(subs_bytes);
+  memcpy(h_subs, P.subs.data(), subs_bytes);
+  XP_CUDA(cudaMemcpyAsync(subs.p, h_subs, subs_bytes, cudaMemcpyHostToDevice,
                           s));
-  XP_CUDA(cudaMemcpyAsync(subs.p, P.subs.data(), (size_t)ns * sizeof(SubRec),
-                          cudaMemcpyHostToDevice, s));
   box.to_device(tabs.p, P.huff, sizeof(P.huff), s);
   box.to_device(tabs.as<uint8_t>() + sizeof(P.huff), P.quant, sizeof(P.quant),
                 s);
-  XP_CUDA(cudaMemsetAsync(coef.p, 0, coef_bytes, s));
   const int grid = div_up(ns, kThreads);
   huff_guess_kernel<<<grid, kThreads, 0, s>>>(j);
   XP_LAUNCHED();
+  // Two synchronisation launches and everything after them are queued
+  // without waiting: the second launch almost always changes nothing (the
+  // first one did the work), which is all that has to be known -- afterwards.
+  // If it did change a state, the round is repeated from there.
   int launches = 0;
-  for (;;) {
-    *flag = 0;
-    huff_sync_kernel<<<grid, kThreads, 0, s>>>(j, static_cast<int*>(d_flag));
+  for (int round = 0;; ++round) {
+    flag[0] = flag[1] = 0;
+    for (int k = 0; k < 2; ++k, ++launches) {
+      huff_sync_kernel<<<grid, kThreads, 0, s>>>(j,
+                                                 static_cast<int*>(d_flag) + k);
+      XP_LAUNCHED();
+    }
+    XP_CUDA(cudaMemsetAsync(coef.p, 0, coef_bytes, s));
+    huff_base_kernel<<<1, 1024, 0, s>>>(j);
+    XP_LAUNCHED();
+    huff_write_kernel<<<grid, kThreads, 0, s>>>(j);
+    XP_LAUNCHED();
+    const dim3 dc_grid(div_up(j.dc_chunks, 256), f.ncomp);
+    dc_partial_kernel<<<dc_grid, 256, 0, s>>>(j);
+    XP_LAUNCHED();
+    dc_prefix_kernel<<<f.ncomp, 1024, 0, s>>>(j);
+    XP_LAUNCHED();
+    dc_apply_kernel<<<dc_grid, 256, 0, s>>>(j);
+    XP_LAUNCHED();
+    idct_kernel<<<div_up(f.total_blocks, 128), 128, 0, s>>>(j);
+    XP_LAUNCHED();
+    dim3 b(32, 8), g(div_up(f.width, 32), div_up(f.height, 8));
+    color_kernel<<<g, b, 0, s>>>(j, d_out, out_pitch);
     XP_LAUNCHED();
     XP_CUDA(cudaStreamSynchronize(s));
-    ++launches;
-    if (!*flag) break;
-    XP_REQUIRE(launches <= grid + 2, "jpeg: synchronisation did not converge");
+    if (!flag[1]) break;
+    XP_REQUIRE(round <= grid + 2, "jpeg: synchronisation did not converge");
   }
-  huff_base_kernel<<<1, 1024, 0, s>>>(j);
-  XP_LAUNCHED();
-  huff_write_kernel<<<grid, kThreads, 0, s>>>(j);
-  XP_LAUNCHED();
-  dc_scan_kernel<<<f.ncomp, 1024, 0, s>>>(j);
-  XP_LAUNCHED();
-  idct_kernel<<<div_up(f.total_blocks, 128), 128, 0, s>>>(j);
-  XP_LAUNCHED();
-  dim3 b(32, 8), g(div_up(f.width, 32), div_up(f.height, 8));
-  color_kernel<<<g, b, 0, s>>>(j, d_out, out_pitch);
-  XP_LAUNCHED();
-  XP_CUDA(cudaStreamSynchronize(s));
   if (stats) stats[0] = ns, stats[1] = launches;
   return true;
 }
