@@ -33,17 +33,20 @@ extern "C" int emu_jpeg_decode(const uint8_t* d, size_t n, int sub_bytes,
   info[3] = (int)P.subs.size();
   if (!bgr) return 0;
   const int ns = (int)P.subs.size();
-  const uint32_t scan_end = (uint32_t)P.scan_end;
+  std::vector<uint32_t> words;
+  const uint32_t total_bits =
+      (uint32_t)(8 * destuff(d, P.scan_begin, P.scan_end, &words));
+  auto sub_end = [&](int i) {
+    return P.subs[i].end < total_bits ? P.subs[i].end : total_bits;
+  };
   std::vector<uint64_t> exit_state(ns);
   std::vector<int> done(ns);
   auto start_of = [&](int i, bool guess) {
     State s;
     const SubRec& r = P.subs[i];
     if (r.is_first || guess) {
-      s.cb = r.start;
-      if (!r.is_first && d[r.start] == 0x00 && d[r.start - 1] == 0xFF)
-        s.cb = r.start + 1;
-      s.k = 0, s.b = 0, s.z = 0;
+      s.p = r.start;
+      s.b = 0, s.z = 0;
     } else {
       s = unpack(exit_state[i - 1]);
     }
@@ -52,8 +55,7 @@ extern "C" int emu_jpeg_decode(const uint8_t* d, size_t n, int sub_bytes,
   // guess pass
   for (int i = 0; i < ns; ++i) {
     State s = start_of(i, true);
-    done[i] = decode_subsequence<false>(d, P.subs[i].end, scan_end, f, P.huff,
-                                        kNatural, &s, nullptr, 0, 0);
+    done[i] = decode_subsequence<false>(words.data(), sub_end(i), f, P.huff, &s, nullptr, nullptr, 0, 0);
     exit_state[i] = pack(s);
   }
   // sweeps until nothing changes; order 0: every subsequence reads the
@@ -71,8 +73,8 @@ extern "C" int emu_jpeg_decode(const uint8_t* d, size_t n, int sub_bytes,
         s = start_of(i, false);
       else
         s = unpack(prev[i - 1]);
-      done[i] = decode_subsequence<false>(d, P.subs[i].end, scan_end, f, P.huff,
-                                          kNatural, &s, nullptr, 0, 0);
+      done[i] = decode_subsequence<false>(words.data(), sub_end(i), f, P.huff,
+                                          &s, nullptr, nullptr, 0, 0);
       if (pack(s) != exit_state[i]) changed = true;
       exit_state[i] = pack(s);
     }
@@ -88,13 +90,14 @@ extern "C" int emu_jpeg_decode(const uint8_t* d, size_t n, int sub_bytes,
     run += done[i];
   }
   std::vector<int16_t> coef((size_t)f.total_blocks * 64, 0);
+  std::vector<int16_t> dcs((size_t)f.total_blocks, 0);
   const long long per = f.restart ? f.restart : (long long)f.mcus_x * f.mcus_y;
   for (int i = 0; i < ns; ++i) {
     State s = start_of(i, false);
     long long limit = ((long long)P.subs[i].first_mcu + per) * f.bpm;
     if (limit > f.total_blocks) limit = f.total_blocks;
-    decode_subsequence<true>(d, P.subs[i].end, scan_end, f, P.huff, kNatural,
-                             &s, coef.data(), base[i], (int)limit);
+    decode_subsequence<true>(words.data(), sub_end(i), f, P.huff, &s,
+                             coef.data(), dcs.data(), base[i], (int)limit);
   }
   // DC prediction
   int pred[3] = {0, 0, 0};
@@ -102,7 +105,7 @@ extern "C" int emu_jpeg_decode(const uint8_t* d, size_t n, int sub_bytes,
   for (int m = 0; m < mcus; ++m) {
     if (f.restart && m % f.restart == 0) pred[0] = pred[1] = pred[2] = 0;
     for (int b = 0; b < f.bpm; ++b) {
-      int16_t& dc = coef[((size_t)m * f.bpm + b) * 64];
+      int16_t& dc = dcs[(size_t)m * f.bpm + b];
       pred[f.blk_comp[b]] += dc;
       dc = (int16_t)pred[f.blk_comp[b]];
     }
@@ -120,7 +123,8 @@ extern "C" int emu_jpeg_decode(const uint8_t* d, size_t n, int sub_bytes,
     for (int b = 0; b < f.bpm; ++b) {
       const int c = f.blk_comp[b];
       uint8_t px[64];
-      idct_islow(&coef[((size_t)m * f.bpm + b) * 64], P.quant[c], px);
+      idct_islow(&coef[((size_t)m * f.bpm + b) * 64],
+                 dcs[(size_t)m * f.bpm + b], P.quant[c], px);
       const int bx = mx * f.hs[c] + f.blk_x[b], by = my * f.vs[c] + f.blk_y[b];
       for (int r = 0; r < 8; ++r)
         memcpy(&planes[c][(size_t)(by * 8 + r) * pitch[c] + bx * 8],

@@ -4,6 +4,7 @@
 // several scans, CMYK, unusual sampling -- are reported as unsupported and
 // go to nvJPEG. Plain C++; also compiled into tests/emu/jpeg_emu.cpp.
 #pragma once
+#include <algorithm>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -217,66 +218,102 @@ inline bool parse(const uint8_t* d, size_t n, int sub_bytes, Parsed* out) {
     return unsupported(out, "image too large");
   f.total_blocks = (int)(total_mcus * f.bpm);
 
-  // restart intervals and the end of the scan
+  for (int k = 0; k < f.bpm; ++k) {
+    f.blk_dc[k] = f.dc_tab[f.blk_comp[k]];
+    f.blk_ac[k] = f.ac_tab[f.blk_comp[k]];
+  }
+
+  // The end of the scan and the restart intervals, as byte ranges of the
+  // DESTUFFED scan (jpeg_sm.h: destuff_keeps).
   struct Seg {
-    size_t begin, end;
+    size_t begin, end;  // destuffed bytes
   };
   std::vector<Seg> segs;
-  size_t q = out->scan_begin, seg_begin = q, end = n;
+  size_t end = n;
   if (!f.restart) {
-    // One interval: its end only has to be at or after the scan's last byte
+    // One interval. Its end only has to be at or after the scan's last byte
     // (decoding stops with the last block), so the last EOI of the stream
-    // serves -- found from the back -- and the scan is not searched at all.
-    q = n;
-    const size_t stop = n > 65536 + out->scan_begin ? n - 65536 : out->scan_begin;
+    // serves -- found from the back -- and the scan is not searched at all;
+    // its destuffed length is bounded by its raw length (the device knows
+    // the exact one).
+    const size_t stop =
+        n > 65536 + out->scan_begin ? n - 65536 : out->scan_begin;
     for (size_t k = n; k >= stop + 2; --k)
       if (d[k - 2] == 0xFF && d[k - 1] == 0xD9) {
         end = k - 2;
         break;
       }
-  }
-  while (q < n) {
-    const uint8_t* hit =
-        static_cast<const uint8_t*>(memchr(d + q, 0xFF, n - q));
-    if (!hit) break;
-    const size_t at = (size_t)(hit - d);
-    if (at + 1 >= n) {
-      end = at;
-      break;
+    segs.push_back({0, end - out->scan_begin});
+  } else {
+    size_t q = out->scan_begin, kept = 0, seg_begin = 0, last = q;
+    while (q < n) {
+      const uint8_t* hit =
+          static_cast<const uint8_t*>(memchr(d + q, 0xFF, n - q));
+      if (!hit) {
+        q = n;
+        break;
+      }
+      const size_t at = (size_t)(hit - d);
+      if (at + 1 >= n) {
+        q = at;
+        break;
+      }
+      const uint8_t m = d[at + 1];
+      if (m == 0x00) {  // FF kept, 00 dropped
+        kept += at + 1 - last;
+        last = q = at + 2;
+      } else if (m >= 0xD0 && m <= 0xD7) {  // both dropped
+        kept += at - last;
+        last = q = at + 2;
+        segs.push_back({seg_begin, kept});
+        seg_begin = kept;
+      } else if (m == 0xFF) {
+        return unsupported(out, "fill bytes inside the scan");
+      } else {
+        q = at;
+        break;
+      }
     }
-    const uint8_t m = d[at + 1];
-    if (m == 0x00) {
-      q = at + 2;
-    } else if (m >= 0xD0 && m <= 0xD7) {
-      segs.push_back({seg_begin, at});
-      seg_begin = q = at + 2;
-    } else if (m == 0xFF) {
-      return unsupported(out, "fill bytes inside the scan");
-    } else {
-      end = at;
-      break;
-    }
+    end = q;
+    kept += end - last;
+    segs.push_back({seg_begin, kept});
   }
-  segs.push_back({seg_begin, end});
   out->scan_end = end;
+  if (end <= out->scan_begin) return unsupported(out, "empty scan");
   const long long per = f.restart ? f.restart : total_mcus;
   const long long want = (total_mcus + per - 1) / per;
   if ((long long)segs.size() != want)
     return unsupported(out, "restart markers do not match the interval");
+  if ((end - out->scan_begin) >= 0x1FFFFFF0u)
+    return unsupported(out, "scan too large");
   out->subs.clear();
   for (size_t k = 0; k < segs.size(); ++k) {
     if (segs[k].end <= segs[k].begin)
       return unsupported(out, "empty restart interval");
     for (size_t b = segs[k].begin; b < segs[k].end; b += (size_t)sub_bytes) {
       SubRec r;
-      r.start = (uint32_t)b;
-      r.end = (uint32_t)std::min(b + (size_t)sub_bytes, segs[k].end);
+      r.start = (uint32_t)(8 * b);
+      r.end = (uint32_t)(8 * std::min(b + (size_t)sub_bytes, segs[k].end));
       r.first_mcu = (uint32_t)(k * per);
       r.is_first = b == segs[k].begin;
       out->subs.push_back(r);
     }
   }
   return true;
+}
+
+// Host form of the destuffing kernels (the emulation's): -> big-endian words
+// with two zero words behind the last byte; returns the destuffed bytes.
+inline size_t destuff(const uint8_t* d, size_t begin, size_t end,
+                      std::vector<uint32_t>* words) {
+  std::vector<uint8_t> bytes;
+  bytes.reserve(end - begin);
+  for (size_t i = begin; i < end; ++i)
+    if (destuff_keeps(d, i, begin, end)) bytes.push_back(d[i]);
+  words->assign(bytes.size() / 4 + 3, 0);
+  for (size_t i = 0; i < bytes.size(); ++i)
+    (*words)[i / 4] |= (uint32_t)bytes[i] << (24 - 8 * (i % 4));
+  return bytes.size();
 }
 
 }  // namespace jpg

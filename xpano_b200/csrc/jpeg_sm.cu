@@ -1,7 +1,10 @@
 // Baseline JPEG decoded on the SMs (the cv::imread side,
 // xpano/algorithm/image.cc:83). nvJPEG decodes the Huffman scan of a 12-MP
-// source on ONE host thread (37 ms, codec.cu); here the scan is cut into
-// subsequences of kSubBytes raw bytes, one thread each:
+// source on ONE host thread (37 ms, codec.cu); here the scan is destuffed
+// (stuffed zeros and restart markers taken out by a count / scan / scatter
+// compaction, bytes packed big-endian into words, so that any 32 bits of it
+// are two loads and a funnel shift) and cut into subsequences of kSubBytes
+// bytes, one thread each:
 //   1. guess pass: every thread decodes its subsequence from "start of a
 //      block" -- wrong for most, but Huffman streams resynchronise within a
 //      few dozen symbols, so most EXIT states are already right;
@@ -39,24 +42,30 @@ static int sub_bytes() {
 }
 constexpr int kThreads = 256;
 
-__constant__ uint8_t c_natural[64] = XP_JPG_NATURAL;
-
 struct Job {
   Frame f;
-  const uint8_t* raw;
+  const uint8_t* raw;  // the stream from a 256-byte boundary before the scan
+  uint32_t scan_begin, scan_end;  // the scan's bytes in raw[]
+  uint32_t* words;       // the destuffed scan: big-endian words, zero padded
+  uint32_t* total_bits;  // its length (device)
+  int* ds_count;         // kept bytes per destuffing block, then their offsets
+  int ds_blocks;
   const SubRec* subs;
   int n_sub;
-  uint32_t scan_end;
   const HuffTab* tabs;
   const uint16_t* quant;  // [3][64]
   uint64_t* exit_state;   // state after a subsequence's last symbol
   uint64_t* in_state;     // start state its last decode used
   int* done;              // blocks it completed
-  int* base;              // block index of its first symbol
+  int* base;              // block index of its first symbol: absolute with
+                          // bit 31, else relative to its CTA's base_cta
+  int* base_has;          // per CTA of the write pass: it holds an interval
+  int* base_cta;          //   start; blocks completed (then: its prefix)
   int* dc_has;            // [3][dc_chunks] DC scan: chunk saw a restart,
   int* dc_val;            //                its sum since the last one
   int dc_chunks;
-  int16_t* coef;
+  int16_t* coef;  // [block][64] zigzag order, AC
+  int16_t* dc;    // [block] DC difference, then value
   uint8_t* plane[3];
 };
 
@@ -68,15 +77,105 @@ __device__ __forceinline__ void load_tabs(const HuffTab* g, HuffTab* sh) {
   __syncthreads();
 }
 
-__device__ __forceinline__ State first_state(const SubRec& r,
-                                             const uint8_t* raw) {
+__device__ __forceinline__ State first_state(const SubRec& r) {
   State s;
-  s.cb = r.start;
-  // a guess must not begin on a stuffed zero
-  if (!r.is_first && raw[r.start] == 0x00 && raw[r.start - 1] == 0xFF)
-    s.cb = r.start + 1;
-  s.k = 0, s.b = 0, s.z = 0;
+  s.p = r.start;
+  s.b = 0, s.z = 0;
   return s;
+}
+
+// ---------------------------------------------------------------------------
+// Destuffing, 16 raw bytes per thread. keep16 -> bit k set when byte i0 + k
+// stays (jpeg_sm.h: destuff_keeps), v = the bytes.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t keep16(const Job& j, uint32_t i0,
+                                           uint8_t v[16]) {
+  const uint4 q = *reinterpret_cast<const uint4*>(j.raw + i0);
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int k = 0; k < 16; ++k) v[k] = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
+  const uint32_t prev = i0 ? j.raw[i0 - 1] : 0;
+  const uint32_t next = j.raw[i0 + 16];  // the buffer is padded with zeros
+  uint32_t mask = 0;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const uint32_t i = i0 + k;
+    const uint32_t c = v[k], p = k ? v[k - 1] : prev,
+                   n = k < 15 ? v[k + 1] : next;
+    const bool in = i >= j.scan_begin && i < j.scan_end;
+    const bool drop =
+        (i > j.scan_begin && p == 0xFF && (c == 0 || (c & 0xF8) == 0xD0)) ||
+        (c == 0xFF && i + 1 < j.scan_end && (n & 0xF8) == 0xD0);
+    if (in && !drop) mask |= 1u << k;
+  }
+  return mask;
+}
+
+__global__ void __launch_bounds__(256) destuff_count_kernel(const Job j) {
+  __shared__ int s_sum[8];
+  const uint32_t g = blockIdx.x * 256 + threadIdx.x;
+  uint8_t v[16];
+  int n = 16 * g < j.scan_end ? __popc(keep16(j, 16 * g, v)) : 0;
+#pragma unroll
+  for (int o = 16; o; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+  if ((threadIdx.x & 31) == 0) s_sum[threadIdx.x >> 5] = n;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int k = 0; k < 8; ++k) t += s_sum[k];
+    j.ds_count[blockIdx.x] = t;
+  }
+}
+
+// block counts -> exclusive offsets; the total is the scan's length
+__global__ void __launch_bounds__(1024) destuff_offsets_kernel(const Job j) {
+  __shared__ int s_val[1024];
+  const int t = threadIdx.x;
+  const int per = (j.ds_blocks + 1023) / 1024;
+  const int lo = min(j.ds_blocks, t * per), hi = min(j.ds_blocks, lo + per);
+  int sum = 0;
+  for (int k = lo; k < hi; ++k) sum += j.ds_count[k];
+  s_val[t] = sum;
+  __syncthreads();
+  for (int off = 1; off < 1024; off <<= 1) {
+    const int add = t >= off ? s_val[t - off] : 0;
+    __syncthreads();
+    s_val[t] += add;
+    __syncthreads();
+  }
+  int run = s_val[t] - sum;
+  for (int k = lo; k < hi; ++k) {
+    const int c = j.ds_count[k];
+    j.ds_count[k] = run;
+    run += c;
+  }
+  if (t == 1023) *j.total_bits = 8u * (uint32_t)s_val[t];
+}
+
+__global__ void __launch_bounds__(256) destuff_scatter_kernel(const Job j) {
+  __shared__ int s_sum[8];
+  const uint32_t g = blockIdx.x * 256 + threadIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint8_t v[16];
+  const uint32_t mask = 16 * g < j.scan_end ? keep16(j, 16 * g, v) : 0;
+  const int n = __popc(mask);
+  int incl = n;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int up = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += up;
+  }
+  if (lane == 31) s_sum[warp] = incl;
+  __syncthreads();
+  int off = j.ds_count[blockIdx.x] + incl - n;
+  for (int k = 0; k < warp; ++k) off += s_sum[k];
+  uint8_t* out = reinterpret_cast<uint8_t*>(j.words);
+#pragma unroll
+  for (int k = 0; k < 16; ++k)
+    if (mask >> k & 1) {
+      out[off ^ 3] = v[k];  // big-endian inside each word
+      ++off;
+    }
 }
 
 __global__ void __launch_bounds__(kThreads) huff_guess_kernel(const Job j) {
@@ -85,10 +184,11 @@ __global__ void __launch_bounds__(kThreads) huff_guess_kernel(const Job j) {
   const int i = blockIdx.x * kThreads + threadIdx.x;
   if (i >= j.n_sub) return;
   const SubRec r = j.subs[i];
-  State s = first_state(r, j.raw);
+  State s = first_state(r);
   j.in_state[i] = ~0ull;  // not a state: the first sweep decodes everything
-  j.done[i] = decode_subsequence<false>(j.raw, r.end, j.scan_end, j.f, tabs,
-                                        c_natural, &s, nullptr, 0, 0);
+  j.done[i] = decode_subsequence<false>(j.words, min(r.end, *j.total_bits),
+                                        j.f, tabs, &s, nullptr, nullptr, 0,
+                                        0);
   j.exit_state[i] = pack(s);
 }
 
@@ -101,9 +201,11 @@ __global__ void __launch_bounds__(kThreads)
   const bool active = i < j.n_sub;
   SubRec r = {0, 0, 0, 1};
   uint64_t cur = 0, last_in = ~0ull;
+  uint32_t sub_end = 0;
   int done = 0;
   if (active) {
     r = j.subs[i];
+    sub_end = min(r.end, *j.total_bits);
     cur = j.exit_state[i];
     last_in = j.in_state[i];
     done = j.done[i];
@@ -115,7 +217,7 @@ __global__ void __launch_bounds__(kThreads)
     uint64_t in = last_in;
     if (active) {
       if (r.is_first)
-        in = pack(first_state(r, j.raw));
+        in = pack(first_state(r));
       else if (t > 0)
         in = sh_exit[t - 1];
       else
@@ -126,8 +228,8 @@ __global__ void __launch_bounds__(kThreads)
     if (active && in != last_in) {
       State s = unpack(in);
       if (s.b >= j.f.bpm) s.b = 0;
-      done = decode_subsequence<false>(j.raw, r.end, j.scan_end, j.f, tabs,
-                                       c_natural, &s, nullptr, 0, 0);
+      done = decode_subsequence<false>(j.words, sub_end, j.f, tabs, &s,
+                                       nullptr, nullptr, 0, 0);
       last_in = in;
       const uint64_t o = pack(s);
       if (o != cur) {
@@ -173,25 +275,63 @@ __device__ __forceinline__ void block_scan_1024(int* has, int* val, int* s_has,
 }
 
 // base[i] = first block of subsequence i: its restart interval's first block
-// plus the blocks completed by the interval's earlier subsequences
-__global__ void __launch_bounds__(1024) huff_base_kernel(const Job j) {
+// plus the blocks completed by the interval's earlier subsequences. Per CTA
+// of kThreads subsequences (the write pass' CTAs): a scan inside the CTA,
+// then one CTA scans the CTA totals.
+__global__ void __launch_bounds__(kThreads) huff_base_kernel(const Job j) {
+  __shared__ int s_has[kThreads], s_val[kThreads];
+  const int t = threadIdx.x, i = blockIdx.x * kThreads + t;
+  int h = 0, v = 0, first = 0, abs0 = 0;
+  if (i < j.n_sub) {
+    const SubRec r = j.subs[i];
+    first = (int)r.is_first;
+    abs0 = (int)r.first_mcu * j.f.bpm;
+    h = first;
+    v = (first ? abs0 : 0) + j.done[i];
+  }
+  s_has[t] = h;
+  s_val[t] = v;
+  __syncthreads();
+  for (int off = 1; off < kThreads; off <<= 1) {
+    if (t >= off && !h) {
+      v += s_val[t - off];
+      h = s_has[t - off];
+    }
+    __syncthreads();
+    s_has[t] = h;
+    s_val[t] = v;
+    __syncthreads();
+  }
+  if (i < j.n_sub) {
+    const int eh = t ? s_has[t - 1] : 0, ev = t ? s_val[t - 1] : 0;
+    j.base[i] = first ? (abs0 | (int)0x80000000)
+                      : (eh ? (ev | (int)0x80000000) : ev);
+  }
+  if (t == kThreads - 1) {
+    j.base_has[blockIdx.x] = h;
+    j.base_cta[blockIdx.x] = v;
+  }
+}
+
+__global__ void __launch_bounds__(1024) huff_base_prefix_kernel(const Job j,
+                                                                int ctas) {
   __shared__ int s_has[1024], s_val[1024];
   const int t = threadIdx.x;
-  const int chunk = (j.n_sub + 1023) / 1024;
-  const int lo = min(j.n_sub, t * chunk), hi = min(j.n_sub, lo + chunk);
+  const int per = (ctas + 1023) / 1024;
+  const int lo = min(ctas, t * per), hi = min(ctas, lo + per);
   int has = 0, val = 0;
-  for (int i = lo; i < hi; ++i) {
-    const SubRec r = j.subs[i];
-    if (r.is_first) has = 1, val = (int)r.first_mcu * j.f.bpm;
-    val += j.done[i];
+  for (int k = lo; k < hi; ++k) {
+    if (j.base_has[k])
+      has = 1, val = j.base_cta[k];
+    else
+      val += j.base_cta[k];
   }
   block_scan_1024(&has, &val, s_has, s_val);
   int run = val;
-  for (int i = lo; i < hi; ++i) {
-    const SubRec r = j.subs[i];
-    if (r.is_first) run = (int)r.first_mcu * j.f.bpm;
-    j.base[i] = run;
-    run += j.done[i];
+  for (int k = lo; k < hi; ++k) {
+    const int h = j.base_has[k], v = j.base_cta[k];
+    j.base_cta[k] = run;
+    run = h ? v : run + v;
   }
 }
 
@@ -201,14 +341,17 @@ __global__ void __launch_bounds__(kThreads) huff_write_kernel(const Job j) {
   const int i = blockIdx.x * kThreads + threadIdx.x;
   if (i >= j.n_sub) return;
   const SubRec r = j.subs[i];
-  State s = r.is_first ? first_state(r, j.raw) : unpack(j.exit_state[i - 1]);
+  State s = r.is_first ? first_state(r) : unpack(j.exit_state[i - 1]);
   if (s.b >= j.f.bpm) s.b = 0;
   const long long per =
       j.f.restart ? j.f.restart : (long long)j.f.mcus_x * j.f.mcus_y;
   long long limit = ((long long)r.first_mcu + per) * j.f.bpm;
   if (limit > j.f.total_blocks) limit = j.f.total_blocks;
-  decode_subsequence<true>(j.raw, r.end, j.scan_end, j.f, tabs, c_natural, &s,
-                           j.coef, j.base[i], (int)limit);
+  const int rel = j.base[i];
+  const int block =
+      rel < 0 ? (rel & 0x7fffffff) : j.base_cta[blockIdx.x] + rel;
+  decode_subsequence<true>(j.words, min(r.end, *j.total_bits), j.f, tabs, &s,
+                           j.coef, j.dc, block, (int)limit);
 }
 
 // DC differences -> DC values: per component a prefix sum over its blocks in
@@ -227,7 +370,7 @@ __global__ void __launch_bounds__(256) dc_partial_kernel(const Job j) {
   for (int m = lo; m < hi; ++m) {
     if (j.f.restart && m % j.f.restart == 0) has = 1, val = 0;
     for (int b = 0; b < nb; ++b)
-      val += j.coef[((size_t)m * j.f.bpm + first + b) * 64];
+      val += j.dc[(size_t)m * j.f.bpm + first + b];
   }
   j.dc_has[c * j.dc_chunks + q] = has;
   j.dc_val[c * j.dc_chunks + q] = val;
@@ -266,7 +409,7 @@ __global__ void __launch_bounds__(256) dc_apply_kernel(const Job j) {
   for (int m = lo; m < hi; ++m) {
     if (j.f.restart && m % j.f.restart == 0) run = 0;
     for (int b = 0; b < nb; ++b) {
-      int16_t* dc = j.coef + ((size_t)m * j.f.bpm + first + b) * 64;
+      int16_t* dc = j.dc + (size_t)m * j.f.bpm + first + b;
       run += *dc;
       *dc = (int16_t)run;
     }
@@ -292,7 +435,7 @@ __global__ void __launch_bounds__(128) idct_kernel(const Job j) {
   for (int k = 0; k < 8; ++k)
     *reinterpret_cast<int4*>(in + 8 * k) = src[k];
   uint8_t px[64];
-  idct_islow(in, q[c], px);
+  idct_islow(in, j.dc[blk], q[c], px);
   uint8_t* dst = j.plane[c] + (size_t)by * 8 * j.f.plane_w[c] + (size_t)bx * 8;
 #pragma unroll
   for (int r = 0; r < 8; ++r) {
@@ -305,19 +448,93 @@ __global__ void __launch_bounds__(128) idct_kernel(const Job j) {
   }
 }
 
+// Four chroma samples at full resolution for pixels 4g .. 4g + 3 of row Y,
+// away from the plane's left and right edges (jpeg_sm.h has the general form)
+__device__ __forceinline__ void chroma4(const Frame& f, const uint8_t* p,
+                                        int pitch, int ch, int g, int Y,
+                                        int c[4]) {
+  const int i = 2 * g;
+  if (f.chroma == 2) {
+    const int r = Y >> 1;
+    int rn = (Y & 1) ? r + 1 : r - 1;
+    rn = rn < 0 ? 0 : rn > ch - 1 ? ch - 1 : rn;
+    const uint8_t* a = p + (size_t)r * pitch + i;
+    const uint8_t* b = p + (size_t)rn * pitch + i;
+    const int s0 = 3 * a[-1] + b[-1], s1 = 3 * a[0] + b[0],
+              s2 = 3 * a[1] + b[1], s3 = 3 * a[2] + b[2];
+    c[0] = (3 * s1 + s0 + 8) >> 4;
+    c[1] = (3 * s1 + s2 + 7) >> 4;
+    c[2] = (3 * s2 + s1 + 8) >> 4;
+    c[3] = (3 * s2 + s3 + 7) >> 4;
+  } else {
+    const uint8_t* a = p + (size_t)Y * pitch + i;
+    const int s0 = a[-1], s1 = a[0], s2 = a[1], s3 = a[2];
+    c[0] = (3 * s1 + s0 + 1) >> 2;
+    c[1] = (3 * s1 + s2 + 2) >> 2;
+    c[2] = (3 * s2 + s1 + 1) >> 2;
+    c[3] = (3 * s2 + s3 + 2) >> 2;
+  }
+}
+
+// four pixels per thread; `aligned`: rows of `out` start on 4-byte boundaries
 __global__ void __launch_bounds__(256)
-    color_kernel(const Job j, uint8_t* __restrict__ out, size_t pitch) {
-  const int X = blockIdx.x * blockDim.x + threadIdx.x;
+    color_kernel(const Job j, uint8_t* __restrict__ out, size_t pitch,
+                 int aligned) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
   const int Y = blockIdx.y * blockDim.y + threadIdx.y;
-  if (X >= j.f.width || Y >= j.f.height) return;
+  const int X0 = 4 * g;
+  if (X0 >= j.f.width || Y >= j.f.height) return;
   const uint8_t* pl[3] = {j.plane[0], j.plane[1], j.plane[2]};
   const int pp[3] = {j.f.plane_w[0], j.f.plane_w[1], j.f.plane_w[2]};
-  uint8_t bgr[3];
-  pixel_bgr(j.f, pl, pp, X, Y, bgr);
-  uint8_t* d = out + (size_t)Y * pitch + 3 * (size_t)X;
-  d[0] = bgr[0];
-  d[1] = bgr[1];
-  d[2] = bgr[2];
+  uint8_t* d = out + (size_t)Y * pitch + 3 * (size_t)X0;
+  uint8_t px[12];
+  const bool whole = X0 + 3 < j.f.width;
+  const bool inner = j.f.ncomp == 3 && j.f.chroma && j.f.fancy && g > 0 &&
+                     2 * g + 2 <= j.f.comp_w[1] - 1;
+  if (whole && (inner || j.f.ncomp == 1 || j.f.chroma == 0)) {
+    const uint32_t y4 =
+        *reinterpret_cast<const uint32_t*>(pl[0] + (size_t)Y * pp[0] + X0);
+    int cb[4], cr[4];
+    if (j.f.ncomp == 3) {
+      if (j.f.chroma) {
+        chroma4(j.f, pl[1], pp[1], j.f.comp_h[1], g, Y, cb);
+        chroma4(j.f, pl[2], pp[2], j.f.comp_h[2], g, Y, cr);
+      } else {
+        const uint32_t b4 =
+            *reinterpret_cast<const uint32_t*>(pl[1] + (size_t)Y * pp[1] + X0);
+        const uint32_t r4 =
+            *reinterpret_cast<const uint32_t*>(pl[2] + (size_t)Y * pp[2] + X0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          cb[k] = (b4 >> (8 * k)) & 255, cr[k] = (r4 >> (8 * k)) & 255;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int y = (y4 >> (8 * k)) & 255;
+      if (j.f.ncomp == 1)
+        px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = (uint8_t)y;
+      else
+        ycc_to_bgr(y, cb[k], cr[k], px + 3 * k);
+    }
+    if (aligned) {
+      uint32_t* o = reinterpret_cast<uint32_t*>(d);
+#pragma unroll
+      for (int k = 0; k < 3; ++k)
+        o[k] = px[4 * k] | (px[4 * k + 1] << 8) | (px[4 * k + 2] << 16) |
+               ((uint32_t)px[4 * k + 3] << 24);
+    } else {
+#pragma unroll
+      for (int k = 0; k < 12; ++k) d[k] = px[k];
+    }
+    return;
+  }
+  for (int k = 0; k < 4 && X0 + k < j.f.width; ++k) {
+    pixel_bgr(j.f, pl, pp, X0 + k, Y, px);
+    d[3 * k] = px[0];
+    d[3 * k + 1] = px[1];
+    d[3 * k + 2] = px[2];
+  }
 }
 
 }  // namespace jpg
@@ -354,7 +571,6 @@ bool sm_jpeg_decode(const uint8_t* data, size_t len, uint8_t* d_out,
   Job j;
   j.f = f;
   j.n_sub = ns;
-  j.scan_end = (uint32_t)P.scan_end;
   size_t plane_bytes[3] = {0, 0, 0}, planes_total = 0;
   for (int c = 0; c < f.ncomp; ++c) {
     plane_bytes[c] = ((size_t)f.plane_w[c] * f.plane_h[c] + 255) & ~(size_t)255;
@@ -364,24 +580,30 @@ bool sm_jpeg_decode(const uint8_t* data, size_t len, uint8_t* d_out,
   // the scan is uploaded with the bytes before it left out
   const size_t skip = P.scan_begin & ~(size_t)255;
   const size_t raw_bytes = P.scan_end - skip;
-  DevBuf raw, subs, tabs, state, coef, planes;
-  raw.reserve(raw_bytes + 16);
-  subs.reserve((size_t)ns * sizeof(SubRec));
-  tabs.reserve(sizeof(P.huff) + sizeof(P.quant));
+  j.scan_begin = (uint32_t)(P.scan_begin - skip);
+  j.scan_end = (uint32_t)raw_bytes;
+  j.ds_blocks = div_up((int)div_up(raw_bytes, (size_t)16), 256);
+  const size_t words_bytes = ((raw_bytes + 3) & ~(size_t)3) + 16;
+  const int grid = div_up(ns, kThreads);
+  const size_t subs_bytes = (size_t)ns * sizeof(SubRec);
+  const size_t meta_bytes = subs_bytes + sizeof(P.huff) + sizeof(P.quant);
+  const size_t dc_bytes =
+      (((size_t)f.total_blocks * sizeof(int16_t)) + 255) & ~(size_t)255;
+  DevBuf raw, words, meta, state, coef, planes;
+  raw.reserve(raw_bytes + 64);
+  words.reserve(words_bytes);
+  meta.reserve(meta_bytes);
   j.dc_chunks = div_up(f.mcus_x * f.mcus_y, kDcChunk);
   state.reserve((size_t)ns * (2 * sizeof(uint64_t) + 2 * sizeof(int)) +
-                (size_t)j.dc_chunks * 6 * sizeof(int));
-  coef.reserve(coef_bytes);
+                (size_t)j.dc_chunks * 6 * sizeof(int) +
+                ((size_t)j.ds_blocks + 1 + 2 * (size_t)grid) * sizeof(int));
+  coef.reserve(dc_bytes + coef_bytes);
   planes.reserve(planes_total);
-  for (SubRec& r : P.subs) {
-    r.start -= (uint32_t)skip;
-    r.end -= (uint32_t)skip;
-  }
-  j.scan_end -= (uint32_t)skip;
   j.raw = raw.as<uint8_t>();
-  j.subs = subs.as<SubRec>();
-  j.tabs = tabs.as<HuffTab>();
-  j.quant = reinterpret_cast<const uint16_t*>(tabs.as<uint8_t>() +
+  j.words = words.as<uint32_t>();
+  j.subs = meta.as<SubRec>();
+  j.tabs = reinterpret_cast<const HuffTab*>(meta.as<uint8_t>() + subs_bytes);
+  j.quant = reinterpret_cast<const uint16_t*>(meta.as<uint8_t>() + subs_bytes +
                                               sizeof(P.huff));
   j.exit_state = state.as<uint64_t>();
   j.in_state = j.exit_state + ns;
@@ -389,53 +611,66 @@ bool sm_jpeg_decode(const uint8_t* data, size_t len, uint8_t* d_out,
   j.base = j.done + ns;
   j.dc_has = j.base + ns;
   j.dc_val = j.dc_has + 3 * (size_t)j.dc_chunks;
-  j.coef = coef.as<int16_t>();
+  j.ds_count = j.dc_val + 3 * (size_t)j.dc_chunks;
+  j.total_bits = reinterpret_cast<uint32_t*>(j.ds_count + j.ds_blocks);
+  j.base_has = reinterpret_cast<int*>(j.total_bits + 1);
+  j.base_cta = j.base_has + grid;
+  j.dc = coef.as<int16_t>();
+  j.coef = reinterpret_cast<int16_t*>(coef.as<uint8_t>() + dc_bytes);
   uint8_t* pp = planes.as<uint8_t>();
   for (int c = 0; c < 3; ++c) {
     j.plane[c] = c < f.ncomp ? pp : nullptr;
     pp += plane_bytes[c];
   }
-  // The stream's bytes and the subsequence table go through pinned staging
-  // memory of our own: a cudaMemcpyAsync from pageable memory is staged by
-  // the driver under a lock that the other decoding threads also wait for.
+  // The stream's bytes and the tables (subsequences, Huffman, quantisation)
+  // go through pinned staging memory of our own, two copies: a
+  // cudaMemcpyAsync from pageable memory is staged by the driver under a
+  // lock that the other decoding threads also wait for. Sizes are rounded up
+  // to a power of two, so that the cached pinned blocks of one panorama's
+  // sources serve the next one's.
   Mailbox box;
-  const size_t subs_bytes = (size_t)ns * sizeof(SubRec);
-  // (sizes rounded up to a power of two, so that the cached pinned blocks of
-  // one panorama's sources serve the next one's)
   size_t pinned = 65536;
-  while (pinned < raw_bytes + subs_bytes + sizeof(P.huff) + sizeof(P.quant) + 256)
-    pinned *= 2;
+  while (pinned < raw_bytes + meta_bytes + 256) pinned *= 2;
   box.reset(pinned);
-  int* flag = static_cast<int*>(box.take(2 * sizeof(int)));
+  int* flag = static_cast<int*>(box.take(4 * sizeof(int)));
   void* d_flag = nullptr;
   XP_CUDA(cudaHostGetDevicePointer(&d_flag, flag, 0));
   void* h_raw = box.take(raw_bytes);
   memcpy(h_raw, data + skip, raw_bytes);
   XP_CUDA(cudaMemcpyAsync(raw.p, h_raw, raw_bytes, cudaMemcpyHostToDevice, s));
-  void* h_subs = box.take(subs_bytes);
-  memcpy(h_subs, P.subs.data(), subs_bytes);
-  XP_CUDA(cudaMemcpyAsync(subs.p, h_subs, subs_bytes, cudaMemcpyHostToDevice,
+  uint8_t* h_meta = static_cast<uint8_t*>(box.take(meta_bytes));
+  memcpy(h_meta, P.subs.data(), subs_bytes);
+  memcpy(h_meta + subs_bytes, P.huff, sizeof(P.huff));
+  memcpy(h_meta + subs_bytes + sizeof(P.huff), P.quant, sizeof(P.quant));
+  XP_CUDA(cudaMemcpyAsync(meta.p, h_meta, meta_bytes, cudaMemcpyHostToDevice,
                           s));
-  box.to_device(tabs.p, P.huff, sizeof(P.huff), s);
-  box.to_device(tabs.as<uint8_t>() + sizeof(P.huff), P.quant, sizeof(P.quant),
-                s);
-  const int grid = div_up(ns, kThreads);
+  XP_CUDA(cudaMemsetAsync(raw.as<uint8_t>() + raw_bytes, 0, 64, s));
+  XP_CUDA(cudaMemsetAsync(words.p, 0, words_bytes, s));
+  destuff_count_kernel<<<j.ds_blocks, 256, 0, s>>>(j);
+  XP_LAUNCHED();
+  destuff_offsets_kernel<<<1, 1024, 0, s>>>(j);
+  XP_LAUNCHED();
+  destuff_scatter_kernel<<<j.ds_blocks, 256, 0, s>>>(j);
+  XP_LAUNCHED();
   huff_guess_kernel<<<grid, kThreads, 0, s>>>(j);
   XP_LAUNCHED();
-  // Two synchronisation launches and everything after them are queued
-  // without waiting: the second launch almost always changes nothing (the
-  // first one did the work), which is all that has to be known -- afterwards.
+  // Three synchronisation launches and everything after them are queued
+  // without waiting: the first one does the work, the second one repairs what
+  // started from a neighbouring block's guessed state, the third one almost
+  // always changes nothing, which is all that has to be known -- afterwards.
   // If it did change a state, the round is repeated from there.
   int launches = 0;
   for (int round = 0;; ++round) {
-    flag[0] = flag[1] = 0;
-    for (int k = 0; k < 2; ++k, ++launches) {
+    flag[0] = flag[1] = flag[2] = 0;
+    for (int k = 0; k < 3; ++k, ++launches) {
       huff_sync_kernel<<<grid, kThreads, 0, s>>>(j,
                                                  static_cast<int*>(d_flag) + k);
       XP_LAUNCHED();
     }
-    XP_CUDA(cudaMemsetAsync(coef.p, 0, coef_bytes, s));
-    huff_base_kernel<<<1, 1024, 0, s>>>(j);
+    XP_CUDA(cudaMemsetAsync(coef.p, 0, dc_bytes + coef_bytes, s));
+    huff_base_kernel<<<grid, kThreads, 0, s>>>(j);
+    XP_LAUNCHED();
+    huff_base_prefix_kernel<<<1, 1024, 0, s>>>(j, grid);
     XP_LAUNCHED();
     huff_write_kernel<<<grid, kThreads, 0, s>>>(j);
     XP_LAUNCHED();
@@ -448,11 +683,13 @@ bool sm_jpeg_decode(const uint8_t* data, size_t len, uint8_t* d_out,
     XP_LAUNCHED();
     idct_kernel<<<div_up(f.total_blocks, 128), 128, 0, s>>>(j);
     XP_LAUNCHED();
-    dim3 b(32, 8), g(div_up(f.width, 32), div_up(f.height, 8));
-    color_kernel<<<g, b, 0, s>>>(j, d_out, out_pitch);
+    dim3 b(32, 8), g(div_up(div_up(f.width, 4), 32), div_up(f.height, 8));
+    const int aligned =
+        out_pitch % 4 == 0 && reinterpret_cast<uintptr_t>(d_out) % 4 == 0;
+    color_kernel<<<g, b, 0, s>>>(j, d_out, out_pitch, aligned);
     XP_LAUNCHED();
     XP_CUDA(cudaStreamSynchronize(s));
-    if (!flag[1]) break;
+    if (!flag[2]) break;
     XP_REQUIRE(round <= grid + 2, "jpeg: synchronisation did not converge");
   }
   if (stats) stats[0] = ns, stats[1] = launches;

@@ -1,7 +1,7 @@
 // Baseline JPEG decoding arithmetic shared by the CUDA kernels (jpeg_sm.cu)
 // and the host emulation the CPU tests run (tests/emu/jpeg_emu.cpp): the
-// Huffman-coded scan is cut into fixed-size subsequences that are decoded
-// independently and synchronise on their neighbours' exit states; then the
+// Huffman-coded scan, destuffed, is cut into fixed-size subsequences that are
+// decoded independently and synchronise on their neighbours' exit states; then the
 // inverse DCT, chroma upsampling and colour conversion of libjpeg-turbo, the
 // decoder behind cv::imread (xpano/algorithm/image.cc:83), restated so that
 // the pixels are cv::imread's bit for bit: jidctint.c (jpeg_idct_islow),
@@ -38,6 +38,7 @@ struct Frame {
   int blk_comp[10], blk_x[10], blk_y[10];  // blocks of an MCU in scan order
   int blk_first[3];          // first block of a component within the MCU
   int dc_tab[3], ac_tab[3];  // Huffman tables (0..1 DC, 2..3 AC)
+  int blk_dc[10], blk_ac[10];  // the same per block of the MCU
   int qt[3];
   int restart;               // MCUs per restart interval, 0 = none
   int comp_w[3], comp_h[3];  // samples that exist (downsampled_width/height)
@@ -48,7 +49,7 @@ struct Frame {
 };
 
 struct SubRec {  // one subsequence of the scan
-  uint32_t start, end;  // raw byte range (stuffing included)
+  uint32_t start, end;  // bit range in the destuffed scan
   uint32_t first_mcu;   // of its restart interval
   uint32_t is_first;    // starts the interval (state known)
 };
@@ -60,63 +61,50 @@ struct SubRec {  // one subsequence of the scan
    35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51,      \
    58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63}
 
+// The scan is decoded from a DESTUFFED copy: the zero after every FF and the
+// restart markers are taken out first (what remains of a restart interval
+// still starts on a byte), and the bytes are packed big-endian into 32-bit
+// words, so that any 32 bits of the stream are two loads and a funnel shift.
+// A byte of [begin, end) is dropped when it is the 00 or Dn after an FF, or
+// the FF before a Dn.
+XP_HD bool destuff_keeps(const uint8_t* d, size_t i, size_t begin,
+                         size_t end) {
+  const uint8_t v = d[i];
+  if (i > begin && d[i - 1] == 0xFF && (v == 0x00 || (v >= 0xD0 && v <= 0xD7)))
+    return false;
+  if (v == 0xFF && i + 1 < end && d[i + 1] >= 0xD0 && d[i + 1] <= 0xD7)
+    return false;
+  return true;
+}
+
 // Decoder state between two symbols, packed so that one 64-bit load or store
-// moves it whole: position (byte of the next unread bit -- never a stuffed
-// zero -- and the bit inside it), block of the MCU, zigzag index.
+// moves it whole: bit position in the destuffed scan, block of the MCU,
+// zigzag index.
 struct State {
-  uint32_t cb;
-  int k, b, z;
+  uint32_t p;
+  int b, z;
 };
 XP_HD uint64_t pack(const State& s) {
-  return ((uint64_t)s.cb << 16) | ((uint64_t)s.k << 12) |
-         ((uint64_t)s.b << 8) | (uint64_t)s.z;
+  return ((uint64_t)s.p << 16) | ((uint64_t)s.b << 8) | (uint64_t)s.z;
 }
 XP_HD State unpack(uint64_t v) {
   State s;
-  s.cb = (uint32_t)(v >> 16);
-  s.k = (int)(v >> 12) & 7;
+  s.p = (uint32_t)(v >> 16);
   s.b = (int)(v >> 8) & 15;
   s.z = (int)v & 63;
   return s;
 }
 
-// Eight data bytes of the scan from a canonical position on; stuffed zeros
-// (FF 00) are skipped while refilling, bytes past `end` read as zero.
-struct BitWindow {
-  const uint8_t* raw;
-  uint32_t end;  // of the restart interval
-  uint64_t w;    // data bytes cb .. (oldest in the top byte)
-  uint32_t cb;   // raw index of the oldest byte
-  uint32_t nx;   // raw index of the next byte to load
-  uint32_t sq;   // bit 7 - i: byte i of the window was followed by a stuffed zero
-  int k;         // bits of the oldest byte already consumed
-
-  XP_HD void push() {
-    uint32_t v = 0, ff = 0;
-    if (nx < end) {
-      v = raw[nx];
-      ff = v == 0xFF;
-    }
-    nx += 1 + ff;
-    w = (w << 8) | v;
-    sq = ((sq << 1) | ff) & 0xFF;
-  }
-  XP_HD void open(const uint8_t* r, uint32_t e, uint32_t cb0, int k0) {
-    raw = r, end = e, cb = cb0, nx = cb0, k = k0, w = 0, sq = 0;
-    for (int i = 0; i < 8; ++i) push();
-  }
-  XP_HD uint32_t peek(int n) const {  // 1 <= n <= 32
-    return (uint32_t)((w << k) >> (64 - n));
-  }
-  XP_HD void skip(int n) {
-    k += n;
-    while (k >= 8) {
-      k -= 8;
-      cb += 1 + ((sq >> 7) & 1);
-      push();
-    }
-  }
-};
+// the 32 bits of the destuffed scan from bit p on (words are zero past its end)
+XP_HD uint32_t peek32(const uint32_t* w, uint32_t p) {
+  const uint32_t i = p >> 5, s = p & 31;
+  const uint32_t a = w[i], b = w[i + 1];
+#if defined(__CUDA_ARCH__)
+  return __funnelshift_l(b, a, s);
+#else
+  return s ? (a << s) | (b >> (32 - s)) : a;
+#endif
+}
 
 XP_HD void huff_symbol(const HuffTab& t, uint32_t v16, int* len, int* sym) {
   const uint32_t e = t.look[v16 >> (16 - kLook)];
@@ -140,24 +128,21 @@ XP_HD void huff_symbol(const HuffTab& t, uint32_t v16, int* len, int* sym) {
   *sym = t.val[(code + t.valoff[l]) & 255];
 }
 
-// Decode the symbols that START in [s.cb, sub_end) and return how many blocks
-// they completed. With `coef` (the write pass) the coefficients go to
-// coef[64 * block + natural index], DC as the difference to the previous
-// block of the component; `block` is the index of the block in progress and
-// blocks from block_limit on are not stored.
+// Decode the symbols that START in [s.p, sub_end) and return how many blocks
+// they completed. With kWrite (the write pass) the AC coefficients go to
+// coef[64 * block + zigzag index] and the DC difference to the previous block
+// of the component to dc[block]; `block` is the index of the block in
+// progress and blocks from block_limit on are not stored.
 template <bool kWrite>
-XP_HD int decode_subsequence(const uint8_t* raw, uint32_t sub_end,
-                             uint32_t seg_end, const Frame& f,
-                             const HuffTab* tabs, const uint8_t* natural,
-                             State* s, int16_t* coef, int block,
+XP_HD int decode_subsequence(const uint32_t* words, uint32_t sub_end,
+                             const Frame& f, const HuffTab* tabs, State* s,
+                             int16_t* coef, int16_t* dc, int block,
                              int block_limit) {
-  BitWindow bw;
-  bw.open(raw, seg_end, s->cb, s->k);
+  uint32_t p = s->p;
   int b = s->b, z = s->z, done = 0;
-  while (bw.cb < sub_end) {
-    const int c = f.blk_comp[b];
-    const HuffTab& t = tabs[z == 0 ? f.dc_tab[c] : f.ac_tab[c]];
-    const uint32_t v = bw.peek(32);
+  while (p < sub_end) {
+    const HuffTab& t = tabs[z == 0 ? f.blk_dc[b] : f.blk_ac[b]];
+    const uint32_t v = peek32(words, p);
     int len, sym;
     huff_symbol(t, v >> 16, &len, &sym);
     int run = 0, size = sym & 15;
@@ -176,14 +161,18 @@ XP_HD int decode_subsequence(const uint8_t* raw, uint32_t sub_end,
       value = (int)((v << len) >> (32 - size));
       if (value < (1 << (size - 1))) value -= (1 << size) - 1;
     }
-    bw.skip(len + size);
+    p += (uint32_t)(len + size);
     if (eob) {
       z = 64;
     } else {
       z += run;
       if (size || z == 0) {
-        if (kWrite && z < 64 && block < block_limit)
-          coef[(size_t)block * 64 + natural[z]] = (int16_t)value;
+        if (kWrite && z < 64 && block < block_limit) {
+          if (z == 0)
+            dc[block] = (int16_t)value;
+          else
+            coef[(size_t)block * 64 + z] = (int16_t)value;
+        }
         ++z;
       }
     }
@@ -194,8 +183,7 @@ XP_HD int decode_subsequence(const uint8_t* raw, uint32_t sub_end,
       ++done;
     }
   }
-  s->cb = bw.cb;
-  s->k = bw.k;
+  s->p = p;
   s->b = b;
   s->z = z;
   return done;
@@ -203,7 +191,9 @@ XP_HD int decode_subsequence(const uint8_t* raw, uint32_t sub_end,
 
 // ---------------------------------------------------------------------------
 // jpeg_idct_islow (jidctint.c), 8x8, 8-bit samples: `in` are the quantised
-// coefficients in natural order, q the quantisation table, out[8][8] samples.
+// coefficients in ZIGZAG order (as the scan stores them; in[0] is ignored, the
+// DC value is passed separately), q the quantisation table in natural order,
+// out[8][8] samples.
 // ---------------------------------------------------------------------------
 XP_HD int32_t mul32(int32_t a, int32_t b) {
   return (int32_t)((uint32_t)a * (uint32_t)b);
@@ -258,15 +248,22 @@ XP_HD void idct_1d(const int32_t i[8], int32_t even_shift, int32_t o[8],
   o[4] = descale(tmp13 - tmp0, shift);
 }
 
-XP_HD void idct_islow(const int16_t in[64], const uint16_t q[64],
+XP_HD void idct_islow(const int16_t in[64], int dc, const uint16_t q[64],
                       uint8_t out[64]) {
+  // natural (row-major) index -> zigzag position
+  constexpr uint8_t zz[64] = {
+      0,  1,  5,  6,  14, 15, 27, 28, 2,  4,  7,  13, 16, 26, 29, 42,
+      3,  8,  12, 17, 25, 30, 41, 43, 9,  11, 18, 24, 31, 40, 44, 53,
+      10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38, 46, 51, 55, 60,
+      21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48, 49, 57, 58, 62, 63};
   int32_t ws[64];
   XP_UNROLL
   for (int c = 0; c < 8; ++c) {  // columns, CONST_BITS - PASS1_BITS
     int32_t i[8], o[8];
     XP_UNROLL
     for (int r = 0; r < 8; ++r)
-      i[r] = (int32_t)in[8 * r + c] * (int32_t)q[8 * r + c];
+      i[r] = (int32_t)(8 * r + c == 0 ? dc : in[zz[8 * r + c]]) *
+             (int32_t)q[8 * r + c];
     idct_1d(i, 13, o, 11);
     XP_UNROLL
     for (int r = 0; r < 8; ++r) ws[8 * r + c] = o[r];
