@@ -1,10 +1,12 @@
-"""JPEG either side of the path through the C ABI (xp_codec_*, nvJPEG on the
-device) against cv2's libjpeg-turbo: cv::imread of the sources
+"""JPEG either side of the path through the C ABI (xp_codec_*)
+against cv2's libjpeg-turbo: cv::imread of the sources
 (xpano/algorithm/image.cc:83) and cv::imwrite of the panorama
 (xpano/pipeline/stitcher_pipeline.cc:94-116).
 
-Bars: a JPEG decoder's inverse DCT and chroma upsampling are its own, so the
-decoded pixels are held to PSNR >= 40 dB against cv2.imdecode (measured ~47 dB
+Bars: baseline streams are decoded by the library's own kernels and equal
+cv2.imdecode bit for bit (tests/test_jpeg_sm.py has the sweep); with
+XP_JPEG_SM=0 every stream goes to nvJPEG, whose inverse DCT and chroma
+upsampling are its own: PSNR >= 40 dB against cv2.imdecode (measured ~47 dB
 on the reference's photographs), sizes exact. Encoded streams are valid JPEG
 (cv2 decodes them), PSNR >= 38 dB against the source at quality 95, within a
 factor 1.5 of cv2.imencode's size at the same settings. Compressed in,
@@ -36,7 +38,7 @@ def photos():
     return g, [g[f"jpeg_{i}"] for i in range(3)]
 
 
-def test_decode_against_cv2(photos):
+def test_decode_against_cv2(photos, monkeypatch):
     import xpano_b200 as xb
     _, jpegs = photos
     codec = xb.JpegCodec()
@@ -46,7 +48,16 @@ def test_decode_against_cv2(photos):
         assert (h, w) == ref.shape[:2] and nc == 3
         got = codec.decode(j)
         assert got.shape == ref.shape and got.dtype == np.uint8
+        assert np.array_equal(got, ref)          # our kernels: exact
+    assert codec.stats() == (len(jpegs), 0)
+    monkeypatch.setenv("XP_JPEG_SM", "0")        # nvJPEG for everything
+    codec = xb.JpegCodec()
+    for j in jpegs:
+        ref = cv2.imdecode(j, cv2.IMREAD_COLOR)
+        got = codec.decode(j)
+        assert got.shape == ref.shape
         assert psnr(got, ref) >= 40.0, psnr(got, ref)
+    assert codec.stats() == (0, len(jpegs))
 
 
 def test_decode_errors(photos):
@@ -116,8 +127,8 @@ def test_compressed_in_compressed_out(photos):
     one = torch.empty_like(dev[1])        # the batch equals one-by-one decodes
     codec.decode_device(jpegs[1], one.data_ptr())
     assert torch.equal(one, dev[1])
-    assert psnr(dev[1].cpu().numpy(),
-                cv2.imdecode(jpegs[1], cv2.IMREAD_COLOR)) >= 40.0
+    assert np.array_equal(dev[1].cpu().numpy(),
+                          cv2.imdecode(jpegs[1], cv2.IMREAD_COLOR))
     c = xb.Composer(projection=wo.SPHERICAL, warp_scale=f * s, depth=8)
     c.set_images_device([t.data_ptr() for t in dev], [(w, h)] * 3, Ks, Rs)
     info = c.run()

@@ -2,17 +2,18 @@
 // (xpano/algorithm/image.cc:83) and cv::imwrite of the panorama
 // (xpano/pipeline/stitcher_pipeline.cc:94-116, parameters of
 // CompressionParameters, :40-65: quality, progressive, optimised Huffman
-// tables, chroma subsampling). Both are done by nvJPEG -- a library, linked
-// statically; the only kernel of this repository here applies the EXIF
-// orientation, as cv::imread does -- so that only compressed bytes cross
-// PCIe: a 12-MP source is 3-5 MB instead of 36 MB, a
-// 60-MP panorama ~15 MB instead of 182 MB. Decoded pixels are written straight
-// into the buffer the composer warps from (XP_MEM_DEVICE), the panorama is
-// encoded from the blender's device buffer.
+// tables, chroma subsampling), both on the device, so that only compressed
+// bytes cross PCIe: a 12-MP source is 3-5 MB instead of 36 MB, a 60-MP
+// panorama ~15 MB instead of 182 MB. Decoded pixels are written straight into
+// the buffer the composer warps from (XP_MEM_DEVICE), the panorama is encoded
+// from the blender's device buffer.
 //
-// JPEG decoders differ in their inverse DCT and chroma upsampling, so the
-// decoded pixels are not libjpeg-turbo's bit for bit (what cv::imread gives);
-// the tests hold them to PSNR >= 40 dB against cv2.imdecode.
+// Decoding: baseline / sequential Huffman streams go to the kernels of
+// jpeg_sm.cu, whose pixels are libjpeg-turbo's -- cv::imread's -- bit for bit;
+// what those do not cover (progressive, ...) goes to nvJPEG, a library,
+// linked statically, whose inverse DCT and chroma upsampling are its own
+// (tests: PSNR >= 40 dB against cv2.imdecode for those). Encoding: nvJPEG.
+// The kernel in this file applies the EXIF orientation, as cv::imread does.
 #include <nvjpeg.h>
 
 #include <algorithm>

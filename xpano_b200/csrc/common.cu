@@ -83,13 +83,19 @@ void Mailbox::reset(size_t need) {
     if (host) c.free_list.emplace_back(host, cap);
     host = nullptr;
     cap = 0;
+    // best fit: a small request must not take the megabyte-sized staging
+    // blocks of the JPEG decoder while a small block is free
+    size_t best = c.free_list.size();
     for (size_t i = 0; i < c.free_list.size(); ++i)
-      if (c.free_list[i].second >= need) {
-        host = c.free_list[i].first;
-        cap = c.free_list[i].second;
-        c.free_list.erase(c.free_list.begin() + i);
-        break;
-      }
+      if (c.free_list[i].second >= need &&
+          (best == c.free_list.size() ||
+           c.free_list[i].second < c.free_list[best].second))
+        best = i;
+    if (best < c.free_list.size()) {
+      host = c.free_list[best].first;
+      cap = c.free_list[best].second;
+      c.free_list.erase(c.free_list.begin() + best);
+    }
   }
   if (!host) {
     void* p = nullptr;
