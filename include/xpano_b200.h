@@ -500,10 +500,15 @@ xp_status xp_multiband_fetch(xp_multiband* b, void* dst_bgr, size_t dst_stride,
  * cameras write) are decoded by this library's own kernels (csrc/jpeg_sm.cu:
  * parallel Huffman decoding, libjpeg-turbo's inverse DCT, fancy upsampling
  * and colour conversion restated), and the pixels equal cv::imread's bit for
- * bit; everything else (progressive, ...) and all encoding go to nvJPEG
- * (library code, linked statically), whose decoded pixels are close to
- * libjpeg-turbo's, not identical. XP_JPEG_SM=0 in the environment sends every
- * stream to nvJPEG, =2 makes a stream the kernels do not cover an error.
+ * bit. Encoding: baseline streams with the standard Huffman tables (what
+ * CompressionParameters' defaults ask for) are written by this library's own
+ * kernels too (csrc/jpeg_enc.cu: libjpeg-turbo's colour conversion,
+ * downsampling, forward DCT, quantisation and Huffman coding restated), and
+ * the stream equals cv::imwrite's byte for byte. Everything else (progressive,
+ * optimised tables, ...) goes to nvJPEG (library code, linked statically),
+ * whose decoded pixels / streams are close to libjpeg-turbo's, not identical.
+ * XP_JPEG_SM=0 in the environment sends everything to nvJPEG, =2 makes a
+ * stream or setting the kernels do not cover an error.
  * Pixels are interleaved 8-bit BGR, oriented by EXIF, as cv::imread returns.
  *   info   : width, height, channel count of a JPEG stream (host bytes)
  *   decode : -> dst_bgr (mem = XP_MEM_DEVICE: e.g. straight into the buffer
@@ -521,8 +526,9 @@ void xp_codec_destroy(xp_codec* c);
 xp_status xp_codec_jpeg_info(xp_codec* c, const uint8_t* data, size_t len,
                              int wh[2], int* channels);
 /* out = {images decoded by the library's own kernels, images decoded by
+ * nvJPEG, images encoded by the library's own kernels, images encoded by
  * nvJPEG} since the codec was created */
-xp_status xp_codec_stats(xp_codec* c, int out[2]);
+xp_status xp_codec_stats(xp_codec* c, int out[4]);
 xp_status xp_codec_jpeg_decode(xp_codec* c, const uint8_t* data, size_t len,
                                void* dst_bgr, size_t stride, int mem);
 /* n streams into n device buffers at once, several host threads each with

@@ -137,3 +137,104 @@ extern "C" int emu_jpeg_decode(const uint8_t* d, size_t n, int sub_bytes,
       pixel_bgr(f, pl, pitch, x, y, bgr + (size_t)y * stride + 3 * (size_t)x);
   return 0;
 }
+
+// ---------------------------------------------------------------------------
+// The encoder: the same steps as xpano_b200/csrc/jpeg_enc.cu, as loops.
+// -> bytes written (0: unsupported or `cap` too small)
+// ---------------------------------------------------------------------------
+#include "../../xpano_b200/csrc/jpeg_enc_host.h"
+
+extern "C" size_t emu_jpeg_encode(const uint8_t* bgr, int w, int h,
+                                  size_t stride, int quality, int subsampling,
+                                  uint8_t* out, size_t cap) {
+  EncHost E;
+  if (!enc_setup(w, h, quality, subsampling, &E)) return 0;
+  const EncFrame& f = E.f;
+  // component planes with libjpeg's edge expansion
+  std::vector<uint8_t> plane[3];
+  int pw[3], ph[3];
+  for (int c = 0; c < 3; ++c) {
+    pw[c] = f.blocks_w[c] * 8;
+    ph[c] = f.blocks_h[c] * 8;
+    plane[c].assign((size_t)pw[c] * ph[c], 0);
+  }
+  auto ycc = [&](int x, int y, int* Y, int* Cb, int* Cr) {
+    x = x < w - 1 ? x : w - 1;
+    y = y < h - 1 ? y : h - 1;
+    const uint8_t* p = bgr + (size_t)y * stride + 3 * (size_t)x;
+    bgr_to_ycc(p[0], p[1], p[2], Y, Cb, Cr);
+  };
+  for (int y = 0; y < ph[0]; ++y)
+    for (int x = 0; x < pw[0]; ++x) {
+      int Y, Cb, Cr;
+      ycc(x, y, &Y, &Cb, &Cr);
+      plane[0][(size_t)y * pw[0] + x] = (uint8_t)Y;
+    }
+  for (int cy = 0; cy < ph[1]; ++cy)
+    for (int cx = 0; cx < pw[1]; ++cx) {
+      const int r = cy < f.comp_h[1] - 1 ? cy : f.comp_h[1] - 1;
+      int sb = 0, sr = 0;
+      for (int dy = 0; dy < f.vs; ++dy)
+        for (int dx = 0; dx < f.hs; ++dx) {
+          int Y, Cb, Cr;
+          ycc(cx * f.hs + dx, r * f.vs + dy, &Y, &Cb, &Cr);
+          sb += Cb;
+          sr += Cr;
+        }
+      int vb = sb, vr = sr;
+      if (f.hs == 2 && f.vs == 1) {
+        vb = (sb + (cx & 1)) >> 1;
+        vr = (sr + (cx & 1)) >> 1;
+      } else if (f.hs == 2 && f.vs == 2) {
+        vb = (sb + 1 + (cx & 1)) >> 2;
+        vr = (sr + 1 + (cx & 1)) >> 2;
+      }
+      plane[1][(size_t)cy * pw[1] + cx] = (uint8_t)vb;
+      plane[2][(size_t)cy * pw[2] + cx] = (uint8_t)vr;
+    }
+  // blocks in scan order
+  std::vector<int16_t> coef((size_t)f.total_blocks * 64, 0);
+  for (int blk = 0; blk < f.total_blocks; ++blk) {
+    const BlockPos p = block_pos(f, blk);
+    if (p.dummy) continue;
+    uint8_t px[64];
+    for (int r = 0; r < 8; ++r)
+      memcpy(px + 8 * r,
+             &plane[p.comp][(size_t)(p.by * 8 + r) * pw[p.comp] + p.bx * 8], 8);
+    fdct_quantise(px, E.t.q[p.comp ? 1 : 0], &coef[(size_t)blk * 64]);
+  }
+  for (int blk = 0; blk < f.total_blocks; ++blk)
+    if (block_pos(f, blk).dummy)
+      coef[(size_t)blk * 64] = coef[(size_t)dummy_source(f, blk) * 64];
+  // entropy coding
+  std::vector<uint8_t> scan;
+  uint64_t acc = 0;
+  int nacc = 0;
+  auto emit = [&](uint32_t bits, int n) {
+    acc = (acc << n) | bits;
+    nacc += n;
+    while (nacc >= 8) {
+      const uint8_t b = (uint8_t)(acc >> (nacc - 8));
+      scan.push_back(b);
+      if (b == 0xFF) scan.push_back(0);
+      nacc -= 8;
+    }
+  };
+  int pred[3] = {0, 0, 0};
+  for (int blk = 0; blk < f.total_blocks; ++blk) {
+    const int c = block_pos(f, blk).comp;
+    const int16_t* b = &coef[(size_t)blk * 64];
+    encode_block(b, pred[c], E.t, c ? 2 : 0, c ? 3 : 1, emit);
+    pred[c] = b[0];
+  }
+  if (nacc) emit(0x7F, 7);  // pad the last byte with ones
+  std::vector<uint8_t> head;
+  enc_headers(E, &head);
+  const size_t total = head.size() + scan.size() + 2;
+  if (!out || cap < total) return out ? 0 : total;
+  memcpy(out, head.data(), head.size());
+  memcpy(out + head.size(), scan.data(), scan.size());
+  out[total - 2] = 0xFF;
+  out[total - 1] = 0xD9;
+  return total;
+}

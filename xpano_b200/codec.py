@@ -51,9 +51,14 @@ class JpegCodec:
     def stats(self):
         """-> (images decoded by the library's kernels, images decoded by
         nvJPEG) since this codec was created."""
-        out = (ctypes.c_int * 2)()
+        return self.all_stats()[:2]
+
+    def all_stats(self):
+        """-> (decoded by own kernels, decoded by nvJPEG, encoded by own
+        kernels, encoded by nvJPEG)."""
+        out = (ctypes.c_int * 4)()
         check(self._lib.xp_codec_stats(self._h, out))
-        return out[0], out[1]
+        return tuple(out)
 
     def decode(self, data):
         """-> (h, w, 3) uint8 BGR host array, like cv2.imdecode(IMREAD_COLOR)."""

@@ -35,6 +35,12 @@ bool sm_jpeg_decode(const uint8_t* data, size_t len, uint8_t* d_out,
                     size_t out_pitch, cudaStream_t s, std::string* why,
                     int stats[2]);
 
+// jpeg_enc.cu: baseline streams with the standard Huffman tables, encoded by
+// this repository's kernels, byte-identical to cv::imwrite's
+bool sm_jpeg_encode(const uint8_t* d_bgr, int w, int h, size_t pitch,
+                    int quality, int subsampling, cudaStream_t s,
+                    Mailbox* hold, const uint8_t** stream, size_t* len);
+
 static const char* nvjpeg_name(nvjpegStatus_t s) {
   switch (s) {
     case NVJPEG_STATUS_SUCCESS: return "success";
@@ -154,6 +160,10 @@ struct Codec {
   // everything, 2 = a stream the SM decoder does not cover is an error
   int sm_mode = 1;
   std::atomic<int> n_sm{0}, n_lib{0};  // images decoded by either
+  std::atomic<int> e_sm{0}, e_lib{0};  // images encoded by either
+  Mailbox own_box;  // pinned memory holding the stream our encoder produced
+  const uint8_t* own_stream = nullptr;
+  size_t own_len = 0;
 
   // -> true when the SM decoder produced the image
   bool decode_sm(const uint8_t* data, size_t len, uint8_t* d_out, size_t pitch,
@@ -372,6 +382,15 @@ struct Codec {
     XP_REQUIRE(quality >= 1 && quality <= 100, "jpeg_encode: quality 1..100");
     // A size query (out == NULL) encodes and keeps the stream in the encoder
     // state; the call that follows with a buffer only retrieves it.
+    if (out && pending && pending_own) {
+      XP_REQUIRE(cap >= pending, "jpeg_encode: %zu bytes needed, %zu given",
+                 pending, cap);
+      copy_bytes(out, own_stream, pending);
+      *len = pending;
+      pending = 0;
+      pending_own = false;
+      return;
+    }
     if (out && pending) {
       size_t need = pending;
       XP_REQUIRE(cap >= need, "jpeg_encode: %zu bytes needed, %zu given", need,
@@ -383,6 +402,29 @@ struct Codec {
       return;
     }
     pending = 0;
+    pending_own = false;
+    // Baseline with the standard tables: our own kernels, whose stream is
+    // cv::imwrite's byte for byte. Progressive streams and optimised tables
+    // stay with nvJPEG (XP_JPEG_SM=0: everything does).
+    if (sm_mode && !progressive && !optimize &&
+        (subsampling == 444 || subsampling == 422 || subsampling == 420) &&
+        sm_jpeg_encode(d_bgr, w, h, stride, quality, subsampling, stream,
+                       &own_box, &own_stream, &own_len)) {
+      ++e_sm;
+      *len = own_len;
+      if (!out) {
+        pending = own_len;
+        pending_own = true;
+        return;
+      }
+      XP_REQUIRE(cap >= own_len, "jpeg_encode: %zu bytes needed, %zu given",
+                 own_len, cap);
+      copy_bytes(out, own_stream, own_len);
+      return;
+    }
+    if (sm_mode == 2)
+      fail(XP_ERR_UNSUPPORTED, "jpeg_encode: not covered by the SM encoder");
+    ++e_lib;
     nvjpegChromaSubsampling_t css;
     switch (subsampling) {
       case 444: css = NVJPEG_CSS_444; break;
@@ -421,6 +463,7 @@ struct Codec {
     *len = need;
   }
   size_t pending = 0;  // a stream of this many bytes waits in the encoder
+  bool pending_own = false;  // ... in own_stream, not in nvJPEG's state
 };
 
 }  // namespace xp
@@ -449,11 +492,13 @@ xp_status xp_codec_jpeg_info(xp_codec* c, const uint8_t* data, size_t len,
   });
 }
 
-xp_status xp_codec_stats(xp_codec* c, int out[2]) {
+xp_status xp_codec_stats(xp_codec* c, int out[4]) {
   return xp::guard([&] {
     XP_REQUIRE(c && out, "codec_stats: null argument");
     out[0] = c->n_sm.load();
     out[1] = c->n_lib.load();
+    out[2] = c->e_sm.load();
+    out[3] = c->e_lib.load();
   });
 }
 

@@ -140,6 +140,26 @@ void* Mailbox::to_host(const void* src, size_t bytes, cudaStream_t s) {
   return slot;
 }
 
+void copy_bytes(void* dst, const void* src, size_t n) {
+  const int t = n >= ((size_t)4 << 20) ? std::min(4, host_worker_threads(4)) : 1;
+  if (t <= 1) {
+    memcpy(dst, src, n);
+    return;
+  }
+  const size_t part = ((n / t) + 4095) & ~(size_t)4095;
+  std::vector<std::thread> th;
+  for (int k = 1; k < t; ++k) {
+    const size_t o = std::min(n, part * k), e = std::min(n, o + part);
+    if (e > o)
+      th.emplace_back([=] {
+        memcpy(static_cast<char*>(dst) + o, static_cast<const char*>(src) + o,
+               e - o);
+      });
+  }
+  memcpy(dst, src, std::min(n, part));
+  for (std::thread& x : th) x.join();
+}
+
 void* pool_alloc(size_t n, size_t* got, int* device) {
   int dev = 0;
   XP_CUDA(cudaGetDevice(&dev));
