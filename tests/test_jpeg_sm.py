@@ -1,6 +1,9 @@
 """The SM JPEG decoder (xpano_b200/csrc/jpeg_sm.{h,cu}, jpeg_parse.h; SURVEY.md
 8f2, the cv::imread side, xpano/algorithm/image.cc:83) against cv2.imdecode --
 libjpeg-turbo, the decoder cv::imread uses. Bar: bit-exact, every pixel.
+And the SM JPEG encoder (jpeg_enc.{h,cu}, jpeg_enc_host.h; the cv::imwrite
+side, xpano/pipeline/stitcher_pipeline.cc:94-116) against cv2.imencode. Bar:
+the stream is identical, byte for byte.
 
 CPU part: tests/emu/jpeg_emu.cpp compiles the SAME headers as the CUDA kernels
 and runs their steps as loops (guess pass, synchronisation sweeps in three

@@ -2,8 +2,9 @@
 the sources (xpano/algorithm/image.cc:83) and cv::imwrite of the panorama
 (xpano/pipeline/stitcher_pipeline.cc:94-116) -- executed on the device inside
 libxpano_b200.so, so that only compressed bytes cross PCIe: baseline streams
-are decoded by the library's own kernels (bit-identical to cv::imread), the
-rest and all encoding by nvJPEG. SURVEY.md 8(f2)."""
+are decoded (bit-identical to cv::imread) and encoded (byte-identical to
+cv::imwrite) by the library's own kernels, progressive streams and optimised
+Huffman tables by nvJPEG. SURVEY.md 8(f2)."""
 from __future__ import annotations
 
 import ctypes

@@ -12,7 +12,10 @@
 // jpeg_sm.cu, whose pixels are libjpeg-turbo's -- cv::imread's -- bit for bit;
 // what those do not cover (progressive, ...) goes to nvJPEG, a library,
 // linked statically, whose inverse DCT and chroma upsampling are its own
-// (tests: PSNR >= 40 dB against cv2.imdecode for those). Encoding: nvJPEG.
+// (tests: PSNR >= 40 dB against cv2.imdecode for those). Encoding: baseline
+// streams with the standard Huffman tables go to the kernels of jpeg_enc.cu,
+// whose stream is cv::imwrite's byte for byte; progressive streams and
+// optimised tables to nvJPEG.
 // The kernel in this file applies the EXIF orientation, as cv::imread does.
 #include <nvjpeg.h>
 
