@@ -206,46 +206,52 @@ XP_HD uint8_t idct_limit(int32_t x) {  // range_limit[(x) & RANGE_MASK]
   return (uint8_t)(v < 0 ? 0 : v > 255 ? 255 : v);
 }
 
-XP_HD void idct_1d(const int32_t i[8], int32_t even_shift, int32_t o[8],
+// (unsigned arithmetic: a damaged stream may overflow 32 bits, which wraps
+// here as it does on the device instead of being undefined on the host)
+XP_HD void idct_1d(const int32_t in[8], int32_t even_shift, int32_t o[8],
                    int shift) {
+  typedef uint32_t u32;
+  u32 i[8];
+  XP_UNROLL
+  for (int k = 0; k < 8; ++k) i[k] = (u32)in[k];
   // even part
-  int32_t z2 = i[2], z3 = i[6];
-  int32_t z1 = mul32(z2 + z3, 4433);
-  int32_t tmp2 = z1 + mul32(z3, -15137);
-  int32_t tmp3 = z1 + mul32(z2, 6270);
-  int32_t tmp0 = (int32_t)((uint32_t)(i[0] + i[4]) << even_shift);
-  int32_t tmp1 = (int32_t)((uint32_t)(i[0] - i[4]) << even_shift);
-  const int32_t tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3;
-  const int32_t tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
+  u32 z2 = i[2], z3 = i[6];
+  u32 z1 = (z2 + z3) * 4433u;
+  u32 tmp2 = z1 + z3 * (u32)-15137;
+  u32 tmp3 = z1 + z2 * 6270u;
+  u32 tmp0 = (i[0] + i[4]) << even_shift;
+  u32 tmp1 = (i[0] - i[4]) << even_shift;
+  const u32 tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3;
+  const u32 tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
   // odd part
   tmp0 = i[7], tmp1 = i[5], tmp2 = i[3], tmp3 = i[1];
   z1 = tmp0 + tmp3;
   z2 = tmp1 + tmp2;
   z3 = tmp0 + tmp2;
-  int32_t z4 = tmp1 + tmp3;
-  const int32_t z5 = mul32(z3 + z4, 9633);
-  tmp0 = mul32(tmp0, 2446);
-  tmp1 = mul32(tmp1, 16819);
-  tmp2 = mul32(tmp2, 25172);
-  tmp3 = mul32(tmp3, 12299);
-  z1 = mul32(z1, -7373);
-  z2 = mul32(z2, -20995);
-  z3 = mul32(z3, -16069);
-  z4 = mul32(z4, -3196);
+  u32 z4 = tmp1 + tmp3;
+  const u32 z5 = (z3 + z4) * 9633u;
+  tmp0 *= 2446u;
+  tmp1 *= 16819u;
+  tmp2 *= 25172u;
+  tmp3 *= 12299u;
+  z1 *= (u32)-7373;
+  z2 *= (u32)-20995;
+  z3 *= (u32)-16069;
+  z4 *= (u32)-3196;
   z3 += z5;
   z4 += z5;
   tmp0 += z1 + z3;
   tmp1 += z2 + z4;
   tmp2 += z2 + z3;
   tmp3 += z1 + z4;
-  o[0] = descale(tmp10 + tmp3, shift);
-  o[7] = descale(tmp10 - tmp3, shift);
-  o[1] = descale(tmp11 + tmp2, shift);
-  o[6] = descale(tmp11 - tmp2, shift);
-  o[2] = descale(tmp12 + tmp1, shift);
-  o[5] = descale(tmp12 - tmp1, shift);
-  o[3] = descale(tmp13 + tmp0, shift);
-  o[4] = descale(tmp13 - tmp0, shift);
+  o[0] = descale((int32_t)(tmp10 + tmp3), shift);
+  o[7] = descale((int32_t)(tmp10 - tmp3), shift);
+  o[1] = descale((int32_t)(tmp11 + tmp2), shift);
+  o[6] = descale((int32_t)(tmp11 - tmp2), shift);
+  o[2] = descale((int32_t)(tmp12 + tmp1), shift);
+  o[5] = descale((int32_t)(tmp12 - tmp1), shift);
+  o[3] = descale((int32_t)(tmp13 + tmp0), shift);
+  o[4] = descale((int32_t)(tmp13 - tmp0), shift);
 }
 
 XP_HD void idct_islow(const int16_t in[64], int dc, const uint16_t q[64],
