@@ -500,12 +500,13 @@ xp_status xp_multiband_fetch(xp_multiband* b, void* dst_bgr, size_t dst_stride,
  * cameras write) are decoded by this library's own kernels (csrc/jpeg_sm.cu:
  * parallel Huffman decoding, libjpeg-turbo's inverse DCT, fancy upsampling
  * and colour conversion restated), and the pixels equal cv::imread's bit for
- * bit. Encoding: baseline streams with the standard Huffman tables (what
- * CompressionParameters' defaults ask for) are written by this library's own
- * kernels too (csrc/jpeg_enc.cu: libjpeg-turbo's colour conversion,
- * downsampling, forward DCT, quantisation and Huffman coding restated), and
- * the stream equals cv::imwrite's byte for byte. Everything else (progressive,
- * optimised tables, ...) goes to nvJPEG (library code, linked statically),
+ * bit. Encoding: baseline streams (the standard Huffman tables that
+ * CompressionParameters' defaults ask for, or tables optimised for the image)
+ * are written by this library's own kernels too (csrc/jpeg_enc.cu:
+ * libjpeg-turbo's colour conversion, downsampling, forward DCT, quantisation
+ * and Huffman coding restated), and the stream equals cv::imwrite's byte for
+ * byte. Everything else (progressive, ...) goes to nvJPEG (library code,
+ * linked statically),
  * whose decoded pixels / streams are close to libjpeg-turbo's, not identical.
  * XP_JPEG_SM=0 in the environment sends everything to nvJPEG, =2 makes a
  * stream or setting the kernels do not cover an error.

@@ -146,7 +146,7 @@ extern "C" int emu_jpeg_decode(const uint8_t* d, size_t n, int sub_bytes,
 
 extern "C" size_t emu_jpeg_encode(const uint8_t* bgr, int w, int h,
                                   size_t stride, int quality, int subsampling,
-                                  uint8_t* out, size_t cap) {
+                                  int optimize, uint8_t* out, size_t cap) {
   EncHost E;
   if (!enc_setup(w, h, quality, subsampling, &E)) return 0;
   const EncFrame& f = E.f;
@@ -221,6 +221,19 @@ extern "C" size_t emu_jpeg_encode(const uint8_t* bgr, int w, int h,
     }
   };
   int pred[3] = {0, 0, 0};
+  if (optimize) {  // symbol statistics first, tables from them
+    long hist[4][257];
+    memset(hist, 0, sizeof(hist));
+    for (int blk = 0; blk < f.total_blocks; ++blk) {
+      const int c = block_pos(f, blk).comp;
+      const int16_t* b = &coef[(size_t)blk * 64];
+      block_symbols(b, pred[c], c ? 2 : 0, c ? 3 : 1,
+                    [&](int tab, int sym, uint32_t, int) { hist[tab][sym]++; });
+      pred[c] = b[0];
+    }
+    enc_optimise(hist, &E);
+    pred[0] = pred[1] = pred[2] = 0;
+  }
   for (int blk = 0; blk < f.total_blocks; ++blk) {
     const int c = block_pos(f, blk).comp;
     const int16_t* b = &coef[(size_t)blk * 64];

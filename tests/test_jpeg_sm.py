@@ -85,7 +85,7 @@ def emu():
     lib.emu_jpeg_encode.restype = ctypes.c_size_t
     lib.emu_jpeg_encode.argtypes = [ctypes.c_void_p, ctypes.c_int,
                                     ctypes.c_int, ctypes.c_size_t,
-                                    ctypes.c_int, ctypes.c_int,
+                                    ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                     ctypes.c_void_p, ctypes.c_size_t]
     return lib
 
@@ -190,14 +190,14 @@ ENC_CASES = [(h, w, sub, q)
              for sub in (444, 422, 420) for q in (10, 50, 95, 100)]
 
 
-def emu_encode(lib, img, quality, sub):
+def emu_encode(lib, img, quality, sub, optimize=0):
     img = np.ascontiguousarray(img)
     h, w = img.shape[:2]
     n = lib.emu_jpeg_encode(img.ctypes.data, w, h, img.strides[0], quality,
-                            sub, None, 0)
+                            sub, optimize, None, 0)
     out = np.zeros(n, np.uint8)
     assert lib.emu_jpeg_encode(img.ctypes.data, w, h, img.strides[0], quality,
-                               sub, out.ctypes.data, n) == n
+                               sub, optimize, out.ctypes.data, n) == n
     return out
 
 
@@ -207,13 +207,16 @@ def test_emulated_encoder_equals_cv2(emu):
     expansion, dummy blocks of partial MCUs, Huffman coding, padding."""
     for k, (h, w, sub, q) in enumerate(ENC_CASES):
         img = scene(h, w, 100 + k)
-        assert np.array_equal(emu_encode(emu, img, q, sub),
-                              encode(img, sub, q)), (h, w, sub, q)
+        for opt in (0, 1):   # standard tables / jpeg_gen_optimal_table
+            assert np.array_equal(emu_encode(emu, img, q, sub, opt),
+                                  encode(img, sub, q, optimize=opt)), \
+                (h, w, sub, q, opt)
     g = np.load(os.path.join(GOLD, "real_photos.npz"))
     photo = reference(g["jpeg_0"])[:700, :900]
     for sub in (444, 422, 420):
-        assert np.array_equal(emu_encode(emu, photo, 95, sub),
-                              encode(photo, sub, 95))
+        for opt in (0, 1):
+            assert np.array_equal(emu_encode(emu, photo, 95, sub, opt),
+                                  encode(photo, sub, 95, optimize=opt))
 
 
 def test_standard_tables_header_is_current():
@@ -317,16 +320,18 @@ def test_gpu_encoder_equals_cv2(sm_only):
     codec = xb.JpegCodec()
     for k, (h, w, sub, q) in enumerate(ENC_CASES):
         img = scene(h, w, 100 + k)
-        got = np.frombuffer(codec.encode(img, quality=q, subsampling=sub),
-                            np.uint8)
-        assert np.array_equal(got, encode(img, sub, q)), (h, w, sub, q)
+        opt = k % 2          # standard tables / tables optimised for the image
+        got = np.frombuffer(codec.encode(img, quality=q, subsampling=sub,
+                                         optimize=bool(opt)), np.uint8)
+        assert np.array_equal(got, encode(img, sub, q, optimize=opt)), \
+            (h, w, sub, q, opt)
     g = np.load(os.path.join(GOLD, "real_photos.npz"))
     big = cv2.resize(reference(g["jpeg_0"]), (4000, 3000),
                      interpolation=cv2.INTER_CUBIC)
-    for sub in (422, 420):
-        got = np.frombuffer(codec.encode(big, quality=95, subsampling=sub),
-                            np.uint8)
-        assert np.array_equal(got, encode(big, sub, 95))
+    for sub, opt in ((422, 0), (420, 1)):
+        got = np.frombuffer(codec.encode(big, quality=95, subsampling=sub,
+                                         optimize=bool(opt)), np.uint8)
+        assert np.array_equal(got, encode(big, sub, 95, optimize=opt))
     view = big[5:1205, 7:1800]            # a strided view (a cv::Mat ROI)
     got = np.frombuffer(codec.encode(view, quality=90, subsampling=444),
                         np.uint8)

@@ -3,8 +3,8 @@ the sources (xpano/algorithm/image.cc:83) and cv::imwrite of the panorama
 (xpano/pipeline/stitcher_pipeline.cc:94-116) -- executed on the device inside
 libxpano_b200.so, so that only compressed bytes cross PCIe: baseline streams
 are decoded (bit-identical to cv::imread) and encoded (byte-identical to
-cv::imwrite) by the library's own kernels, progressive streams and optimised
-Huffman tables by nvJPEG. SURVEY.md 8(f2)."""
+cv::imwrite, standard or optimised Huffman tables) by the library's own
+kernels, progressive streams by nvJPEG. SURVEY.md 8(f2)."""
 from __future__ import annotations
 
 import ctypes

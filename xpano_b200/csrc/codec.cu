@@ -13,9 +13,9 @@
 // what those do not cover (progressive, ...) goes to nvJPEG, a library,
 // linked statically, whose inverse DCT and chroma upsampling are its own
 // (tests: PSNR >= 40 dB against cv2.imdecode for those). Encoding: baseline
-// streams with the standard Huffman tables go to the kernels of jpeg_enc.cu,
-// whose stream is cv::imwrite's byte for byte; progressive streams and
-// optimised tables to nvJPEG.
+// streams (standard or optimised Huffman tables) go to the kernels of
+// jpeg_enc.cu, whose stream is cv::imwrite's byte for byte; progressive
+// streams to nvJPEG.
 // The kernel in this file applies the EXIF orientation, as cv::imread does.
 #include <nvjpeg.h>
 
@@ -41,8 +41,9 @@ bool sm_jpeg_decode(const uint8_t* data, size_t len, uint8_t* d_out,
 // jpeg_enc.cu: baseline streams with the standard Huffman tables, encoded by
 // this repository's kernels, byte-identical to cv::imwrite's
 bool sm_jpeg_encode(const uint8_t* d_bgr, int w, int h, size_t pitch,
-                    int quality, int subsampling, cudaStream_t s,
-                    Mailbox* hold, const uint8_t** stream, size_t* len);
+                    int quality, int subsampling, int optimize,
+                    cudaStream_t s, Mailbox* hold, const uint8_t** stream,
+                    size_t* len);
 
 static const char* nvjpeg_name(nvjpegStatus_t s) {
   switch (s) {
@@ -406,13 +407,13 @@ struct Codec {
     }
     pending = 0;
     pending_own = false;
-    // Baseline with the standard tables: our own kernels, whose stream is
-    // cv::imwrite's byte for byte. Progressive streams and optimised tables
-    // stay with nvJPEG (XP_JPEG_SM=0: everything does).
-    if (sm_mode && !progressive && !optimize &&
+    // Baseline (standard or optimised Huffman tables): our own kernels,
+    // whose stream is cv::imwrite's byte for byte. Progressive streams stay
+    // with nvJPEG (XP_JPEG_SM=0: everything does).
+    if (sm_mode && !progressive &&
         (subsampling == 444 || subsampling == 422 || subsampling == 420) &&
-        sm_jpeg_encode(d_bgr, w, h, stride, quality, subsampling, stream,
-                       &own_box, &own_stream, &own_len)) {
+        sm_jpeg_encode(d_bgr, w, h, stride, quality, subsampling, optimize,
+                       stream, &own_box, &own_stream, &own_len)) {
       ++e_sm;
       *len = own_len;
       if (!out) {

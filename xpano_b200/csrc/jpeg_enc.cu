@@ -1,8 +1,8 @@
 // Baseline JPEG encoded on the SMs (the cv::imwrite side,
 // xpano/pipeline/stitcher_pipeline.cc:94-116): the stream equals the one
 // cv::imwrite / libjpeg-turbo writes for the same pixels and settings, byte
-// for byte (baseline, Annex K Huffman tables, 4:4:4 / 4:2:2 / 4:2:0, any
-// quality). Arithmetic in jpeg_enc.h, tables and headers in jpeg_enc_host.h;
+// for byte (baseline; the Annex K Huffman tables or tables optimised for the
+// image, jchuff.c jpeg_gen_optimal_table; 4:4:4 / 4:2:2 / 4:2:0, any quality). Arithmetic in jpeg_enc.h, tables and headers in jpeg_enc_host.h;
 // tests/emu/jpeg_emu.cpp compiles the same headers for the host.
 //   1. colour conversion and chroma downsampling into component planes with
 //      libjpeg's edge expansion (enc_planes_kernel);
@@ -39,6 +39,7 @@ struct EncJob {
   uint32_t* words;     // the unstuffed scan, big-endian words
   uint32_t* total;     // [0] bits of the scan, [1] stuffed bytes
   uint32_t* ff_count;  // per stuffing block: FF bytes, then prefix
+  uint32_t* hist;      // [4][257] symbol counts per table (optimised tables)
   uint8_t* stuffed;
   int ctas, st_blocks;
 };
@@ -153,6 +154,26 @@ __device__ __forceinline__ void load_block(const EncJob& j, int blk,
   const int4* src = reinterpret_cast<const int4*>(j.coef + (size_t)blk * 64);
 #pragma unroll
   for (int k = 0; k < 8; ++k) *reinterpret_cast<int4*>(c + 8 * k) = src[k];
+}
+
+// symbol statistics for optimised Huffman tables (jchuff.c htest_one_block)
+__global__ void __launch_bounds__(256) enc_hist_kernel(const EncJob j) {
+  __shared__ uint32_t sh[4 * 257];
+  for (int i = threadIdx.x; i < 4 * 257; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const int blk = blockIdx.x * 256 + threadIdx.x;
+  if (blk < j.f.total_blocks) {
+    __align__(16) int16_t c[64];
+    load_block(j, blk, c);
+    const int comp = block_pos(j.f, blk).comp;
+    block_symbols(c, dc_pred(j, blk), comp ? 2 : 0, comp ? 3 : 1,
+                  [&](int tab, int sym, uint32_t, int) {
+                    atomicAdd(&sh[tab * 257 + sym], 1u);
+                  });
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 4 * 257; i += blockDim.x)
+    if (sh[i]) atomicAdd(&j.hist[i], sh[i]);
 }
 
 // code length of every block; inside a CTA of 256 blocks an exclusive scan,
@@ -328,8 +349,9 @@ __global__ void __launch_bounds__(256) stuff_scatter_kernel(const EncJob j) {
 // (*stream, *len; valid until hold is reset). False when the settings are
 // not covered (nothing queued). Complete at return.
 bool sm_jpeg_encode(const uint8_t* d_bgr, int w, int h, size_t pitch,
-                    int quality, int subsampling, cudaStream_t s,
-                    Mailbox* hold, const uint8_t** stream, size_t* len) {
+                    int quality, int subsampling, int optimize,
+                    cudaStream_t s, Mailbox* hold, const uint8_t** stream,
+                    size_t* len) {
   using namespace jpg;
   EncHost E;
   if (!enc_setup(w, h, quality, subsampling, &E)) return false;
@@ -361,7 +383,8 @@ bool sm_jpeg_encode(const uint8_t* d_bgr, int w, int h, size_t pitch,
   j.st_blocks = div_up((int)div_up(cap_bytes, (size_t)16), 256);
   const size_t meta_bytes =
       sizeof(EncTabs) + 16 +
-      ((size_t)f.total_blocks + j.ctas + j.st_blocks + 8) * sizeof(uint32_t);
+      ((size_t)f.total_blocks + j.ctas + j.st_blocks + 8 + 4 * 257) *
+          sizeof(uint32_t);
   meta.reserve(meta_bytes);
   scan.reserve(cap_bytes + 64 + 2 * cap_bytes + 64);
   uint8_t* pp = planes.as<uint8_t>();
@@ -376,10 +399,11 @@ bool sm_jpeg_encode(const uint8_t* d_bgr, int w, int h, size_t pitch,
   j.bits = j.total + 4;
   j.cta_bits = j.bits + f.total_blocks;
   j.ff_count = j.cta_bits + j.ctas;
+  j.hist = j.ff_count + j.st_blocks;
   j.words = scan.as<uint32_t>();
   j.stuffed = scan.as<uint8_t>() + cap_bytes + 64;
   Mailbox box;
-  box.reset(sizeof(EncTabs) + 256);
+  box.reset(2 * sizeof(EncTabs) + 4 * 257 * sizeof(uint32_t) + 256);
   box.to_device(meta.p, &E.t, sizeof(EncTabs), s);
   uint32_t* h_total = static_cast<uint32_t*>(box.take(4 * sizeof(uint32_t)));
   XP_CUDA(cudaMemsetAsync(j.words, 0, cap_bytes + 64, s));
@@ -391,6 +415,21 @@ bool sm_jpeg_encode(const uint8_t* d_bgr, int w, int h, size_t pitch,
   XP_LAUNCHED();
   enc_dummy_kernel<<<j.ctas, 256, 0, s>>>(j);
   XP_LAUNCHED();
+  if (optimize) {  // tables from the image's own symbol statistics
+    uint32_t* h_hist =
+        static_cast<uint32_t*>(box.take(4 * 257 * sizeof(uint32_t)));
+    XP_CUDA(cudaMemsetAsync(j.hist, 0, 4 * 257 * sizeof(uint32_t), s));
+    enc_hist_kernel<<<j.ctas, 256, 0, s>>>(j);
+    XP_LAUNCHED();
+    XP_CUDA(cudaMemcpyAsync(h_hist, j.hist, 4 * 257 * sizeof(uint32_t),
+                            cudaMemcpyDeviceToHost, s));
+    XP_CUDA(cudaStreamSynchronize(s));
+    long hist[4][257];
+    for (int k = 0; k < 4; ++k)
+      for (int i = 0; i < 257; ++i) hist[k][i] = (long)h_hist[k * 257 + i];
+    enc_optimise(hist, &E);
+    box.to_device(meta.p, &E.t, sizeof(EncTabs), s);
+  }
   enc_count_kernel<<<j.ctas, 256, 0, s>>>(j);
   XP_LAUNCHED();
   scan_u32_kernel<<<1, 1024, 0, s>>>(j.cta_bits, j.ctas, j.total);

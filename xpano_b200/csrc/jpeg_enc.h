@@ -162,16 +162,16 @@ XP_HD void fdct_quantise(const uint8_t px[64], const uint16_t q[64],
 }
 
 // jchuff.c encode_one_block: coef in zigzag order, pred = the component's
-// previous DC. emit(bits, n) receives every code and value, n <= 16 each.
-template <class Emit>
-XP_HD void encode_block(const int16_t coef[64], int pred, const EncTabs& t,
-                        int dc_tab, int ac_tab, Emit&& emit) {
+// previous DC. sink(table, symbol, extra, nbits) receives every Huffman
+// symbol (table: dc_tab or ac_tab) and the nbits value bits that follow it.
+template <class Sink>
+XP_HD void block_symbols(const int16_t coef[64], int pred, int dc_tab,
+                         int ac_tab, Sink&& sink) {
   int diff = coef[0] - pred;
   int v = diff < 0 ? -diff : diff;
   int nbits = bit_length(v);
-  emit((uint32_t)t.code[dc_tab][nbits], (int)t.len[dc_tab][nbits]);
-  if (nbits)
-    emit((uint32_t)(diff < 0 ? diff - 1 : diff) & ((1u << nbits) - 1), nbits);
+  sink(dc_tab, nbits,
+       (uint32_t)(diff < 0 ? diff - 1 : diff) & ((1u << nbits) - 1), nbits);
   int run = 0;
   for (int k = 1; k < 64; ++k) {
     const int c = coef[k];
@@ -180,17 +180,27 @@ XP_HD void encode_block(const int16_t coef[64], int pred, const EncTabs& t,
       continue;
     }
     while (run > 15) {
-      emit((uint32_t)t.code[ac_tab][0xF0], (int)t.len[ac_tab][0xF0]);
+      sink(ac_tab, 0xF0, 0u, 0);
       run -= 16;
     }
     v = c < 0 ? -c : c;
     nbits = bit_length(v);
-    const int sym = (run << 4) + nbits;
-    emit((uint32_t)t.code[ac_tab][sym], (int)t.len[ac_tab][sym]);
-    emit((uint32_t)(c < 0 ? c - 1 : c) & ((1u << nbits) - 1), nbits);
+    sink(ac_tab, (run << 4) + nbits,
+         (uint32_t)(c < 0 ? c - 1 : c) & ((1u << nbits) - 1), nbits);
     run = 0;
   }
-  if (run > 0) emit((uint32_t)t.code[ac_tab][0], (int)t.len[ac_tab][0]);
+  if (run > 0) sink(ac_tab, 0, 0u, 0);
+}
+
+// the same as bits: emit(bits, n) receives every code and value, n <= 16
+template <class Emit>
+XP_HD void encode_block(const int16_t coef[64], int pred, const EncTabs& t,
+                        int dc_tab, int ac_tab, Emit&& emit) {
+  block_symbols(coef, pred, dc_tab, ac_tab,
+                [&](int tab, int sym, uint32_t extra, int nbits) {
+                  emit((uint32_t)t.code[tab][sym], (int)t.len[tab][sym]);
+                  if (nbits) emit(extra, nbits);
+                });
 }
 
 }  // namespace jpg
