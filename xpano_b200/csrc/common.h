@@ -137,6 +137,17 @@ struct DevBuf {
   }
 };
 
+// Declared AFTER the DevBufs of a function that queues work on `s`: on every
+// way out, an exception included, the stream is drained before the buffers
+// go back to the pool (which is not stream-ordered).
+struct SyncOnExit {
+  cudaStream_t s;
+  explicit SyncOnExit(cudaStream_t stream) : s(stream) {}
+  SyncOnExit(const SyncOnExit&) = delete;
+  SyncOnExit& operator=(const SyncOnExit&) = delete;
+  ~SyncOnExit() { cudaStreamSynchronize(s); }
+};
+
 // Non-blocking stream of the highest (main chain: seams, pyramid tail) or
 // lowest (work that runs beside it) priority the device offers: when both
 // have blocks pending, the main chain's are placed first.

@@ -378,6 +378,8 @@ bool sm_jpeg_encode(const uint8_t* d_bgr, int w, int h, size_t pitch,
       std::min(max_scan, ((size_t)w * h * 3 + 4096 + 15) & ~(size_t)15);
   if (cap_bytes >= 0x1FFFFFF0u) return false;
   DevBuf planes, coef, meta, scan;
+  Mailbox box;  // pinned staging: released after the stream is drained too
+  SyncOnExit drain(s);
   planes.reserve(planes_total);
   coef.reserve(coef_bytes);
   j.st_blocks = div_up((int)div_up(cap_bytes, (size_t)16), 256);
@@ -402,7 +404,6 @@ bool sm_jpeg_encode(const uint8_t* d_bgr, int w, int h, size_t pitch,
   j.hist = j.ff_count + j.st_blocks;
   j.words = scan.as<uint32_t>();
   j.stuffed = scan.as<uint8_t>() + cap_bytes + 64;
-  Mailbox box;
   box.reset(2 * sizeof(EncTabs) + 4 * 257 * sizeof(uint32_t) + 256);
   box.to_device(meta.p, &E.t, sizeof(EncTabs), s);
   uint32_t* h_total = static_cast<uint32_t*>(box.take(4 * sizeof(uint32_t)));

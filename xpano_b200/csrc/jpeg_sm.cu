@@ -539,19 +539,6 @@ __global__ void __launch_bounds__(256)
 
 }  // namespace jpg
 
-// Size of a stream this decoder covers; false (and the reason) otherwise.
-bool sm_jpeg_probe(const uint8_t* data, size_t len, int wh[2],
-                   std::string* why) {
-  jpg::Parsed P;
-  if (!jpg::parse(data, len, jpg::sub_bytes(), &P)) {
-    if (why) *why = P.why;
-    return false;
-  }
-  wh[0] = P.f.width;
-  wh[1] = P.f.height;
-  return true;
-}
-
 // data (host) -> d_out: width x height interleaved 8-bit BGR as stored (EXIF
 // orientation is the caller's), queued on `s` and complete at return. False
 // when the stream is not covered (nothing was queued). stats, when given,
@@ -590,6 +577,8 @@ bool sm_jpeg_decode(const uint8_t* data, size_t len, uint8_t* d_out,
   const size_t dc_bytes =
       (((size_t)f.total_blocks * sizeof(int16_t)) + 255) & ~(size_t)255;
   DevBuf raw, words, meta, state, coef, planes;
+  Mailbox box;  // pinned staging: released after the stream is drained too
+  SyncOnExit drain(s);
   raw.reserve(raw_bytes + 64);
   words.reserve(words_bytes);
   meta.reserve(meta_bytes);
@@ -628,7 +617,6 @@ bool sm_jpeg_decode(const uint8_t* data, size_t len, uint8_t* d_out,
   // lock that the other decoding threads also wait for. Sizes are rounded up
   // to a power of two, so that the cached pinned blocks of one panorama's
   // sources serve the next one's.
-  Mailbox box;
   size_t pinned = 65536;
   while (pinned < raw_bytes + meta_bytes + 256) pinned *= 2;
   box.reset(pinned);
