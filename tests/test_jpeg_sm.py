@@ -219,6 +219,28 @@ def test_emulated_encoder_equals_cv2(emu):
                                   encode(photo, sub, 95, optimize=opt))
 
 
+def test_emulated_codec_random_sweep(emu):
+    """Seeded random sizes (1..259), qualities (1..100), samplings, noise /
+    flat / smooth content, standard and optimised tables: the encoder's stream
+    equals cv2.imencode's, and the decoder decodes it to cv2.imdecode's
+    pixels."""
+    rng = np.random.default_rng(123)
+    for it in range(90):
+        h, w = int(rng.integers(1, 260)), int(rng.integers(1, 260))
+        sub, q, opt = (444, 422, 420)[it % 3], int(rng.integers(1, 101)), it % 2
+        if it % 4 == 0:
+            img = rng.integers(0, 256, (h, w, 3)).astype(np.uint8)
+        elif it % 4 == 1:
+            img = np.full((h, w, 3), rng.integers(0, 256, 3), np.uint8)
+        else:
+            img = scene(h, w, it)
+        got = emu_encode(emu, img, q, sub, opt)
+        assert np.array_equal(got, encode(img, sub, q, optimize=opt)), \
+            (h, w, sub, q, opt)
+        r, info, pixels = emu_decode(emu, got, 64, it % 3)
+        assert r == 0 and np.array_equal(pixels, reference(got)), (h, w, sub, q)
+
+
 def test_standard_tables_header_is_current():
     subprocess.check_call([sys.executable,
                            os.path.join(os.path.dirname(HERE), "tools",
