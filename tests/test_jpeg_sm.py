@@ -394,3 +394,30 @@ def test_gpu_damaged_streams_end_cleanly():
     assert "pixels" in outcomes
     good = bases[0]
     assert np.array_equal(codec.decode(good), reference(good))
+
+
+@pytest.mark.gpu
+def test_gpu_codec_random_sweep(sm_only):
+    """The kernels on seeded random sizes, qualities, samplings and content:
+    encoded streams equal cv2.imencode's, decoded pixels cv2.imdecode's."""
+    import xpano_b200 as xb
+    codec = xb.JpegCodec()
+    rng = np.random.default_rng(321)
+    for it in range(60):
+        h, w = int(rng.integers(1, 700)), int(rng.integers(1, 900))
+        sub, q, opt = (444, 422, 420)[it % 3], int(rng.integers(1, 101)), it % 2
+        if it % 4 == 0:
+            img = rng.integers(0, 256, (h, w, 3)).astype(np.uint8)
+        elif it % 4 == 1:
+            img = np.full((h, w, 3), rng.integers(0, 256, 3), np.uint8)
+        else:
+            img = scene(h, w, it)
+        got = np.frombuffer(codec.encode(img, quality=q, subsampling=sub,
+                                         optimize=bool(opt)), np.uint8)
+        assert np.array_equal(got, encode(img, sub, q, optimize=opt)), \
+            (h, w, sub, q, opt)
+        rst = int(rng.integers(0, 4))
+        src = encode(img, sub, q, rst, opt)
+        assert np.array_equal(codec.decode(src), reference(src)), \
+            (h, w, sub, q, rst)
+    assert codec.all_stats() == (60, 0, 60, 0)
